@@ -1,0 +1,332 @@
+#!/usr/bin/env python
+"""bench.py -- headline measurement of the B200 PPO rollout-and-update engine.
+
+Metric (BASELINE.json): CartPole env-steps/sec incl. policy inference; PPO update samples/sec.
+Workload at N GPUs: BASELINE.json configs[2] per GPU -- 65,536 envs x 128-step horizon, default
+6-64-32-1 MLPs (weak scaling: every rank owns its own 65,536 envs; gradients all-reduced over NCCL).
+
+One "step" = one pass of the hot path over one batch: fused rollout (K1) + returns scan (K2) [timed as the
+rollout leg -> `value`, env-steps/s], then the PPO update (K3-K5, `--epochs` full-batch epochs) [timed as
+the update leg -> `update.value`, sample-epochs/s].  Everything is timed on the device with CUDA events on
+the engine's stream, max over ranks.  `e2e` repeats the rollout leg through the C ABI with HOST buffers:
+weights H2D from pinned memory in, the whole trajectory batch D2H into pinned memory out.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--precision f64|f32]
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FLOP_PHYS = 12000      # 300 RK stages x 40 flop per env-step
+FLOP_ACTOR = 4928      # 2 x (6*64 + 64*32 + 32*1)
+FLOP_UPDATE = 28032    # per sample-epoch, default MLP (fwd 9856 + dW 9856 + dX 8320)
+BYTES_STEP = 41        # obs 24 + a 4 + logp 4 + r 4 + V 4 + flag 1 written once per env-step
+BYTES_UPDATE = 36      # obs 24 + a 4 + old logp 4 + R 4 read per sample-epoch
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--precision", default="f64", choices=["f64", "f32"])
+    ap.add_argument("--envs", type=int, default=65536)
+    ap.add_argument("--horizon", type=int, default=128)
+    ap.add_argument("--epochs", type=int, default=4, help="full-batch PPO epochs per timed update leg")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-update", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------
+# reference arm / cpu_baseline: the reference's OWN CPU path (oracle/_ref/ref_harness, built from the
+# unmodified sources) timed on this box's host cores.  Its learner is a single serial process and the
+# libtorch intra-op pool slows it down, so it is run with 1 thread and cores = 1.
+# ------------------------------------------------------------------------------------------------
+def run_reference(updates, K=80, threads=1, nenv=1, episodes=20):
+    exe = os.path.join(ROOT, "oracle", "_ref", "ref_harness")
+    if not os.path.exists(exe):
+        return None
+    t0 = time.time()
+    out = subprocess.run([exe, "bench", str(nenv), str(episodes), str(K), str(threads), str(updates)],
+                         capture_output=True, text=True, timeout=1800)
+    if out.returncode != 0:
+        return None
+    r = json.loads(out.stdout.strip().splitlines()[-1])
+    r["wall_s"] = time.time() - t0
+    return r
+
+
+def cpu_port_baseline(seconds=6.0):
+    """Fallback when the reference binary is absent: the C oracle port (OpenMP over envs)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import numpy as np
+    import helpers as H
+    params = H.gold("init_params.f32")
+    N, T = 256, 100
+    t0 = time.time()
+    n = 0
+    while time.time() - t0 < seconds:
+        H.oracle_rollout(params, N, T, seed=1)
+        n += N * T
+    dt = time.time() - t0
+    return {"value": n / dt, "unit": "env-steps/s", "cores": os.cpu_count(), "kind": "port",
+            "sample": f"{n} env-steps of orc_rollout ({N} envs x {T} steps per call, OpenMP)"}
+
+
+def reference_arm(args, rank):
+    if rank != 0:
+        return
+    per_update = 2000
+    ups = max(1, args.steps + args.warmup)
+    r = run_reference(ups)
+    if r is None:
+        b = cpu_port_baseline()
+        v, kind, cores, sample = b["value"], "port", b["cores"], b["sample"]
+        upd = None
+    else:
+        v = r["env_steps"] / r["rollout_s"]
+        upd = r["sample_epochs"] / r["update_s"]
+        kind, cores = "reference", 1
+        sample = (f"{r['updates']} cycles of (1 env x 20 episodes x 100 steps rollout + PPO::update K=80), "
+                  f"in-process replay of src/main.cpp's protocol without MPI latency, stdout discarded, "
+                  f"{r['torch_threads']} libtorch thread")
+    line = {"impl": "reference", "metric": "cartpole_env_steps_per_sec_incl_policy_inference", "value": v,
+            "unit": "env-steps/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * per_update / v, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "reference default config (config:1-6): 1 learner + 1 env, 2000 env-steps per update",
+                       "n_envs": 1, "horizon": 2000},
+            "cpu_baseline": {"value": v, "unit": "env-steps/s", "cores": cores, "kind": kind, "sample": sample},
+            "update": {"value": upd, "unit": "sample-epochs/s"},
+            "e2e": {"value": v, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.p = index, [], None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.p = None
+
+    def _read(self):
+        for line in self.p.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.p:
+            self.p.terminate()
+        sm = sorted(int(float(r[0])) for r in self.rows if r and r[0].replace(".", "").isdigit())
+        mx = [int(float(r[1])) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
+        # the kernel keeps the SMs busy for most samples; take the median of the upper half as "under load"
+        load = sm[len(sm) // 2:] if sm else []
+        return {"sm_mhz": (load[len(load) // 2] if load else None), "sm_max_mhz": (max(mx) if mx else None),
+                "reasons": reasons, "samples": len(sm)}
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        reference_arm(args, rank)
+        return
+
+    import numpy as np
+    import torch
+    import __graft_entry__ as ge
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the engine has no CPU fallback")
+    import reinforcement_learning_cpp_parallel_b200 as pkg
+    from reinforcement_learning_cpp_parallel_b200 import capi
+    if not os.path.exists(pkg.lib_path()):
+        ge.build(oracle=False)
+
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    prec = pkg.PREC_F64 if args.precision == "f64" else pkg.PREC_F32
+    N, T = args.envs, args.horizon
+
+    def engine(k_epochs):
+        return pkg.Engine(capi.default_config(n_envs=N, horizon=T, precision=prec, seed=0x5EED, env_offset=rank * N,
+                                              k_epochs=k_epochs, device=local))
+
+    E = engine(args.epochs)
+    # identical synthetic weights on every rank: Linear-style init from the Philox host stream (seed 0)
+    E.init_params(0)
+    if world > 1:
+        uid = [pkg.Engine.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        E.comm_init(rank, world, uid[0])
+
+    def barrier():
+        E.sync()
+        torch.cuda.synchronize()
+        if dist:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if not dist:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # roofline denominators measured live (MEASURED_PEAKS.json only has HBM and bf16-tensor)
+    peak32 = E.measure_fma_peak(False)
+    peak64 = E.measure_fma_peak(True)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = peaks.get("hbm_gbs", 6650.0)
+    hbm_src = "MEASURED_PEAKS.json" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
+
+    # ---------------- warm-up ----------------
+    for _ in range(max(args.warmup, 3)):
+        E.rollout(T)
+        if not args.no_update:
+            E.update_resident()
+    barrier()
+
+    # ---------------- timed: rollout leg and update leg, K steps ----------------
+    # inputs: the 344 MB trajectory buffer written by each rollout is larger than the 126 MB L2, and the
+    # update streams the whole buffer every epoch -> no explicit flush needed ("inputs larger than L2").
+    cs = ClockSampler(local)
+    if rank == 0:
+        cs.start()
+    l0 = E.kernel_launches()
+    roll_ms, upd_ms = [], []
+    barrier()
+    t_wall0 = time.time()
+    for _ in range(args.steps):
+        E.timer_start()
+        E.rollout(T)
+        roll_ms.append(E.timer_stop_ms())
+        if not args.no_update:
+            E.timer_start()
+            st = E.update_resident()
+            upd_ms.append(E.timer_stop_ms())
+    barrier()
+    t_wall = time.time() - t_wall0
+    launches = E.kernel_launches() - l0
+    clocks = cs.stop() if rank == 0 else None
+    roll_total = max_over_ranks(sum(roll_ms))
+    upd_total = max_over_ranks(sum(upd_ms)) if upd_ms else 0.0
+    steps_all = N * T * args.steps * world
+    value = steps_all / (roll_total * 1e-3)
+    upd_value = (N * T * args.epochs * args.steps * world) / (upd_total * 1e-3) if upd_ms else None
+
+    # ---------------- e2e: C ABI with host buffers (pinned), copies inside the timed region ----------------
+    e2e = None
+    if not args.no_e2e:
+        hp = capi.pinned_empty((E.P,), np.float32)
+        hp[:] = E.get_params()
+        out = {"obs": capi.pinned_empty((T, N, 6), np.float32), "action": capi.pinned_empty((T, N), np.float32),
+               "logp": capi.pinned_empty((T, N), np.float32), "reward": capi.pinned_empty((T, N), np.float32),
+               "flags": capi.pinned_empty((T, N), np.uint8)}
+        fields = tuple(out)
+        for _ in range(2):
+            E.set_params(hp); E.rollout(T); E.traj_download(T, fields=fields, out=out)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            E.set_params(hp)                                  # H2D: the learner's current weights
+            E.rollout(T)                                      # K1 on device
+            E.traj_download(T, fields=fields, out=out)        # D2H: everything MemoryNN holds, into host buffers
+        barrier()
+        dt = max_over_ranks(time.perf_counter() - t0)
+        d2h = sum(a.nbytes for a in out.values())
+        e2e = {"value": steps_all / dt, "unit": "env-steps/s", "h2d_bytes_per_step": int(hp.nbytes),
+               "d2h_bytes_per_step": int(d2h), "api": "b2_set_params + b2_rollout + b2_traj_download (host buffers)"}
+
+    if rank != 0:
+        if dist:
+            dist.destroy_process_group()
+        return
+
+    # ---------------- roofline of the dominant kernel (k_rollout) ----------------
+    ms_launch = sum(roll_ms) / len(roll_ms)           # one k_rollout launch per rollout leg (rank 0's own)
+    steps_launch = N * T
+    if args.precision == "f64":
+        bound, peak = "fp64-fma", peak64
+        achieved = FLOP_PHYS * steps_launch / (ms_launch * 1e-3) / 1e12
+    else:
+        bound, peak = "fp32-fma", peak32
+        achieved = (FLOP_PHYS + FLOP_ACTOR) * steps_launch / (ms_launch * 1e-3) / 1e12
+    roofline = {"kernel": "k_rollout", "bound": bound, "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                "frac": achieved / peak if peak else None, "traffic": None,
+                "peak_source": "b2_measure_fma_peak (live FMA-issue microbenchmark, this GPU, this run)",
+                "flop_per_env_step": FLOP_PHYS if args.precision == "f64" else FLOP_PHYS + FLOP_ACTOR,
+                "hbm": {"achieved_gbs": BYTES_STEP * steps_launch / (ms_launch * 1e-3) / 1e9, "peak_gbs": hbm_peak,
+                        "peak_source": hbm_src}}
+    update = None
+    if upd_ms:
+        ums = sum(upd_ms) / len(upd_ms)
+        ua = FLOP_UPDATE * N * T * args.epochs / (ums * 1e-3) / 1e12
+        update = {"value": upd_value, "unit": "sample-epochs/s", "ms_per_update": ums, "epochs": args.epochs,
+                  "minibatches": 1, "samples": N * T,
+                  "roofline": {"kernel": "k_ppo_grad", "bound": "fp32-fma", "achieved": ua, "peak": peak32,
+                               "unit": "TFLOP/s", "frac": ua / peak32 if peak32 else None,
+                               "hbm_achieved_gbs": BYTES_UPDATE * N * T * args.epochs / (ums * 1e-3) / 1e9},
+                  "last_loss": st.loss}
+
+    cpu_baseline = None
+    if not args.no_cpu_baseline and world == 1:
+        r = run_reference(10)
+        if r:
+            cpu_baseline = {"value": r["env_steps"] / r["rollout_s"], "unit": "env-steps/s", "cores": 1,
+                            "kind": "reference",
+                            "sample": f"{r['env_steps']} env-steps + {r['updates']} PPO::update(K=80) of the unmodified "
+                                      f"reference sources via oracle/_ref/ref_harness (no MPI latency), {r['wall_s']:.1f} s wall",
+                            "update_sample_epochs_per_s": r["sample_epochs"] / r["update_s"]}
+        else:
+            cpu_baseline = cpu_port_baseline()
+
+    line = {"metric": "cartpole_env_steps_per_sec_incl_policy_inference", "value": value, "unit": "env-steps/s",
+            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": roll_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": args.precision, "data": "synthetic",
+            "config": {"workload": "BASELINE configs[2]: batched CartPole 65,536 envs/GPU x 128-step horizon, default MLP",
+                       "n_envs_per_gpu": N, "horizon": T, "episode_len": 100, "mlp": "6-64-32-1 x2", "precision": args.precision,
+                       "l2": "inputs larger than L2 (344 MB trajectory buffer rewritten per step)",
+                       "parallelism": f"env-sharded x{world}, NCCL grad all-reduce"},
+            "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "update": update,
+            "cpu_baseline": cpu_baseline, "fma_peaks_tflops": {"fp32": peak32, "fp64": peak64},
+            "wall_s_timed_region": t_wall}
+    print(json.dumps(line), flush=True)
+    if dist:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

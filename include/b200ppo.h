@@ -1,0 +1,172 @@
+/* include/b200ppo.h -- C ABI of libb200ppo.so, the B200-native PPO rollout-and-update engine.
+ *
+ * The reference (haotianh9/Reinforcement_learning_cpp_parallel) has no FFI: its boundary is the
+ * C++ class API of include/ppo_nn.h plus the header-only env of include/cart_pole.h, both consumed
+ * by src/main.cpp in one binary.  This header is what a binding for that path
+ * would link against; each entry point cites the reference interface it replaces (paths relative
+ * to the reference checkout).  include/compat/ppo_nn.h and include/compat/cart_pole.h are thin
+ * C++ shims over this ABI that keep the reference's own names and call shapes.
+ *
+ * Conventions: plain pointers and sizes only; every function returns B2_OK (0) or a negative
+ * b2_status and never exits or throws; b2_last_error() gives the message (thread-local).
+ * Host pointers unless a name ends in _dev.  A handle owns its device memory and one CUDA
+ * stream; calls on one handle are not re-entrant.  There is NO CPU fallback: without a CUDA
+ * device b2_create fails with B2_ERR_NO_DEVICE.
+ */
+#ifndef B200PPO_H
+#define B200PPO_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2_ABI_VERSION 1
+
+typedef enum {
+  B2_OK = 0,
+  B2_ERR_INVALID = -1,     /* bad argument / unsupported shape */
+  B2_ERR_NO_DEVICE = -2,   /* no CUDA device: the engine has no CPU path */
+  B2_ERR_CUDA = -3,        /* a CUDA runtime call failed */
+  B2_ERR_NONFINITE = -4,   /* NaN/Inf action or loss detected on device (cf. src/main.cpp:50-55) */
+  B2_ERR_IO = -5,          /* config / checkpoint file problem */
+  B2_ERR_COMM = -6,        /* NCCL failure */
+  B2_ERR_STATE = -7        /* call order (e.g. update before any rollout) */
+} b2_status;
+
+/* TRAIN_STATUS on the wire (include/ppo_nn.h:15) becomes a flag byte per record. */
+#define B2_FLAG_TERMINAL 1u /* TERMINATE: return restarts from 0      (src/ppo_nn.cpp:229-230) */
+#define B2_FLAG_TIMEUP 2u   /* TIMEUP: bootstrap with V(pre-step obs) (src/ppo_nn.cpp:226-228) */
+#define B2_FLAG_TRUNC 4u    /* engine extension: rollout horizon cut an episode; bootstraps like TIMEUP */
+
+/* physics arithmetic of the rollout kernel */
+#define B2_PREC_F64 0 /* double state + double Diff: the parity-gated path (reference is double) */
+#define B2_PREC_F32 1 /* float everything: throughput path, drift vs reference is reported, not gated */
+
+typedef struct b2_engine* b2_handle;
+
+typedef struct {
+  /* -- the reference's 6-line config file (config:1-6; src/main.cpp:356-382, include/cart_MPI.h:13-28) */
+  int control_vars;     /* action dim, must be 1 (src/ppo_nn.cpp:107) */
+  int obs_vars;         /* observation dim, must be 6 (include/cart_pole.h:120-131) */
+  int n_episodes;       /* Nepisodes */
+  int n_timestep;       /* N_timestep: steps per episode before TIMEUP */
+  int max_timestep;     /* Max_timestep */
+  int update_timestep;  /* updateTimestep */
+  /* -- hyper-parameters the reference hard-codes at src/main.cpp:196-203 */
+  double action_std, lr, beta1, beta2, gamma, eps_clip;
+  int k_epochs;
+  /* -- engine-only knobs (no reference analogue) */
+  int hidden1, hidden2;   /* 64, 32 (include/ppo_nn.h:85-96) */
+  int64_t n_envs;         /* environments resident on THIS device */
+  int horizon;            /* max T per b2_rollout call (sizes the trajectory buffer) */
+  int n_minibatches;      /* 1 == the reference's full-batch epochs (Q9) */
+  int precision;          /* B2_PREC_* */
+  uint64_t seed;          /* Philox key */
+  uint64_t env_offset;    /* global id of local env 0: same global seed => same trajectories for any sharding */
+  int device;             /* CUDA ordinal */
+  int reserved[7];
+} b2_config;
+
+/* One trajectory batch in host memory: what MemoryNN holds (include/ppo_nn.h:20-29).
+ * Record k is a transition: obs/action/logp from when the action was chosen,
+ * reward/flags from the env's next message.  Layout is time-major [T][N] (k = t*n_envs + e); the
+ * reference's merged memory (src/main.cpp:290-303) is the special case n_envs = 1, horizon = B. */
+typedef struct {
+  int64_t n_envs;
+  int64_t horizon;
+  const float* obs;     /* [B][obs_vars] */
+  const float* action;  /* [B] raw network-space action (not the scaled force) */
+  const float* logp;    /* [B] */
+  const float* reward;  /* [B] */
+  const uint8_t* flags; /* [B] B2_FLAG_* */
+} b2_batch;
+
+/* mutable twin of b2_batch for downloads; any pointer may be NULL */
+typedef struct {
+  float* obs; float* action; float* logp; float* mu; float* reward; uint8_t* flags; float* returns;
+} b2_batch_out;
+
+typedef struct {
+  double loss1, loss2, loss3, loss; /* means over the LAST optimizer step's samples (src/ppo_nn.cpp:292-297) */
+  double clip_frac;
+  int64_t samples;   /* B */
+  int64_t adam_step; /* persists across updates (optimizer is built once, include/ppo_nn.h:166-170) */
+  int optimizer_steps;
+} b2_update_stats;
+
+/* ---- library ---- */
+int b2_abi_version(void);
+const char* b2_last_error(void);
+int b2_device_count(void);
+
+/* ---- configuration: replaces read_parameters (src/main.cpp:356-382) + hard-coded hyper-parameters */
+int b2_config_default(b2_config* cfg);
+int b2_config_read(const char* path, b2_config* cfg); /* positional "<int> = comment" lines; unread fields keep their value */
+
+/* ---- lifetime: replaces PPO::PPO (include/ppo_nn.h:146-173) + CartPole construction (src/main.cpp:20) */
+int b2_create(const b2_config* cfg, b2_handle* out);
+int b2_destroy(b2_handle h);
+int b2_get_config(b2_handle h, b2_config* out);
+
+/* ---- parameters.  Order = policy.parameters(): actor W1[H1][S] b1 W2[H2][H1] b2 W3[A][H2] b3, then critic */
+int64_t b2_n_params(b2_handle h);
+int b2_init_params(b2_handle h, uint64_t seed);              /* torch::nn::Linear default init U(+-1/sqrt(fan_in)) */
+int b2_set_params(b2_handle h, const float* p, int64_t n);
+int b2_get_params(b2_handle h, float* p, int64_t n);
+int b2_set_adam_state(b2_handle h, const float* m, const float* v, int64_t n, int64_t step);
+int b2_get_adam_state(b2_handle h, float* m, float* v, int64_t n, int64_t* step);
+int b2_get_grads(b2_handle h, float* g, int64_t n);          /* gradient of the last optimizer step (after all-reduce) */
+int b2_save_checkpoint(b2_handle h, const char* path);       /* params + Adam m, v, step */
+int b2_load_checkpoint(b2_handle h, const char* path);
+
+/* ---- action query: replaces getAction -> PPO::select_action -> ActorCritic::act
+ *      (src/ppo_nn.cpp:308-331,196-203,99-125).  eps NULL => engine Philox stream; mu may be NULL. */
+int b2_act(b2_handle h, const float* obs, int64_t n, const float* eps, float* action, float* logp, float* mu);
+/* ---- value estimate: replaces policy.critic->forward (src/ppo_nn.cpp:189,227) */
+int b2_value(b2_handle h, const float* obs, int64_t n, float* value);
+
+/* ---- update on a trajectory batch: replaces PPO::update(MemoryNN) (src/ppo_nn.cpp:205-307) */
+int b2_update(b2_handle h, const b2_batch* batch, b2_update_stats* stats);
+int b2_returns(b2_handle h, const b2_batch* batch, float* returns); /* the returns part only (:207-236) */
+/* loss terms of every optimizer step of the last update (n = optimizer_steps; arrays may be NULL) */
+int b2_last_update_losses(b2_handle h, double* loss1, double* loss2, double* loss3, double* loss, int n);
+
+/* ---- device-resident path: replaces env_run + NN_run messaging (src/main.cpp:12-148,190-354).
+ *      b2_rollout advances every resident env T steps with the current policy (cart_pole.h semantics,
+ *      action scaling src/main.cpp:57-60, TIMEUP at n_timestep :86-88); trajectories stay in HBM.
+ *      forced_action (host, [T][N]) replaces sampling for replay-parity runs, else NULL. */
+int b2_env_reset(b2_handle h);                                 /* CartPole::reset on all envs (include/cart_pole.h:77-90) */
+int b2_env_set_state(b2_handle h, const double* u, const int32_t* ep_step, int64_t n); /* u: [n][4] = y1,y2,y3,y4 */
+int b2_env_get_state(b2_handle h, double* u, int32_t* ep_step, int64_t n);
+int b2_rollout(b2_handle h, int T, const float* forced_action);
+int b2_update_resident(b2_handle h, b2_update_stats* stats);   /* returns + K epochs on the resident trajectory */
+int b2_train_iteration(b2_handle h, int T, b2_update_stats* stats); /* rollout + update_resident */
+int b2_traj_download(b2_handle h, b2_batch_out* out, double* state_trace /* [T][N][4] or NULL, only if tracing on */);
+int b2_set_state_trace(b2_handle h, int enable);               /* record fp64 post-step states (parity tests) */
+/* per-env episode bookkeeping of the last rollout (src/main.cpp:74,137-142): completed episodes and their
+ * reward sums; returns[e * max_eps + i] for i < counts[e] */
+int b2_episode_stats(b2_handle h, int32_t* counts, float* returns, int max_eps, int64_t n);
+int64_t b2_total_env_steps(b2_handle h);
+
+/* ---- multi-GPU: one process per GPU, envs sharded, gradients all-reduced (replaces include/cart_MPI.h) */
+#define B2_COMM_ID_BYTES 128
+int b2_comm_unique_id(char id[B2_COMM_ID_BYTES]);              /* rank 0 makes it, the caller broadcasts it */
+int b2_comm_init(b2_handle h, int rank, int world, const char id[B2_COMM_ID_BYTES]);
+int b2_comm_world(b2_handle h);
+
+/* ---- measurement helpers (CUDA events on the handle's stream) */
+int b2_sync(b2_handle h);
+int b2_timer_start(b2_handle h);
+int b2_timer_stop_ms(b2_handle h, float* ms);
+int64_t b2_kernel_launches(b2_handle h);                       /* kernels this handle has launched so far */
+void* b2_stream(b2_handle h);                                  /* cudaStream_t */
+int b2_flush_l2(b2_handle h);                                  /* overwrite a >L2 scratch buffer */
+int b2_measure_fma_peak(b2_handle h, int fp64, double* tflops); /* CUDA-core FMA issue peak of this GPU (roofline denominator) */
+int b2_host_alloc(void** p, size_t bytes);                     /* pinned host memory for the host-buffer entry points */
+int b2_host_free(void* p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200PPO_H */

@@ -1,0 +1,767 @@
+// engine.cu -- the b2_handle and every extern "C" entry point of include/b200ppo.h.
+//
+// Host side of the engine: owns device memory and one stream per handle, turns the reference's
+// per-step learner<->env messaging (src/main.cpp:12-148,190-354) into a handful of kernel launches
+// per rollout/update, and never touches the data path on the CPU.  No libtorch, no CPU fallback.
+#include "engine.h"
+
+#include <dlfcn.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <fstream>
+#include <new>
+#include <sstream>
+
+#include "common.cuh"
+
+// ---- NCCL is bound at run time (dlopen) so that the library loads on hosts without it ----
+typedef struct ncclComm* ncclComm_t;
+typedef struct { char internal[128]; } ncclUniqueId_t;
+enum { NCCL_FLOAT32 = 7, NCCL_SUM = 0 };
+struct NcclApi {
+  void* lib = nullptr;
+  int (*GetUniqueId)(ncclUniqueId_t*) = nullptr;
+  int (*CommInitRank)(ncclComm_t*, int, ncclUniqueId_t, int) = nullptr;
+  int (*CommDestroy)(ncclComm_t) = nullptr;
+  int (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+};
+static NcclApi g_nccl;
+
+namespace b2 {
+
+static thread_local char g_err[512] = "";
+int set_error(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof g_err, fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+static bool load_nccl() {
+  if (g_nccl.lib) return true;
+  const char* names[] = {"libnccl.so.2", "libnccl.so"};
+  for (const char* n : names) {
+    g_nccl.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+    if (g_nccl.lib) break;
+  }
+  if (!g_nccl.lib) return false;
+  g_nccl.GetUniqueId = (int (*)(ncclUniqueId_t*))dlsym(g_nccl.lib, "ncclGetUniqueId");
+  g_nccl.CommInitRank = (int (*)(ncclComm_t*, int, ncclUniqueId_t, int))dlsym(g_nccl.lib, "ncclCommInitRank");
+  g_nccl.CommDestroy = (int (*)(ncclComm_t))dlsym(g_nccl.lib, "ncclCommDestroy");
+  g_nccl.AllReduce = (int (*)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t))dlsym(g_nccl.lib, "ncclAllReduce");
+  g_nccl.GetErrorString = (const char* (*)(int))dlsym(g_nccl.lib, "ncclGetErrorString");
+  return g_nccl.GetUniqueId && g_nccl.CommInitRank && g_nccl.AllReduce;
+}
+
+}  // namespace b2
+
+using namespace b2;
+
+struct b2_engine {
+  b2_config cfg;
+  int P = 0, pstride = 0, sm_count = 148;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  // learner state
+  float *params = nullptr, *adam_m = nullptr, *adam_v = nullptr, *grads = nullptr, *partials = nullptr;
+  int64_t* adam_step = nullptr;
+  double* loss_log = nullptr;
+  int loss_log_cap = 0;
+  std::vector<double> last_losses;  // [steps][4]
+  int partial_rows = 0;
+  // env state
+  double* state = nullptr;
+  int32_t *ep_step = nullptr, *ep_count = nullptr;
+  float *ep_ret = nullptr, *ep_log = nullptr;
+  int max_eps = 0;
+  uint64_t global_step = 0;
+  int64_t total_env_steps = 0;
+  // trajectories
+  Traj tr;
+  bool trace = false;
+  bool have_traj = false;
+  float* forced = nullptr;
+  int64_t forced_cap = 0;
+  // staging for the host-buffer entry points
+  float* stage = nullptr;
+  int64_t stage_floats = 0;
+  uint8_t* stage_u8 = nullptr;
+  int64_t stage_u8_n = 0;
+  int* status = nullptr;
+  int* status_host = nullptr;  // pinned
+  uint64_t act_calls = 0;
+  int64_t launches = 0;
+  float* flush_buf = nullptr;
+  int64_t flush_n = 0;
+  // comm
+  ncclComm_t comm = nullptr;
+  int rank = 0, world = 1;
+  HyperDev hp;
+};
+
+namespace {
+
+#define CK(expr) B2_CUDA_CHECK(expr)
+#define NEED(h) \
+  if (!(h)) return set_error(B2_ERR_INVALID, "null handle")
+
+void make_hyper(b2_engine* E) {
+  const b2_config& c = E->cfg;
+  HyperDev& h = E->hp;
+  const float var = (float)(c.action_std * c.action_std);        // ppo_nn.h:124-126 action_var is f32
+  h.sigma = (float)c.action_std;
+  h.sigma_d = c.action_std;
+  h.inv_var = 1.0f / var;                                        // src/ppo_nn.cpp:24
+  h.half_log_norm = (logf(var) + (float)(log(2 * M_PI) * 1)) / 2;  // :42-44
+  const float v1 = (float)pow(2 * M_PI * M_E, 1);                // :56 (Q8: (2 pi e)^k, not its log)
+  h.loss3 = (float)(-0.01 * (double)(0.5f * (logf(var) + v1)));  // :64, :289
+  h.gamma = (float)c.gamma;
+  h.clip_lo = (float)(1 - c.eps_clip);
+  h.clip_hi = (float)(1 + c.eps_clip);
+  h.lr = c.lr; h.beta1 = c.beta1; h.beta2 = c.beta2; h.eps = 1e-8;  // libtorch AdamOptions default eps
+}
+
+int ensure_traj(b2_engine* E, int64_t cap) {
+  Traj& t = E->tr;
+  if (cap <= t.cap && (!E->trace || t.state_trace)) return B2_OK;
+  if (cap > t.cap) {
+    cudaFree(t.obs); cudaFree(t.action); cudaFree(t.logp); cudaFree(t.mu); cudaFree(t.reward);
+    cudaFree(t.ret); cudaFree(t.vboot); cudaFree(t.vcur); cudaFree(t.flags); cudaFree(t.state_trace);
+    t = Traj();
+    t.cap = cap;
+    CK(cudaMalloc(&t.obs, sizeof(float) * OBS * cap));
+    CK(cudaMalloc(&t.action, sizeof(float) * cap));
+    CK(cudaMalloc(&t.logp, sizeof(float) * cap));
+    CK(cudaMalloc(&t.mu, sizeof(float) * cap));
+    CK(cudaMalloc(&t.reward, sizeof(float) * cap));
+    CK(cudaMalloc(&t.ret, sizeof(float) * cap));
+    CK(cudaMalloc(&t.vboot, sizeof(float) * cap));
+    CK(cudaMalloc(&t.vcur, sizeof(float) * cap));
+    CK(cudaMalloc(&t.flags, cap));
+    E->have_traj = false;
+  }
+  if (E->trace && !t.state_trace) CK(cudaMalloc(&t.state_trace, sizeof(double) * 4 * t.cap));
+  return B2_OK;
+}
+
+int ensure_stage(b2_engine* E, int64_t floats, int64_t bytes_u8) {
+  if (floats > E->stage_floats) {
+    cudaFree(E->stage);
+    E->stage = nullptr;
+    CK(cudaMalloc(&E->stage, sizeof(float) * floats));
+    E->stage_floats = floats;
+  }
+  if (bytes_u8 > E->stage_u8_n) {
+    cudaFree(E->stage_u8);
+    E->stage_u8 = nullptr;
+    CK(cudaMalloc(&E->stage_u8, bytes_u8));
+    E->stage_u8_n = bytes_u8;
+  }
+  return B2_OK;
+}
+
+int check_status(b2_engine* E, const char* where) {
+  CK(cudaMemcpyAsync(E->status_host, E->status, sizeof(int), cudaMemcpyDeviceToHost, E->stream));
+  CK(cudaStreamSynchronize(E->stream));
+  if (*E->status_host & 1) {
+    cudaMemsetAsync(E->status, 0, sizeof(int), E->stream);
+    return set_error(B2_ERR_NONFINITE, "%s: non-finite action on device (cf. src/main.cpp:50-55)", where);
+  }
+  return B2_OK;
+}
+
+// K2 + K optimizer steps on whatever E->tr currently holds.
+int run_update(b2_engine* E, b2_update_stats* stats) {
+  Traj& t = E->tr;
+  const int64_t B = t.n_envs * t.horizon;
+  if (B <= 0) return set_error(B2_ERR_STATE, "update: empty trajectory");
+  const int K = E->cfg.k_epochs, M = std::max(1, E->cfg.n_minibatches);
+  const int steps = K * M;
+  int nl = 0;
+  cudaError_t ce = launch_returns(E->params, t, E->hp, E->stream, &nl);  // once, at entry (:207-236)
+  if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "returns: %s", cudaGetErrorString(ce));
+  E->launches += nl;
+  if (steps > E->loss_log_cap) {
+    cudaFree(E->loss_log);
+    E->loss_log = nullptr;
+    CK(cudaMalloc(&E->loss_log, sizeof(double) * 4 * steps));
+    E->loss_log_cap = steps;
+  }
+  CK(cudaMemsetAsync(E->loss_log, 0, sizeof(double) * 4 * steps, E->stream));
+  const int64_t per = B / M;
+  int rows_needed = update_grid_for(per + (B % M), E->sm_count);
+  if (rows_needed > E->partial_rows) {
+    cudaFree(E->partials);
+    E->partials = nullptr;
+    CK(cudaMalloc(&E->partials, sizeof(float) * (size_t)rows_needed * E->pstride));
+    E->partial_rows = rows_needed;
+  }
+  UpdateArgs a{};
+  a.params = E->params; a.adam_m = E->adam_m; a.adam_v = E->adam_v; a.grads = E->grads;
+  a.partials = E->partials; a.adam_step = E->adam_step; a.loss_log = E->loss_log;
+  a.tr = t; a.idx = nullptr; a.hp = E->hp;
+  int slot = 0;
+  for (int k = 0; k < K; k++) {           // :245
+    for (int m = 0; m < M; m++, slot++) { // M == 1 is the reference (full batch, Q9)
+      a.first = (int64_t)m * per;
+      a.count = (m == M - 1) ? (B - a.first) : per;
+      a.denom = a.count * E->world;       // every rank holds an equal shard of the global minibatch
+      a.grid = update_grid_for(a.count, E->sm_count);
+      a.step_slot = slot;
+      if ((ce = launch_ppo_grad(a, E->stream)) != cudaSuccess) return set_error(B2_ERR_CUDA, "ppo_grad: %s", cudaGetErrorString(ce));
+      if (E->world == 1) {
+        if ((ce = launch_reduce(a, true, E->stream)) != cudaSuccess) return set_error(B2_ERR_CUDA, "reduce: %s", cudaGetErrorString(ce));
+        E->launches += 2;
+      } else {
+        if ((ce = launch_reduce(a, false, E->stream)) != cudaSuccess) return set_error(B2_ERR_CUDA, "reduce: %s", cudaGetErrorString(ce));
+        int ne = g_nccl.AllReduce(E->grads, E->grads, (size_t)E->pstride, NCCL_FLOAT32, NCCL_SUM, E->comm, E->stream);
+        if (ne != 0) return set_error(B2_ERR_COMM, "ncclAllReduce: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(ne) : "?");
+        if ((ce = launch_adam(a, E->stream)) != cudaSuccess) return set_error(B2_ERR_CUDA, "adam: %s", cudaGetErrorString(ce));
+        E->launches += 3;
+      }
+    }
+  }
+  E->last_losses.assign((size_t)4 * steps, 0.0);
+  int64_t step_host = 0;
+  CK(cudaMemcpyAsync(E->last_losses.data(), E->loss_log, sizeof(double) * 4 * steps, cudaMemcpyDeviceToHost, E->stream));
+  CK(cudaMemcpyAsync(&step_host, E->adam_step, sizeof(int64_t), cudaMemcpyDeviceToHost, E->stream));
+  CK(cudaStreamSynchronize(E->stream));
+  bool finite = true;
+  for (double v : E->last_losses) finite &= std::isfinite(v);
+  if (stats) {
+    const double* L = &E->last_losses[(size_t)4 * (steps - 1)];
+    stats->loss1 = L[0]; stats->loss2 = L[1]; stats->loss3 = (double)E->hp.loss3;
+    stats->loss = L[0] + L[1] + (double)E->hp.loss3;  // :290, :302
+    stats->clip_frac = L[2];
+    stats->samples = B; stats->adam_step = step_host; stats->optimizer_steps = steps;
+  }
+  if (!finite) return set_error(B2_ERR_NONFINITE, "update: non-finite loss");
+  return B2_OK;
+}
+
+int upload_batch(b2_engine* E, const b2_batch* b) {
+  if (!b || !b->obs || !b->reward || !b->flags) return set_error(B2_ERR_INVALID, "batch: null field");
+  const int64_t B = b->n_envs * b->horizon;
+  if (B <= 0) return set_error(B2_ERR_INVALID, "batch: empty");
+  int rc = ensure_traj(E, B);
+  if (rc) return rc;
+  if ((rc = ensure_stage(E, B * OBS, 0))) return rc;
+  Traj& t = E->tr;
+  CK(cudaMemcpyAsync(E->stage, b->obs, sizeof(float) * OBS * B, cudaMemcpyHostToDevice, E->stream));
+  cudaError_t ce = launch_aos_to_soa(E->stage, t.obs, t.cap, B, E->stream);
+  if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "aos_to_soa: %s", cudaGetErrorString(ce));
+  E->launches += 1;
+  if (b->action) CK(cudaMemcpyAsync(t.action, b->action, sizeof(float) * B, cudaMemcpyHostToDevice, E->stream));
+  if (b->logp) CK(cudaMemcpyAsync(t.logp, b->logp, sizeof(float) * B, cudaMemcpyHostToDevice, E->stream));
+  CK(cudaMemcpyAsync(t.reward, b->reward, sizeof(float) * B, cudaMemcpyHostToDevice, E->stream));
+  CK(cudaMemcpyAsync(t.flags, b->flags, B, cudaMemcpyHostToDevice, E->stream));
+  t.n_envs = b->n_envs;
+  t.horizon = b->horizon;
+  E->have_traj = true;
+  return B2_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int b2_abi_version(void) { return B2_ABI_VERSION; }
+const char* b2_last_error(void) { return g_err; }
+int b2_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+int b2_create(const b2_config* cfg, b2_handle* out) {
+  if (!cfg || !out) return set_error(B2_ERR_INVALID, "b2_create: null argument");
+  *out = nullptr;
+  if (cfg->control_vars != 1) return set_error(B2_ERR_INVALID, "control_vars must be 1 (src/ppo_nn.cpp:107)");
+  if (cfg->obs_vars != 6) return set_error(B2_ERR_INVALID, "obs_vars must be 6 (include/cart_pole.h:120-131)");
+  if (cfg->hidden1 != 64 || cfg->hidden2 != 32) return set_error(B2_ERR_INVALID, "hidden widths %dx%d not built (64x32 only)", cfg->hidden1, cfg->hidden2);
+  if (cfg->n_envs < 1 || cfg->horizon < 1 || cfg->n_timestep < 1) return set_error(B2_ERR_INVALID, "n_envs, horizon, n_timestep must be >= 1");
+  if (cfg->precision != B2_PREC_F64 && cfg->precision != B2_PREC_F32) return set_error(B2_ERR_INVALID, "unknown precision %d", cfg->precision);
+  if (cfg->k_epochs < 1 || cfg->n_minibatches < 1) return set_error(B2_ERR_INVALID, "k_epochs and n_minibatches must be >= 1");
+  if (!(cfg->action_std > 0)) return set_error(B2_ERR_INVALID, "action_std must be > 0");
+  int ndev = b2_device_count();
+  if (ndev <= 0) return set_error(B2_ERR_NO_DEVICE, "no CUDA device: this engine has no CPU path");
+  if (cfg->device < 0 || cfg->device >= ndev) return set_error(B2_ERR_INVALID, "device %d out of range (%d visible)", cfg->device, ndev);
+  CK(cudaSetDevice(cfg->device));
+  b2_engine* E = new (std::nothrow) b2_engine();
+  if (!E) return set_error(B2_ERR_INVALID, "out of host memory");
+  E->cfg = *cfg;
+  E->P = NetDefault::P;
+  E->pstride = update_partial_stride();
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, cfg->device));
+  E->sm_count = prop.multiProcessorCount;
+  make_hyper(E);
+  CK(cudaStreamCreateWithFlags(&E->stream, cudaStreamNonBlocking));
+  CK(cudaEventCreate(&E->ev0));
+  CK(cudaEventCreate(&E->ev1));
+  const int64_t NE = cfg->n_envs;
+  CK(cudaMalloc(&E->params, sizeof(float) * E->P));
+  CK(cudaMalloc(&E->adam_m, sizeof(float) * E->P));
+  CK(cudaMalloc(&E->adam_v, sizeof(float) * E->P));
+  CK(cudaMalloc(&E->grads, sizeof(float) * E->pstride));
+  CK(cudaMalloc(&E->adam_step, sizeof(int64_t)));
+  CK(cudaMalloc(&E->status, sizeof(int)));
+  CK(cudaMallocHost(&E->status_host, sizeof(int)));
+  CK(cudaMemset(E->params, 0, sizeof(float) * E->P));
+  CK(cudaMemset(E->adam_m, 0, sizeof(float) * E->P));
+  CK(cudaMemset(E->adam_v, 0, sizeof(float) * E->P));
+  CK(cudaMemset(E->grads, 0, sizeof(float) * E->pstride));
+  CK(cudaMemset(E->adam_step, 0, sizeof(int64_t)));
+  CK(cudaMemset(E->status, 0, sizeof(int)));
+  E->max_eps = cfg->horizon / cfg->n_timestep + 2;
+  CK(cudaMalloc(&E->state, sizeof(double) * 4 * NE));
+  CK(cudaMalloc(&E->ep_step, sizeof(int32_t) * NE));
+  CK(cudaMalloc(&E->ep_count, sizeof(int32_t) * NE));
+  CK(cudaMalloc(&E->ep_ret, sizeof(float) * NE));
+  CK(cudaMalloc(&E->ep_log, sizeof(float) * NE * E->max_eps));
+  CK(cudaMemset(E->state, 0, sizeof(double) * 4 * NE));   // CartPole::reset: u = 0 (cart_pole.h:86)
+  CK(cudaMemset(E->ep_step, 0, sizeof(int32_t) * NE));
+  CK(cudaMemset(E->ep_count, 0, sizeof(int32_t) * NE));
+  CK(cudaMemset(E->ep_ret, 0, sizeof(float) * NE));
+  int rc = ensure_traj(E, NE * cfg->horizon);
+  if (rc) { b2_destroy(E); return rc; }
+  *out = E;
+  rc = b2_init_params(E, cfg->seed);
+  if (rc) { b2_destroy(E); *out = nullptr; return rc; }
+  return B2_OK;
+}
+
+int b2_destroy(b2_handle E) {
+  if (!E) return B2_OK;
+  cudaSetDevice(E->cfg.device);
+  if (E->stream) cudaStreamSynchronize(E->stream);
+  if (E->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(E->comm);
+  Traj& t = E->tr;
+  void* ptrs[] = {E->params, E->adam_m, E->adam_v, E->grads, E->partials, E->adam_step, E->loss_log, E->state,
+                  E->ep_step, E->ep_count, E->ep_ret, E->ep_log, t.obs, t.action, t.logp, t.mu, t.reward, t.ret,
+                  t.vboot, t.vcur, t.flags, t.state_trace, E->forced, E->stage, E->stage_u8, E->status, E->flush_buf};
+  for (void* p : ptrs) cudaFree(p);
+  if (E->status_host) cudaFreeHost(E->status_host);
+  if (E->ev0) cudaEventDestroy(E->ev0);
+  if (E->ev1) cudaEventDestroy(E->ev1);
+  if (E->stream) cudaStreamDestroy(E->stream);
+  delete E;
+  return B2_OK;
+}
+
+int b2_get_config(b2_handle E, b2_config* out) {
+  NEED(E);
+  if (!out) return set_error(B2_ERR_INVALID, "null out");
+  *out = E->cfg;
+  return B2_OK;
+}
+
+int64_t b2_n_params(b2_handle E) { return E ? E->P : 0; }
+
+int b2_init_params(b2_handle E, uint64_t seed) {
+  NEED(E);
+  // torch::nn::Linear::reset_parameters: kaiming_uniform(a=sqrt(5)) on W and U(+-1/sqrt(fan_in)) on b,
+  // both = U(-1/sqrt(fan_in), 1/sqrt(fan_in)).  Drawn host-side from Philox (init is not a hot path;
+  // parity runs import the reference's weights through b2_set_params instead).
+  using N = NetDefault;
+  std::vector<float> p((size_t)E->P);
+  uint64_t ctr = 0;
+  auto fill = [&](int off, int n, int fan_in) {
+    const float bound = 1.0f / sqrtf((float)fan_in);
+    for (int i = 0; i < n; i++, ctr++) {
+      uint32_t x[4];
+      philox4x32_10((uint32_t)ctr, (uint32_t)(ctr >> 32), 0x1717u, 0, (uint32_t)seed, (uint32_t)(seed >> 32), x);
+      float u = ((float)(x[0] >> 8) + 0.5f) * (1.0f / 16777216.0f);
+      p[(size_t)off + i] = (2.0f * u - 1.0f) * bound;
+    }
+  };
+  for (int net = 0; net < 2; net++) {
+    int o = net * N::SIZE;
+    fill(o + N::oW1, N::H1 * N::S, N::S); fill(o + N::ob1, N::H1, N::S);
+    fill(o + N::oW2, N::H2 * N::H1, N::H1); fill(o + N::ob2, N::H2, N::H1);
+    fill(o + N::oW3, N::H2, N::H2); fill(o + N::ob3, 1, N::H2);
+  }
+  return b2_set_params(E, p.data(), E->P);
+}
+
+int b2_set_params(b2_handle E, const float* p, int64_t n) {
+  NEED(E);
+  if (!p || n != E->P) return set_error(B2_ERR_INVALID, "set_params: expected %d floats, got %lld", E->P, (long long)n);
+  CK(cudaMemcpyAsync(E->params, p, sizeof(float) * n, cudaMemcpyHostToDevice, E->stream));
+  CK(cudaStreamSynchronize(E->stream));
+  return B2_OK;
+}
+int b2_get_params(b2_handle E, float* p, int64_t n) {
+  NEED(E);
+  if (!p || n != E->P) return set_error(B2_ERR_INVALID, "get_params: expected %d floats", E->P);
+  CK(cudaMemcpyAsync(p, E->params, sizeof(float) * n, cudaMemcpyDeviceToHost, E->stream));
+  CK(cudaStreamSynchronize(E->stream));
+  return B2_OK;
+}
+int b2_set_adam_state(b2_handle E, const float* m, const float* v, int64_t n, int64_t step) {
+  NEED(E);
+  if (!m || !v || n != E->P || step < 0) return set_error(B2_ERR_INVALID, "set_adam_state: bad arguments");
+  CK(cudaMemcpyAsync(E->adam_m, m, sizeof(float) * n, cudaMemcpyHostToDevice, E->stream));
+  CK(cudaMemcpyAsync(E->adam_v, v, sizeof(float) * n, cudaMemcpyHostToDevice, E->stream));
+  CK(cudaMemcpyAsync(E->adam_step, &step, sizeof(int64_t), cudaMemcpyHostToDevice, E->stream));
+  CK(cudaStreamSynchronize(E->stream));
+  return B2_OK;
+}
+int b2_get_adam_state(b2_handle E, float* m, float* v, int64_t n, int64_t* step) {
+  NEED(E);
+  if (n != E->P) return set_error(B2_ERR_INVALID, "get_adam_state: expected %d floats", E->P);
+  if (m) CK(cudaMemcpyAsync(m, E->adam_m, sizeof(float) * n, cudaMemcpyDeviceToHost, E->stream));
+  if (v) CK(cudaMemcpyAsync(v, E->adam_v, sizeof(float) * n, cudaMemcpyDeviceToHost, E->stream));
+  if (step) CK(cudaMemcpyAsync(step, E->adam_step, sizeof(int64_t), cudaMemcpyDeviceToHost, E->stream));
+  CK(cudaStreamSynchronize(E->stream));
+  return B2_OK;
+}
+int b2_get_grads(b2_handle E, float* g, int64_t n) {
+  NEED(E);
+  if (!g || n != E->P) return set_error(B2_ERR_INVALID, "get_grads: expected %d floats", E->P);
+  CK(cudaMemcpyAsync(g, E->grads, sizeof(float) * n, cudaMemcpyDeviceToHost, E->stream));
+  CK(cudaStreamSynchronize(E->stream));
+  return B2_OK;
+}
+
+// checkpoint: "B2CK" | version | P | step | params | m | v   (the reference has none)
+int b2_save_checkpoint(b2_handle E, const char* path) {
+  NEED(E);
+  if (!path) return set_error(B2_ERR_INVALID, "null path");
+  std::vector<float> p(E->P), m(E->P), v(E->P);
+  int64_t step = 0;
+  int rc = b2_get_params(E, p.data(), E->P);
+  if (rc) return rc;
+  if ((rc = b2_get_adam_state(E, m.data(), v.data(), E->P, &step))) return rc;
+  FILE* f = fopen(path, "wb");
+  if (!f) return set_error(B2_ERR_IO, "cannot open %s for writing", path);
+  int32_t hdr[2] = {1, E->P};
+  bool ok = fwrite("B2CK", 1, 4, f) == 4 && fwrite(hdr, sizeof hdr, 1, f) == 1 && fwrite(&step, sizeof step, 1, f) == 1 &&
+            fwrite(p.data(), sizeof(float), E->P, f) == (size_t)E->P && fwrite(m.data(), sizeof(float), E->P, f) == (size_t)E->P &&
+            fwrite(v.data(), sizeof(float), E->P, f) == (size_t)E->P;
+  ok = (fclose(f) == 0) && ok;
+  return ok ? B2_OK : set_error(B2_ERR_IO, "short write to %s", path);
+}
+int b2_load_checkpoint(b2_handle E, const char* path) {
+  NEED(E);
+  if (!path) return set_error(B2_ERR_INVALID, "null path");
+  FILE* f = fopen(path, "rb");
+  if (!f) return set_error(B2_ERR_IO, "cannot open %s", path);
+  char magic[4];
+  int32_t hdr[2];
+  int64_t step = 0;
+  std::vector<float> p(E->P), m(E->P), v(E->P);
+  bool ok = fread(magic, 1, 4, f) == 4 && memcmp(magic, "B2CK", 4) == 0 && fread(hdr, sizeof hdr, 1, f) == 1 &&
+            hdr[0] == 1 && hdr[1] == E->P && fread(&step, sizeof step, 1, f) == 1 &&
+            fread(p.data(), sizeof(float), E->P, f) == (size_t)E->P && fread(m.data(), sizeof(float), E->P, f) == (size_t)E->P &&
+            fread(v.data(), sizeof(float), E->P, f) == (size_t)E->P;
+  fclose(f);
+  if (!ok) return set_error(B2_ERR_IO, "%s is not a matching b200ppo checkpoint", path);
+  int rc = b2_set_params(E, p.data(), E->P);
+  if (rc) return rc;
+  return b2_set_adam_state(E, m.data(), v.data(), E->P, step);
+}
+
+int b2_act(b2_handle E, const float* obs, int64_t n, const float* eps, float* action, float* logp, float* mu) {
+  NEED(E);
+  if (n == 0) return B2_OK;
+  if (!obs || !action || !logp || n < 0) return set_error(B2_ERR_INVALID, "b2_act: null/negative argument");
+  CK(cudaSetDevice(E->cfg.device));
+  // staging: obs[n][6] | eps[n] | action[n] | logp[n] | mu[n]
+  int rc = ensure_stage(E, n * (OBS + 4), 0);
+  if (rc) return rc;
+  float* d_obs = E->stage;
+  float* d_eps = d_obs + n * OBS;
+  float* d_act = d_eps + n;
+  float* d_lp = d_act + n;
+  float* d_mu = d_lp + n;
+  CK(cudaMemcpyAsync(d_obs, obs, sizeof(float) * OBS * n, cudaMemcpyHostToDevice, E->stream));
+  if (eps) CK(cudaMemcpyAsync(d_eps, eps, sizeof(float) * n, cudaMemcpyHostToDevice, E->stream));
+  cudaError_t ce = launch_act(E->params, d_obs, eps ? d_eps : nullptr, n, E->cfg.seed, E->act_calls++, d_act, d_lp,
+                              d_mu, E->hp, E->status, E->stream);
+  if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "act: %s", cudaGetErrorString(ce));
+  E->launches += 1;
+  CK(cudaMemcpyAsync(action, d_act, sizeof(float) * n, cudaMemcpyDeviceToHost, E->stream));
+  CK(cudaMemcpyAsync(logp, d_lp, sizeof(float) * n, cudaMemcpyDeviceToHost, E->stream));
+  if (mu) CK(cudaMemcpyAsync(mu, d_mu, sizeof(float) * n, cudaMemcpyDeviceToHost, E->stream));
+  return check_status(E, "b2_act");
+}
+
+int b2_value(b2_handle E, const float* obs, int64_t n, float* value) {
+  NEED(E);
+  if (n == 0) return B2_OK;
+  if (!obs || !value || n < 0) return set_error(B2_ERR_INVALID, "b2_value: null/negative argument");
+  CK(cudaSetDevice(E->cfg.device));
+  int rc = ensure_stage(E, n * (OBS + 1), 0);
+  if (rc) return rc;
+  float* d_obs = E->stage;
+  float* d_v = d_obs + n * OBS;
+  CK(cudaMemcpyAsync(d_obs, obs, sizeof(float) * OBS * n, cudaMemcpyHostToDevice, E->stream));
+  cudaError_t ce = launch_value(E->params, d_obs, n, d_v, E->stream);
+  if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "value: %s", cudaGetErrorString(ce));
+  E->launches += 1;
+  CK(cudaMemcpyAsync(value, d_v, sizeof(float) * n, cudaMemcpyDeviceToHost, E->stream));
+  CK(cudaStreamSynchronize(E->stream));
+  return B2_OK;
+}
+
+int b2_update(b2_handle E, const b2_batch* batch, b2_update_stats* stats) {
+  NEED(E);
+  CK(cudaSetDevice(E->cfg.device));
+  if (!batch || !batch->action || !batch->logp) return set_error(B2_ERR_INVALID, "b2_update: batch needs obs, action, logp, reward, flags");
+  int rc = upload_batch(E, batch);
+  if (rc) return rc;
+  return run_update(E, stats);
+}
+
+int b2_returns(b2_handle E, const b2_batch* batch, float* returns) {
+  NEED(E);
+  CK(cudaSetDevice(E->cfg.device));
+  if (!returns) return set_error(B2_ERR_INVALID, "b2_returns: null output");
+  int rc = upload_batch(E, batch);
+  if (rc) return rc;
+  int nl = 0;
+  cudaError_t ce = launch_returns(E->params, E->tr, E->hp, E->stream, &nl);
+  if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "returns: %s", cudaGetErrorString(ce));
+  E->launches += nl;
+  CK(cudaMemcpyAsync(returns, E->tr.ret, sizeof(float) * batch->n_envs * batch->horizon, cudaMemcpyDeviceToHost, E->stream));
+  CK(cudaStreamSynchronize(E->stream));
+  return B2_OK;
+}
+
+int b2_last_update_losses(b2_handle E, double* l1, double* l2, double* l3, double* lt, int n) {
+  NEED(E);
+  const int steps = (int)(E->last_losses.size() / 4);
+  if (n > steps) return set_error(B2_ERR_INVALID, "only %d optimizer steps recorded", steps);
+  for (int i = 0; i < n; i++) {
+    const double* L = &E->last_losses[(size_t)4 * i];
+    if (l1) l1[i] = L[0];
+    if (l2) l2[i] = L[1];
+    if (l3) l3[i] = (double)E->hp.loss3;
+    if (lt) lt[i] = L[0] + L[1] + (double)E->hp.loss3;
+  }
+  return B2_OK;
+}
+
+int b2_env_reset(b2_handle E) {
+  NEED(E);
+  CK(cudaSetDevice(E->cfg.device));
+  const int64_t NE = E->cfg.n_envs;
+  CK(cudaMemsetAsync(E->state, 0, sizeof(double) * 4 * NE, E->stream));
+  CK(cudaMemsetAsync(E->ep_step, 0, sizeof(int32_t) * NE, E->stream));
+  CK(cudaMemsetAsync(E->ep_ret, 0, sizeof(float) * NE, E->stream));
+  CK(cudaMemsetAsync(E->ep_count, 0, sizeof(int32_t) * NE, E->stream));
+  E->global_step = 0;
+  return B2_OK;
+}
+
+int b2_env_set_state(b2_handle E, const double* u, const int32_t* ep_step, int64_t n) {
+  NEED(E);
+  if (!u || n != E->cfg.n_envs) return set_error(B2_ERR_INVALID, "env_set_state: expected %lld envs", (long long)E->cfg.n_envs);
+  std::vector<double> soa((size_t)4 * n);
+  for (int64_t e = 0; e < n; e++)
+    for (int j = 0; j < 4; j++) soa[(size_t)j * n + e] = u[4 * e + j];
+  CK(cudaMemcpyAsync(E->state, soa.data(), sizeof(double) * 4 * n, cudaMemcpyHostToDevice, E->stream));
+  if (ep_step) CK(cudaMemcpyAsync(E->ep_step, ep_step, sizeof(int32_t) * n, cudaMemcpyHostToDevice, E->stream));
+  CK(cudaStreamSynchronize(E->stream));
+  return B2_OK;
+}
+int b2_env_get_state(b2_handle E, double* u, int32_t* ep_step, int64_t n) {
+  NEED(E);
+  if (n != E->cfg.n_envs) return set_error(B2_ERR_INVALID, "env_get_state: expected %lld envs", (long long)E->cfg.n_envs);
+  std::vector<double> soa((size_t)4 * n);
+  CK(cudaMemcpyAsync(soa.data(), E->state, sizeof(double) * 4 * n, cudaMemcpyDeviceToHost, E->stream));
+  if (ep_step) CK(cudaMemcpyAsync(ep_step, E->ep_step, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, E->stream));
+  CK(cudaStreamSynchronize(E->stream));
+  if (u)
+    for (int64_t e = 0; e < n; e++)
+      for (int j = 0; j < 4; j++) u[4 * e + j] = soa[(size_t)j * n + e];
+  return B2_OK;
+}
+
+int b2_set_state_trace(b2_handle E, int enable) {
+  NEED(E);
+  E->trace = enable != 0;
+  return ensure_traj(E, E->tr.cap);
+}
+
+int b2_rollout(b2_handle E, int T, const float* forced_action) {
+  NEED(E);
+  CK(cudaSetDevice(E->cfg.device));
+  if (T < 1 || T > E->cfg.horizon) return set_error(B2_ERR_INVALID, "rollout: T=%d outside [1, horizon=%d]", T, E->cfg.horizon);
+  const int64_t NE = E->cfg.n_envs;
+  int rc = ensure_traj(E, NE * T);
+  if (rc) return rc;
+  if (forced_action) {
+    if (NE * T > E->forced_cap) {
+      cudaFree(E->forced);
+      E->forced = nullptr;
+      CK(cudaMalloc(&E->forced, sizeof(float) * NE * T));
+      E->forced_cap = NE * T;
+    }
+    CK(cudaMemcpyAsync(E->forced, forced_action, sizeof(float) * NE * T, cudaMemcpyHostToDevice, E->stream));
+  }
+  RolloutArgs a{};
+  a.params = E->params; a.state = E->state; a.ep_step = E->ep_step; a.ep_ret = E->ep_ret;
+  a.ep_count = E->ep_count; a.ep_log = E->ep_log; a.max_eps = E->max_eps;
+  E->tr.n_envs = NE; E->tr.horizon = T;
+  a.tr = E->tr;
+  a.forced_action = forced_action ? E->forced : nullptr;
+  a.n_envs = NE; a.T = T; a.n_timestep = E->cfg.n_timestep;
+  a.seed = E->cfg.seed; a.env_offset = E->cfg.env_offset; a.step0 = E->global_step;
+  a.hp = E->hp; a.status = E->status;
+  cudaError_t ce = launch_rollout(a, E->cfg.precision, E->trace, E->stream, E->cfg.hidden1, E->cfg.hidden2);
+  if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "rollout: %s", cudaGetErrorString(ce));
+  E->launches += 1;
+  E->global_step += (uint64_t)T;
+  E->total_env_steps += NE * T;
+  E->have_traj = true;
+  return B2_OK;
+}
+
+int b2_update_resident(b2_handle E, b2_update_stats* stats) {
+  NEED(E);
+  CK(cudaSetDevice(E->cfg.device));
+  if (!E->have_traj) return set_error(B2_ERR_STATE, "update_resident: no trajectory on device (call b2_rollout first)");
+  int rc = check_status(E, "rollout");
+  if (rc) return rc;
+  return run_update(E, stats);
+}
+
+int b2_train_iteration(b2_handle E, int T, b2_update_stats* stats) {
+  int rc = b2_rollout(E, T, nullptr);
+  if (rc) return rc;
+  return b2_update_resident(E, stats);
+}
+
+int b2_traj_download(b2_handle E, b2_batch_out* out, double* state_trace) {
+  NEED(E);
+  CK(cudaSetDevice(E->cfg.device));
+  if (!E->have_traj) return set_error(B2_ERR_STATE, "traj_download: nothing on device");
+  if (!out) return set_error(B2_ERR_INVALID, "null out");
+  Traj& t = E->tr;
+  const int64_t B = t.n_envs * t.horizon;
+  if (out->obs) {
+    int rc = ensure_stage(E, B * OBS, 0);
+    if (rc) return rc;
+    cudaError_t ce = launch_soa_to_aos(t.obs, E->stage, t.cap, B, E->stream);
+    if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "soa_to_aos: %s", cudaGetErrorString(ce));
+    E->launches += 1;
+    CK(cudaMemcpyAsync(out->obs, E->stage, sizeof(float) * OBS * B, cudaMemcpyDeviceToHost, E->stream));
+  }
+  if (out->action) CK(cudaMemcpyAsync(out->action, t.action, sizeof(float) * B, cudaMemcpyDeviceToHost, E->stream));
+  if (out->logp) CK(cudaMemcpyAsync(out->logp, t.logp, sizeof(float) * B, cudaMemcpyDeviceToHost, E->stream));
+  if (out->mu) CK(cudaMemcpyAsync(out->mu, t.mu, sizeof(float) * B, cudaMemcpyDeviceToHost, E->stream));
+  if (out->reward) CK(cudaMemcpyAsync(out->reward, t.reward, sizeof(float) * B, cudaMemcpyDeviceToHost, E->stream));
+  if (out->flags) CK(cudaMemcpyAsync(out->flags, t.flags, B, cudaMemcpyDeviceToHost, E->stream));
+  if (out->returns) CK(cudaMemcpyAsync(out->returns, t.ret, sizeof(float) * B, cudaMemcpyDeviceToHost, E->stream));
+  if (state_trace) {
+    if (!E->trace || !t.state_trace) return set_error(B2_ERR_STATE, "state trace was not enabled before the rollout");
+    CK(cudaMemcpyAsync(state_trace, t.state_trace, sizeof(double) * 4 * B, cudaMemcpyDeviceToHost, E->stream));
+  }
+  return check_status(E, "rollout");
+}
+
+int b2_episode_stats(b2_handle E, int32_t* counts, float* returns, int max_eps, int64_t n) {
+  NEED(E);
+  if (n != E->cfg.n_envs || !counts) return set_error(B2_ERR_INVALID, "episode_stats: expected %lld envs", (long long)E->cfg.n_envs);
+  CK(cudaMemcpyAsync(counts, E->ep_count, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, E->stream));
+  std::vector<float> log;
+  if (returns) {
+    log.resize((size_t)n * E->max_eps);
+    CK(cudaMemcpyAsync(log.data(), E->ep_log, sizeof(float) * n * E->max_eps, cudaMemcpyDeviceToHost, E->stream));
+  }
+  CK(cudaStreamSynchronize(E->stream));
+  if (returns)
+    for (int64_t e = 0; e < n; e++)
+      for (int i = 0; i < max_eps; i++)
+        returns[e * max_eps + i] = (i < counts[e] && i < E->max_eps) ? log[(size_t)i * n + e] : 0.0f;
+  return B2_OK;
+}
+
+int64_t b2_total_env_steps(b2_handle E) { return E ? E->total_env_steps : 0; }
+
+int b2_comm_unique_id(char id[B2_COMM_ID_BYTES]) {
+  if (!id) return set_error(B2_ERR_INVALID, "null id");
+  if (!load_nccl()) return set_error(B2_ERR_COMM, "libnccl.so.2 not found: %s", dlerror());
+  ncclUniqueId_t u;
+  int e = g_nccl.GetUniqueId(&u);
+  if (e != 0) return set_error(B2_ERR_COMM, "ncclGetUniqueId failed (%d)", e);
+  static_assert(sizeof(u) == B2_COMM_ID_BYTES, "id size");
+  memcpy(id, &u, sizeof u);
+  return B2_OK;
+}
+
+int b2_comm_init(b2_handle E, int rank, int world, const char id[B2_COMM_ID_BYTES]) {
+  NEED(E);
+  if (world < 1 || rank < 0 || rank >= world || !id) return set_error(B2_ERR_INVALID, "comm_init: bad rank/world");
+  if (world == 1) { E->rank = 0; E->world = 1; return B2_OK; }
+  if (!load_nccl()) return set_error(B2_ERR_COMM, "libnccl.so.2 not found");
+  CK(cudaSetDevice(E->cfg.device));
+  ncclUniqueId_t u;
+  memcpy(&u, id, sizeof u);
+  int e = g_nccl.CommInitRank(&E->comm, world, u, rank);
+  if (e != 0) return set_error(B2_ERR_COMM, "ncclCommInitRank: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(e) : "?");
+  E->rank = rank;
+  E->world = world;
+  return B2_OK;
+}
+int b2_comm_world(b2_handle E) { return E ? E->world : 0; }
+
+int b2_sync(b2_handle E) {
+  NEED(E);
+  CK(cudaStreamSynchronize(E->stream));
+  return B2_OK;
+}
+int b2_timer_start(b2_handle E) {
+  NEED(E);
+  CK(cudaEventRecord(E->ev0, E->stream));
+  return B2_OK;
+}
+int b2_timer_stop_ms(b2_handle E, float* ms) {
+  NEED(E);
+  CK(cudaEventRecord(E->ev1, E->stream));
+  CK(cudaEventSynchronize(E->ev1));
+  if (ms) CK(cudaEventElapsedTime(ms, E->ev0, E->ev1));
+  return B2_OK;
+}
+int64_t b2_kernel_launches(b2_handle E) { return E ? E->launches : 0; }
+void* b2_stream(b2_handle E) { return E ? (void*)E->stream : nullptr; }
+
+int b2_flush_l2(b2_handle E) {
+  NEED(E);
+  if (!E->flush_buf) {
+    E->flush_n = (int64_t)160 << 18;  // 160 MiB of floats: larger than the 126 MB L2
+    CK(cudaMalloc(&E->flush_buf, sizeof(float) * E->flush_n));
+  }
+  cudaError_t ce = launch_flush(E->flush_buf, E->flush_n, E->stream);
+  if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "flush: %s", cudaGetErrorString(ce));
+  return B2_OK;
+}
+
+int b2_measure_fma_peak(b2_handle E, int fp64, double* tflops) {
+  NEED(E);
+  if (!tflops) return set_error(B2_ERR_INVALID, "null out");
+  CK(cudaSetDevice(E->cfg.device));
+  cudaError_t ce = measure_fma_peak(fp64 != 0, E->sm_count, E->stream, tflops);
+  if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "fma peak: %s", cudaGetErrorString(ce));
+  return B2_OK;
+}
+
+int b2_host_alloc(void** p, size_t bytes) {
+  if (!p) return set_error(B2_ERR_INVALID, "null out");
+  CK(cudaMallocHost(p, bytes));
+  return B2_OK;
+}
+int b2_host_free(void* p) {
+  if (p) CK(cudaFreeHost(p));
+  return B2_OK;
+}
+
+}  // extern "C"

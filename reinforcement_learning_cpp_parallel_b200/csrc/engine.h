@@ -1,0 +1,95 @@
+// engine.h -- internal state of one b2_handle and the kernel launch entry points.
+// Host C++ only sees POD + cudaStream_t; every kernel lives in its own .cu.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/b200ppo.h"
+
+namespace b2 {
+
+int set_error(int code, const char* fmt, ...);
+
+// Device-resident trajectory buffer, SoA, flat index k = t * n_envs + e (time-major).
+//   obs[c * cap + k]  c < 6          24 B/record
+//   action, logp, mu, reward, ret    f32 each
+//   flags                            u8
+//   vboot[k]                         critic bootstrap value where flags & (TIMEUP|TRUNC)
+//   vcur[k]                          V of the current epoch (critic pass -> actor pass scratch)
+struct Traj {
+  int64_t cap = 0;  // records
+  float* obs = nullptr;
+  float* action = nullptr;
+  float* logp = nullptr;
+  float* mu = nullptr;
+  float* reward = nullptr;
+  float* ret = nullptr;
+  float* vboot = nullptr;
+  float* vcur = nullptr;
+  uint8_t* flags = nullptr;
+  double* state_trace = nullptr;  // optional [k][4]
+  int64_t n_envs = 0, horizon = 0;  // shape of what is currently stored
+};
+
+struct HyperDev {       // passed by value to kernels
+  float sigma, inv_var, half_log_norm, loss3;
+  float gamma, clip_lo, clip_hi;
+  double sigma_d;
+  double lr, beta1, beta2, eps;
+};
+
+struct RolloutArgs {
+  const float* params;
+  double* state;        // [4][n_envs]
+  int32_t* ep_step;     // [n_envs]
+  float* ep_ret;        // [n_envs] running reward sum of the current episode
+  int32_t* ep_count;    // [n_envs] episodes completed in this rollout
+  float* ep_log;        // [max_eps][n_envs]
+  int max_eps;
+  Traj tr;
+  const float* forced_action;  // [T][N] or null
+  int64_t n_envs;
+  int T, n_timestep;
+  uint64_t seed, env_offset, step0;
+  HyperDev hp;
+  int* status;          // bit0: non-finite action seen
+};
+
+struct UpdateArgs {
+  float* params;
+  float* adam_m;
+  float* adam_v;
+  float* grads;         // [P] reduced gradient of this step
+  float* partials;      // [grid][PSTRIDE]
+  int64_t* adam_step;   // device counter
+  double* loss_log;     // [steps][4] loss1, loss2, clip_frac, (spare)
+  Traj tr;
+  const int32_t* idx;   // minibatch gather indices or null
+  int64_t first, count; // positions [first, first+count) of this minibatch (mapped through idx if set)
+  int64_t denom;        // samples the means are taken over (global minibatch size across ranks)
+  int step_slot;        // row of loss_log
+  int grid;
+  HyperDev hp;
+};
+
+// ---- launchers (each returns cudaGetLastError()) ----
+cudaError_t launch_rollout(const RolloutArgs& a, int precision, bool trace, cudaStream_t st, int hidden1, int hidden2);
+cudaError_t launch_act(const float* params, const float* obs_aos, const float* eps, int64_t n, uint64_t seed,
+                       uint64_t call, float* action, float* logp, float* mu, const HyperDev& hp, int* status,
+                       cudaStream_t st);
+cudaError_t launch_value(const float* params, const float* obs_aos, int64_t n, float* v, cudaStream_t st);
+cudaError_t launch_aos_to_soa(const float* obs_aos, float* obs_soa, int64_t cap, int64_t n, cudaStream_t st);
+cudaError_t launch_soa_to_aos(const float* obs_soa, float* obs_aos, int64_t cap, int64_t n, cudaStream_t st);
+cudaError_t launch_returns(const float* params, const Traj& tr, const HyperDev& hp, cudaStream_t st, int* n_launches);
+int update_grid_for(int64_t count, int sm_count);
+int update_partial_stride();
+cudaError_t launch_ppo_grad(const UpdateArgs& a, cudaStream_t st);
+cudaError_t launch_reduce(const UpdateArgs& a, bool apply_adam, cudaStream_t st);
+cudaError_t launch_adam(const UpdateArgs& a, cudaStream_t st);
+cudaError_t launch_flush(float* buf, int64_t n, cudaStream_t st);
+cudaError_t measure_fma_peak(bool fp64, int sm_count, cudaStream_t st, double* tflops);
+
+}  // namespace b2
