@@ -48,7 +48,7 @@ def test_policy_forward_vs_reference(pkg, case):
     ga, gmu = gold(f"{case}_action.f32"), gold(f"{case}_mu.f32")
     eps = ((ga.astype(np.float64) - gmu.astype(np.float64)) / SIGMA).astype(np.float32)
     a2, lp2, _ = E.act(obs, eps=eps)
-    np.testing.assert_allclose(a2, ga, rtol=0, atol=2e-7)
+    np.testing.assert_allclose(a2, ga, rtol=0, atol=5e-7)  # eps is rounded to f32: <= 2 ulp
     np.testing.assert_allclose(lp2, gold(f"{case}_logp.f32"), rtol=1e-5, atol=2e-6)
     E.close()
 
