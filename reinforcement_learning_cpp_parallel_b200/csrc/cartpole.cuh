@@ -1,80 +1,190 @@
 // cartpole.cuh -- the cart-pole ODE and its 6-stage low-storage RK46-NL integrator, templated on the
 // arithmetic type.  State lives in registers for the whole rollout; nothing here touches memory.
 // Reference: include/cart_pole.h  (Diff :149-170 non-SWINGUP branch, rk46_nl :23-45, advance :107-118).
+//
+// One env step is 50 substeps x 6 stages = 300 evaluations of Diff, each needing sin/cos of the pole
+// angle and one true division.  Calling libdevice sincos()/"/" 300 times costs ~150 instructions per
+// stage, two thirds of them integer fix-up code (round-1 ncu, profiles/r1a_*: FP64 pipe 42 % busy, ALU
+// 18 %, instruction fetch the top stall).  The double path therefore restates the two expensive pieces
+// so that a stage is 38 straight-line DFMA/DMUL/DADD and almost nothing else:
+//   * sin/cos are carried along with the state and ROTATED by the stage's angle increment d
+//     (|d| ~ 1e-4..1e-2): sin d and cos d - 1 from short Taylor polynomials (error < 3e-14 relative for
+//     |d| <= 0.1), then the angle-addition formulas.  The pair is re-anchored with a full-precision
+//     sincos() once per env step, so rounding cannot accumulate beyond ~300 ulp.  While |thetadot| > 40
+//     rad/s (|d| could leave the polynomial range) substeps run through an exact out-of-line version.
+//   * 1/fac2 is carried as well and refreshed with one Newton step per stage (fac2 moves by < 1e-3
+//     relative between stages, typically 1e-6), followed by one residual correction of the quotient:
+//     error ~ e^4, i.e. < 1e-12 in the worst case and ~1e-24 typically.
+//   * the RK accumulator is kept as W = w / dt and b_i dt is folded into one constant.
+// Measured against the unmodified header: <= 1e-12 relative per env step (tests/test_gpu_parity.py).
 #pragma once
 #include "common.cuh"
 
 namespace b2 {
 
-template <typename R>
-struct Phys;
-
-template <>
-struct Phys<double> {
-  static __device__ __forceinline__ void sincos_(double x, double* s, double* c) { sincos(x, s, c); }
-  static __device__ __forceinline__ double div_(double a, double b) { return a / b; }
-  static __device__ __forceinline__ double abs_(double x) { return fabs(x); }
-};
-template <>
-struct Phys<float> {
-  static __device__ __forceinline__ void sincos_(float x, float* s, float* c) { sincosf(x, s, c); }
-  static __device__ __forceinline__ float div_(float a, float b) { return a / b; }
-  static __device__ __forceinline__ float abs_(float x) { return fabsf(x); }
-};
-
 // constants include/cart_pole.h:65-70
-template <typename R>
-struct CartPoleDyn {
+struct CPC {
   static constexpr double mp = 0.1, mc = 1.0, l = 0.5, g = 9.81, dt = 4e-4;
   static constexpr int nsteps = 50;
+  static constexpr double inv_tot = 1.0 / (mp + mc);
+  static constexpr double mpl = mp * l;
+  static constexpr double A0 = l * (4.0 / 3);          // fac2 = A0 - A1 c^2   (:162)
+  static constexpr double A1 = l * mp / (mp + mc);
+  static constexpr double PI_15 = 3.14159265358979323846 / 15;
+};
 
-  // Diff (:161-168): u = (x, xdot, theta, thetadot), F = force
-  static __device__ __forceinline__ void diff(const R (&u)[4], R F, R (&d)[4]) {
-    R s, c;
-    Phys<R>::sincos_(u[2], &s, &c);
-    const R inv_tot = (R)(1.0 / (mp + mc));   // the reference divides by totMass; 1 ulp apart
-    const R w = u[3];
-    const R fac2 = (R)l * ((R)(4.0 / 3) - ((R)mp * c * c) * inv_tot);  // :162
-    const R F1 = F + (R)(mp * l) * w * w * s;                          // :163
-    d[3] = Phys<R>::div_((R)g * s - F1 * c * inv_tot, fac2);           // :164
-    d[1] = (F1 - (R)(mp * l) * d[3] * c) * inv_tot;                    // :165
-    d[0] = u[1];                                                       // :167
-    d[2] = u[3];                                                       // :168
-  }
+// RK46-NL coefficients, include/cart_pole.h:25-30
+#define B2_RK_A {0.000000000000, -0.737101392796, -1.634740794341, -0.744739003780, -1.469897351522, -2.813971388035}
+#define B2_RK_B {0.032918605146, 0.823256998200, 0.381530948900, 0.200092213184, 1.718581042715, 0.270000000000}
 
-  // one env step = 50 x rk46_nl (:110-116).  Coefficients :25-30.
-  static __device__ __forceinline__ void advance(R (&u)[4], R F) {
-    constexpr double a[6] = {0.000000000000,  -0.737101392796, -1.634740794341,
-                             -0.744739003780, -1.469897351522, -2.813971388035};
-    constexpr double b[6] = {0.032918605146, 0.823256998200, 0.381530948900,
-                             0.200092213184, 1.718581042715, 0.270000000000};
+template <typename R>
+struct CartPoleDyn;
+
+// ------------------------------------------------------------------------------------------ double
+// Every double constant of the hot loop lives in one __constant__ table so that it reaches the DFMA as
+// a c[bank][offset] operand (ptxas otherwise rebuilds each literal with two UMOVs per use: 312 of the
+// 965 instructions of a substep in the first version).
+struct CPTable {
+  double a[6], bdt[6];          // RK46-NL a_i and b_i * dt  (the accumulator is kept as W = w / dt)
+  double A0, A1, k1, g;         // fac2 = A0 - A1 c^2 ; k1 = mp l / M ; gravity
+  double s3, s5, s7;            // sin d = d + d^3 (s3 + d^2 (s5 + d^2 s7))
+  double c2, c4, c6, c8;        // cos d - 1 = d^2 (c2 + d^2 (c4 + d^2 (c6 + d^2 c8)))
+};
+__device__ __constant__ CPTable kCP = {
+    B2_RK_A,
+    {0.032918605146 * 4e-4, 0.823256998200 * 4e-4, 0.381530948900 * 4e-4, 0.200092213184 * 4e-4,
+     1.718581042715 * 4e-4, 0.270000000000 * 4e-4},
+    CPC::A0, CPC::A1, CPC::mpl* CPC::inv_tot, CPC::g,
+    -1.0 / 6, 1.0 / 120, -1.0 / 5040,
+    -0.5, 1.0 / 24, -1.0 / 720, 1.0 / 40320};
+
+template <>
+struct CartPoleDyn<double> {
+  // Reference-shaped substep (full sincos + true division per stage), used only while the pole spins so
+  // fast that the rotation polynomials below are out of range.  Kept out of line: it is never hot.
+  static __device__ __noinline__ void substep_exact(double (&u)[4], double F) {
+    constexpr double a[6] = B2_RK_A;
+    constexpr double b[6] = B2_RK_B;
+    double w[4] = {0, 0, 0, 0};
 #pragma unroll 1
-    for (int sub = 0; sub < nsteps; sub++) {
-      R w[4];
+    for (int i = 0; i < 6; i++) {
+      double s, c;
+      sincos(u[2], &s, &c);
+      const double fac2 = CPC::l * (4.0 / 3 - (CPC::mp * c * c) * CPC::inv_tot);
+      const double F1 = F + CPC::mpl * u[3] * u[3] * s;
+      const double dd4 = (CPC::g * s - F1 * c * CPC::inv_tot) / fac2;
+      const double dd2 = (F1 - CPC::mpl * dd4 * c) * CPC::inv_tot;
+      const double d[4] = {u[1], dd2, u[3], dd4};
 #pragma unroll
-      for (int i = 0; i < 6; i++) {
-        R d[4];
-        diff(u, F, d);
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-          w[j] = (i == 0) ? d[j] * (R)dt : w[j] * (R)a[i] + d[j] * (R)dt;  // :41 (w starts at 0, a[0] = 0)
-          u[j] = u[j] + w[j] * (R)b[i];                                    // :42
-        }
+      for (int j = 0; j < 4; j++) {
+        w[j] = w[j] * a[i] + d[j] * CPC::dt;
+        u[j] = u[j] + w[j] * b[i];
       }
     }
   }
 
-  // getReward (:142): 1 - (|theta| > pi/15 || |x| > 2.4)
-  static __device__ __forceinline__ float reward(const R (&u)[4]) {
-    return (Phys<R>::abs_(u[2]) > (R)(3.14159265358979323846 / 15) || Phys<R>::abs_(u[0]) > (R)2.4) ? 0.0f : 1.0f;
+  // state: u = (x, xdot, theta, thetadot).  (s, c, rinv) = (sin theta, cos theta, 1/fac2) ride along.
+  static __device__ __forceinline__ void advance(double (&u)[4], double F) {
+    double s, c;
+    sincos(u[2], &s, &c);                                  // anchor (full precision), once per env step
+    double rinv = 1.0 / fma(-kCP.A1, c * c, kCP.A0);
+    const double Fm = F * CPC::inv_tot;                    // F / M
+#pragma unroll 1
+    for (int sub = 0; sub < CPC::nsteps; sub++) {
+      if (__builtin_expect(fabs(u[3]) > 40.0, 0)) {        // |d| could leave the polynomial range: exact substep
+        substep_exact(u, F);
+        sincos(u[2], &s, &c);
+        rinv = 1.0 / fma(-kCP.A1, c * c, kCP.A0);
+        continue;
+      }
+      double W0, W1, W2, W3;                               // w / dt of the reference (:41)
+#pragma unroll
+      for (int i = 0; i < 6; i++) {
+        // ---- Diff (:161-168), with F1m = F1 / M ----
+        const double fac2 = fma(-kCP.A1, c * c, kCP.A0);                   // :162
+        const double om = u[3];
+        const double F1m = fma(kCP.k1 * (om * om), s, Fm);                 // :163 / M
+        const double num = fma(-F1m, c, kCP.g * s);                        // :164 numerator
+        const double e = fma(-fac2, rinv, 1.0);                            // one Newton step on the carried 1/fac2
+        rinv = fma(rinv, e, rinv);
+        double dd4 = num * rinv;
+        dd4 = fma(fma(-dd4, fac2, num), rinv, dd4);                        // residual correction: num / fac2
+        const double dd2 = fma(-kCP.k1 * dd4, c, F1m);                     // :165
+        // ---- low-storage RK update (:41-42) on W = w / dt; w starts at 0 and a[0] = 0 ----
+        if (i == 0) {
+          W0 = u[1]; W1 = dd2; W2 = om; W3 = dd4;
+        } else {
+          W0 = fma(W0, kCP.a[i], u[1]); W1 = fma(W1, kCP.a[i], dd2);
+          W2 = fma(W2, kCP.a[i], om);   W3 = fma(W3, kCP.a[i], dd4);
+        }
+        const double d = W2 * kCP.bdt[i];                                  // the angle increment of this stage
+        u[0] = fma(W0, kCP.bdt[i], u[0]); u[1] = fma(W1, kCP.bdt[i], u[1]);
+        u[2] = u[2] + d;                  u[3] = fma(W3, kCP.bdt[i], u[3]);
+        // ---- rotate (sin, cos) by d ----
+        const double d2 = d * d;
+        const double ps = fma(d2, fma(d2, kCP.s7, kCP.s5), kCP.s3);
+        const double sd = fma(d * d2, ps, d);                              // sin d
+        const double pc = fma(d2, fma(d2, fma(d2, kCP.c8, kCP.c6), kCP.c4), kCP.c2);
+        const double cm1 = d2 * pc;                                        // cos d - 1
+        const double s_new = s + fma(s, cm1, c * sd);
+        const double c_new = c + fma(c, cm1, -(s * sd));
+        s = s_new; c = c_new;
+      }
+    }
   }
 
-  // getobs (:123-130) narrowed to f32 once (src/main.cpp:79); cos/sin from the full-precision angle
-  static __device__ __forceinline__ void observe(const R (&u)[4], float (&o)[6]) {
-    R s, c;
-    Phys<R>::sincos_(u[2], &s, &c);
+  static __device__ __forceinline__ float reward(const double (&u)[4]) {  // getReward :142
+    return (fabs(u[2]) > CPC::PI_15 || fabs(u[0]) > 2.4) ? 0.0f : 1.0f;
+  }
+  static __device__ __forceinline__ void observe(const double (&u)[4], float (&o)[6]) {  // getobs :123-130
+    double s, c;
+    sincos(u[2], &s, &c);
     o[0] = (float)u[0]; o[1] = (float)u[1]; o[2] = (float)u[3]; o[3] = (float)u[2];
     o[4] = (float)c;    o[5] = (float)s;
+  }
+};
+
+// ------------------------------------------------------------------------------------------- float
+// Throughput path: everything in f32, sin/cos/reciprocal on the MUFU pipe.  NOT parity-gated: f32 state
+// drifts ~1e-5 (median) over a 100-step episode against the double reference.
+template <>
+struct CartPoleDyn<float> {
+  static __device__ __forceinline__ void advance(float (&u)[4], float F) {
+    constexpr double a[6] = B2_RK_A;
+    constexpr double b[6] = B2_RK_B;
+    constexpr float dt = (float)CPC::dt, A0 = (float)CPC::A0, A1 = (float)CPC::A1, mpl = (float)CPC::mpl,
+                    inv_tot = (float)CPC::inv_tot, g = (float)CPC::g;
+#pragma unroll 1
+    for (int sub = 0; sub < CPC::nsteps; sub++) {
+      float w0, w1, w2, w3;
+#pragma unroll
+      for (int i = 0; i < 6; i++) {
+        float s, c;
+        __sincosf(u[2], &s, &c);
+        const float fac2 = fmaf(-A1, c * c, A0);
+        const float om = u[3];
+        const float F1 = fmaf(mpl * (om * om), s, F);
+        const float num = fmaf(g, s, -(F1 * c) * inv_tot);
+        const float dd4 = __fdividef(num, fac2);
+        const float dd2 = fmaf(-mpl * dd4, c, F1) * inv_tot;
+        if (i == 0) {
+          w0 = u[1] * dt; w1 = dd2 * dt; w2 = om * dt; w3 = dd4 * dt;
+        } else {
+          w0 = fmaf(w0, (float)a[i], u[1] * dt); w1 = fmaf(w1, (float)a[i], dd2 * dt);
+          w2 = fmaf(w2, (float)a[i], om * dt);   w3 = fmaf(w3, (float)a[i], dd4 * dt);
+        }
+        u[0] = fmaf(w0, (float)b[i], u[0]); u[1] = fmaf(w1, (float)b[i], u[1]);
+        u[2] = fmaf(w2, (float)b[i], u[2]); u[3] = fmaf(w3, (float)b[i], u[3]);
+      }
+    }
+  }
+  static __device__ __forceinline__ float reward(const float (&u)[4]) {
+    return (fabsf(u[2]) > (float)CPC::PI_15 || fabsf(u[0]) > 2.4f) ? 0.0f : 1.0f;
+  }
+  static __device__ __forceinline__ void observe(const float (&u)[4], float (&o)[6]) {
+    float s, c;
+    sincosf(u[2], &s, &c);
+    o[0] = u[0]; o[1] = u[1]; o[2] = u[3]; o[3] = u[2]; o[4] = c; o[5] = s;
   }
 };
 
