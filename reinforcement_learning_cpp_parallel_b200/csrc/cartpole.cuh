@@ -62,9 +62,11 @@ template <>
 struct CartPoleDyn<double> {
   // Reference-shaped substep (full sincos + true division per stage), used only while the pole spins so
   // fast that the rotation polynomials below are out of range.  Kept out of line: it is never hot.
-  static __device__ __noinline__ void substep_exact(double (&u)[4], double F) {
+  // (by value in and out: passing u by reference would pin the state to the local-memory stack frame)
+  static __device__ __noinline__ double4 substep_exact(double4 u4, double F) {
     constexpr double a[6] = B2_RK_A;
     constexpr double b[6] = B2_RK_B;
+    double u[4] = {u4.x, u4.y, u4.z, u4.w};
     double w[4] = {0, 0, 0, 0};
 #pragma unroll 1
     for (int i = 0; i < 6; i++) {
@@ -81,6 +83,7 @@ struct CartPoleDyn<double> {
         u[j] = u[j] + w[j] * b[i];
       }
     }
+    return make_double4(u[0], u[1], u[2], u[3]);
   }
 
   // state: u = (x, xdot, theta, thetadot).  (s, c, rinv) = (sin theta, cos theta, 1/fac2) ride along.
@@ -92,7 +95,8 @@ struct CartPoleDyn<double> {
 #pragma unroll 1
     for (int sub = 0; sub < CPC::nsteps; sub++) {
       if (__builtin_expect(fabs(u[3]) > 40.0, 0)) {        // |d| could leave the polynomial range: exact substep
-        substep_exact(u, F);
+        const double4 r = substep_exact(make_double4(u[0], u[1], u[2], u[3]), F);
+        u[0] = r.x; u[1] = r.y; u[2] = r.z; u[3] = r.w;
         sincos(u[2], &s, &c);
         rinv = 1.0 / fma(-kCP.A1, c * c, kCP.A0);
         continue;

@@ -16,13 +16,14 @@ __global__ void __launch_bounds__(INFER_BLOCK, 4) k_act(const float* __restrict_
                                                      float* __restrict__ logp, float* __restrict__ mu_out,
                                                      HyperDev hp, int* status) {
   extern __shared__ __align__(16) float sm[];
+  float* hs = sm + NetSmem<N>::FLOATS;
   stage_net<N>(sm, params);
   __syncthreads();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     float x[N::S];
 #pragma unroll
     for (int c = 0; c < N::S; c++) x[c] = obs[i * N::S + c];
-    const float mu = act_tanh(mlp_row<N>(sm, x));
+    const float mu = act_tanh(mlp_row<N>(sm, hs, x));
     const float eps = eps_in ? eps_in[i] : gauss_noise(seed ^ 0xA5A5A5A5A5A5A5A5ull, (uint64_t)i, call);
     const float a = (float)__dadd_rn((double)mu, __dmul_rn(hp.sigma_d, (double)eps));  // src/ppo_nn.cpp:107-108
     action[i] = a;
@@ -36,13 +37,14 @@ template <class N>
 __global__ void __launch_bounds__(INFER_BLOCK, 4) k_value(const float* __restrict__ params, const float* __restrict__ obs,
                                                        int64_t n, float* __restrict__ v) {
   extern __shared__ __align__(16) float sm[];
+  float* hs = sm + NetSmem<N>::FLOATS;
   stage_net<N>(sm, params + N::SIZE);  // critic block follows the actor block
   __syncthreads();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     float x[N::S];
 #pragma unroll
     for (int c = 0; c < N::S; c++) x[c] = obs[i * N::S + c];
-    v[i] = mlp_row<N>(sm, x);
+    v[i] = mlp_row<N>(sm, hs, x);
   }
 }
 
@@ -76,13 +78,13 @@ cudaError_t launch_act(const float* params, const float* obs_aos, const float* e
                        uint64_t call, float* action, float* logp, float* mu, const HyperDev& hp, int* status,
                        cudaStream_t st) {
   using N = NetDefault;
-  k_act<N><<<grid_for(n, INFER_BLOCK), INFER_BLOCK, NetSmem<N>::BYTES, st>>>(params, obs_aos, eps, n, seed, call,
+  k_act<N><<<grid_for(n, INFER_BLOCK), INFER_BLOCK, mlp_smem_bytes<N>(INFER_BLOCK), st>>>(params, obs_aos, eps, n, seed, call,
                                                                                action, logp, mu, hp, status);
   return cudaGetLastError();
 }
 cudaError_t launch_value(const float* params, const float* obs_aos, int64_t n, float* v, cudaStream_t st) {
   using N = NetDefault;
-  k_value<N><<<grid_for(n, INFER_BLOCK), INFER_BLOCK, NetSmem<N>::BYTES, st>>>(params, obs_aos, n, v);
+  k_value<N><<<grid_for(n, INFER_BLOCK), INFER_BLOCK, mlp_smem_bytes<N>(INFER_BLOCK), st>>>(params, obs_aos, n, v);
   return cudaGetLastError();
 }
 cudaError_t launch_aos_to_soa(const float* a, float* s, int64_t cap, int64_t n, cudaStream_t st) {

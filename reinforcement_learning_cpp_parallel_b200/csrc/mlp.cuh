@@ -43,52 +43,69 @@ __device__ __forceinline__ void stage_net(float* sm, const float* __restrict__ g
   if (threadIdx.x == 0) sm[L::ob3] = g[N::ob3];
 }
 
-__device__ __forceinline__ float act_tanh(float x) { return tanhf(x); }
+// tanh(x) = 1 - 2 / (1 + 2^(2 x log2 e)): FMUL + MUFU.EX2 + FADD + MUFU.RCP + FFMA.  Absolute error
+// <= ~2e-7 over the whole range (saturates cleanly to +-1), which keeps mu / V within the 1e-6 parity gate;
+// libdevice tanhf costs ~4x the instructions and its two code paths bloat the unrolled layers.
+__device__ __forceinline__ float act_tanh(float x) {
+  float e, r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * 2.8853900817779268f));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(e + 1.0f));
+  return fmaf(-2.0f, r, 1.0f);
+}
 
-// one row through one net; returns the pre-final-activation output (caller applies tanh for the actor)
+// One observation row through one net, thread-per-row.  Compact on purpose: the fully unrolled version
+// (4.5k instructions per call site) made instruction fetch the top stall of the rollout kernel (ncu r1b:
+// 61 % of the MLP phase's samples were stall_no_inst).  Hidden layer 1 goes through a per-thread column
+// of shared memory (hs[k * blockDim.x + tid]) so that layer 2 can be a rolled loop over k with its 32
+// accumulators in registers; every loop body is a few hundred bytes of SASS and stays in the L0 I-cache.
+// Returns the pre-final-activation output (caller applies tanh for the actor).
 template <class N>
-__device__ __forceinline__ float mlp_row(const float* __restrict__ sm, const float (&x)[N::S]) {
+__device__ __forceinline__ float mlp_row(const float* __restrict__ sm, float* __restrict__ hs,
+                                         const float (&x)[N::S]) {
   using L = NetSmem<N>;
-  float h1[N::H1];
+  const int BS = blockDim.x;
+  float* hcol = hs + threadIdx.x;
+  // ---- layer 1: 8 outputs per iteration ----
+#pragma unroll 2
+  for (int j = 0; j < N::H1; j += 8) {
+    float4 a0 = *reinterpret_cast<const float4*>(sm + L::ob1 + j);
+    float4 a1 = *reinterpret_cast<const float4*>(sm + L::ob1 + j + 4);
 #pragma unroll
-  for (int j = 0; j < N::H1; j += 4) {
-    float4 b = *reinterpret_cast<const float4*>(sm + L::ob1 + j);
-    h1[j] = b.x; h1[j + 1] = b.y; h1[j + 2] = b.z; h1[j + 3] = b.w;
-  }
-#pragma unroll
-  for (int s = 0; s < N::S; s++) {
-#pragma unroll
-    for (int j = 0; j < N::H1; j += 4) {
-      float4 w = *reinterpret_cast<const float4*>(sm + L::oW1T + s * N::H1 + j);
-      h1[j] = fmaf(w.x, x[s], h1[j]);
-      h1[j + 1] = fmaf(w.y, x[s], h1[j + 1]);
-      h1[j + 2] = fmaf(w.z, x[s], h1[j + 2]);
-      h1[j + 3] = fmaf(w.w, x[s], h1[j + 3]);
+    for (int s = 0; s < N::S; s++) {
+      const float4 w0 = *reinterpret_cast<const float4*>(sm + L::oW1T + s * N::H1 + j);
+      const float4 w1 = *reinterpret_cast<const float4*>(sm + L::oW1T + s * N::H1 + j + 4);
+      a0.x = fmaf(w0.x, x[s], a0.x); a0.y = fmaf(w0.y, x[s], a0.y); a0.z = fmaf(w0.z, x[s], a0.z); a0.w = fmaf(w0.w, x[s], a0.w);
+      a1.x = fmaf(w1.x, x[s], a1.x); a1.y = fmaf(w1.y, x[s], a1.y); a1.z = fmaf(w1.z, x[s], a1.z); a1.w = fmaf(w1.w, x[s], a1.w);
     }
+    hcol[(j + 0) * BS] = act_tanh(a0.x); hcol[(j + 1) * BS] = act_tanh(a0.y);
+    hcol[(j + 2) * BS] = act_tanh(a0.z); hcol[(j + 3) * BS] = act_tanh(a0.w);
+    hcol[(j + 4) * BS] = act_tanh(a1.x); hcol[(j + 5) * BS] = act_tanh(a1.y);
+    hcol[(j + 6) * BS] = act_tanh(a1.z); hcol[(j + 7) * BS] = act_tanh(a1.w);
   }
-#pragma unroll
-  for (int j = 0; j < N::H1; j++) h1[j] = act_tanh(h1[j]);
+  // ---- layer 2: accumulators in registers, rolled over k ----
   float h2[N::H2];
 #pragma unroll
   for (int j = 0; j < N::H2; j += 4) {
-    float4 b = *reinterpret_cast<const float4*>(sm + L::ob2 + j);
+    const float4 b = *reinterpret_cast<const float4*>(sm + L::ob2 + j);
     h2[j] = b.x; h2[j + 1] = b.y; h2[j + 2] = b.z; h2[j + 3] = b.w;
   }
-#pragma unroll
+#pragma unroll 4
   for (int k = 0; k < N::H1; k++) {
+    const float hk = hcol[k * BS];
 #pragma unroll
     for (int j = 0; j < N::H2; j += 4) {
-      float4 w = *reinterpret_cast<const float4*>(sm + L::oW2T + k * N::H2 + j);
-      h2[j] = fmaf(w.x, h1[k], h2[j]);
-      h2[j + 1] = fmaf(w.y, h1[k], h2[j + 1]);
-      h2[j + 2] = fmaf(w.z, h1[k], h2[j + 2]);
-      h2[j + 3] = fmaf(w.w, h1[k], h2[j + 3]);
+      const float4 w = *reinterpret_cast<const float4*>(sm + L::oW2T + k * N::H2 + j);
+      h2[j] = fmaf(w.x, hk, h2[j]);
+      h2[j + 1] = fmaf(w.y, hk, h2[j + 1]);
+      h2[j + 2] = fmaf(w.z, hk, h2[j + 2]);
+      h2[j + 3] = fmaf(w.w, hk, h2[j + 3]);
     }
   }
+  // ---- layer 3 ----
   float y = sm[L::ob3];
 #pragma unroll
   for (int j = 0; j < N::H2; j += 4) {
-    float4 w = *reinterpret_cast<const float4*>(sm + L::oW3 + j);
+    const float4 w = *reinterpret_cast<const float4*>(sm + L::oW3 + j);
     y = fmaf(w.x, act_tanh(h2[j]), y);
     y = fmaf(w.y, act_tanh(h2[j + 1]), y);
     y = fmaf(w.z, act_tanh(h2[j + 2]), y);
@@ -96,5 +113,9 @@ __device__ __forceinline__ float mlp_row(const float* __restrict__ sm, const flo
   }
   return y;
 }
+
+// dynamic shared memory a thread-per-row kernel needs: one net image + the hidden-1 scratch columns
+template <class N>
+constexpr int mlp_smem_bytes(int block) { return NetSmem<N>::BYTES + N::H1 * block * 4; }
 
 }  // namespace b2

@@ -18,6 +18,7 @@ namespace b2 {
 template <class N>
 __global__ void __launch_bounds__(128, 4) k_bootstrap(const float* __restrict__ params, Traj tr, int64_t B) {
   extern __shared__ __align__(16) float sm[];
+  float* hs = sm + NetSmem<N>::FLOATS;
   stage_net<N>(sm, params + N::SIZE);
   __syncthreads();
   for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < B; k += (int64_t)gridDim.x * blockDim.x) {
@@ -25,7 +26,7 @@ __global__ void __launch_bounds__(128, 4) k_bootstrap(const float* __restrict__ 
       float x[N::S];
 #pragma unroll
       for (int c = 0; c < N::S; c++) x[c] = tr.obs[c * tr.cap + k];
-      tr.vboot[k] = mlp_row<N>(sm, x);  // src/ppo_nn.cpp:227
+      tr.vboot[k] = mlp_row<N>(sm, hs, x);  // src/ppo_nn.cpp:227
     }
   }
 }
@@ -71,7 +72,7 @@ cudaError_t launch_returns(const float* params, const Traj& tr, const HyperDev& 
   if (B == 0) return cudaSuccess;
   int64_t g = (B + 127) / 128;
   if (g > 148 * 16) g = 148 * 16;
-  k_bootstrap<N><<<(int)g, 128, NetSmem<N>::BYTES, st>>>(params, tr, B);
+  k_bootstrap<N><<<(int)g, 128, mlp_smem_bytes<N>(128), st>>>(params, tr, B);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   k_returns<<<(int)((tr.n_envs + 127) / 128), 128, 0, st>>>(tr, hp.gamma);

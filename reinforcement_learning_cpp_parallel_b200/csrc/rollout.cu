@@ -21,6 +21,7 @@ constexpr int ROLLOUT_BLOCK = 64;   // 65,536 envs -> 1024 CTAs: 6.9 per SM, all
 template <typename Real, class N, bool TRACE>
 __global__ void __launch_bounds__(ROLLOUT_BLOCK, 7) k_rollout(const RolloutArgs a) {
   extern __shared__ __align__(16) float sm[];
+  float* hs = sm + NetSmem<N>::FLOATS;  // hidden-1 scratch, one column per thread
   stage_net<N>(sm, a.params);  // actor only: V is not needed while acting (src/ppo_nn.cpp:100)
   __syncthreads();
   const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -41,7 +42,7 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, 7) k_rollout(const RolloutArgs 
     const int64_t k = (int64_t)t * NE + e;
     float o[6];
     Dyn::observe(u, o);
-    const float mu = act_tanh(mlp_row<N>(sm, o));                       // ppo_nn.h:98-102
+    const float mu = act_tanh(mlp_row<N>(sm, hs, o));                       // ppo_nn.h:98-102
     float act;
     if (a.forced_action) {
       act = a.forced_action[k];
@@ -90,7 +91,7 @@ template <typename Real, bool TRACE>
 static cudaError_t launch_t(const RolloutArgs& a, cudaStream_t st) {
   using N = NetDefault;
   int grid = (int)((a.n_envs + ROLLOUT_BLOCK - 1) / ROLLOUT_BLOCK);
-  k_rollout<Real, N, TRACE><<<grid, ROLLOUT_BLOCK, NetSmem<N>::BYTES, st>>>(a);
+  k_rollout<Real, N, TRACE><<<grid, ROLLOUT_BLOCK, mlp_smem_bytes<N>(ROLLOUT_BLOCK), st>>>(a);
   return cudaGetLastError();
 }
 
