@@ -6,11 +6,12 @@
 // angle and one true division.  Calling libdevice sincos()/"/" 300 times costs ~150 instructions per
 // stage, two thirds of them integer fix-up code (round-1 ncu, profiles/r1a_*: FP64 pipe 42 % busy, ALU
 // 18 %, instruction fetch the top stall).  The double path therefore restates the two expensive pieces
-// so that a stage is 38 straight-line DFMA/DMUL/DADD and almost nothing else:
+// so that a stage is 32 straight-line DFMA/DMUL/DADD and almost nothing else:
 //   * sin/cos are carried along with the state and ROTATED by the stage's angle increment d
-//     (|d| ~ 1e-4..1e-2): sin d and cos d - 1 from short Taylor polynomials (error < 3e-14 relative for
-//     |d| <= 0.1), then the angle-addition formulas.  The pair is re-anchored with a full-precision
-//     sincos() once per env step, so rounding cannot accumulate beyond ~300 ulp.  While |thetadot| > 40
+//     (|d| ~ 1e-5..1e-3; |d| < 1.8e-3 is enforced): sin d and cos d - 1 from two-term Taylor series
+//     (truncation below double rounding in that range), then the angle-addition formulas as two FMAs
+//     per component.  The pair is re-anchored with a full-precision
+//     sincos() once per env step, so rounding cannot accumulate beyond ~300 ulp.  While |thetadot| > 16
 //     rad/s (|d| could leave the polynomial range) substeps run through an exact out-of-line version.
 //   * 1/fac2 is carried as well and refreshed with one Newton step per stage (fac2 moves by < 1e-3
 //     relative between stages, typically 1e-6), followed by one residual correction of the quotient:
@@ -47,16 +48,23 @@ struct CartPoleDyn;
 struct CPTable {
   double a[6], bdt[6];          // RK46-NL a_i and b_i * dt  (the accumulator is kept as W = w / dt)
   double A0, A1, k1, g;         // fac2 = A0 - A1 c^2 ; k1 = mp l / M ; gravity
-  double s3, s5, s7;            // sin d = d + d^3 (s3 + d^2 (s5 + d^2 s7))
-  double c2, c4, c6, c8;        // cos d - 1 = d^2 (c2 + d^2 (c4 + d^2 (c6 + d^2 c8)))
+  double s3;                    // sin d = d + s3 d^3                  |error| <= d^5 / 120
+  double c2, c4;                // cos d - 1 = d^2 (c2 + c4 d^2)       |error| <= d^6 / 720
 };
 __device__ __constant__ CPTable kCP = {
     B2_RK_A,
     {0.032918605146 * 4e-4, 0.823256998200 * 4e-4, 0.381530948900 * 4e-4, 0.200092213184 * 4e-4,
      1.718581042715 * 4e-4, 0.270000000000 * 4e-4},
     CPC::A0, CPC::A1, CPC::mpl* CPC::inv_tot, CPC::g,
-    -1.0 / 6, 1.0 / 120, -1.0 / 5040,
-    -0.5, 1.0 / 24, -1.0 / 720, 1.0 / 40320};
+    -1.0 / 6,
+    -0.5, 1.0 / 24};
+
+// Stage increments of the angle are |d| = |W2 b_i dt| <= 0.27 |thetadot| dt for this scheme (W2 is a
+// convex-like blend of the stage velocities).  Below 16 rad/s that is |d| < 1.8e-3, where the two
+// truncated series are exact to 1.5e-16 (sin) and 5e-20 (cos - 1), i.e. below double rounding.  An
+// untrained policy peaks at ~11 rad/s (oracle, 2048 envs x 128 steps), so the exact path never runs
+// in practice; it is there so that correctness does not depend on that observation.
+constexpr double kOmegaFast = 16.0;
 
 template <>
 struct CartPoleDyn<double> {
@@ -94,7 +102,7 @@ struct CartPoleDyn<double> {
     const double Fm = F * CPC::inv_tot;                    // F / M
 #pragma unroll 1
     for (int sub = 0; sub < CPC::nsteps; sub++) {
-      if (__builtin_expect(fabs(u[3]) > 40.0, 0)) {        // |d| could leave the polynomial range: exact substep
+      if (__builtin_expect(fabs(u[3]) > kOmegaFast, 0)) {  // |d| could leave the polynomial range: exact substep
         const double4 r = substep_exact(make_double4(u[0], u[1], u[2], u[3]), F);
         u[0] = r.x; u[1] = r.y; u[2] = r.z; u[3] = r.w;
         sincos(u[2], &s, &c);
@@ -126,12 +134,10 @@ struct CartPoleDyn<double> {
         u[2] = u[2] + d;                  u[3] = fma(W3, kCP.bdt[i], u[3]);
         // ---- rotate (sin, cos) by d ----
         const double d2 = d * d;
-        const double ps = fma(d2, fma(d2, kCP.s7, kCP.s5), kCP.s3);
-        const double sd = fma(d * d2, ps, d);                              // sin d
-        const double pc = fma(d2, fma(d2, fma(d2, kCP.c8, kCP.c6), kCP.c4), kCP.c2);
-        const double cm1 = d2 * pc;                                        // cos d - 1
-        const double s_new = s + fma(s, cm1, c * sd);
-        const double c_new = c + fma(c, cm1, -(s * sd));
+        const double sd = fma(d * d2, kCP.s3, d);                          // sin d
+        const double cm1 = d2 * fma(d2, kCP.c4, kCP.c2);                   // cos d - 1
+        const double s_new = fma(s, cm1, fma(c, sd, s));                   // s cos d + c sin d
+        const double c_new = fma(c, cm1, fma(-s, sd, c));                  // c cos d - s sin d
         s = s_new; c = c_new;
       }
     }

@@ -79,6 +79,7 @@ struct b2_engine {
   double* state = nullptr;
   int32_t *ep_step = nullptr, *ep_count = nullptr;
   float *ep_ret = nullptr, *ep_log = nullptr;
+  int* progress = nullptr;
   int max_eps = 0;
   uint64_t global_step = 0;
   int64_t total_env_steps = 0;
@@ -325,6 +326,7 @@ int b2_create(const b2_config* cfg, b2_handle* out) {
   CK(cudaMalloc(&E->ep_count, sizeof(int32_t) * NE));
   CK(cudaMalloc(&E->ep_ret, sizeof(float) * NE));
   CK(cudaMalloc(&E->ep_log, sizeof(float) * NE * E->max_eps));
+  CK(cudaMalloc(&E->progress, sizeof(int) * ((NE + 31) / 32)));
   CK(cudaMemset(E->state, 0, sizeof(double) * 4 * NE));   // CartPole::reset: u = 0 (cart_pole.h:86)
   CK(cudaMemset(E->ep_step, 0, sizeof(int32_t) * NE));
   CK(cudaMemset(E->ep_count, 0, sizeof(int32_t) * NE));
@@ -345,7 +347,8 @@ int b2_destroy(b2_handle E) {
   Traj& t = E->tr;
   void* ptrs[] = {E->params, E->adam_m, E->adam_v, E->grads, E->partials, E->adam_step, E->loss_log, E->state,
                   E->ep_step, E->ep_count, E->ep_ret, E->ep_log, t.obs, t.action, t.logp, t.mu, t.reward, t.ret,
-                  t.vboot, t.vcur, t.flags, t.state_trace, E->forced, E->stage, E->stage_u8, E->status, E->flush_buf};
+                  t.vboot, t.vcur, t.flags, t.state_trace, E->forced, E->stage, E->stage_u8, E->status, E->flush_buf,
+                  E->progress};
   for (void* p : ptrs) cudaFree(p);
   if (E->status_host) cudaFreeHost(E->status_host);
   if (E->ev0) cudaEventDestroy(E->ev0);
@@ -615,8 +618,8 @@ int b2_rollout(b2_handle E, int T, const float* forced_action) {
   a.forced_action = forced_action ? E->forced : nullptr;
   a.n_envs = NE; a.T = T; a.n_timestep = E->cfg.n_timestep;
   a.seed = E->cfg.seed; a.env_offset = E->cfg.env_offset; a.step0 = E->global_step;
-  a.hp = E->hp; a.status = E->status;
-  cudaError_t ce = launch_rollout(a, E->cfg.precision, E->trace, E->stream, E->cfg.hidden1, E->cfg.hidden2);
+  a.hp = E->hp; a.status = E->status; a.progress = E->progress;
+  cudaError_t ce = launch_rollout(a, E->cfg.precision, E->trace, E->sm_count, E->stream, E->cfg.hidden1, E->cfg.hidden2);
   if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "rollout: %s", cudaGetErrorString(ce));
   E->launches += 1;
   E->global_step += (uint64_t)T;

@@ -56,6 +56,7 @@ struct RolloutArgs {
   uint64_t seed, env_offset, step0;
   HyperDev hp;
   int* status;          // bit0: non-finite action seen
+  int* progress;        // [ceil(n_envs/32)] steps of this rollout already published per env group (hand-off word)
 };
 
 struct UpdateArgs {
@@ -76,7 +77,8 @@ struct UpdateArgs {
 };
 
 // ---- launchers (each returns cudaGetLastError()) ----
-cudaError_t launch_rollout(const RolloutArgs& a, int precision, bool trace, cudaStream_t st, int hidden1, int hidden2);
+cudaError_t launch_rollout(const RolloutArgs& a, int precision, bool trace, int sm_count, cudaStream_t st, int hidden1,
+                           int hidden2);
 cudaError_t launch_act(const float* params, const float* obs_aos, const float* eps, int64_t n, uint64_t seed,
                        uint64_t call, float* action, float* logp, float* mu, const HyperDev& hp, int* status,
                        cudaStream_t st);

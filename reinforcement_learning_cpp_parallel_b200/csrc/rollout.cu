@@ -1,44 +1,75 @@
 // rollout.cu -- K1: fused batched cart-pole rollout.
 //
-// One thread owns one environment for the whole T-step horizon: the 4-component state, the episode
-// counters and the RK accumulators never leave registers.  Per step the thread (1) forms the f32
-// observation, (2) runs the actor MLP out of shared-memory weights, (3) draws its Philox Gaussian,
-// (4) evaluates the log-density, (5) integrates 50 x 6 RK46-NL stages, (6) emits the transition with
-// one coalesced store per field (SoA, time-major), (7) applies the TIMEUP/reset rule.
-// There is no per-step message and no host involvement: this replaces env_run (src/main.cpp:12-148),
-// respond_to_env/getAction (src/main.cpp:165-188, src/ppo_nn.cpp:308-331,99-125) and the MPI traffic.
+// One LANE owns one environment while it is being advanced: the 4-component state, the episode counters
+// and the RK accumulators stay in registers.  Per step the lane (1) forms the f32 observation, (2) runs the
+// actor MLP out of shared-memory weights, (3) draws its Philox Gaussian, (4) evaluates the log-density,
+// (5) integrates 50 x 6 RK46-NL stages, (6) emits the transition with one coalesced store per field (SoA,
+// time-major), (7) applies the TIMEUP/reset rule.  There is no per-step message and no host involvement:
+// this replaces env_run (src/main.cpp:12-148), respond_to_env/getAction (src/main.cpp:165-188,
+// src/ppo_nn.cpp:308-331,99-125) and the MPI traffic.
+//
+// Scheduling.  Envs are packed into groups of 32 (one warp's worth).  The kernel is PERSISTENT: it launches
+// only warps that are resident at once (up to 4 per SM sub-partition at <= 128 registers) and deals the
+// G x T (group, step) work units out evenly -- warp w owns units [w U / W, (w+1) U / W) of the group-major
+// sequence, W = the largest multiple of the sub-partition count that is <= G and resident.
+// Measured (profiles/r1c_saturation.txt): two warps already saturate a sub-partition's FP64 pipe, so what
+// limits one-group-per-warp scheduling at 65,536 envs is quantisation -- 2048 groups over 592
+// sub-partitions is 3.46 on average but 4 on the busiest, 13.5 % of the machine idle.  Cutting along the
+// time axis removes that: every warp gets the same number of env-steps (+-1).  A warp's range covers the
+// tail of one group, whole groups, and the head of another; it runs the HEAD first, so the next warp
+// (which also starts with its own head) finds the hand-off state ready when it reaches that group's tail:
+// with equal speeds nobody waits.  Hand-off goes through the state arrays in global memory plus a
+// per-group progress word (release/acquire).  All warps are co-resident by construction, and a waiting
+// warp only ever depends on work that a lower-numbered warp does before anything else, so the spin
+// cannot deadlock.
 //
 // Roofline: FP64 (B2_PREC_F64) or FP32 FMA issue, not HBM -- 41 B are written per env-step against
 // ~12k-24k arithmetic instructions.
+#include <stdlib.h>
+
 #include "cartpole.cuh"
 #include "engine.h"
 #include "mlp.cuh"
 
 namespace b2 {
 
-constexpr int ROLLOUT_BLOCK = 64;   // 65,536 envs -> 1024 CTAs: 6.9 per SM, all resident at <= 144 regs
+constexpr int ROLLOUT_BLOCK = 128;  // 4 warps: one per SM sub-partition
+constexpr int ROLLOUT_CTAS_PER_SM = 4;
 
+__device__ __forceinline__ int ld_acquire(const int* p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release(int* p, int v) {
+  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// Advance group g (envs 32 g .. 32 g + 31) over steps [t0, t1) of this rollout.
 template <typename Real, class N, bool TRACE>
-__global__ void __launch_bounds__(ROLLOUT_BLOCK, 7) k_rollout(const RolloutArgs a) {
-  extern __shared__ __align__(16) float sm[];
-  float* hs = sm + NetSmem<N>::FLOATS;  // hidden-1 scratch, one column per thread
-  stage_net<N>(sm, a.params);  // actor only: V is not needed while acting (src/ppo_nn.cpp:100)
-  __syncthreads();
-  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= a.n_envs) return;
-
+__device__ __forceinline__ void rollout_segment(const RolloutArgs& a, const float* sm, float* hs, int64_t g, int t0,
+                                                int t1) {
   using Dyn = CartPoleDyn<Real>;
+  const int lane = threadIdx.x & 31;
   const int64_t NE = a.n_envs;
+  const int64_t e = g * 32 + lane;
+  if (t0 > 0) {  // hand-off: wait until the warp that owns the earlier steps has published the state
+    if (lane == 0)
+      while (ld_acquire(a.progress + g) < t0) __nanosleep(200);
+    __syncwarp();
+  }
+  if (e >= NE) return;  // ragged last group (no warp-level sync below this line)
+
   Real u[4];
 #pragma unroll
-  for (int j = 0; j < 4; j++) u[j] = (Real)a.state[j * NE + e];
-  int es = a.ep_step[e];
-  float er = a.ep_ret[e];
-  int ecount = 0;
+  for (int j = 0; j < 4; j++) u[j] = (Real)__ldcg(a.state + j * NE + e);
+  int es = __ldcg(a.ep_step + e);
+  float er = __ldcg(a.ep_ret + e);
+  int ecount = (t0 == 0) ? 0 : __ldcg(a.ep_count + e);
   bool bad = false;
   const int64_t cap = a.tr.cap;
 
-  for (int t = 0; t < a.T; t++) {
+  for (int t = t0; t < t1; t++) {
     const int64_t k = (int64_t)t * NE + e;
     float o[6];
     Dyn::observe(u, o);
@@ -61,11 +92,11 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, 7) k_rollout(const RolloutArgs 
     const uint8_t fl = timeup ? (uint8_t)B2_FLAG_TIMEUP : ((t == a.T - 1) ? (uint8_t)B2_FLAG_TRUNC : (uint8_t)0);
 
 #pragma unroll
-    for (int c = 0; c < 6; c++) a.tr.obs[c * cap + k] = o[c];
-    a.tr.action[k] = act;
-    a.tr.logp[k] = lp;
-    a.tr.mu[k] = mu;
-    a.tr.reward[k] = r;
+    for (int c = 0; c < 6; c++) __stcs(a.tr.obs + c * cap + k, o[c]);   // streaming: written once, read by K3 later
+    __stcs(a.tr.action + k, act);
+    __stcs(a.tr.logp + k, lp);
+    __stcs(a.tr.mu + k, mu);
+    __stcs(a.tr.reward + k, r);
     a.tr.flags[k] = fl;
     if (TRACE) {
       double4 s4 = make_double4((double)u[0], (double)u[1], (double)u[2], (double)u[3]);
@@ -80,25 +111,85 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, 7) k_rollout(const RolloutArgs 
     }
   }
 #pragma unroll
-  for (int j = 0; j < 4; j++) a.state[j * NE + e] = (double)u[j];
-  a.ep_step[e] = es;
-  a.ep_ret[e] = er;
-  a.ep_count[e] = ecount;
+  for (int j = 0; j < 4; j++) __stcg(a.state + j * NE + e, (double)u[j]);
+  __stcg(a.ep_step + e, es);
+  __stcg(a.ep_ret + e, er);
+  __stcg(a.ep_count + e, ecount);
   if (bad) atomicOr(a.status, 1);
 }
 
+template <typename Real, class N, bool TRACE>
+__global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_CTAS_PER_SM) k_rollout(const RolloutArgs a) {
+  extern __shared__ __align__(16) float sm[];
+  float* hs = sm + NetSmem<N>::FLOATS;  // hidden-1 scratch, one column per thread
+  stage_net<N>(sm, a.params);  // actor only: V is not needed while acting (src/ppo_nn.cpp:100)
+  __syncthreads();
+
+  const int wpb = blockDim.x >> 5;
+  const int64_t w = (int64_t)blockIdx.x * wpb + (threadIdx.x >> 5);
+  const int64_t W = (int64_t)gridDim.x * wpb;
+  const int64_t T = a.T;
+  const int64_t G = (a.n_envs + 31) >> 5;
+  const int64_t U = G * T;
+  const int64_t u0 = w * U / W, u1 = (w + 1) * U / W;   // U W < 2^63 for any shape that fits in HBM
+  if (u0 >= u1) return;
+  const int64_t g_first = u0 / T, g_last = (u1 - 1) / T;
+  const int ng = (int)(g_last - g_first) + 1;
+  for (int i = 0; i < ng; i++) {
+    // head of the last group first, then the whole groups, then the tail of the first group
+    const int64_t g = (i == 0) ? g_last : ((i == ng - 1) ? g_first : g_first + i);
+    const int64_t lo = g * T, hi = lo + T;
+    const int t0 = (int)((u0 > lo ? u0 : lo) - lo);
+    const int t1 = (int)((u1 < hi ? u1 : hi) - lo);
+    rollout_segment<Real, N, TRACE>(a, sm, hs, g, t0, t1);
+    if (t1 < (int)T) {  // publish: every lane's stores, then the progress word
+      __threadfence();
+      __syncwarp();
+      if ((threadIdx.x & 31) == 0) st_release(a.progress + g, t1);
+    }
+  }
+}
+
 template <typename Real, bool TRACE>
-static cudaError_t launch_t(const RolloutArgs& a, cudaStream_t st) {
+static cudaError_t launch_t(const RolloutArgs& a, int sm_count, cudaStream_t st) {
   using N = NetDefault;
-  int grid = (int)((a.n_envs + ROLLOUT_BLOCK - 1) / ROLLOUT_BLOCK);
-  k_rollout<Real, N, TRACE><<<grid, ROLLOUT_BLOCK, mlp_smem_bytes<N>(ROLLOUT_BLOCK), st>>>(a);
+  auto kern = k_rollout<Real, N, TRACE>;
+  const int smem = mlp_smem_bytes<N>(ROLLOUT_BLOCK);
+  static int per_sm = 0;  // per instantiation
+  if (per_sm == 0) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    int n = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, ROLLOUT_BLOCK, smem);
+    if (e != cudaSuccess) return e;
+    if (n < 1) return cudaErrorLaunchOutOfResources;
+    if (const char* env = getenv("B2_ROLLOUT_CTAS_PER_SM")) {  // experiment knob: fewer resident warps
+      const int v = atoi(env);
+      if (v >= 1 && v < n) n = v;
+    }
+    per_sm = n;
+  }
+  const int64_t G = (a.n_envs + 31) / 32;
+  const int wpb = ROLLOUT_BLOCK / 32;
+  // Warps W = 4 * grid.  The no-wait ordering needs every warp to own at least one group's worth of steps
+  // (W <= G), and the balance needs the same number of warps on every sub-partition (grid a multiple of the
+  // SM count): take the largest such grid that is resident at once.  Tiny batches (G < one warp per
+  // sub-partition) run one group per warp.
+  int64_t k = G / ((int64_t)sm_count * wpb);
+  if (k > per_sm) k = per_sm;
+  const int64_t grid = k >= 1 ? (int64_t)sm_count * k : (G + wpb - 1) / wpb;
+  cudaError_t e = cudaMemsetAsync(a.progress, 0, sizeof(int) * (size_t)G, st);
+  if (e != cudaSuccess) return e;
+  kern<<<(int)grid, ROLLOUT_BLOCK, smem, st>>>(a);
   return cudaGetLastError();
 }
 
-cudaError_t launch_rollout(const RolloutArgs& a, int precision, bool trace, cudaStream_t st, int h1, int h2) {
+cudaError_t launch_rollout(const RolloutArgs& a, int precision, bool trace, int sm_count, cudaStream_t st, int h1,
+                           int h2) {
   if (h1 != NetDefault::H1 || h2 != NetDefault::H2) return cudaErrorInvalidValue;
-  if (precision == B2_PREC_F64) return trace ? launch_t<double, true>(a, st) : launch_t<double, false>(a, st);
-  return trace ? launch_t<float, true>(a, st) : launch_t<float, false>(a, st);
+  if (precision == B2_PREC_F64)
+    return trace ? launch_t<double, true>(a, sm_count, st) : launch_t<double, false>(a, sm_count, st);
+  return trace ? launch_t<float, true>(a, sm_count, st) : launch_t<float, false>(a, sm_count, st);
 }
 
 }  // namespace b2
