@@ -140,6 +140,12 @@ int b2_env_reset(b2_handle h);                                 /* CartPole::rese
 int b2_env_set_state(b2_handle h, const double* u, const int32_t* ep_step, int64_t n); /* u: [n][4] = y1,y2,y3,y4 */
 int b2_env_get_state(b2_handle h, double* u, int32_t* ep_step, int64_t n);
 int b2_rollout(b2_handle h, int T, const float* forced_action);
+/* cart_pole.h-shaped batched env for callers that drive the simulator themselves (no policy, no trajectory):
+ * b2_env_step = CartPole::advance (include/cart_pole.h:107-118) on every resident env, force[e] in newtons
+ * (already scaled, as env_run passes it, src/main.cpp:69-71); b2_env_observe = getobs (:120-133, 6 doubles per
+ * env: x, xdot, thetadot, theta, cos, sin) and getReward (:135-147).  Either output may be NULL. */
+int b2_env_step(b2_handle h, const double* force, int64_t n);
+int b2_env_observe(b2_handle h, double* obs, double* reward, int64_t n);
 int b2_update_resident(b2_handle h, b2_update_stats* stats);   /* returns + K epochs on the resident trajectory */
 int b2_train_iteration(b2_handle h, int T, b2_update_stats* stats); /* rollout + update_resident */
 int b2_traj_download(b2_handle h, b2_batch_out* out, double* state_trace /* [T][N][4] or NULL, only if tracing on */);

@@ -80,6 +80,8 @@ SYMBOLS = {
     "b2_env_set_state": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_int64]),
     "b2_env_get_state": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_int64]),
     "b2_rollout": (C.c_int, [_H, C.c_int, C.c_void_p]),
+    "b2_env_step": (C.c_int, [_H, C.c_void_p, C.c_int64]),
+    "b2_env_observe": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_int64]),
     "b2_update_resident": (C.c_int, [_H, _P(UpdateStats)]),
     "b2_train_iteration": (C.c_int, [_H, C.c_int, _P(UpdateStats)]),
     "b2_traj_download": (C.c_int, [_H, _P(BatchOut), C.c_void_p]),
@@ -270,6 +272,19 @@ class Engine:
         es = np.empty(n, np.int32)
         _ck(self.L.b2_env_get_state(self.h, _vp(u), _vp(es), n))
         return u, es
+
+    def env_step(self, force):
+        """CartPole::advance on every resident env (include/cart_pole.h:107-118); force in newtons."""
+        f = np.ascontiguousarray(force, np.float64).reshape(-1)
+        _ck(self.L.b2_env_step(self.h, _vp(f), f.size))
+
+    def env_observe(self):
+        """getobs + getReward (include/cart_pole.h:120-147): (obs[n][6] f64, reward[n] f64)."""
+        n = int(self.cfg.n_envs)
+        o = np.empty((n, 6), np.float64)
+        r = np.empty(n, np.float64)
+        _ck(self.L.b2_env_observe(self.h, _vp(o), _vp(r), n))
+        return o, r
 
     def set_state_trace(self, on=True):
         _ck(self.L.b2_set_state_trace(self.h, int(on)))

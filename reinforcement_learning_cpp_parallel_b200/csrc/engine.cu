@@ -588,6 +588,41 @@ int b2_env_get_state(b2_handle E, double* u, int32_t* ep_step, int64_t n) {
   return B2_OK;
 }
 
+int b2_env_step(b2_handle E, const double* force, int64_t n) {
+  NEED(E);
+  if (!force || n != E->cfg.n_envs) return set_error(B2_ERR_INVALID, "env_step: expected %lld forces", (long long)E->cfg.n_envs);
+  CK(cudaSetDevice(E->cfg.device));
+  // staging (as doubles): force[n] | obs[n][6] | reward[n]
+  int rc = ensure_stage(E, 2 * 8 * n, 0);
+  if (rc) return rc;
+  double* d_force = reinterpret_cast<double*>(E->stage);
+  CK(cudaMemcpyAsync(d_force, force, sizeof(double) * n, cudaMemcpyHostToDevice, E->stream));
+  cudaError_t ce = launch_env_step(E->state, E->ep_step, d_force, n, E->cfg.precision, E->stream);
+  if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "env_step: %s", cudaGetErrorString(ce));
+  E->launches += 1;
+  E->total_env_steps += n;
+  CK(cudaStreamSynchronize(E->stream));  // the caller may reuse `force` right away
+  return B2_OK;
+}
+
+int b2_env_observe(b2_handle E, double* obs, double* reward, int64_t n) {
+  NEED(E);
+  if (n != E->cfg.n_envs) return set_error(B2_ERR_INVALID, "env_observe: expected %lld envs", (long long)E->cfg.n_envs);
+  if (!obs && !reward) return B2_OK;
+  CK(cudaSetDevice(E->cfg.device));
+  int rc = ensure_stage(E, 2 * 8 * n, 0);
+  if (rc) return rc;
+  double* d_obs = reinterpret_cast<double*>(E->stage) + n;
+  double* d_rew = d_obs + 6 * n;
+  cudaError_t ce = launch_env_observe(E->state, obs ? d_obs : nullptr, reward ? d_rew : nullptr, n, E->stream);
+  if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "env_observe: %s", cudaGetErrorString(ce));
+  E->launches += 1;
+  if (obs) CK(cudaMemcpyAsync(obs, d_obs, sizeof(double) * 6 * n, cudaMemcpyDeviceToHost, E->stream));
+  if (reward) CK(cudaMemcpyAsync(reward, d_rew, sizeof(double) * n, cudaMemcpyDeviceToHost, E->stream));
+  CK(cudaStreamSynchronize(E->stream));
+  return B2_OK;
+}
+
 int b2_set_state_trace(b2_handle E, int enable) {
   NEED(E);
   E->trace = enable != 0;

@@ -91,6 +91,9 @@ int update_partial_stride();
 cudaError_t launch_ppo_grad(const UpdateArgs& a, cudaStream_t st);
 cudaError_t launch_reduce(const UpdateArgs& a, bool apply_adam, cudaStream_t st);
 cudaError_t launch_adam(const UpdateArgs& a, cudaStream_t st);
+cudaError_t launch_env_step(double* state, int32_t* ep_step, const double* force, int64_t n, int precision,
+                            cudaStream_t st);
+cudaError_t launch_env_observe(const double* state, double* obs, double* reward, int64_t n, cudaStream_t st);
 cudaError_t launch_flush(float* buf, int64_t n, cudaStream_t st);
 cudaError_t measure_fma_peak(bool fp64, int sm_count, cudaStream_t st, double* tflops);
 

@@ -1,0 +1,92 @@
+"""Host-side C++ over the C ABI: include/compat/*.h and tools/b2_train (the reference's driver semantics)."""
+import json
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "tools", "bin")
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+@pytest.fixture(scope="module")
+def tools():
+    import __graft_entry__ as ge
+    ge.build(oracle=False)
+    return BIN
+
+
+def _run(args, **kw):
+    return subprocess.run(args, capture_output=True, text=True, timeout=600, **kw)
+
+
+# ------------------------------------------------------------------------------------------- CPU
+def test_tools_build_and_fail_loudly_without_a_gpu(tools):
+    """The shims compile with plain g++ (no nvcc, no libtorch) and there is no CPU path behind them."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present: covered by the gpu tests")
+    r = _run([os.path.join(tools, "compat_check"), GOLD])
+    assert r.returncode == 3 and "no CUDA device" in r.stdout, (r.stdout, r.stderr)
+    r = _run([os.path.join(tools, "b2_train"), os.path.join(ROOT, "tools", "config.default"), "--iters", "1"])
+    assert r.returncode == 1 and "no CUDA device" in r.stderr, (r.stdout, r.stderr)
+
+
+def test_b2_train_rejects_a_bad_config(tools, tmp_path):
+    """std::stoi on a non-integer line aborts the reference (src/main.cpp:368); here it is a clean error."""
+    bad = tmp_path / "config"
+    bad.write_text("1 = control_vars\nsix = obs_vars\n")
+    r = _run([os.path.join(tools, "b2_train"), str(bad)])
+    assert r.returncode == 1 and "does not start with an integer" in r.stderr
+    r = _run([os.path.join(tools, "b2_train"), str(tmp_path / "missing")])
+    assert r.returncode == 1 and "config file not found" in r.stderr
+
+
+# ------------------------------------------------------------------------------------------- GPU
+@pytest.mark.gpu
+def test_compat_shims_match_reference_goldens(tools):
+    """PPO/MemoryNN/getAction/CartPole used the way src/main.cpp uses them, against the reference's vectors."""
+    r = _run([os.path.join(tools, "compat_check"), GOLD])
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    assert r.returncode == 0 and out["ok"], out
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("envs,records", [(1, 2000), (3, 2100)])
+def test_b2_train_driver_semantics(tools, tmp_path, envs, records):
+    """Batch sizes of the reference's update trigger and its per-env log format."""
+    cfg = tmp_path / "config"
+    cfg.write_text("1 = a\n6 = b\n600 = Nepisodes\n100 = N_timestep\n1000000 = Max\n2000 = updateTimestep\n")
+    r = _run([os.path.join(tools, "b2_train"), str(cfg), "--envs", str(envs), "--iters", "2", "--epochs", "2",
+              "--log-dir", str(tmp_path)])
+    assert r.returncode == 0, (r.stdout, r.stderr)
+    assert f"records per update: {records}" in r.stdout
+    assert "update 2 " in r.stdout
+    pat = re.compile(r"^myid: (\d+)\t episode:(\d+)\t reward:(\d+\.\d{8})$")
+    for e in range(envs):
+        lines = (tmp_path / f"proc{e + 1}_log.txt").read_text().splitlines()
+        assert len(lines) == 2 * records // (100 * envs)
+        for i, ln in enumerate(lines):
+            m = pat.match(ln)
+            assert m and int(m.group(1)) == e + 1 and int(m.group(2)) == i and 0 <= float(m.group(3)) <= 100, ln
+
+
+@pytest.mark.gpu
+def test_b2_train_learns_and_checkpoints(tools, tmp_path):
+    """End to end through the C++ driver: the trailing mean episode reward rises well above the untrained
+    policy's (~25 of 100, results/carpole1node/proc1_log.txt first 100 episodes), and --save/--resume work."""
+    cfg = tmp_path / "config"
+    cfg.write_text("1 = a\n6 = b\n64000 = Nepisodes\n100 = N_timestep\n100000000 = Max\n2000 = updateTimestep\n")
+    ck = tmp_path / "ck.b2"
+    r = _run([os.path.join(tools, "b2_train"), str(cfg), "--envs", "64", "--iters", "60", "--epochs", "20",
+              "--log-dir", str(tmp_path), "--log-envs", "4", "--save", str(ck)])
+    assert r.returncode == 0, (r.stdout, r.stderr)
+    means = [float(m) for m in re.findall(r"mean episode reward ([0-9.]+)", r.stdout)]
+    assert len(means) == 60 and np.mean(means[-5:]) > 80 > np.mean(means[:2]), means
+    r2 = _run([os.path.join(tools, "b2_train"), str(cfg), "--envs", "64", "--iters", "1", "--epochs", "1",
+               "--log-dir", str(tmp_path), "--resume", str(ck)])
+    first = float(re.findall(r"mean episode reward ([0-9.]+)", r2.stdout)[0])
+    assert first > 80, r2.stdout
