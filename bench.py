@@ -41,6 +41,7 @@ def parse():
     ap.add_argument("--envs", type=int, default=65536)
     ap.add_argument("--horizon", type=int, default=128)
     ap.add_argument("--epochs", type=int, default=4, help="full-batch PPO epochs per timed update leg")
+    ap.add_argument("--chunks", type=int, default=8, help="launches per rollout in the e2e leg (copy/compute overlap)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-update", action="store_true")
@@ -124,7 +125,7 @@ class ClockSampler:
     def start(self):
         try:
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                       "--format=csv,noheader,nounits", "-lms", "100"],
+                                       "--format=csv,noheader,nounits", "-lms", "20"],
                                       stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except Exception:
@@ -254,20 +255,18 @@ def main():
         out = {"obs": capi.pinned_empty((T, N, 6), np.float32), "action": capi.pinned_empty((T, N), np.float32),
                "logp": capi.pinned_empty((T, N), np.float32), "reward": capi.pinned_empty((T, N), np.float32),
                "flags": capi.pinned_empty((T, N), np.uint8)}
-        fields = tuple(out)
         for _ in range(2):
-            E.set_params(hp); E.rollout(T); E.traj_download(T, fields=fields, out=out)
+            E.set_params(hp); E.rollout_host(T, out, n_chunks=args.chunks)
         barrier()
         t0 = time.perf_counter()
         for _ in range(args.steps):
             E.set_params(hp)                                  # H2D: the learner's current weights
-            E.rollout(T)                                      # K1 on device
-            E.traj_download(T, fields=fields, out=out)        # D2H: everything MemoryNN holds, into host buffers
+            E.rollout_host(T, out, n_chunks=args.chunks)      # K1 in chunks; D2H of chunk i overlaps chunk i+1
         barrier()
         dt = max_over_ranks(time.perf_counter() - t0)
         d2h = sum(a.nbytes for a in out.values())
         e2e = {"value": steps_all / dt, "unit": "env-steps/s", "h2d_bytes_per_step": int(hp.nbytes),
-               "d2h_bytes_per_step": int(d2h), "api": "b2_set_params + b2_rollout + b2_traj_download (host buffers)"}
+               "d2h_bytes_per_step": int(d2h), "api": f"b2_set_params + b2_rollout_host (pinned host buffers, {args.chunks} chunks: D2H overlaps simulation)"}
 
     if rank != 0:
         if dist:
@@ -283,8 +282,16 @@ def main():
     else:
         bound, peak = "fp32-fma", peak32
         achieved = (FLOP_PHYS + FLOP_ACTOR) * steps_launch / (ms_launch * 1e-3) / 1e12
+    # dram__bytes_read.sum + dram__bytes_write.sum of one k_rollout launch at this exact shape, from the committed
+    # `ncu --set full` capture (profiles/NCU_TRAFFIC.json; algorithmic bytes are 41 B x N x T = 344 MB)
+    traffic = None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "NCU_TRAFFIC.json")))
+        traffic = tj.get(f"k_rollout_{args.precision}_{N}x{T}")
+    except Exception:
+        pass
     roofline = {"kernel": "k_rollout", "bound": bound, "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                "frac": achieved / peak if peak else None, "traffic": None,
+                "frac": achieved / peak if peak else None, "traffic": traffic,
                 "peak_source": "b2_measure_fma_peak (live FMA-issue microbenchmark, this GPU, this run)",
                 "flop_per_env_step": FLOP_PHYS if args.precision == "f64" else FLOP_PHYS + FLOP_ACTOR,
                 "hbm": {"achieved_gbs": BYTES_STEP * steps_launch / (ms_launch * 1e-3) / 1e9, "peak_gbs": hbm_peak,

@@ -146,6 +146,11 @@ int b2_rollout(b2_handle h, int T, const float* forced_action);
  * env: x, xdot, thetadot, theta, cos, sin) and getReward (:135-147).  Either output may be NULL. */
 int b2_env_step(b2_handle h, const double* force, int64_t n);
 int b2_env_observe(b2_handle h, double* obs, double* reward, int64_t n);
+/* b2_rollout whose trajectory lands in HOST buffers (what MemoryNN holds after a collection phase): the horizon is
+ * simulated in n_chunks launches and each finished chunk is copied out on a second stream while the next one is
+ * being simulated.  Fields of `out` may be NULL (skipped); `returns` is ignored (no returns exist yet).  Pinned
+ * buffers (b2_host_alloc) are needed for the overlap; pageable ones work but serialise. */
+int b2_rollout_host(b2_handle h, int T, int n_chunks, const b2_batch_out* out);
 int b2_update_resident(b2_handle h, b2_update_stats* stats);   /* returns + K epochs on the resident trajectory */
 int b2_train_iteration(b2_handle h, int T, b2_update_stats* stats); /* rollout + update_resident */
 int b2_traj_download(b2_handle h, b2_batch_out* out, double* state_trace /* [T][N][4] or NULL, only if tracing on */);

@@ -80,6 +80,7 @@ SYMBOLS = {
     "b2_env_set_state": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_int64]),
     "b2_env_get_state": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_int64]),
     "b2_rollout": (C.c_int, [_H, C.c_int, C.c_void_p]),
+    "b2_rollout_host": (C.c_int, [_H, C.c_int, C.c_int, _P(BatchOut)]),
     "b2_env_step": (C.c_int, [_H, C.c_void_p, C.c_int64]),
     "b2_env_observe": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_int64]),
     "b2_update_resident": (C.c_int, [_H, _P(UpdateStats)]),
@@ -294,6 +295,13 @@ class Engine:
         if fa is not None:
             assert fa.size == T * int(self.cfg.n_envs)
         _ck(self.L.b2_rollout(self.h, T, _vp(fa)))
+
+    def rollout_host(self, T, out, n_chunks=8):
+        """b2_rollout_host: rollout T steps, trajectory delivered into the HOST arrays of `out` (pinned for overlap)."""
+        bo = BatchOut(*[out[k].ctypes.data if k in out else None
+                        for k in ("obs", "action", "logp", "mu", "reward", "flags")], None)
+        _ck(self.L.b2_rollout_host(self.h, T, n_chunks, C.byref(bo)))
+        return out
 
     def update_resident(self):
         st = UpdateStats()

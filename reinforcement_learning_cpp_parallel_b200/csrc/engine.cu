@@ -63,10 +63,13 @@ static bool load_nccl() {
 
 using namespace b2;
 
+constexpr int B2_MAX_CHUNKS = 32;
+
 struct b2_engine {
   b2_config cfg;
   int P = 0, pstride = 0, sm_count = 148;
-  cudaStream_t stream = nullptr;
+  cudaStream_t stream = nullptr, copy_stream = nullptr;
+  cudaEvent_t chunk_ev[B2_MAX_CHUNKS] = {}, copy_done = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   // learner state
   float *params = nullptr, *adam_m = nullptr, *adam_v = nullptr, *grads = nullptr, *partials = nullptr;
@@ -351,6 +354,12 @@ int b2_destroy(b2_handle E) {
                   E->progress};
   for (void* p : ptrs) cudaFree(p);
   if (E->status_host) cudaFreeHost(E->status_host);
+  if (E->copy_stream) {
+    cudaStreamSynchronize(E->copy_stream);
+    for (auto ev : E->chunk_ev) if (ev) cudaEventDestroy(ev);
+    if (E->copy_done) cudaEventDestroy(E->copy_done);
+    cudaStreamDestroy(E->copy_stream);
+  }
   if (E->ev0) cudaEventDestroy(E->ev0);
   if (E->ev1) cudaEventDestroy(E->ev1);
   if (E->stream) cudaStreamDestroy(E->stream);
@@ -629,8 +638,23 @@ int b2_set_state_trace(b2_handle E, int enable) {
   return ensure_traj(E, E->tr.cap);
 }
 
-int b2_rollout(b2_handle E, int T, const float* forced_action) {
-  NEED(E);
+// one k_rollout launch covering steps [t_begin, t_end) of a T-step rollout that started at E->global_step
+static int rollout_window(b2_engine* E, int T, int t_begin, int t_end, bool forced) {
+  RolloutArgs a{};
+  a.params = E->params; a.state = E->state; a.ep_step = E->ep_step; a.ep_ret = E->ep_ret;
+  a.ep_count = E->ep_count; a.ep_log = E->ep_log; a.max_eps = E->max_eps;
+  a.tr = E->tr;
+  a.forced_action = forced ? E->forced : nullptr;
+  a.n_envs = E->cfg.n_envs; a.T = T; a.t_begin = t_begin; a.t_end = t_end; a.n_timestep = E->cfg.n_timestep;
+  a.seed = E->cfg.seed; a.env_offset = E->cfg.env_offset; a.step0 = E->global_step;
+  a.hp = E->hp; a.status = E->status; a.progress = E->progress;
+  cudaError_t ce = launch_rollout(a, E->cfg.precision, E->trace, E->sm_count, E->stream, E->cfg.hidden1, E->cfg.hidden2);
+  if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "rollout: %s", cudaGetErrorString(ce));
+  E->launches += 1;
+  return B2_OK;
+}
+
+static int rollout_prepare(b2_engine* E, int T, const float* forced_action) {
   CK(cudaSetDevice(E->cfg.device));
   if (T < 1 || T > E->cfg.horizon) return set_error(B2_ERR_INVALID, "rollout: T=%d outside [1, horizon=%d]", T, E->cfg.horizon);
   const int64_t NE = E->cfg.n_envs;
@@ -645,22 +669,69 @@ int b2_rollout(b2_handle E, int T, const float* forced_action) {
     }
     CK(cudaMemcpyAsync(E->forced, forced_action, sizeof(float) * NE * T, cudaMemcpyHostToDevice, E->stream));
   }
-  RolloutArgs a{};
-  a.params = E->params; a.state = E->state; a.ep_step = E->ep_step; a.ep_ret = E->ep_ret;
-  a.ep_count = E->ep_count; a.ep_log = E->ep_log; a.max_eps = E->max_eps;
   E->tr.n_envs = NE; E->tr.horizon = T;
-  a.tr = E->tr;
-  a.forced_action = forced_action ? E->forced : nullptr;
-  a.n_envs = NE; a.T = T; a.n_timestep = E->cfg.n_timestep;
-  a.seed = E->cfg.seed; a.env_offset = E->cfg.env_offset; a.step0 = E->global_step;
-  a.hp = E->hp; a.status = E->status; a.progress = E->progress;
-  cudaError_t ce = launch_rollout(a, E->cfg.precision, E->trace, E->sm_count, E->stream, E->cfg.hidden1, E->cfg.hidden2);
-  if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "rollout: %s", cudaGetErrorString(ce));
-  E->launches += 1;
-  E->global_step += (uint64_t)T;
-  E->total_env_steps += NE * T;
-  E->have_traj = true;
   return B2_OK;
+}
+
+static void rollout_finish(b2_engine* E, int T) {
+  E->global_step += (uint64_t)T;
+  E->total_env_steps += E->cfg.n_envs * T;
+  E->have_traj = true;
+}
+
+int b2_rollout(b2_handle E, int T, const float* forced_action) {
+  NEED(E);
+  int rc = rollout_prepare(E, T, forced_action);
+  if (rc) return rc;
+  if ((rc = rollout_window(E, T, 0, T, forced_action != nullptr))) return rc;
+  rollout_finish(E, T);
+  return B2_OK;
+}
+
+// Rollout with the trajectory delivered into HOST buffers.  The horizon is cut into n_chunks launches; while
+// chunk i+1 is being simulated, chunk i (a contiguous k-range of every field, the buffer being time-major) is
+// transposed to MemoryNN's AoS observation layout and copied out on a second stream, so the PCIe transfer
+// (37 B per env-step) hides behind the simulation instead of following it.
+int b2_rollout_host(b2_handle E, int T, int n_chunks, const b2_batch_out* out) {
+  NEED(E);
+  if (!out) return set_error(B2_ERR_INVALID, "rollout_host: null out");
+  int rc = rollout_prepare(E, T, nullptr);
+  if (rc) return rc;
+  if (n_chunks < 1) n_chunks = 1;
+  if (n_chunks > T) n_chunks = T;
+  if (n_chunks > B2_MAX_CHUNKS) n_chunks = B2_MAX_CHUNKS;
+  const int64_t NE = E->cfg.n_envs;
+  Traj& t = E->tr;
+  if (out->obs && (rc = ensure_stage(E, NE * T * OBS, 0))) return rc;
+  if (!E->copy_stream) {
+    CK(cudaStreamCreateWithFlags(&E->copy_stream, cudaStreamNonBlocking));
+    for (auto& ev : E->chunk_ev) CK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&E->copy_done, cudaEventDisableTiming));
+  }
+  for (int c = 0; c < n_chunks; c++) {
+    const int t0 = (int)((int64_t)T * c / n_chunks), t1 = (int)((int64_t)T * (c + 1) / n_chunks);
+    if ((rc = rollout_window(E, T, t0, t1, false))) return rc;
+    CK(cudaEventRecord(E->chunk_ev[c], E->stream));
+    CK(cudaStreamWaitEvent(E->copy_stream, E->chunk_ev[c], 0));
+    const int64_t k0 = (int64_t)t0 * NE, n = (int64_t)(t1 - t0) * NE;
+    if (out->obs) {
+      cudaError_t ce = launch_soa_to_aos(t.obs + k0, E->stage + k0 * OBS, t.cap, n, E->copy_stream);
+      if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "soa_to_aos: %s", cudaGetErrorString(ce));
+      E->launches += 1;
+      CK(cudaMemcpyAsync(out->obs + k0 * OBS, E->stage + k0 * OBS, sizeof(float) * OBS * n, cudaMemcpyDeviceToHost, E->copy_stream));
+    }
+    if (out->action) CK(cudaMemcpyAsync(out->action + k0, t.action + k0, sizeof(float) * n, cudaMemcpyDeviceToHost, E->copy_stream));
+    if (out->logp) CK(cudaMemcpyAsync(out->logp + k0, t.logp + k0, sizeof(float) * n, cudaMemcpyDeviceToHost, E->copy_stream));
+    if (out->mu) CK(cudaMemcpyAsync(out->mu + k0, t.mu + k0, sizeof(float) * n, cudaMemcpyDeviceToHost, E->copy_stream));
+    if (out->reward) CK(cudaMemcpyAsync(out->reward + k0, t.reward + k0, sizeof(float) * n, cudaMemcpyDeviceToHost, E->copy_stream));
+    if (out->flags) CK(cudaMemcpyAsync(out->flags + k0, t.flags + k0, (size_t)n, cudaMemcpyDeviceToHost, E->copy_stream));
+  }
+  rollout_finish(E, T);
+  // the main stream must not overwrite the buffer (next rollout) before the copies have drained
+  CK(cudaEventRecord(E->copy_done, E->copy_stream));
+  CK(cudaStreamWaitEvent(E->stream, E->copy_done, 0));
+  CK(cudaStreamSynchronize(E->copy_stream));
+  return check_status(E, "rollout");
 }
 
 int b2_update_resident(b2_handle E, b2_update_stats* stats) {

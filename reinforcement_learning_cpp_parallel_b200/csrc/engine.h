@@ -52,7 +52,8 @@ struct RolloutArgs {
   Traj tr;
   const float* forced_action;  // [T][N] or null
   int64_t n_envs;
-  int T, n_timestep;
+  int T, n_timestep;    // T: horizon of the whole rollout (trajectory index and TRUNC flag use absolute t)
+  int t_begin, t_end;   // this launch advances steps [t_begin, t_end) of it
   uint64_t seed, env_offset, step0;
   HyperDev hp;
   int* status;          // bit0: non-finite action seen

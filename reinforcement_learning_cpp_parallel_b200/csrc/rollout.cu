@@ -45,7 +45,7 @@ __device__ __forceinline__ void st_release(int* p, int v) {
   asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
-// Advance group g (envs 32 g .. 32 g + 31) over steps [t0, t1) of this rollout.
+// Advance group g (envs 32 g .. 32 g + 31) over steps [t0, t1) of this LAUNCH (absolute step = t_begin + t).
 template <typename Real, class N, bool TRACE>
 __device__ __forceinline__ void rollout_segment(const RolloutArgs& a, const float* sm, float* hs, int64_t g, int t0,
                                                 int t1) {
@@ -65,11 +65,11 @@ __device__ __forceinline__ void rollout_segment(const RolloutArgs& a, const floa
   for (int j = 0; j < 4; j++) u[j] = (Real)__ldcg(a.state + j * NE + e);
   int es = __ldcg(a.ep_step + e);
   float er = __ldcg(a.ep_ret + e);
-  int ecount = (t0 == 0) ? 0 : __ldcg(a.ep_count + e);
+  int ecount = (a.t_begin + t0 == 0) ? 0 : __ldcg(a.ep_count + e);
   bool bad = false;
   const int64_t cap = a.tr.cap;
 
-  for (int t = t0; t < t1; t++) {
+  for (int t = a.t_begin + t0; t < a.t_begin + t1; t++) {
     const int64_t k = (int64_t)t * NE + e;
     float o[6];
     Dyn::observe(u, o);
@@ -128,7 +128,7 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_CTAS_PER_SM) k_rollout(
   const int wpb = blockDim.x >> 5;
   const int64_t w = (int64_t)blockIdx.x * wpb + (threadIdx.x >> 5);
   const int64_t W = (int64_t)gridDim.x * wpb;
-  const int64_t T = a.T;
+  const int64_t T = a.t_end - a.t_begin;
   const int64_t G = (a.n_envs + 31) >> 5;
   const int64_t U = G * T;
   const int64_t u0 = w * U / W, u1 = (w + 1) * U / W;   // U W < 2^63 for any shape that fits in HBM

@@ -192,3 +192,31 @@ def test_training_learns_cartpole(pkg):
     print("episode reward per update:", np.round(hist, 1))
     assert np.mean(hist[-5:]) >= 95, hist
     E.close()
+
+
+def test_rollout_host_pipelined_equals_resident_rollout(pkg):
+    from reinforcement_learning_cpp_parallel_b200 import capi
+    """b2_rollout_host (chunked launches + overlapped D2H into host buffers) delivers exactly what b2_rollout +
+    b2_traj_download deliver, for chunk counts that do and do not divide the horizon, and carries env state on."""
+    N, T = 200, 37
+    ref = make_engine(pkg, n_envs=N, horizon=T, seed=5)
+    ref.init_params(3)
+    ref.rollout(T)
+    a = ref.traj_download(T)
+    ref.rollout(T)
+    a2 = ref.traj_download(T)
+    for chunks in (1, 4, 37):
+        E = make_engine(pkg, n_envs=N, horizon=T, seed=5)
+        E.init_params(3)
+        out = {"obs": capi.pinned_empty((T, N, 6), np.float32), "action": capi.pinned_empty((T, N), np.float32),
+               "logp": capi.pinned_empty((T, N), np.float32), "reward": capi.pinned_empty((T, N), np.float32),
+               "flags": capi.pinned_empty((T, N), np.uint8)}
+        E.rollout_host(T, out, n_chunks=chunks)
+        for k in out:
+            np.testing.assert_array_equal(out[k], a[k], err_msg=f"{k} chunks={chunks}")
+        E.rollout_host(T, out, n_chunks=chunks)
+        for k in out:
+            np.testing.assert_array_equal(out[k], a2[k], err_msg=f"{k} second rollout chunks={chunks}")
+        np.testing.assert_array_equal(E.env_get_state()[0], ref.env_get_state()[0])
+        E.close()
+    ref.close()
