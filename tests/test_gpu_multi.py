@@ -1,0 +1,80 @@
+"""T9: two GPUs, one process each -- env sharding + NCCL gradient all-reduce against one GPU holding every env.
+Skipped on a single-GPU box (the driver's 1-GPU tier); run with `gpurun --gpus 2 -- python -m pytest tests/test_gpu_multi.py -m gpu`."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+NG, T, K = 512, 100, 3
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _rank(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    import reinforcement_learning_cpp_parallel_b200 as pkg
+    from reinforcement_learning_cpp_parallel_b200 import capi, sharding
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        n_local, off = sharding.shard_envs(NG, rank, world)
+        E = pkg.Engine(capi.default_config(n_envs=n_local, horizon=T, seed=21, env_offset=off, k_epochs=K, device=rank))
+        E.init_params(4)
+        uid = sharding.broadcast_comm_id(dist, pkg.Engine.comm_unique_id)
+        E.comm_init(rank, world, uid)
+        E.rollout(T)
+        traj = E.traj_download(T, fields=("obs", "action", "reward", "flags"))
+        st = E.update_resident()
+        q.put((rank, off, n_local, traj, E.get_grads(), E.get_params(), st.loss, st.adam_step))
+        E.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_gpu_update_matches_one_gpu():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    import reinforcement_learning_cpp_parallel_b200 as pkg
+    from reinforcement_learning_cpp_parallel_b200 import capi
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_rank, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=300) for _ in procs], key=lambda r: r[0])
+    for p in procs:
+        p.join(60)
+    # single GPU, all envs
+    E = pkg.Engine(capi.default_config(n_envs=NG, horizon=T, seed=21, k_epochs=K))
+    E.init_params(4)
+    E.rollout(T)
+    full = E.traj_download(T, fields=("obs", "action", "reward", "flags"))
+    st = E.update_resident()
+    g1, p1 = E.get_grads(), E.get_params()
+    E.close()
+    # identical trajectories for any sharding (Philox keyed by the global env id)
+    for rank, off, n, traj, *_ in res:
+        for k in traj:
+            np.testing.assert_array_equal(traj[k], full[k][:, off:off + n], err_msg=k)
+    # weights bit-identical across ranks (Adam applied redundantly on all-reduced gradients)
+    np.testing.assert_array_equal(res[0][5], res[1][5])
+    np.testing.assert_array_equal(res[0][4], res[1][4])
+    rel = lambda a, b: float(np.linalg.norm(a.astype(np.float64) - b) / np.linalg.norm(b.astype(np.float64)))
+    assert rel(res[0][4], g1) < 1e-5, rel(res[0][4], g1)        # different reduction tree only
+    assert rel(res[0][5], p1) < 1e-6, rel(res[0][5], p1)
+    assert abs(res[0][6] - st.loss) < 1e-5 * abs(st.loss) and res[0][7] == st.adam_step == K
