@@ -51,7 +51,9 @@ constexpr int oW2T = oW1T + 8 * H1;          // [H1+1][H2] rows k<H1 W2^T (permu
 constexpr int oW2N = oW2T + (H1 + 1) * H2;   // [H2][H1]  W2 natural rows, permuted cols
 constexpr int oW3 = oW2N + H2 * H1;          // [H2+4]    W3, b3, 0..
 constexpr int oRed = oW3 + H2 + 4;           // 32 floats reduction scratch
-constexpr int SMEM_FLOATS = oRed + 32;
+constexpr int oX1 = oRed + 32;                // second X tile buffer (prefetch target)
+constexpr int oVec1 = oX1 + XR * PS;          // second act/oldlp/R/V buffer (4 x TS)
+constexpr int SMEM_FLOATS = oVec1 + 4 * TS;
 constexpr int SMEM_BYTES = SMEM_FLOATS * 4;
 static_assert(2 * SMEM_BYTES <= 227 * 1024, "two CTAs per SM");
 // end-of-pass scratch (aliases the activation rows, which are dead by then)
@@ -100,6 +102,15 @@ __device__ __forceinline__ void st4(float* p, float a, float b, float c, float d
 __device__ __forceinline__ float dot4(const float4& a, const float4& b) {
   return fmaf(a.x, b.x, fmaf(a.y, b.y, fmaf(a.z, b.z, a.w * b.w)));
 }
+__device__ __forceinline__ void fma_dot4(float& acc, const float4& a, const float4& b) {  // 4 FFMA, no FADD
+  acc = fmaf(a.x, b.x, acc); acc = fmaf(a.y, b.y, acc); acc = fmaf(a.z, b.z, acc); acc = fmaf(a.w, b.w, acc);
+}
+__device__ __forceinline__ void cp_async4(float* smem_dst, const float* gmem_src) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ float sum4(const float4& a) { return (a.x + a.y) + (a.z + a.w); }
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
@@ -129,7 +140,7 @@ __global__ void __launch_bounds__(NT, 2) k_ppo_grad(const UpdateArgs a) {
   const int w1_kt = tid & 15;
   const int w1_sl = tid >> 4;
 
-  float loss1_sum = 0.f, loss2_sum = 0.f, clip_sum = 0.f;  // meaningful in threads < TS
+  float loss1_sum = 0.f, loss2_sum = 0.f, clip_sum = 0.f;  // accumulated by lanes < 16 of every warp
 
 #pragma unroll 1
   for (int net = 1; net >= 0; net--) {   // critic first: the actor's advantage needs the current V (:274)
@@ -146,40 +157,57 @@ __global__ void __launch_bounds__(NT, 2) k_ppo_grad(const UpdateArgs a) {
 #pragma unroll
     for (int i = 0; i < 9; i++) gRow[i] = 0.f;
 
-#pragma unroll 1
-    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-      __syncthreads();  // previous tile's readers are done (and weights are staged)
-      // ---- load the tile: observations as rows, per-sample vectors ----
+    // constant rows (bias columns) -- rewritten every pass: the end-of-pass scratch aliases them
+    for (int i = tid; i < 2 * TS; i += NT) {
+      const float v = (i < TS) ? 1.0f : 0.0f;           // row S: ones, row S+1: zeros
+      sm[oX + S * PS + (i % TS) + (i / TS) * PS] = v;
+      sm[oX1 + S * PS + (i % TS) + (i / TS) * PS] = v;
+    }
+    if (tid < TS) {
+      sm[oH1 + H1 * PS + tid] = 1.0f;
+      sm[oH2 + H2 * PS + tid] = 1.0f;
+    }
+    // Asynchronous tile fetch (LDGSTS): tile i+1 streams into the other buffer while tile i is being computed.
+    auto prefetch = [&](int64_t tile, int b) {
+      float* xb = sm + (b ? oX1 : oX);
+      float* vb = sm + (b ? oVec1 : oVec);
       const int64_t p0 = a.first + tile * TS;
-      for (int i = tid; i < XR * TS; i += NT) {
+      for (int i = tid; i < (S + 4) * TS; i += NT) {
         const int r = i / TS, s = i % TS;
-        const int64_t p = p0 + s;
         const bool valid = (tile * TS + s) < a.count;
-        float v = 0.f;
-        if (r < S) {
-          if (valid) { const int64_t k = a.idx ? (int64_t)a.idx[p] : p; v = a.tr.obs[r * cap + k]; }
-        } else if (r == S) v = 1.0f;
-        sm[oX + r * PS + s] = v;
+        float* dst = (r < S) ? (xb + r * PS + s) : (vb + (r - S) * TS + s);
+        const float* src = nullptr;
+        if (valid) {
+          const int64_t k = a.idx ? (int64_t)a.idx[p0 + s] : (p0 + s);
+          if (r < S) src = a.tr.obs + r * cap + k;
+          else if (r == S) src = a.tr.action + k;
+          else if (r == S + 1) src = a.tr.logp + k;
+          else if (r == S + 2) src = a.tr.ret + k;
+          else if (net == 0) src = a.tr.vcur + k;
+        }
+        if (src) cp_async4(dst, src);
+        else *dst = 0.f;
       }
-      if (tid < TS) {
-        const int64_t p = p0 + tid;
-        const bool valid = (tile * TS + tid) < a.count;
-        const int64_t k = valid ? (a.idx ? (int64_t)a.idx[p] : p) : 0;
-        sm[oVec + 0 * TS + tid] = valid ? a.tr.action[k] : 0.f;
-        sm[oVec + 1 * TS + tid] = valid ? a.tr.logp[k] : 0.f;
-        sm[oVec + 2 * TS + tid] = valid ? a.tr.ret[k] : 0.f;
-        sm[oVec + 3 * TS + tid] = (valid && net == 0) ? a.tr.vcur[k] : 0.f;
-        sm[oH1 + H1 * PS + tid] = 1.0f;   // ones rows (bias columns)
-        sm[oH2 + H2 * PS + tid] = 1.0f;
-      }
-      __syncthreads();
+      cp_async_commit();
+    };
+    int cur = 0;
+    if ((int64_t)blockIdx.x < ntiles) prefetch(blockIdx.x, 0);
+
+#pragma unroll 1
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, cur ^= 1) {
+      cp_async_wait_all();
+      __syncthreads();  // this tile has landed; the previous tile's readers are done (and weights are staged)
+      if (tile + gridDim.x < ntiles) prefetch(tile + gridDim.x, cur ^ 1);
+      const float* xb = sm + (cur ? oX1 : oX);
+      const float* vb = sm + (cur ? oVec1 : oVec);
+      const int64_t p0 = a.first + tile * TS;
 
       // ---- L1: H1 = tanh(W1 x + b1), two strided feature groups per thread ----
       {
         float acc0[4][4] = {}, acc1[4][4] = {};
 #pragma unroll
         for (int k = 0; k < S + 1; k++) {
-          const float4 av = ld4(sm + oX + k * PS + s0);
+          const float4 av = ld4(xb + k * PS + s0);
           fma44(acc0, ld4(sm + oW1T + k * H1 + 4 * ft), av);
           fma44(acc1, ld4(sm + oW1T + k * H1 + 32 + 4 * ft), av);
         }
@@ -191,7 +219,7 @@ __global__ void __launch_bounds__(NT, 2) k_ppo_grad(const UpdateArgs a) {
               act_tanh(acc1[i][2]), act_tanh(acc1[i][3]));
         }
       }
-      __syncthreads();
+      __syncwarp();  // H1 columns of this warp's 16 samples are produced and consumed by the same warp
       // ---- L2: H2 = tanh(W2 h1 + b2) ----
       {
         float acc[4][4] = {};
@@ -202,14 +230,22 @@ __global__ void __launch_bounds__(NT, 2) k_ppo_grad(const UpdateArgs a) {
           st4(sm + oH2 + (ft + 8 * i) * PS + s0, act_tanh(acc[i][0]), act_tanh(acc[i][1]), act_tanh(acc[i][2]),
               act_tanh(acc[i][3]));
       }
-      __syncthreads();
-      // ---- L3 + loss head: one thread per sample ----
-      if (tid < TS) {
-        float y = 0.f;
+      __syncwarp();
+      // ---- L3 + loss head, warp-local: lane l and lane l+16 split the 33-term dot product of sample 16 warp + (l & 15)
+      {
+        const int sl = 16 * warp + (lane & 15);
+        const int jb = (lane >> 4) * 16;
+        float y0 = 0.f, y1 = 0.f;
 #pragma unroll
-        for (int j = 0; j < H2 + 1; j++) y = fmaf(sm[oW3 + j], sm[oH2 + j * PS + tid], y);
-        const bool valid = (tile * TS + tid) < a.count;
-        const float R = sm[oVec + 2 * TS + tid];
+        for (int j = 0; j < 16; j += 2) {
+          y0 = fmaf(sm[oW3 + jb + j], sm[oH2 + (jb + j) * PS + sl], y0);
+          y1 = fmaf(sm[oW3 + jb + j + 1], sm[oH2 + (jb + j + 1) * PS + sl], y1);
+        }
+        float y = y0 + y1;
+        y += __shfl_xor_sync(0xffffffffu, y, 16);
+        y += sm[oW3 + H2];                                     // b3 (the ones row of H2 is not needed here)
+        const bool valid = (lane < 16) && (tile * TS + sl) < a.count;
+        const float R = vb[2 * TS + sl];
         float dz3 = 0.f;
         if (net == 1) {
           const float V = y;                                   // critic: no final activation (ppo_nn.h:118-122)
@@ -217,15 +253,15 @@ __global__ void __launch_bounds__(NT, 2) k_ppo_grad(const UpdateArgs a) {
           if (valid) {
             loss2_sum = fmaf(e, e, loss2_sum);                 // :288  0.5 * MSE
             dz3 = e * inv_denom;
-            const int64_t p = p0 + tid;
+            const int64_t p = p0 + sl;
             a.tr.vcur[a.idx ? (int64_t)a.idx[p] : p] = V;
           }
         } else if (valid) {
           const float mu = act_tanh(y);                        // ppo_nn.h:102
-          const float act = sm[oVec + tid];
+          const float act = vb[sl];
           const float lp = gauss_logprob(act, mu, a.hp.inv_var, a.hp.half_log_norm);  // :140
-          const float ratio = expf(lp - sm[oVec + TS + tid]);  // :263
-          const float A = R - sm[oVec + 3 * TS + tid];         // :274 (detached)
+          const float ratio = expf(lp - vb[TS + sl]);          // :263
+          const float A = R - vb[3 * TS + sl];                 // :274 (detached)
           const float surr1 = ratio * A;                       // :284
           const float rc = fminf(fmaxf(ratio, a.hp.clip_lo), a.hp.clip_hi);
           const float surr2 = rc * A;                          // :285
@@ -241,9 +277,9 @@ __global__ void __launch_bounds__(NT, 2) k_ppo_grad(const UpdateArgs a) {
           const float dmu = dlogp * (act - mu) * a.hp.inv_var; // :20-31
           dz3 = dmu * (1.0f - mu * mu);
         }
-        sm[oVec + 4 * TS + tid] = dz3;
+        if (lane < 16) sm[oVec + 4 * TS + sl] = dz3;
       }
-      __syncthreads();
+      __syncwarp();
       // ---- D2 = dz3 (x) W3 .* (1 - H2^2) ----
       {
         const float4 dz = ld4(sm + oVec + 4 * TS + s0);
@@ -264,7 +300,7 @@ __global__ void __launch_bounds__(NT, 2) k_ppo_grad(const UpdateArgs a) {
         for (int i = 0; i < 4; i++) {
           const int j = warp + 8 * i;
           gRow[i] += sum4(ld4(sm + oD2 + j * PS + 4 * lane));
-          gRow[4 + i] += dot4(dz, ld4(sm + oH2 + j * PS + 4 * lane));
+          fma_dot4(gRow[4 + i], dz, ld4(sm + oH2 + j * PS + 4 * lane));
         }
         if (warp == 0) gRow[8] += sum4(dz);
       }
@@ -281,7 +317,7 @@ __global__ void __launch_bounds__(NT, 2) k_ppo_grad(const UpdateArgs a) {
 #pragma unroll
           for (int i = 0; i < 4; i++)
 #pragma unroll
-            for (int j = 0; j < 4; j++) gW2[i][j] += dot4(d[i], h[j]);
+            for (int j = 0; j < 4; j++) fma_dot4(gW2[i][j], d[i], h[j]);
         }
       }
       __syncthreads();  // H1 is about to be overwritten by D1
@@ -313,12 +349,12 @@ __global__ void __launch_bounds__(NT, 2) k_ppo_grad(const UpdateArgs a) {
         for (int s = 0; s < 8; s += 4) {
           float4 xv[S + 1];
 #pragma unroll
-          for (int c = 0; c < S + 1; c++) xv[c] = ld4(sm + oX + c * PS + sb + s);
+          for (int c = 0; c < S + 1; c++) xv[c] = ld4(xb + c * PS + sb + s);
 #pragma unroll
           for (int i = 0; i < 4; i++) {
             const float4 d = ld4(sm + oH1 + (w1_kt + 16 * i) * PS + sb + s);
 #pragma unroll
-            for (int c = 0; c < S + 1; c++) gW1[i][c] += dot4(d, xv[c]);
+            for (int c = 0; c < S + 1; c++) fma_dot4(gW1[i][c], d, xv[c]);
           }
         }
       }
