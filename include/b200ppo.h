@@ -176,6 +176,9 @@ int b2_flush_l2(b2_handle h);                                  /* overwrite a >L
 int b2_measure_fma_peak(b2_handle h, int fp64, double* tflops); /* CUDA-core FMA issue peak of this GPU (roofline denominator) */
 int b2_host_alloc(void** p, size_t bytes);                     /* pinned host memory for the host-buffer entry points */
 int b2_host_free(void* p);
+/* diagnostic for the tensor-core path of wide nets: C[M][N] = A[M][K] . B[N][K]^T (host fp32 in/out) through the
+ * bf16x3 tcgen05 GEMM that the 2x256 update uses; N % 32 == 0, N <= 256; splits > 1 exercises the split-K partials */
+int b2_selftest_gemm(b2_handle h, int M, int N, int K, const float* A, const float* B, float* C, int splits);
 
 #ifdef __cplusplus
 }

@@ -101,6 +101,7 @@ SYMBOLS = {
     "b2_measure_fma_peak": (C.c_int, [_H, C.c_int, _P(C.c_double)]),
     "b2_host_alloc": (C.c_int, [_P(C.c_void_p), C.c_size_t]),
     "b2_host_free": (C.c_int, [C.c_void_p]),
+    "b2_selftest_gemm": (C.c_int, [_H, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),
 }
 
 _lib = None
@@ -373,6 +374,21 @@ class Engine:
         t = C.c_double()
         _ck(self.L.b2_measure_fma_peak(self.h, int(fp64), C.byref(t)))
         return t.value
+
+
+def _selftest_gemm(self, A, B, splits=1):
+    """C = A @ B.T through the bf16x3 tcgen05 GEMM of the wide-net update (diagnostic)."""
+    A = np.ascontiguousarray(A, np.float32)
+    B = np.ascontiguousarray(B, np.float32)
+    M, K = A.shape
+    N = B.shape[0]
+    assert B.shape[1] == K
+    out = np.empty((M, N), np.float32)
+    _ck(self.L.b2_selftest_gemm(self.h, M, N, K, _vp(A), _vp(B), _vp(out), int(splits)))
+    return out
+
+
+Engine.selftest_gemm = _selftest_gemm
 
 
 def pinned_empty(shape, dtype):

@@ -4,6 +4,7 @@
 // per-step learner<->env messaging (src/main.cpp:12-148,190-354) into a handful of kernel launches
 // per rollout/update, and never touches the data path on the CPU.  No libtorch, no CPU fallback.
 #include "engine.h"
+#include "wide.h"
 
 #include <dlfcn.h>
 #include <math.h>
@@ -868,6 +869,26 @@ int b2_host_alloc(void** p, size_t bytes) {
   CK(cudaMallocHost(p, bytes));
   return B2_OK;
 }
+int b2_selftest_gemm(b2_handle E, int M, int N, int K, const float* A, const float* B, float* C, int splits) {
+  NEED(E);
+  if (!A || !B || !C || M < 1 || N < 1 || K < 1) return set_error(B2_ERR_INVALID, "selftest_gemm: bad argument");
+  CK(cudaSetDevice(E->cfg.device));
+  float *dA = nullptr, *dB = nullptr, *dC = nullptr;
+  CK(cudaMalloc(&dA, sizeof(float) * (size_t)M * K));
+  CK(cudaMalloc(&dB, sizeof(float) * (size_t)N * K));
+  CK(cudaMalloc(&dC, sizeof(float) * (size_t)M * N));
+  CK(cudaMemcpyAsync(dA, A, sizeof(float) * (size_t)M * K, cudaMemcpyHostToDevice, E->stream));
+  CK(cudaMemcpyAsync(dB, B, sizeof(float) * (size_t)N * K, cudaMemcpyHostToDevice, E->stream));
+  int rc = wide_selftest_gemm(M, N, K, dA, dB, dC, splits, E->sm_count, E->stream);
+  E->launches += 4;
+  if (!rc) {
+    cudaError_t ce = cudaMemcpy(C, dC, sizeof(float) * (size_t)M * N, cudaMemcpyDeviceToHost);
+    if (ce != cudaSuccess) rc = set_error(B2_ERR_CUDA, "selftest_gemm D2H: %s", cudaGetErrorString(ce));
+  }
+  cudaFree(dA); cudaFree(dB); cudaFree(dC);
+  return rc;
+}
+
 int b2_host_free(void* p) {
   if (p) CK(cudaFreeHost(p));
   return B2_OK;

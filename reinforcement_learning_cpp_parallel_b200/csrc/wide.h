@@ -1,0 +1,79 @@
+// wide.h -- the tensor-core update path for hidden widths that make the PPO update a real dense GEMM
+// (BASELINE.json configs[4]: 2x256 MLPs).  The default 6-64-32-1 nets never come here (ppo_update.cu).
+//
+// Per optimizer step and per net the reference computes (src/ppo_nn.cpp:126-194 evaluate, :263-290 loss,
+// :301-303 backward + Adam):
+//     H1 = tanh(X W1^T + b1)        K = 6      -> FP32 FMA      (k_wide_l1)
+//     H2 = tanh(H1 W2^T + b2)       K = H1     -> tcgen05 GEMM  (k_gemm_x3<EPI_TANH>)
+//     y  = H2 W3^T + b3, loss head, D2 = dz3 (x) W3 .* (1 - H2^2)   (k_wide_head)
+//     D1 = (D2 W2) .* (1 - H1^2)    K = H2     -> tcgen05 GEMM  (k_gemm_x3<EPI_DTANH>)
+//     dW2 = D2^T H1                 K = samples-> tcgen05 GEMM  (k_gemm_x3<EPI_RAW>, split-K partials)
+//     dW1 = D1^T X, db1, db2, dW3, db3         -> FP32 FMA      (k_wide_dw1, k_wide_head)
+// The three GEMMs hold 99 % of the 801,792 flop per sample-epoch.  The 1e-4 gradient gate
+// rules out single-pass BF16/TF32, so every fp32 operand is split into a (hi, mid) bf16 pair and each product
+// is issued as three bf16 MMAs hi*hi + mid*hi + hi*mid with fp32 accumulation in TMEM ("bf16x3", error
+// ~2^-16 relative): 1.5x cheaper on the tensor pipe than 3xTF32 and the same 4 B per element in memory.
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "engine.h"
+
+namespace b2 {
+
+// runtime layout of policy.parameters() for arbitrary hidden widths (same order as common.cuh Net<>)
+struct NetDims {
+  int S, H1, H2;
+  int oW1, ob1, oW2, ob2, oW3, ob3, SIZE, P;
+  __host__ __device__ static NetDims make(int S, int H1, int H2) {
+    NetDims d;
+    d.S = S; d.H1 = H1; d.H2 = H2;
+    d.oW1 = 0; d.ob1 = d.oW1 + H1 * S; d.oW2 = d.ob1 + H1; d.ob2 = d.oW2 + H2 * H1;
+    d.oW3 = d.ob2 + H2; d.ob3 = d.oW3 + H2; d.SIZE = d.ob3 + 1; d.P = 2 * d.SIZE;
+    return d;
+  }
+};
+
+enum { EPI_TANH = 0, EPI_DTANH = 1, EPI_RAW = 2 };
+
+struct GemmArgs {
+  int G, M, N, K;                // per group g < G: C[M][N] = A[M][K] . B[N][K]^T ; K % 64 == 0, N % 16 == 0, N <= 256
+  int m_tiles, splits, kb_per_split, stages;
+  float* out;                    // EPI_TANH / EPI_DTANH: [G][out_rows][N] ; EPI_RAW: [G][splits][M][N]
+  int64_t out_g_stride;          // floats between groups
+  const float* bias;             // EPI_TANH: [G][N]
+  const __nv_bfloat16* hpl;      // EPI_DTANH: activation planes [G*2][h_rows][N] (hi, mid)
+  int64_t h_plane_stride;        // elements between planes
+};
+
+cudaError_t launch_gemm_x3(int epi, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& a, int sm_count,
+                           cudaStream_t st);
+int gemm_x3_stages(int N);
+
+// 3-D bf16 tensor map (K fastest, rows, planes) with a (64 x box_rows x 1) box and the 128-B swizzle.
+// Returns 0 on success; the driver entry point is resolved through the runtime (no -lcuda link dependency).
+int make_operand_map(CUtensorMap* out, const void* base, uint64_t K, uint64_t rows, uint64_t planes,
+                     uint64_t row_stride_elems, uint64_t plane_stride_elems, uint32_t box_rows);
+
+// ---- the whole wide-net learner: buffers, tensor maps and the per-step kernel sequence ----
+struct WideNet;
+int wide_create(WideNet** out, int H1, int H2, int64_t max_chunk, int sm_count);
+void wide_destroy(WideNet* w);
+int64_t wide_chunk_cap(const WideNet* w);
+// gradient of one minibatch [first, first+count) (mapped through idx if set) into a.grads (P grads + 3 loss sums in
+// the tail, same convention as k_reduce); apply_adam fuses the Adam step (single GPU).  *launches += kernels launched.
+int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st, int64_t* launches);
+cudaError_t launch_wide_adam(WideNet* w, const UpdateArgs& a, cudaStream_t st);
+int wide_pstride(int H1, int H2);
+// forward-only helpers (action query / value estimate / bootstrap) for wide nets
+cudaError_t launch_wide_forward(const NetDims& d, const float* net_params, const float* obs, int64_t obs_stride_c,
+                                int64_t obs_stride_k, const int32_t* rows, int64_t n, int final_tanh, float* y,
+                                cudaStream_t st);
+
+// diagnostic: C = A . B^T through the bf16x3 tcgen05 GEMM on device buffers (fp32 in, fp32 out)
+int wide_selftest_gemm(int M, int N, int K, const float* A_dev, const float* B_dev, float* C_dev, int splits,
+                       int sm_count, cudaStream_t st);
+
+}  // namespace b2

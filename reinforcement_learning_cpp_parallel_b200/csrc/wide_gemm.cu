@@ -1,0 +1,303 @@
+// wide_gemm.cu -- k_gemm_x3: persistent, warp-specialised tcgen05 GEMM with bf16x3 operands and fused epilogues.
+//
+//   C[g][M][N] = A[g][M][K] . B[g][N][K]^T        (both operands K-major, fp32 values stored as (hi, mid) bf16 planes)
+//
+// One CTA per SM, 192 threads:
+//   warp 0  : TMA producer   -- one lane streams 64-wide K blocks of A_hi, A_mid (128 rows) and B_hi, B_mid (N rows)
+//                               into a ring of shared-memory stages (cp.async.bulk.tensor, 128-B swizzle, mbarrier tx)
+//   warp 1  : MMA issuer     -- one lane issues 4 (K steps of 16) x 3 (hi*hi, mid*hi, hi*mid) tcgen05.mma per stage,
+//                               M = 128, N = whole width (<= 256), fp32 accumulator in TMEM; tcgen05.commit frees the
+//                               stage and, after the last K block, publishes the accumulator
+//   warps 2-5: epilogue      -- thread = accumulator row; tcgen05.ld 32 columns at a time, bias/tanh or tanh' or raw
+//                               store, 128 B contiguous per thread
+// TMEM holds two accumulators (2 x 256 columns) so the epilogue of tile i overlaps the MMAs of tile i+1.
+// Tiles are dealt statically: item = ((g * m_tiles) + mt) * splits + split, strided by gridDim.x.
+// Roofline: tensor (bf16 dense); algorithmic flop = 2 M N K per group, issued flop = 3x that.
+#include "tc_ptx.cuh"
+#include "wide.h"
+#include "mlp.cuh"
+
+namespace b2 {
+
+namespace {
+
+constexpr int BM = 128, BK = 64;
+constexpr int GEMM_THREADS = 192;
+constexpr int A_PLANE_BYTES = BM * BK * 2;          // 16 KB
+constexpr int SMEM_LIMIT = 227 * 1024;
+constexpr int BAR_BYTES = 256;
+
+__host__ __device__ constexpr int stage_bytes(int N) { return 2 * A_PLANE_BYTES + 2 * N * BK * 2; }
+
+template <int EPI>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = tc::smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);   // 1024-B alignment for the 128-B swizzle atoms
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int N = a.N, stages = a.stages;
+  const int SB = stage_bytes(N);
+  const int B_PLANE_BYTES = N * BK * 2;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)stages * SB);
+  uint64_t* empty = full + 8;
+  uint64_t* tfull = empty + 8;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int kb_total = a.K / BK;
+  const int n_items = a.G * a.m_tiles * a.splits;
+
+  if (warp == 0 && lane == 0) {
+    tc::tma_prefetch_desc(&tmA);
+    tc::tma_prefetch_desc(&tmB);
+    for (int s = 0; s < stages; s++) { tc::mbar_init(&full[s], 1); tc::mbar_init(&empty[s], 1); }
+    for (int b = 0; b < 2; b++) { tc::mbar_init(&tfull[b], 1); tc::mbar_init(&tempty[b], 128); }
+    tc::fence_barrier_init();
+  }
+  if (warp == 1) tc::tmem_alloc(tmem_slot, 512);
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+        const int sp = item % a.splits;
+        const int mt = (item / a.splits) % a.m_tiles;
+        const int g = item / (a.splits * a.m_tiles);
+        const int kb0 = sp * a.kb_per_split;
+        const int kb1 = min(kb0 + a.kb_per_split, kb_total);
+        for (int kb = kb0; kb < kb1; kb++) {
+          tc::mbar_wait(&empty[stage], phase ^ 1);
+          uint8_t* s = smem + (size_t)stage * SB;
+          tc::mbar_arrive_expect_tx(&full[stage], (uint32_t)SB);
+          tc::tma_load_3d(s, &tmA, &full[stage], kb * BK, mt * BM, g * 2 + 0);
+          tc::tma_load_3d(s + A_PLANE_BYTES, &tmA, &full[stage], kb * BK, mt * BM, g * 2 + 1);
+          tc::tma_load_3d(s + 2 * A_PLANE_BYTES, &tmB, &full[stage], kb * BK, 0, g * 2 + 0);
+          tc::tma_load_3d(s + 2 * A_PLANE_BYTES + B_PLANE_BYTES, &tmB, &full[stage], kb * BK, 0, g * 2 + 1);
+          if (++stage == stages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = tc::idesc_bf16_f32(BM, N);
+      int stage = 0; uint32_t phase = 0;
+      int it = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x, it++) {
+        const int sp = item % a.splits;
+        const int kb0 = sp * a.kb_per_split;
+        const int kb1 = min(kb0 + a.kb_per_split, kb_total);
+        const int buf = it & 1;
+        const uint32_t bphase = (uint32_t)(it >> 1) & 1u;
+        tc::mbar_wait(&tempty[buf], bphase ^ 1);       // epilogue has drained this accumulator
+        tc::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)buf * 256u;
+        uint32_t acc = 0;
+        for (int kb = kb0; kb < kb1; kb++) {
+          tc::mbar_wait(&full[stage], phase);
+          tc::tc_fence_after();
+          const uint32_t s = tc::smem_u32(smem + (size_t)stage * SB);
+          const uint64_t dAh = tc::smem_desc_sw128(s), dAm = tc::smem_desc_sw128(s + A_PLANE_BYTES);
+          const uint64_t dBh = tc::smem_desc_sw128(s + 2 * A_PLANE_BYTES);
+          const uint64_t dBm = tc::smem_desc_sw128(s + 2 * A_PLANE_BYTES + B_PLANE_BYTES);
+#pragma unroll
+          for (int k = 0; k < BK / 16; k++) {
+            const uint64_t off = (uint64_t)((k * 32) >> 4);    // 16 bf16 = 32 B along K inside the swizzle atom
+            tc::umma_bf16(d_tmem, dAm + off, dBh + off, idesc, acc);   // small terms first
+            tc::umma_bf16(d_tmem, dAh + off, dBm + off, idesc, 1u);
+            tc::umma_bf16(d_tmem, dAh + off, dBh + off, idesc, 1u);
+            acc = 1u;
+          }
+          tc::umma_commit(&empty[stage]);               // stage reusable once these MMAs have read it
+          if (++stage == stages) { stage = 0; phase ^= 1; }
+        }
+        tc::umma_commit(&tfull[buf]);                   // accumulator complete
+      }
+    }
+    __syncwarp();
+  } else {
+    const int q = warp & 3;                             // TMEM lane quarter this warp may read
+    const int row_in_tile = q * 32 + lane;
+    int it = 0;
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x, it++) {
+      const int sp = item % a.splits;
+      const int mt = (item / a.splits) % a.m_tiles;
+      const int g = item / (a.splits * a.m_tiles);
+      const int buf = it & 1;
+      const uint32_t bphase = (uint32_t)(it >> 1) & 1u;
+      tc::mbar_wait(&tfull[buf], bphase);
+      tc::tc_fence_after();
+      const int row = mt * BM + row_in_tile;
+      const bool valid = row < a.M;
+      const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * 256u;
+      float* orow;
+      if (EPI == EPI_RAW) orow = a.out + (int64_t)g * a.out_g_stride + ((int64_t)sp * a.M + row) * N;
+      else orow = a.out + (int64_t)g * a.out_g_stride + (int64_t)row * N;
+      for (int c = 0; c < N; c += 32) {
+        float v[32];
+        tc::tmem_ld32(t0 + (uint32_t)c, v);
+        tc::tmem_ld_wait();
+        if (EPI == EPI_TANH) {
+          const float4* b4 = reinterpret_cast<const float4*>(a.bias + g * N + c);
+#pragma unroll
+          for (int i = 0; i < 8; i++) {
+            const float4 b = __ldg(b4 + i);
+            v[4 * i + 0] = act_tanh(v[4 * i + 0] + b.x); v[4 * i + 1] = act_tanh(v[4 * i + 1] + b.y);
+            v[4 * i + 2] = act_tanh(v[4 * i + 2] + b.z); v[4 * i + 3] = act_tanh(v[4 * i + 3] + b.w);
+          }
+        } else if (EPI == EPI_DTANH) {
+          if (valid) {
+            const __nv_bfloat16* hh = a.hpl + (int64_t)(g * 2) * a.h_plane_stride + (int64_t)row * N + c;
+            const __nv_bfloat16* hm = hh + a.h_plane_stride;
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+              const uint4 ph = __ldg(reinterpret_cast<const uint4*>(hh) + i);
+              const uint4 pm = __ldg(reinterpret_cast<const uint4*>(hm) + i);
+              const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&ph);
+              const __nv_bfloat162* m2 = reinterpret_cast<const __nv_bfloat162*>(&pm);
+#pragma unroll
+              for (int j = 0; j < 4; j++) {
+                const float2 fh = __bfloat1622float2(h2[j]), fm = __bfloat1622float2(m2[j]);
+                const float h0 = fh.x + fm.x, h1 = fh.y + fm.y;
+                v[8 * i + 2 * j] *= (1.0f - h0 * h0);
+                v[8 * i + 2 * j + 1] *= (1.0f - h1 * h1);
+              }
+            }
+          }
+        }
+        if (valid) {
+          float4* o4 = reinterpret_cast<float4*>(orow + c);
+#pragma unroll
+          for (int i = 0; i < 8; i++) o4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        }
+      }
+      tc::tc_fence_before();
+      tc::mbar_arrive(&tempty[buf]);
+    }
+  }
+
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc::tc_fence_after();
+    tc::tmem_dealloc(tmem_base, 512);
+  }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn g_encode = nullptr;
+
+}  // namespace
+
+int gemm_x3_stages(int N) {
+  int s = (SMEM_LIMIT - 1024 - BAR_BYTES) / stage_bytes(N);
+  if (s > 6) s = 6;
+  return s;
+}
+
+int make_operand_map(CUtensorMap* out, const void* base, uint64_t K, uint64_t rows, uint64_t planes,
+                     uint64_t row_stride_elems, uint64_t plane_stride_elems, uint32_t box_rows) {
+  if (!g_encode) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn)
+      return set_error(B2_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+    g_encode = reinterpret_cast<EncodeTiledFn>(fn);
+  }
+  cuuint64_t dims[3] = {K, rows, planes};
+  cuuint64_t strides[2] = {row_stride_elems * 2, plane_stride_elems * 2};  // bytes, dims 1 and 2
+  cuuint32_t box[3] = {(cuuint32_t)BK, box_rows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_error(B2_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d): K=%llu rows=%llu planes=%llu box_rows=%u",
+                                          (int)r, (unsigned long long)K, (unsigned long long)rows, (unsigned long long)planes, box_rows);
+  return B2_OK;
+}
+
+cudaError_t launch_gemm_x3(int epi, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& a, int sm_count,
+                           cudaStream_t st) {
+  const int smem = a.stages * stage_bytes(a.N) + BAR_BYTES + 1024;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e;
+    if ((e = cudaFuncSetAttribute(k_gemm_x3<EPI_TANH>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_gemm_x3<EPI_DTANH>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_gemm_x3<EPI_RAW>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)) != cudaSuccess) return e;
+    attr_set = true;
+  }
+  const int n_items = a.G * a.m_tiles * a.splits;
+  int grid = n_items < sm_count ? n_items : sm_count;
+  if (grid < 1) return cudaSuccess;
+  // 1 CTA per SM is assumed by the 512-column TMEM allocation: always ask for more than half of the shared memory
+  const int smem_req = smem > 120 * 1024 ? smem : 120 * 1024;
+  if (epi == EPI_TANH) k_gemm_x3<EPI_TANH><<<grid, GEMM_THREADS, smem_req, st>>>(tmA, tmB, a);
+  else if (epi == EPI_DTANH) k_gemm_x3<EPI_DTANH><<<grid, GEMM_THREADS, smem_req, st>>>(tmA, tmB, a);
+  else k_gemm_x3<EPI_RAW><<<grid, GEMM_THREADS, smem_req, st>>>(tmA, tmB, a);
+  return cudaGetLastError();
+}
+
+// ---- diagnostic GEMM: fp32 device operands -> planes -> k_gemm_x3<EPI_RAW> ----
+__global__ void k_split_planes(const float* __restrict__ src, __nv_bfloat16* __restrict__ hi,
+                               __nv_bfloat16* __restrict__ mid, int64_t rows, int64_t K, int64_t Kp) {
+  const int64_t n = rows * Kp;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / Kp, k = i % Kp;
+    const float x = k < K ? src[r * K + k] : 0.0f;
+    tc::split_bf16(x, hi[i], mid[i]);
+  }
+}
+
+__global__ void k_sum_splits(const float* __restrict__ part, float* __restrict__ out, int64_t n, int splits) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float s = 0.f;
+    for (int p = 0; p < splits; p++) s += part[(int64_t)p * n + i];
+    out[i] = s;
+  }
+}
+
+int wide_selftest_gemm(int M, int N, int K, const float* A_dev, const float* B_dev, float* C_dev, int splits,
+                       int sm_count, cudaStream_t st) {
+  if (M < 1 || N < 32 || N > 256 || (N % 32) || K < 1) return set_error(B2_ERR_INVALID, "selftest gemm: need N %% 32 == 0, 32 <= N <= 256");
+  const int64_t Kp = ((int64_t)K + BK - 1) / BK * BK;
+  __nv_bfloat16 *pa = nullptr, *pb = nullptr;
+  float* part = nullptr;
+  const int kb_total = (int)(Kp / BK);
+  if (splits < 1) splits = 1;
+  if (splits > kb_total) splits = kb_total;
+  const int kbps = (kb_total + splits - 1) / splits;
+  splits = (kb_total + kbps - 1) / kbps;
+  B2_CUDA_CHECK(cudaMalloc(&pa, sizeof(__nv_bfloat16) * 2 * M * Kp));
+  B2_CUDA_CHECK(cudaMalloc(&pb, sizeof(__nv_bfloat16) * 2 * N * Kp));
+  B2_CUDA_CHECK(cudaMalloc(&part, sizeof(float) * (size_t)splits * M * N));
+  k_split_planes<<<256, 256, 0, st>>>(A_dev, pa, pa + (int64_t)M * Kp, M, K, Kp);
+  k_split_planes<<<256, 256, 0, st>>>(B_dev, pb, pb + (int64_t)N * Kp, N, K, Kp);
+  CUtensorMap tmA, tmB;
+  int rc = make_operand_map(&tmA, pa, Kp, M, 2, Kp, (uint64_t)M * Kp, BM);
+  if (!rc) rc = make_operand_map(&tmB, pb, Kp, N, 2, Kp, (uint64_t)N * Kp, (uint32_t)N);
+  if (!rc) {
+    GemmArgs g{};
+    g.G = 1; g.M = M; g.N = N; g.K = (int)Kp;
+    g.m_tiles = (M + BM - 1) / BM; g.splits = splits; g.kb_per_split = kbps; g.stages = gemm_x3_stages(N);
+    g.out = part; g.out_g_stride = 0;
+    cudaError_t e = launch_gemm_x3(EPI_RAW, tmA, tmB, g, sm_count, st);
+    if (e != cudaSuccess) rc = set_error(B2_ERR_CUDA, "gemm_x3: %s", cudaGetErrorString(e));
+    else {
+      k_sum_splits<<<256, 256, 0, st>>>(part, C_dev, (int64_t)M * N, splits);
+      e = cudaStreamSynchronize(st);
+      if (e != cudaSuccess) rc = set_error(B2_ERR_CUDA, "gemm_x3 sync: %s", cudaGetErrorString(e));
+    }
+  }
+  cudaFree(pa); cudaFree(pb); cudaFree(part);
+  return rc;
+}
+
+}  // namespace b2
