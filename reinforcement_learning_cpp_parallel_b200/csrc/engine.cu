@@ -107,6 +107,9 @@ struct b2_engine {
   // comm
   ncclComm_t comm = nullptr;
   int rank = 0, world = 1;
+  // wide hidden layers (tensor-core update path, wide.h); null for the reference's 64/32 nets
+  WideNet* wide = nullptr;
+  NetDims dims;
   HyperDev hp;
 };
 
@@ -181,6 +184,19 @@ int check_status(b2_engine* E, const char* where) {
   return B2_OK;
 }
 
+// K2 on whatever E->tr holds: bootstrap values at the flagged records, then the reverse scan.
+int run_returns(b2_engine* E) {
+  int nl = 0;
+  if (E->wide) {
+    int rc = wide_bootstrap(E->wide, E->params, E->tr, E->stream, &E->launches);
+    if (rc) return rc;
+  }
+  cudaError_t ce = launch_returns(E->params, E->tr, E->hp, E->stream, &nl, E->wide != nullptr);
+  if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "returns: %s", cudaGetErrorString(ce));
+  E->launches += nl;
+  return B2_OK;
+}
+
 // K2 + K optimizer steps on whatever E->tr currently holds.
 int run_update(b2_engine* E, b2_update_stats* stats) {
   Traj& t = E->tr;
@@ -188,10 +204,9 @@ int run_update(b2_engine* E, b2_update_stats* stats) {
   if (B <= 0) return set_error(B2_ERR_STATE, "update: empty trajectory");
   const int K = E->cfg.k_epochs, M = std::max(1, E->cfg.n_minibatches);
   const int steps = K * M;
-  int nl = 0;
-  cudaError_t ce = launch_returns(E->params, t, E->hp, E->stream, &nl);  // once, at entry (:207-236)
-  if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "returns: %s", cudaGetErrorString(ce));
-  E->launches += nl;
+  cudaError_t ce;
+  int rc0 = run_returns(E);  // once, at entry (:207-236)
+  if (rc0) return rc0;
   if (steps > E->loss_log_cap) {
     cudaFree(E->loss_log);
     E->loss_log = nullptr;
@@ -200,7 +215,7 @@ int run_update(b2_engine* E, b2_update_stats* stats) {
   }
   CK(cudaMemsetAsync(E->loss_log, 0, sizeof(double) * 4 * steps, E->stream));
   const int64_t per = B / M;
-  int rows_needed = update_grid_for(per + (B % M), E->sm_count);
+  int rows_needed = E->wide ? 0 : update_grid_for(per + (B % M), E->sm_count);
   if (rows_needed > E->partial_rows) {
     cudaFree(E->partials);
     E->partials = nullptr;
@@ -219,6 +234,17 @@ int run_update(b2_engine* E, b2_update_stats* stats) {
       a.denom = a.count * E->world;       // every rank holds an equal shard of the global minibatch
       a.grid = update_grid_for(a.count, E->sm_count);
       a.step_slot = slot;
+      if (E->wide) {
+        int rc = wide_step(E->wide, a, E->world == 1, E->stream, &E->launches);
+        if (rc) return rc;
+        if (E->world > 1) {
+          int ne = g_nccl.AllReduce(E->grads, E->grads, (size_t)E->pstride, NCCL_FLOAT32, NCCL_SUM, E->comm, E->stream);
+          if (ne != 0) return set_error(B2_ERR_COMM, "ncclAllReduce: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(ne) : "?");
+          if ((ce = launch_wide_adam(E->wide, a, E->stream)) != cudaSuccess) return set_error(B2_ERR_CUDA, "adam: %s", cudaGetErrorString(ce));
+          E->launches += 2;
+        }
+        continue;
+      }
       if ((ce = launch_ppo_grad(a, E->stream)) != cudaSuccess) return set_error(B2_ERR_CUDA, "ppo_grad: %s", cudaGetErrorString(ce));
       if (E->world == 1) {
         if ((ce = launch_reduce(a, true, E->stream)) != cudaSuccess) return set_error(B2_ERR_CUDA, "reduce: %s", cudaGetErrorString(ce));
@@ -289,7 +315,9 @@ int b2_create(const b2_config* cfg, b2_handle* out) {
   *out = nullptr;
   if (cfg->control_vars != 1) return set_error(B2_ERR_INVALID, "control_vars must be 1 (src/ppo_nn.cpp:107)");
   if (cfg->obs_vars != 6) return set_error(B2_ERR_INVALID, "obs_vars must be 6 (include/cart_pole.h:120-131)");
-  if (cfg->hidden1 != 64 || cfg->hidden2 != 32) return set_error(B2_ERR_INVALID, "hidden widths %dx%d not built (64x32 only)", cfg->hidden1, cfg->hidden2);
+  const bool is_default_net = cfg->hidden1 == NetDefault::H1 && cfg->hidden2 == NetDefault::H2;
+  if (!is_default_net && (cfg->hidden1 < 64 || cfg->hidden2 < 64 || cfg->hidden1 > 256 || cfg->hidden2 > 256 || cfg->hidden1 % 64 || cfg->hidden2 % 64))
+    return set_error(B2_ERR_INVALID, "hidden widths %dx%d not built: 64x32 (reference) or both in {64,128,192,256}", cfg->hidden1, cfg->hidden2);
   if (cfg->n_envs < 1 || cfg->horizon < 1 || cfg->n_timestep < 1) return set_error(B2_ERR_INVALID, "n_envs, horizon, n_timestep must be >= 1");
   if (cfg->precision != B2_PREC_F64 && cfg->precision != B2_PREC_F32) return set_error(B2_ERR_INVALID, "unknown precision %d", cfg->precision);
   if (cfg->k_epochs < 1 || cfg->n_minibatches < 1) return set_error(B2_ERR_INVALID, "k_epochs and n_minibatches must be >= 1");
@@ -301,8 +329,9 @@ int b2_create(const b2_config* cfg, b2_handle* out) {
   b2_engine* E = new (std::nothrow) b2_engine();
   if (!E) return set_error(B2_ERR_INVALID, "out of host memory");
   E->cfg = *cfg;
-  E->P = NetDefault::P;
-  E->pstride = update_partial_stride();
+  E->dims = NetDims::make(OBS, cfg->hidden1, cfg->hidden2);
+  E->P = E->dims.P;
+  E->pstride = is_default_net ? update_partial_stride() : wide_pstride(cfg->hidden1, cfg->hidden2);
   cudaDeviceProp prop;
   CK(cudaGetDeviceProperties(&prop, cfg->device));
   E->sm_count = prop.multiProcessorCount;
@@ -337,6 +366,11 @@ int b2_create(const b2_config* cfg, b2_handle* out) {
   CK(cudaMemset(E->ep_ret, 0, sizeof(float) * NE));
   int rc = ensure_traj(E, NE * cfg->horizon);
   if (rc) { b2_destroy(E); return rc; }
+  if (!is_default_net) {
+    const int64_t B0 = NE * cfg->horizon;
+    rc = wide_create(&E->wide, cfg->hidden1, cfg->hidden2, (B0 + cfg->n_minibatches - 1) / cfg->n_minibatches + cfg->n_minibatches, E->sm_count);
+    if (rc) { b2_destroy(E); return rc; }
+  }
   *out = E;
   rc = b2_init_params(E, cfg->seed);
   if (rc) { b2_destroy(E); *out = nullptr; return rc; }
@@ -348,6 +382,7 @@ int b2_destroy(b2_handle E) {
   cudaSetDevice(E->cfg.device);
   if (E->stream) cudaStreamSynchronize(E->stream);
   if (E->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(E->comm);
+  wide_destroy(E->wide);
   Traj& t = E->tr;
   void* ptrs[] = {E->params, E->adam_m, E->adam_v, E->grads, E->partials, E->adam_step, E->loss_log, E->state,
                   E->ep_step, E->ep_count, E->ep_ret, E->ep_log, t.obs, t.action, t.logp, t.mu, t.reward, t.ret,
@@ -382,7 +417,7 @@ int b2_init_params(b2_handle E, uint64_t seed) {
   // torch::nn::Linear::reset_parameters: kaiming_uniform(a=sqrt(5)) on W and U(+-1/sqrt(fan_in)) on b,
   // both = U(-1/sqrt(fan_in), 1/sqrt(fan_in)).  Drawn host-side from Philox (init is not a hot path;
   // parity runs import the reference's weights through b2_set_params instead).
-  using N = NetDefault;
+  const NetDims& N = E->dims;
   std::vector<float> p((size_t)E->P);
   uint64_t ctr = 0;
   auto fill = [&](int off, int n, int fan_in) {
@@ -395,10 +430,10 @@ int b2_init_params(b2_handle E, uint64_t seed) {
     }
   };
   for (int net = 0; net < 2; net++) {
-    int o = net * N::SIZE;
-    fill(o + N::oW1, N::H1 * N::S, N::S); fill(o + N::ob1, N::H1, N::S);
-    fill(o + N::oW2, N::H2 * N::H1, N::H1); fill(o + N::ob2, N::H2, N::H1);
-    fill(o + N::oW3, N::H2, N::H2); fill(o + N::ob3, 1, N::H2);
+    int o = net * N.SIZE;
+    fill(o + N.oW1, N.H1 * N.S, N.S); fill(o + N.ob1, N.H1, N.S);
+    fill(o + N.oW2, N.H2 * N.H1, N.H1); fill(o + N.ob2, N.H2, N.H1);
+    fill(o + N.oW3, N.H2, N.H2); fill(o + N.ob3, 1, N.H2);
   }
   return b2_set_params(E, p.data(), E->P);
 }
@@ -496,8 +531,15 @@ int b2_act(b2_handle E, const float* obs, int64_t n, const float* eps, float* ac
   float* d_mu = d_lp + n;
   CK(cudaMemcpyAsync(d_obs, obs, sizeof(float) * OBS * n, cudaMemcpyHostToDevice, E->stream));
   if (eps) CK(cudaMemcpyAsync(d_eps, eps, sizeof(float) * n, cudaMemcpyHostToDevice, E->stream));
-  cudaError_t ce = launch_act(E->params, d_obs, eps ? d_eps : nullptr, n, E->cfg.seed, E->act_calls++, d_act, d_lp,
-                              d_mu, E->hp, E->status, E->stream);
+  cudaError_t ce;
+  if (E->wide) {
+    ce = launch_wide_forward(E->dims, E->params, d_obs, 1, OBS, nullptr, n, 1, d_mu, E->stream);
+    if (ce == cudaSuccess)
+      ce = launch_wide_act_finish(d_mu, eps ? d_eps : nullptr, n, E->cfg.seed, E->act_calls++, d_act, d_lp, E->hp, E->status, E->stream);
+    E->launches += 1;
+  } else
+    ce = launch_act(E->params, d_obs, eps ? d_eps : nullptr, n, E->cfg.seed, E->act_calls++, d_act, d_lp,
+                    d_mu, E->hp, E->status, E->stream);
   if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "act: %s", cudaGetErrorString(ce));
   E->launches += 1;
   CK(cudaMemcpyAsync(action, d_act, sizeof(float) * n, cudaMemcpyDeviceToHost, E->stream));
@@ -516,7 +558,8 @@ int b2_value(b2_handle E, const float* obs, int64_t n, float* value) {
   float* d_obs = E->stage;
   float* d_v = d_obs + n * OBS;
   CK(cudaMemcpyAsync(d_obs, obs, sizeof(float) * OBS * n, cudaMemcpyHostToDevice, E->stream));
-  cudaError_t ce = launch_value(E->params, d_obs, n, d_v, E->stream);
+  cudaError_t ce = E->wide ? launch_wide_forward(E->dims, E->params + E->dims.SIZE, d_obs, 1, OBS, nullptr, n, 0, d_v, E->stream)
+                           : launch_value(E->params, d_obs, n, d_v, E->stream);
   if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "value: %s", cudaGetErrorString(ce));
   E->launches += 1;
   CK(cudaMemcpyAsync(value, d_v, sizeof(float) * n, cudaMemcpyDeviceToHost, E->stream));
@@ -539,10 +582,8 @@ int b2_returns(b2_handle E, const b2_batch* batch, float* returns) {
   if (!returns) return set_error(B2_ERR_INVALID, "b2_returns: null output");
   int rc = upload_batch(E, batch);
   if (rc) return rc;
-  int nl = 0;
-  cudaError_t ce = launch_returns(E->params, E->tr, E->hp, E->stream, &nl);
-  if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "returns: %s", cudaGetErrorString(ce));
-  E->launches += nl;
+  rc = run_returns(E);
+  if (rc) return rc;
   CK(cudaMemcpyAsync(returns, E->tr.ret, sizeof(float) * batch->n_envs * batch->horizon, cudaMemcpyDeviceToHost, E->stream));
   CK(cudaStreamSynchronize(E->stream));
   return B2_OK;
@@ -656,6 +697,7 @@ static int rollout_window(b2_engine* E, int T, int t_begin, int t_end, bool forc
 }
 
 static int rollout_prepare(b2_engine* E, int T, const float* forced_action) {
+  if (E->wide) return set_error(B2_ERR_INVALID, "the fused rollout kernel is built for the reference's 64x32 nets only; wide nets (%dx%d) support act/value/returns/update", E->cfg.hidden1, E->cfg.hidden2);
   CK(cudaSetDevice(E->cfg.device));
   if (T < 1 || T > E->cfg.horizon) return set_error(B2_ERR_INVALID, "rollout: T=%d outside [1, horizon=%d]", T, E->cfg.horizon);
   const int64_t NE = E->cfg.n_envs;

@@ -86,7 +86,8 @@ cudaError_t launch_act(const float* params, const float* obs_aos, const float* e
 cudaError_t launch_value(const float* params, const float* obs_aos, int64_t n, float* v, cudaStream_t st);
 cudaError_t launch_aos_to_soa(const float* obs_aos, float* obs_soa, int64_t cap, int64_t n, cudaStream_t st);
 cudaError_t launch_soa_to_aos(const float* obs_soa, float* obs_aos, int64_t cap, int64_t n, cudaStream_t st);
-cudaError_t launch_returns(const float* params, const Traj& tr, const HyperDev& hp, cudaStream_t st, int* n_launches);
+cudaError_t launch_returns(const float* params, const Traj& tr, const HyperDev& hp, cudaStream_t st, int* n_launches,
+                           bool skip_bootstrap = false);
 int update_grid_for(int64_t count, int sm_count);
 int update_partial_stride();
 cudaError_t launch_ppo_grad(const UpdateArgs& a, cudaStream_t st);

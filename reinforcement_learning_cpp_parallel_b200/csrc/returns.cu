@@ -66,17 +66,21 @@ __global__ void __launch_bounds__(128) k_returns(Traj tr, float gamma) {
   }
 }
 
-cudaError_t launch_returns(const float* params, const Traj& tr, const HyperDev& hp, cudaStream_t st, int* n_launches) {
+cudaError_t launch_returns(const float* params, const Traj& tr, const HyperDev& hp, cudaStream_t st, int* n_launches,
+                           bool skip_bootstrap) {
   using N = NetDefault;
   const int64_t B = tr.n_envs * tr.horizon;
   if (B == 0) return cudaSuccess;
   int64_t g = (B + 127) / 128;
   if (g > 148 * 16) g = 148 * 16;
-  k_bootstrap<N><<<(int)g, 128, mlp_smem_bytes<N>(128), st>>>(params, tr, B);
-  cudaError_t e = cudaGetLastError();
-  if (e != cudaSuccess) return e;
+  cudaError_t e = cudaSuccess;
+  if (!skip_bootstrap) {   // wide nets bootstrap through wide_bootstrap (wide_update.cu)
+    k_bootstrap<N><<<(int)g, 128, mlp_smem_bytes<N>(128), st>>>(params, tr, B);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    if (n_launches) *n_launches += 1;
+  }
   k_returns<<<(int)((tr.n_envs + 127) / 128), 128, 0, st>>>(tr, hp.gamma);
-  if (n_launches) *n_launches += 2;
+  if (n_launches) *n_launches += 1;
   return cudaGetLastError();
 }
 

@@ -66,11 +66,15 @@ int64_t wide_chunk_cap(const WideNet* w);
 // the tail, same convention as k_reduce); apply_adam fuses the Adam step (single GPU).  *launches += kernels launched.
 int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st, int64_t* launches);
 cudaError_t launch_wide_adam(WideNet* w, const UpdateArgs& a, cudaStream_t st);
+int wide_bootstrap(WideNet* w, const float* params, const Traj& tr, cudaStream_t st, int64_t* launches);
 int wide_pstride(int H1, int H2);
 // forward-only helpers (action query / value estimate / bootstrap) for wide nets
 cudaError_t launch_wide_forward(const NetDims& d, const float* net_params, const float* obs, int64_t obs_stride_c,
                                 int64_t obs_stride_k, const int32_t* rows, int64_t n, int final_tanh, float* y,
                                 cudaStream_t st);
+
+cudaError_t launch_wide_act_finish(const float* mu, const float* eps, int64_t n, uint64_t seed, uint64_t call, float* action,
+                                   float* logp, const HyperDev& hp, int* status, cudaStream_t st);
 
 // diagnostic: C = A . B^T through the bf16x3 tcgen05 GEMM on device buffers (fp32 in, fp32 out)
 int wide_selftest_gemm(int M, int N, int K, const float* A_dev, const float* B_dev, float* C_dev, int splits,

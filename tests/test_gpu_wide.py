@@ -29,3 +29,141 @@ def test_gemm_bf16x3_matches_fp64(eng, M, N, K, splits):
     rel = np.linalg.norm(C - ref) / np.linalg.norm(ref)
     print(f"gemm {M}x{N}x{K} splits {splits}: max err {err:.2e}, rel fro {rel:.2e}")
     assert rel < 2e-5, (rel, err)
+
+
+# ------------------------------------------------------------------------------------------------------------
+# wide nets through the C ABI: action query, value estimate, returns bootstrap, update (BASELINE configs[4])
+# ------------------------------------------------------------------------------------------------------------
+import ctypes as C
+
+WIDE = [(128, 64), (256, 256)]
+
+
+def wide_engine(H1, H2, n=256, **kw):
+    import reinforcement_learning_cpp_parallel_b200 as pkg
+    from reinforcement_learning_cpp_parallel_b200 import capi
+    return pkg.Engine(capi.default_config(n_envs=n, horizon=1, hidden1=H1, hidden2=H2, **kw))
+
+
+def wide_case(H1, H2):
+    tag = f"wide{H1}x{H2}"
+    g = lambda n: H.gold(f"{tag}_{n}")
+    return dict(dims=H.Dims(6, H1, H2, 1), params=g("params.f32"), obs=g("obs.f32").reshape(-1, 6), action=g("action.f32"),
+                oldlp=g("oldlogp.f32"), R=g("R.f32"), mu=g("mu.f32"), V=g("V.f32"), grads=g("grads.f32"), loss=g("loss.f64"))
+
+
+def synth_batch(dims, B, seed, params=None):
+    """random weights + a batch with ratios around 1 (some clipped), episodes of 50 steps ending in TIMEUP"""
+    rng = np.random.default_rng(seed)
+    L = H.oracle()
+    P = L.orc_n_params(C.byref(dims))
+    if params is None:
+        params = np.zeros(P, np.float32)
+        for name, sl in H.param_slices(dims):
+            fan = {"W1": 6, "b1": 6, "W2": dims.H1, "b2": dims.H1, "W3": dims.H2, "b3": dims.H2}[name.split(".")[1]]
+            params[sl] = rng.uniform(-1, 1, sl.stop - sl.start).astype(np.float32) / np.sqrt(fan)
+    th = 0.3 * rng.standard_normal(B)
+    obs = np.stack([rng.standard_normal(B), rng.standard_normal(B), rng.standard_normal(B), th, np.cos(th), np.sin(th)],
+                   axis=1).astype(np.float32)
+    mu, act, lp = (np.zeros(B, np.float32) for _ in range(3))
+    eps = rng.standard_normal(B).astype(np.float32)
+    L.orc_act(C.byref(dims), params, obs, B, H.ptr(eps), H.SIGMA, mu, act, lp)
+    oldlp = (lp + 0.1 * rng.standard_normal(B)).astype(np.float32)
+    reward = (rng.random(B) < 0.9).astype(np.float32)
+    flags = np.zeros(B, np.uint8)
+    flags[49::50] = 2
+    flags[-1] = 2
+    return params, obs, act, oldlp, reward, flags
+
+
+@pytest.mark.parametrize("H1,H2", WIDE)
+def test_wide_act_value_match_golden(H1, H2):
+    c = wide_case(H1, H2)
+    with wide_engine(H1, H2) as E:
+        assert E.P == c["params"].size
+        E.set_params(c["params"])
+        v = E.value(c["obs"])
+        assert np.abs(v - c["V"]).max() < 2e-6 * max(1.0, np.abs(c["V"]).max())
+        eps = np.linspace(-2, 2, c["R"].size).astype(np.float32)
+        a, lp, mu = E.act(c["obs"], eps)
+        assert np.abs(mu - c["mu"]).max() < 1e-6
+        mo, ao, lo = (np.zeros_like(a) for _ in range(3))
+        H.oracle().orc_act(C.byref(c["dims"]), c["params"], c["obs"], a.size, H.ptr(eps), H.SIGMA, mo, ao, lo)
+        assert np.abs(a - ao).max() < 1e-6 and np.abs(lp - lo).max() < 2e-5
+
+
+@pytest.mark.parametrize("H1,H2", WIDE)
+def test_wide_gradient_matches_torch_golden(H1, H2):
+    """one epoch on the torch-minted batch: loss terms and all 12 gradient tensors within 1e-4 (north_star gate)"""
+    c = wide_case(H1, H2)
+    B = c["R"].size
+    with wide_engine(H1, H2, k_epochs=1) as E:
+        E.set_params(c["params"])
+        # returns fed directly: every record terminal => R_k = r_k (src/ppo_nn.cpp:229-231)
+        st = E.update(c["obs"], c["action"], c["oldlp"], c["R"], np.ones(B, np.uint8))
+        g = E.get_grads()
+        gl = c["loss"]
+        assert abs(st.loss1 - gl[0]) < 1e-4 * abs(gl[0]) + 1e-6 and abs(st.loss2 - gl[1]) < 1e-4 * abs(gl[1])
+        assert abs(st.loss - gl[3]) < 1e-4 * abs(gl[3]) and abs(st.clip_frac - gl[4]) < 1e-6
+        worst = max((H.relerr(g[sl], c["grads"][sl]), name) for name, sl in H.param_slices(c["dims"]))
+        print("wide grad worst tensor:", worst)
+        assert worst[0] < 1e-4, worst
+        assert st.adam_step == 1
+
+
+@pytest.mark.parametrize("H1,H2,B,K", [(256, 256, 1000, 4), (128, 64, 333, 3), (192, 128, 2048, 2)])
+def test_wide_update_matches_oracle(H1, H2, B, K):
+    """K full-batch epochs incl. returns with TIMEUP bootstraps, ragged B: weights, Adam state, per-epoch losses"""
+    dims = H.Dims(6, H1, H2, 1)
+    params, obs, act, oldlp, reward, flags = synth_batch(dims, B, 5 + B)
+    z = np.zeros_like(params)
+    po, mo, vo, so, losses, go, Ro = H.oracle_update(params, z, z, 0, obs, act, oldlp, reward, flags, K, dims=dims)
+    with wide_engine(H1, H2, k_epochs=K) as E:
+        E.set_params(params)
+        R = E.returns(obs, reward, flags)
+        assert H.relerr(R, Ro) < 1e-5
+        st = E.update(obs, act, oldlp, reward, flags)
+        l1, l2, l3, lt = E.last_update_losses(K)
+        for k in range(K):
+            assert abs(lt[k] - losses[k].loss) < 1e-4 * abs(losses[k].loss) + 1e-6, (k, lt[k], losses[k].loss)
+        assert H.relerr(E.get_grads(), go) < 1e-4
+        p = E.get_params()
+        m, v, step = E.get_adam_state()
+        assert step == so == K
+        assert H.relerr(p, po) < 1e-5 and H.relerr(m, mo) < 1e-4 and H.relerr(v, vo) < 2e-4
+
+
+def test_wide_update_chunked_and_minibatched():
+    """a batch larger than the activation chunk (forces gradient accumulation over chunks) and 3 minibatches per epoch"""
+    H1, H2, B, K, M = 256, 256, 1500, 2, 3
+    dims = H.Dims(6, H1, H2, 1)
+    params, obs, act, oldlp, reward, flags = synth_batch(dims, B, 77)
+    L = H.oracle()
+    R = np.zeros(B, np.float32)
+    L.orc_returns(C.byref(dims), params, obs, reward, flags, B, H.GAMMA, R)
+    p, m, v = params.copy(), np.zeros_like(params), np.zeros_like(params)
+    per, step = B // M, 0
+    for k in range(K):
+        for mb in range(M):
+            lo = mb * per
+            hi = B if mb == M - 1 else lo + per
+            idx = np.arange(lo, hi, dtype=np.int64)
+            g, out = np.zeros_like(params), H.Loss()
+            L.orc_loss_grad(C.byref(dims), p, obs, act, oldlp, R, idx.ctypes.data_as(C.c_void_p), idx.size, H.SIGMA,
+                            H.EPS_CLIP, C.byref(out), g)
+            step += 1
+            L.orc_adam(p, g, m, v, p.size, step, H.LR, H.B1, H.B2, 1e-8)
+    # engine created for 256 records => activation chunk of 384 samples; minibatches of 500 need 2 chunks each
+    with wide_engine(H1, H2, n=256, k_epochs=K, n_minibatches=M) as E:
+        E.set_params(params)
+        st = E.update(obs, act, oldlp, reward, flags)
+        assert st.optimizer_steps == K * M and st.adam_step == K * M
+        assert H.relerr(E.get_grads(), g) < 1e-4
+        assert H.relerr(E.get_params(), p) < 1e-5
+
+
+def test_wide_rollout_is_refused_loudly():
+    from reinforcement_learning_cpp_parallel_b200 import capi
+    with wide_engine(256, 256) as E:
+        with pytest.raises(capi.B2Error):
+            E.rollout(1)

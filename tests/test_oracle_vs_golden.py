@@ -5,6 +5,8 @@ import ctypes as C
 import numpy as np
 import pytest
 
+import helpers as H
+
 from helpers import (B1, B2, DEFAULT_DIMS, EPS_CLIP, GAMMA, LR, SIGMA, Loss, flags_of, gold, oracle,
                      oracle_rollout, oracle_update, param_slices, relerr)
 
@@ -177,3 +179,30 @@ def test_gauss_stream_statistics():
     x = np.array([L.orc_gauss(0x5EED, e, 7) for e in range(20000)])
     assert abs(x.mean()) < 0.03 and abs(x.std() - 1) < 0.03
     assert L.orc_gauss(1, 2, 3) == L.orc_gauss(1, 2, 3) != L.orc_gauss(1, 2, 4)
+
+
+# ---- widths other than the reference's 64/32: goldens minted by tests/golden/make_wide_golden.py (torch CPU) ----
+@pytest.mark.parametrize("H1,H2", [(128, 64), (256, 256)])
+def test_oracle_wide_nets_match_torch_golden(H1, H2):
+    L = H.oracle()
+    dims = H.Dims(6, H1, H2, 1)
+    tag = f"wide{H1}x{H2}"
+    params, obs = H.gold(f"{tag}_params.f32"), H.gold(f"{tag}_obs.f32").reshape(-1, 6)
+    action, oldlp, R = H.gold(f"{tag}_action.f32"), H.gold(f"{tag}_oldlogp.f32"), H.gold(f"{tag}_R.f32")
+    B = R.shape[0]
+    assert L.orc_n_params(C.byref(dims)) == params.shape[0]
+    v = np.zeros(B, np.float32)
+    L.orc_value(C.byref(dims), params, obs, B, v)
+    assert H.relerr(v, H.gold(f"{tag}_V.f32")) < 1e-6
+    mu, a2, lp = (np.zeros(B, np.float32) for _ in range(3))
+    L.orc_act(C.byref(dims), params, obs, B, H.ptr(np.zeros(B, np.float32)), H.SIGMA, mu, a2, lp)
+    assert np.abs(mu - H.gold(f"{tag}_mu.f32")).max() < 1e-6
+    g = np.zeros_like(params)
+    out = H.Loss()
+    L.orc_loss_grad(C.byref(dims), params, obs, action, oldlp, R, None, B, H.SIGMA, H.EPS_CLIP, C.byref(out), g)
+    gl = H.gold(f"{tag}_loss.f64")
+    assert abs(out.loss1 - gl[0]) < 1e-5 * abs(gl[0]) and abs(out.loss2 - gl[1]) < 1e-5 * abs(gl[1])
+    assert abs(out.loss - gl[3]) < 1e-5 * abs(gl[3]) and abs(out.clip_frac - gl[4]) < 1e-7
+    gg = H.gold(f"{tag}_grads.f32")
+    for name, sl in H.param_slices(dims):
+        assert H.relerr(g[sl], gg[sl]) < 1e-4, name
