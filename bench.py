@@ -27,6 +27,7 @@ sys.path.insert(0, ROOT)
 FLOP_PHYS = 12000      # 300 RK stages x 40 flop per env-step
 FLOP_ACTOR = 4928      # 2 x (6*64 + 64*32 + 32*1)
 FLOP_UPDATE = 28032    # per sample-epoch, default MLP (fwd 9856 + dW 9856 + dX 8320)
+FLOP_UPDATE_WIDE = 801792  # per sample-epoch, 2x256 MLPs (fwd 269,312 + dW 269,312 + dX 263,168)
 BYTES_STEP = 41        # obs 24 + a 4 + logp 4 + r 4 + V 4 + flag 1 written once per env-step
 BYTES_UPDATE = 36      # obs 24 + a 4 + old logp 4 + R 4 read per sample-epoch
 
@@ -45,6 +46,8 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-update", action="store_true")
+    ap.add_argument("--no-wide", action="store_true", help="skip the configs[4] leg (2x256 MLP update sweep on tensor cores)")
+    ap.add_argument("--wide-samples", type=int, default=524288, help="samples per GPU of the configs[4] leg (4M over 8 GPUs)")
     return ap.parse_args()
 
 
@@ -148,6 +151,72 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
+def wide_leg(args, pkg, capi, np, rank, local, world, dist, barrier, max_over_ranks, bf16_peak, bf16_src):
+    """BASELINE configs[4]: PPO update sweep, 2x256 MLPs, 4M-sample batch over 8 GPUs = 524,288 samples per GPU,
+    32 minibatches x 10 epochs; weak scaling (every rank owns its own 524,288 samples, gradients all-reduced)."""
+    B, T, M, K = args.wide_samples, 128, 32, 10
+    N = B // T
+    E = pkg.Engine(capi.default_config(n_envs=N, horizon=T, hidden1=256, hidden2=256, k_epochs=K, n_minibatches=M,
+                                       seed=0x5EED, device=local))
+    E.init_params(0)
+    if world > 1:
+        uid = [pkg.Engine.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        E.comm_init(rank, world, uid[0])
+    rng = np.random.default_rng(1234 + rank)
+    th = 0.3 * rng.standard_normal(B)
+    obs = capi.pinned_empty((B, 6), np.float32)
+    obs[:] = np.stack([rng.standard_normal(B), rng.standard_normal(B), rng.standard_normal(B), th, np.cos(th), np.sin(th)], 1)
+    a0, l0, _ = E.act(obs)                       # actions = mu + 0.5 eps from the initial policy (SURVEY.md s8d)
+    act, lp = capi.pinned_empty((B,), np.float32), capi.pinned_empty((B,), np.float32)
+    act[:], lp[:] = a0, l0
+    reward = capi.pinned_empty((B,), np.float32)
+    reward[:] = rng.random(B) < 0.9
+    flags = capi.pinned_empty((T, N), np.uint8)
+    flags[:] = 0
+    flags[99] = 2                                # TIMEUP after 100 steps (config: N_timestep)
+    flags[T - 1] = 4                             # horizon cut
+    fl = flags.reshape(-1)
+    w0 = E.get_params()
+    st = E.update(obs, act, lp, reward, fl, n_envs=N, horizon=T)       # upload + warm-up 1
+    for _ in range(2):
+        E.set_params(w0); E.update_resident()
+    barrier(E)
+    ms = []
+    l_before = E.kernel_launches()
+    for _ in range(args.steps):
+        E.timer_start()
+        st = E.update_resident()                 # returns scan + K x M optimizer steps on the resident batch
+        ms.append(E.timer_stop_ms())
+    launches = E.kernel_launches() - l_before
+    barrier(E)
+    tot = max_over_ranks(sum(ms))
+    value = B * K * args.steps * world / (tot * 1e-3)
+    # e2e: the ppo_nn.h-shaped call, PPO::update(MemoryNN) on HOST buffers (pinned): H2D of the batch inside the timed region
+    barrier(E)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        st2 = E.update(obs, act, lp, reward, fl, n_envs=N, horizon=T)
+    barrier(E)
+    dt = max_over_ranks(time.perf_counter() - t0)
+    h2d = obs.nbytes + act.nbytes + lp.nbytes + reward.nbytes + fl.nbytes
+    mine = sum(ms) / len(ms)
+    ach = FLOP_UPDATE_WIDE * B * K / (mine * 1e-3) / 1e12
+    E.close()
+    return {"value": value, "unit": "sample-epochs/s", "ms_per_update": tot / args.steps,
+            "config": {"workload": "BASELINE configs[4]: PPO update sweep, 2x256 MLP, 4M-sample batch / 8 GPUs = 524,288 "
+                                   "samples per GPU, 32 minibatches x 10 epochs", "samples_per_gpu": B, "minibatches": M,
+                       "epochs": K, "mlp": "6-256-256-1 x2", "operands": "bf16x3 (hi/mid split, fp32 accumulate in TMEM)"},
+            "gpu_launches": int(launches),
+            "e2e": {"value": B * K * args.steps * world / dt, "unit": "sample-epochs/s", "h2d_bytes_per_step": int(h2d),
+                    "d2h_bytes_per_step": 4 * 8 * K * M, "api": "b2_update on pinned host buffers (PPO::update(MemoryNN))"},
+            "roofline": {"kernel": "k_gemm_x3", "bound": "tensor", "achieved": ach, "peak": bf16_peak / 3.0,
+                         "unit": "TFLOP/s", "frac": ach / (bf16_peak / 3.0) if bf16_peak else None,
+                         "peak_source": bf16_src + " / 3 (every fp32 product is three bf16 MMAs)",
+                         "issued_bf16_tflops": 3 * ach, "flop_per_sample_epoch": FLOP_UPDATE_WIDE, "traffic": None},
+            "last_loss": st.loss}
+
+
 def main():
     args = parse()
     rank = int(os.environ.get("RANK", "0"))
@@ -187,8 +256,8 @@ def main():
         dist.broadcast_object_list(uid, src=0)
         E.comm_init(rank, world, uid[0])
 
-    def barrier():
-        E.sync()
+    def barrier(eng=None):
+        (eng or E).sync()
         torch.cuda.synchronize()
         if dist:
             dist.barrier()
@@ -211,6 +280,9 @@ def main():
         pass
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     hbm_src = "MEASURED_PEAKS.json" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
+    bf16_peak = peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops", 1590.0))
+    bf16_src = ("MEASURED_PEAKS.json bf16_tflops_sustained" if "bf16_tflops_sustained" in peaks else
+                "fallback 1590 TFLOP/s (B200_PROFILING.md)")
 
     # ---------------- warm-up ----------------
     for _ in range(max(args.warmup, 3)):
@@ -267,6 +339,10 @@ def main():
         d2h = sum(a.nbytes for a in out.values())
         e2e = {"value": steps_all / dt, "unit": "env-steps/s", "h2d_bytes_per_step": int(hp.nbytes),
                "d2h_bytes_per_step": int(d2h), "api": f"b2_set_params + b2_rollout_host (pinned host buffers, {args.chunks} chunks: D2H overlaps simulation)"}
+
+    update_wide = None
+    if not args.no_wide:
+        update_wide = wide_leg(args, pkg, capi, np, rank, local, world, dist, barrier, max_over_ranks, bf16_peak, bf16_src)
 
     if rank != 0:
         if dist:
@@ -328,7 +404,7 @@ def main():
                        "l2": "inputs larger than L2 (344 MB trajectory buffer rewritten per step)",
                        "parallelism": f"env-sharded x{world}, NCCL grad all-reduce"},
             "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "update": update,
-            "cpu_baseline": cpu_baseline, "fma_peaks_tflops": {"fp32": peak32, "fp64": peak64},
+            "update_wide": update_wide, "cpu_baseline": cpu_baseline, "fma_peaks_tflops": {"fp32": peak32, "fp64": peak64},
             "wall_s_timed_region": t_wall}
     print(json.dumps(line), flush=True)
     if dist:

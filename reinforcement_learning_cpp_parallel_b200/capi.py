@@ -101,7 +101,7 @@ SYMBOLS = {
     "b2_measure_fma_peak": (C.c_int, [_H, C.c_int, _P(C.c_double)]),
     "b2_host_alloc": (C.c_int, [_P(C.c_void_p), C.c_size_t]),
     "b2_host_free": (C.c_int, [C.c_void_p]),
-    "b2_selftest_gemm": (C.c_int, [_H, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),
+    "b2_selftest_gemm": (C.c_int, [_H, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
 }
 
 _lib = None
@@ -376,15 +376,21 @@ class Engine:
         return t.value
 
 
-def _selftest_gemm(self, A, B, splits=1):
-    """C = A @ B.T through the bf16x3 tcgen05 GEMM of the wide-net update (diagnostic)."""
+def _selftest_gemm(self, A, B, splits=1, mn_major=False):
+    """C = A @ B.T (A [M][K], B [N][K]) or, mn_major, C = A.T @ B (A [K][M], B [K][N]) through the bf16x3 tcgen05
+    GEMM of the wide-net update (diagnostic)."""
     A = np.ascontiguousarray(A, np.float32)
     B = np.ascontiguousarray(B, np.float32)
-    M, K = A.shape
-    N = B.shape[0]
-    assert B.shape[1] == K
+    if mn_major:
+        K, M = A.shape
+        N = B.shape[1]
+        assert B.shape[0] == K
+    else:
+        M, K = A.shape
+        N = B.shape[0]
+        assert B.shape[1] == K
     out = np.empty((M, N), np.float32)
-    _ck(self.L.b2_selftest_gemm(self.h, M, N, K, _vp(A), _vp(B), _vp(out), int(splits)))
+    _ck(self.L.b2_selftest_gemm(self.h, M, N, K, _vp(A), _vp(B), _vp(out), int(splits), int(mn_major)))
     return out
 
 

@@ -911,7 +911,7 @@ int b2_host_alloc(void** p, size_t bytes) {
   CK(cudaMallocHost(p, bytes));
   return B2_OK;
 }
-int b2_selftest_gemm(b2_handle E, int M, int N, int K, const float* A, const float* B, float* C, int splits) {
+int b2_selftest_gemm(b2_handle E, int M, int N, int K, const float* A, const float* B, float* C, int splits, int mn_major) {
   NEED(E);
   if (!A || !B || !C || M < 1 || N < 1 || K < 1) return set_error(B2_ERR_INVALID, "selftest_gemm: bad argument");
   CK(cudaSetDevice(E->cfg.device));
@@ -921,7 +921,7 @@ int b2_selftest_gemm(b2_handle E, int M, int N, int K, const float* A, const flo
   CK(cudaMalloc(&dC, sizeof(float) * (size_t)M * N));
   CK(cudaMemcpyAsync(dA, A, sizeof(float) * (size_t)M * K, cudaMemcpyHostToDevice, E->stream));
   CK(cudaMemcpyAsync(dB, B, sizeof(float) * (size_t)N * K, cudaMemcpyHostToDevice, E->stream));
-  int rc = wide_selftest_gemm(M, N, K, dA, dB, dC, splits, E->sm_count, E->stream);
+  int rc = wide_selftest_gemm(M, N, K, dA, dB, dC, splits, mn_major, E->sm_count, E->stream);
   E->launches += 4;
   if (!rc) {
     cudaError_t ce = cudaMemcpy(C, dC, sizeof(float) * (size_t)M * N, cudaMemcpyDeviceToHost);

@@ -110,6 +110,17 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr) {
   d |= (uint64_t)2 << 61;
   return d;
 }
+// MN-major operand, SWIZZLE_128B: 64 MN elements (128 B) contiguous, 8 K rows per 1024-B group (SBO = 1024),
+// consecutive 64-element MN blocks lbo_bytes apart (LBO).
+__device__ __forceinline__ uint64_t smem_desc_mn_sw128(uint32_t saddr, uint32_t lbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+  d |= (uint64_t)(lbo_bytes >> 4) << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
 // Instruction descriptor, kind::f16: D = f32 (bits 4-5 = 1), A = B = bf16 (bits 7-9, 10-12 = 1), both K-major
 // (bits 15, 16 = 0), N >> 3 at bits 17-22, M >> 4 at bits 24-28.
 __host__ __device__ constexpr uint32_t idesc_bf16_f32(int M, int N) {

@@ -41,6 +41,7 @@ enum { EPI_TANH = 0, EPI_DTANH = 1, EPI_RAW = 2 };
 struct GemmArgs {
   int G, M, N, K;                // per group g < G: C[M][N] = A[M][K] . B[N][K]^T ; K % 64 == 0, N % 16 == 0, N <= 256
   int m_tiles, splits, kb_per_split, stages;
+  int mn_major;                  // 1: C[M][N] = A[K][M]^T . B[K][N] (EPI_RAW only, K blocks of 32, K % 32 == 0, N % 64 == 0)
   float* out;                    // EPI_TANH / EPI_DTANH: [G][out_rows][N] ; EPI_RAW: [G][splits][M][N]
   int64_t out_g_stride;          // floats between groups
   const float* bias;             // EPI_TANH: [G][N]
@@ -50,12 +51,13 @@ struct GemmArgs {
 
 cudaError_t launch_gemm_x3(int epi, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& a, int sm_count,
                            cudaStream_t st);
-int gemm_x3_stages(int N);
+int gemm_x3_stages(int N, bool mn_major = false);
 
 // 3-D bf16 tensor map (K fastest, rows, planes) with a (64 x box_rows x 1) box and the 128-B swizzle.
 // Returns 0 on success; the driver entry point is resolved through the runtime (no -lcuda link dependency).
 int make_operand_map(CUtensorMap* out, const void* base, uint64_t K, uint64_t rows, uint64_t planes,
                      uint64_t row_stride_elems, uint64_t plane_stride_elems, uint32_t box_rows);
+enum { MN_BOX_ROWS = 32 };   // box rows of the maps the MN-major GEMM reads (samples per K block)
 
 // ---- the whole wide-net learner: buffers, tensor maps and the per-step kernel sequence ----
 struct WideNet;
@@ -78,6 +80,6 @@ cudaError_t launch_wide_act_finish(const float* mu, const float* eps, int64_t n,
 
 // diagnostic: C = A . B^T through the bf16x3 tcgen05 GEMM on device buffers (fp32 in, fp32 out)
 int wide_selftest_gemm(int M, int N, int K, const float* A_dev, const float* B_dev, float* C_dev, int splits,
-                       int sm_count, cudaStream_t st);
+                       int mn_major, int sm_count, cudaStream_t st);
 
 }  // namespace b2

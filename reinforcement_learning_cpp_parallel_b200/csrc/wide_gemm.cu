@@ -29,7 +29,14 @@ constexpr int BAR_BYTES = 256;
 
 __host__ __device__ constexpr int stage_bytes(int N) { return 2 * A_PLANE_BYTES + 2 * N * BK * 2; }
 
-template <int EPI>
+// MN = true: both operands are MN-major (the contraction index is the slow one in memory): C[M][N] = A[K][M]^T . B[K][N].
+// Used for dW2 = D2^T H1, where K = samples and the activations are stored sample-major.  A K block is 32 samples; an
+// operand block of 64 features x 32 samples is one TMA box (32 rows of 128 B, 128-B swizzle) = one UMMA MN-major
+// swizzle atom column: 8 sample rows per 1024-B group (SBO), 64-feature blocks MNB_BYTES apart (LBO).
+constexpr int BKS = 32;                       // samples per K block in MN mode
+constexpr int MNB_BYTES = BKS * 128;          // one 64-feature x 32-sample block
+
+template <int EPI, bool MN>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmArgs a) {
   extern __shared__ uint8_t smem_raw[];
@@ -37,15 +44,16 @@ k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
   uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);   // 1024-B alignment for the 128-B swizzle atoms
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int N = a.N, stages = a.stages;
-  const int SB = stage_bytes(N);
-  const int B_PLANE_BYTES = N * BK * 2;
+  const int SB = MN ? (4 + 2 * (N / 64)) * MNB_BYTES : stage_bytes(N);
+  const int B_PLANE_BYTES = MN ? (N / 64) * MNB_BYTES : N * BK * 2;
+  const int A_PLANE = MN ? 2 * MNB_BYTES : A_PLANE_BYTES;
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)stages * SB);
   uint64_t* empty = full + 8;
   uint64_t* tfull = empty + 8;
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
-  const int kb_total = a.K / BK;
+  const int kb_total = a.K / (MN ? BKS : BK);
   const int n_items = a.G * a.m_tiles * a.splits;
 
   if (warp == 0 && lane == 0) {
@@ -74,6 +82,17 @@ k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
           tc::mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* s = smem + (size_t)stage * SB;
           tc::mbar_arrive_expect_tx(&full[stage], (uint32_t)SB);
+          if (MN) {
+            for (int pl = 0; pl < 2; pl++) {
+              for (int fb = 0; fb < 2; fb++)
+                tc::tma_load_3d(s + pl * A_PLANE + fb * MNB_BYTES, &tmA, &full[stage], (mt * 2 + fb) * 64, kb * BKS, g * 2 + pl);
+              for (int fb = 0; fb < N / 64; fb++)
+                tc::tma_load_3d(s + 2 * A_PLANE + pl * B_PLANE_BYTES + fb * MNB_BYTES, &tmB, &full[stage], fb * 64, kb * BKS,
+                                g * 2 + pl);
+            }
+            if (++stage == stages) { stage = 0; phase ^= 1; }
+            continue;
+          }
           tc::tma_load_3d(s, &tmA, &full[stage], kb * BK, mt * BM, g * 2 + 0);
           tc::tma_load_3d(s + A_PLANE_BYTES, &tmA, &full[stage], kb * BK, mt * BM, g * 2 + 1);
           tc::tma_load_3d(s + 2 * A_PLANE_BYTES, &tmB, &full[stage], kb * BK, 0, g * 2 + 0);
@@ -84,7 +103,7 @@ k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      const uint32_t idesc = tc::idesc_bf16_f32(BM, N);
+      const uint32_t idesc = tc::idesc_bf16_f32(BM, N) | (MN ? ((1u << 15) | (1u << 16)) : 0u);
       int stage = 0; uint32_t phase = 0;
       int it = 0;
       for (int item = blockIdx.x; item < n_items; item += gridDim.x, it++) {
@@ -101,6 +120,22 @@ k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
           tc::mbar_wait(&full[stage], phase);
           tc::tc_fence_after();
           const uint32_t s = tc::smem_u32(smem + (size_t)stage * SB);
+          if (MN) {
+            const uint64_t mAh = tc::smem_desc_mn_sw128(s, MNB_BYTES), mAm = tc::smem_desc_mn_sw128(s + A_PLANE, MNB_BYTES);
+            const uint64_t mBh = tc::smem_desc_mn_sw128(s + 2 * A_PLANE, MNB_BYTES);
+            const uint64_t mBm = tc::smem_desc_mn_sw128(s + 2 * A_PLANE + B_PLANE_BYTES, MNB_BYTES);
+#pragma unroll
+            for (int k = 0; k < BKS / 16; k++) {
+              const uint64_t off = (uint64_t)((k * 2048) >> 4);   // 16 samples = two 8-row groups of 1024 B
+              tc::umma_bf16(d_tmem, mAm + off, mBh + off, idesc, acc);
+              tc::umma_bf16(d_tmem, mAh + off, mBm + off, idesc, 1u);
+              tc::umma_bf16(d_tmem, mAh + off, mBh + off, idesc, 1u);
+              acc = 1u;
+            }
+            tc::umma_commit(&empty[stage]);
+            if (++stage == stages) { stage = 0; phase ^= 1; }
+            continue;
+          }
           const uint64_t dAh = tc::smem_desc_sw128(s), dAm = tc::smem_desc_sw128(s + A_PLANE_BYTES);
           const uint64_t dBh = tc::smem_desc_sw128(s + 2 * A_PLANE_BYTES);
           const uint64_t dBm = tc::smem_desc_sw128(s + 2 * A_PLANE_BYTES + B_PLANE_BYTES);
@@ -195,8 +230,8 @@ EncodeTiledFn g_encode = nullptr;
 
 }  // namespace
 
-int gemm_x3_stages(int N) {
-  int s = (SMEM_LIMIT - 1024 - BAR_BYTES) / stage_bytes(N);
+int gemm_x3_stages(int N, bool mn_major) {
+  int s = (SMEM_LIMIT - 1024 - BAR_BYTES) / (mn_major ? (4 + 2 * (N / 64)) * MNB_BYTES : stage_bytes(N));
   if (s > 6) s = 6;
   return s;
 }
@@ -225,13 +260,14 @@ int make_operand_map(CUtensorMap* out, const void* base, uint64_t K, uint64_t ro
 
 cudaError_t launch_gemm_x3(int epi, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& a, int sm_count,
                            cudaStream_t st) {
-  const int smem = a.stages * stage_bytes(a.N) + BAR_BYTES + 1024;
+  const int smem = a.stages * (a.mn_major ? (4 + 2 * (a.N / 64)) * MNB_BYTES : stage_bytes(a.N)) + BAR_BYTES + 1024;
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e;
-    if ((e = cudaFuncSetAttribute(k_gemm_x3<EPI_TANH>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(k_gemm_x3<EPI_DTANH>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(k_gemm_x3<EPI_RAW>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_gemm_x3<EPI_TANH, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_gemm_x3<EPI_DTANH, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_gemm_x3<EPI_RAW, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_gemm_x3<EPI_RAW, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)) != cudaSuccess) return e;
     attr_set = true;
   }
   const int n_items = a.G * a.m_tiles * a.splits;
@@ -239,9 +275,12 @@ cudaError_t launch_gemm_x3(int epi, const CUtensorMap& tmA, const CUtensorMap& t
   if (grid < 1) return cudaSuccess;
   // 1 CTA per SM is assumed by the 512-column TMEM allocation: always ask for more than half of the shared memory
   const int smem_req = smem > 120 * 1024 ? smem : 120 * 1024;
-  if (epi == EPI_TANH) k_gemm_x3<EPI_TANH><<<grid, GEMM_THREADS, smem_req, st>>>(tmA, tmB, a);
-  else if (epi == EPI_DTANH) k_gemm_x3<EPI_DTANH><<<grid, GEMM_THREADS, smem_req, st>>>(tmA, tmB, a);
-  else k_gemm_x3<EPI_RAW><<<grid, GEMM_THREADS, smem_req, st>>>(tmA, tmB, a);
+  if (a.mn_major) {
+    if (epi != EPI_RAW || (a.N % 64)) return cudaErrorInvalidValue;
+    k_gemm_x3<EPI_RAW, true><<<grid, GEMM_THREADS, smem_req, st>>>(tmA, tmB, a);
+  } else if (epi == EPI_TANH) k_gemm_x3<EPI_TANH, false><<<grid, GEMM_THREADS, smem_req, st>>>(tmA, tmB, a);
+  else if (epi == EPI_DTANH) k_gemm_x3<EPI_DTANH, false><<<grid, GEMM_THREADS, smem_req, st>>>(tmA, tmB, a);
+  else k_gemm_x3<EPI_RAW, false><<<grid, GEMM_THREADS, smem_req, st>>>(tmA, tmB, a);
   return cudaGetLastError();
 }
 
@@ -265,12 +304,14 @@ __global__ void k_sum_splits(const float* __restrict__ part, float* __restrict__
 }
 
 int wide_selftest_gemm(int M, int N, int K, const float* A_dev, const float* B_dev, float* C_dev, int splits,
-                       int sm_count, cudaStream_t st) {
+                       int mn_major, int sm_count, cudaStream_t st) {
   if (M < 1 || N < 32 || N > 256 || (N % 32) || K < 1) return set_error(B2_ERR_INVALID, "selftest gemm: need N %% 32 == 0, 32 <= N <= 256");
-  const int64_t Kp = ((int64_t)K + BK - 1) / BK * BK;
+  if (mn_major && ((M % 64) || (N % 64))) return set_error(B2_ERR_INVALID, "selftest gemm (MN-major): need M %% 64 == 0 and N %% 64 == 0");
+  const int kblk = mn_major ? BKS : BK;
+  const int64_t Kp = ((int64_t)K + kblk - 1) / kblk * kblk;
   __nv_bfloat16 *pa = nullptr, *pb = nullptr;
   float* part = nullptr;
-  const int kb_total = (int)(Kp / BK);
+  const int kb_total = (int)(Kp / kblk);
   if (splits < 1) splits = 1;
   if (splits > kb_total) splits = kb_total;
   const int kbps = (kb_total + splits - 1) / splits;
@@ -278,15 +319,25 @@ int wide_selftest_gemm(int M, int N, int K, const float* A_dev, const float* B_d
   B2_CUDA_CHECK(cudaMalloc(&pa, sizeof(__nv_bfloat16) * 2 * M * Kp));
   B2_CUDA_CHECK(cudaMalloc(&pb, sizeof(__nv_bfloat16) * 2 * N * Kp));
   B2_CUDA_CHECK(cudaMalloc(&part, sizeof(float) * (size_t)splits * M * N));
-  k_split_planes<<<256, 256, 0, st>>>(A_dev, pa, pa + (int64_t)M * Kp, M, K, Kp);
-  k_split_planes<<<256, 256, 0, st>>>(B_dev, pb, pb + (int64_t)N * Kp, N, K, Kp);
   CUtensorMap tmA, tmB;
-  int rc = make_operand_map(&tmA, pa, Kp, M, 2, Kp, (uint64_t)M * Kp, BM);
-  if (!rc) rc = make_operand_map(&tmB, pb, Kp, N, 2, Kp, (uint64_t)N * Kp, (uint32_t)N);
+  int rc;
+  if (mn_major) {   // A_dev [K][M], B_dev [K][N]; rows K..Kp stay zero
+    B2_CUDA_CHECK(cudaMemsetAsync(pa, 0, sizeof(__nv_bfloat16) * 2 * M * Kp, st));
+    B2_CUDA_CHECK(cudaMemsetAsync(pb, 0, sizeof(__nv_bfloat16) * 2 * N * Kp, st));
+    k_split_planes<<<256, 256, 0, st>>>(A_dev, pa, pa + (int64_t)M * Kp, K, M, M);
+    k_split_planes<<<256, 256, 0, st>>>(B_dev, pb, pb + (int64_t)N * Kp, K, N, N);
+    rc = make_operand_map(&tmA, pa, M, Kp, 2, M, (uint64_t)M * Kp, MN_BOX_ROWS);
+    if (!rc) rc = make_operand_map(&tmB, pb, N, Kp, 2, N, (uint64_t)N * Kp, MN_BOX_ROWS);
+  } else {
+    k_split_planes<<<256, 256, 0, st>>>(A_dev, pa, pa + (int64_t)M * Kp, M, K, Kp);
+    k_split_planes<<<256, 256, 0, st>>>(B_dev, pb, pb + (int64_t)N * Kp, N, K, Kp);
+    rc = make_operand_map(&tmA, pa, Kp, M, 2, Kp, (uint64_t)M * Kp, BM);
+    if (!rc) rc = make_operand_map(&tmB, pb, Kp, N, 2, Kp, (uint64_t)N * Kp, (uint32_t)N);
+  }
   if (!rc) {
     GemmArgs g{};
-    g.G = 1; g.M = M; g.N = N; g.K = (int)Kp;
-    g.m_tiles = (M + BM - 1) / BM; g.splits = splits; g.kb_per_split = kbps; g.stages = gemm_x3_stages(N);
+    g.G = 1; g.M = M; g.N = N; g.K = (int)Kp; g.mn_major = mn_major ? 1 : 0;
+    g.m_tiles = (M + BM - 1) / BM; g.splits = splits; g.kb_per_split = kbps; g.stages = gemm_x3_stages(N, mn_major != 0);
     g.out = part; g.out_g_stride = 0;
     cudaError_t e = launch_gemm_x3(EPI_RAW, tmA, tmB, g, sm_count, st);
     if (e != cudaSuccess) rc = set_error(B2_ERR_CUDA, "gemm_x3: %s", cudaGetErrorString(e));

@@ -4,12 +4,13 @@
 // (src/ppo_nn.cpp:126-194), the loss (:263-290), autograd backward (:301-302) and Adam::step (:303).
 //
 // Memory plan for a chunk of CAP samples (CAP % 128 == 0), g = net (0 actor, 1 critic), pl = bf16 plane (hi, mid):
-//   w2p  [g*2+pl][H2][H1]   w2tp [g*2+pl][H1][H2]   bias2 [g][H2]                    (re-split every step)
-//   h1p  [g*2+pl][CAP][H1]  h1tp [g*2+pl][H1][CAP]                                   (layer-1 activations, both majors)
-//   h2   [g][CAP][H2] f32                                                            (layer-2 activations)
-//   d2p  [g*2+pl][CAP][H2]  d2tp [g*2+pl][H2][CAP]                                   (dL/dz2, both majors)
-//   d1   [g][CAP][H1] f32                                                            (dL/dz1)
-// Both majors exist so that every GEMM reads K-major operands through plain 128-B-swizzled TMA boxes.
+//   w2p  [g*2+pl][H2][H1]   w2tp [g*2+pl][H1][H2]   bias2 [g][H2]    (re-split every step)
+//   h1p  [g*2+pl][CAP][H1]                                           (layer-1 activations, sample-major)
+//   h2   [g][CAP][H2] f32                                            (layer-2 activations)
+//   d2p  [g*2+pl][CAP][H2]                                           (dL/dz2, sample-major)
+//   d1   [g][CAP][H1] f32                                            (dL/dz1)
+// The layer-2 forward and dX GEMMs read h1p / d2p as K-major operands (K = features); the dW2 GEMM reads the SAME
+// planes as MN-major operands (K = samples), so no transposed copy of any activation is ever written.
 // Samples in [count, round_up(count, 128)) are written as zeros by the producers, so the sample-contraction GEMM
 // (dW2) needs no masking.
 #include <algorithm>
@@ -24,7 +25,6 @@ namespace b2 {
 namespace {
 
 constexpr int S = OBS;
-constexpr int TILE_S = 32;   // samples per tile of the FP32 side kernels
 
 struct WideArgs {
   NetDims d;
@@ -36,10 +36,11 @@ struct WideArgs {
   int64_t cap;        // CAP
   float inv_denom;
   HyperDev hp;
-  __nv_bfloat16 *w2p, *w2tp, *h1p, *h1tp, *d2p, *d2tp;
+  __nv_bfloat16 *w2p, *w2tp, *h1p, *d2p;
   float *bias2, *h2, *d1;
   float *part_head, *part_dw1;   // [blocks][2][head_row] , [blocks][2][H1 * 8]
   int head_row;
+  int64_t* bump_step;   // non-null on the first chunk of an optimizer step: adam_step += 1
 };
 
 __device__ __forceinline__ int64_t sample_pos(const WideArgs& a, int s) {
@@ -47,10 +48,10 @@ __device__ __forceinline__ int64_t sample_pos(const WideArgs& a, int s) {
   return a.idx ? (int64_t)a.idx[p] : p;
 }
 
-// weights -> bf16 planes in both majors (runs once per optimizer step: the weights just changed)
-__global__ void __launch_bounds__(256) k_wide_prep(const WideArgs a, int64_t* adam_step) {
+// weights -> bf16 planes in both majors.  Runs at the start of an update; afterwards the Adam step itself rewrites the
+// planes of every W2 element it changes (wide_store_planes), so the steady state has no conversion pass.
+__global__ void __launch_bounds__(256) k_wide_prep(const WideArgs a) {
   const int H1 = a.d.H1, H2 = a.d.H2;
-  if (blockIdx.x == 0 && threadIdx.x == 0) *adam_step += 1;   // one prep launch == one optimizer step
   const int n = 2 * H2 * H1;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const int g = i / (H2 * H1), r = i % (H2 * H1), j = r / H1, k = r % H1;
@@ -67,63 +68,63 @@ __global__ void __launch_bounds__(256) k_wide_prep(const WideArgs a, int64_t* ad
     a.bias2[i] = a.params[(i / H2) * a.d.SIZE + a.d.ob2 + (i % H2)];
 }
 
-// layer 1: H1 = tanh(W1 x + b1) for a tile of 32 samples; thread = feature.  grid (m_pad / 32, 2 nets)
+// layer 1: H1 = tanh(W1 x + b1) -> (hi, mid) bf16 planes, sample-major.  A block walks a tile of 128 samples; a thread
+// owns 8 consecutive features (their 56 weights stay in registers) and strides over the samples, so every store is a
+// 16-B vector and a warp writes 512 contiguous bytes of one row.  grid (m_pad / 128, 2 nets)
+constexpr int L1_TILE = 64;
 __global__ void __launch_bounds__(256) k_wide_l1(const WideArgs a) {
-  __shared__ float xs[TILE_S][S + 2];
+  __shared__ float xs[L1_TILE][S + 2];
+  __shared__ float ws[256 * (S + 1)];          // W1 [H1][S] then b1 [H1] of this net (contiguous in the parameter vector)
   const int H1 = a.d.H1, g = blockIdx.y;
-  const int s0 = blockIdx.x * TILE_S;
-  for (int i = threadIdx.x; i < TILE_S * S; i += blockDim.x) {
+  const int s0 = blockIdx.x * L1_TILE;
+  if (blockIdx.x == 0 && g == 0 && threadIdx.x == 0 && a.bump_step) *a.bump_step += 1;   // one optimizer step
+  for (int i = threadIdx.x; i < H1 * (S + 1); i += blockDim.x) ws[i] = a.params[g * a.d.SIZE + a.d.oW1 + i];
+  for (int i = threadIdx.x; i < L1_TILE * S; i += blockDim.x) {
     const int s = i / S, c = i % S;
     xs[s][c] = (s0 + s < a.count) ? a.tr.obs[c * a.tr.cap + sample_pos(a, s0 + s)] : 0.0f;
   }
   __syncthreads();
-  const float* net = a.params + g * a.d.SIZE;
   const int64_t plane = a.cap * H1;
-  for (int k = threadIdx.x; k < H1; k += blockDim.x) {
-    float w[S];
+  const int groups = H1 / 8;                    // feature groups of 8
+  const int kg = threadIdx.x % groups, sl = threadIdx.x / groups, sstep = blockDim.x / groups;
+  if (sl >= sstep) return;                      // H1 = 192: 24 groups, 10 sample lanes, 16 idle threads
+  float w[8][S], b[8];
 #pragma unroll
-    for (int c = 0; c < S; c++) w[c] = net[a.d.oW1 + k * S + c];
-    const float b = net[a.d.ob1 + k];
-    __align__(16) __nv_bfloat16 th[TILE_S], tm[TILE_S];
+  for (int u = 0; u < 8; u++) {
 #pragma unroll
-    for (int s = 0; s < TILE_S; s++) {
-      float z = b;
+    for (int c = 0; c < S; c++) w[u][c] = ws[(kg * 8 + u) * S + c];
+    b[u] = ws[H1 * S + kg * 8 + u];
+  }
+  for (int s = sl; s < L1_TILE; s += sstep) {
+    const bool valid = s0 + s < a.count;
+    __align__(16) __nv_bfloat16 th[8], tm[8];
 #pragma unroll
-      for (int c = 0; c < S; c++) z = fmaf(w[c], xs[s][c], z);
-      const float h = (s0 + s < a.count) ? act_tanh(z) : 0.0f;
-      tc::split_bf16(h, th[s], tm[s]);
-      const int64_t o = (int64_t)(s0 + s) * H1 + k;
-      a.h1p[(g * 2 + 0) * plane + o] = th[s];
-      a.h1p[(g * 2 + 1) * plane + o] = tm[s];
+    for (int u = 0; u < 8; u++) {
+      float z = b[u];
+#pragma unroll
+      for (int c = 0; c < S; c++) z = fmaf(w[u][c], xs[s][c], z);
+      tc::split_bf16(valid ? act_tanh(z) : 0.0f, th[u], tm[u]);
     }
-    // feature-major copy: 32 consecutive samples of one feature = 64 B contiguous
-    uint4* oh = reinterpret_cast<uint4*>(a.h1tp + (g * 2 + 0) * plane + (int64_t)k * a.cap + s0);
-    uint4* om = reinterpret_cast<uint4*>(a.h1tp + (g * 2 + 1) * plane + (int64_t)k * a.cap + s0);
-#pragma unroll
-    for (int v = 0; v < 4; v++) {
-      oh[v] = *reinterpret_cast<const uint4*>(&th[8 * v]);
-      om[v] = *reinterpret_cast<const uint4*>(&tm[8 * v]);
-    }
+    const int64_t o = (int64_t)(s0 + s) * H1 + kg * 8;
+    *reinterpret_cast<uint4*>(a.h1p + (g * 2 + 0) * plane + o) = *reinterpret_cast<const uint4*>(th);
+    *reinterpret_cast<uint4*>(a.h1p + (g * 2 + 1) * plane + o) = *reinterpret_cast<const uint4*>(tm);
   }
 }
 
-// layer 3 + loss head + D2 for both nets.  One warp per sample (lanes own j = i*32 + lane), 8 warps walk a tile of
-// 32 samples; D2 goes out sample-major directly and feature-major through a shared-memory transpose.  dW3, db2, db3 and
-// the loss sums are accumulated per lane over all tiles of the block and written once, to this block's partial row.
+// layer 3 + loss head + D2 for both nets.  One warp per sample; lane l owns the NJ consecutive features
+// j = l*NJ .. l*NJ+NJ-1, so the H2 row is read and the D2 planes are written as contiguous vectors.  dW3, db2, db3 and
+// the loss sums are accumulated per lane over all samples of the block and written once, to this block's partial row.
 template <int NJ>   // H2 / 32
 __global__ void __launch_bounds__(256) k_wide_head(const WideArgs a) {
-  extern __shared__ __align__(16) uint8_t sm_raw[];
+  extern __shared__ __align__(16) float red[];             // [8 warps][2 nets][2 * H2 + 4]
   constexpr int H2 = NJ * 32;
-  constexpr int ROWW = 17;                                 // words per transposed row: 32 bf16 + 1 pad word
-  uint32_t* tileT = reinterpret_cast<uint32_t*>(sm_raw);   // [4 planes][H2][ROWW]
-  float* red = reinterpret_cast<float*>(tileT + 4 * H2 * ROWW);  // [8 warps][2 nets][2 * H2 + 4]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const NetDims d = a.d;
   float w3[2][NJ], b3[2];
 #pragma unroll
   for (int g = 0; g < 2; g++) {
 #pragma unroll
-    for (int i = 0; i < NJ; i++) w3[g][i] = a.params[g * d.SIZE + d.oW3 + i * 32 + lane];
+    for (int i = 0; i < NJ; i++) w3[g][i] = a.params[g * d.SIZE + d.oW3 + lane * NJ + i];
     b3[g] = a.params[g * d.SIZE + d.ob3];
   }
   float gW3[2][NJ], gb2[2][NJ], gb3[2] = {0.f, 0.f};
@@ -133,84 +134,81 @@ __global__ void __launch_bounds__(256) k_wide_head(const WideArgs a) {
     for (int i = 0; i < NJ; i++) { gW3[g][i] = 0.f; gb2[g][i] = 0.f; }
   float loss1 = 0.f, loss2 = 0.f, clipped = 0.f;
   const int64_t plane = a.cap * H2;
-  const int n_tiles = a.m_pad / TILE_S;
-  __nv_bfloat16* tileH = reinterpret_cast<__nv_bfloat16*>(tileT);
 
-  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    const int s0 = tile * TILE_S;
-    for (int q = 0; q < TILE_S / 8; q++) {
-      const int sl = warp * (TILE_S / 8) + q;
-      const int s = s0 + sl;
-      const bool valid = s < a.count;
-      float h[2][NJ], y[2] = {0.f, 0.f};
+  for (int s = blockIdx.x * 8 + warp; s < a.m_pad; s += gridDim.x * 8) {
+    const bool valid = s < a.count;
+    float h[2][NJ], y[2] = {0.f, 0.f};
 #pragma unroll
-      for (int g = 0; g < 2; g++)
+    for (int g = 0; g < 2; g++) {
+      const float2* hp = reinterpret_cast<const float2*>(a.h2 + ((int64_t)g * a.cap + s) * H2 + lane * NJ);
 #pragma unroll
-        for (int i = 0; i < NJ; i++) {
-          h[g][i] = valid ? a.h2[((int64_t)g * a.cap + s) * H2 + i * 32 + lane] : 0.0f;
-          y[g] = fmaf(w3[g][i], h[g][i], y[g]);
-        }
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        y[0] += __shfl_xor_sync(0xffffffffu, y[0], o);
-        y[1] += __shfl_xor_sync(0xffffffffu, y[1], o);
+      for (int i = 0; i < NJ; i += 2) {
+        const float2 t = valid ? hp[i >> 1] : make_float2(0.f, 0.f);
+        h[g][i] = t.x; h[g][i + 1] = t.y;
+        y[g] = fmaf(w3[g][i], t.x, y[g]);
+        y[g] = fmaf(w3[g][i + 1], t.y, y[g]);
       }
-      float dz[2] = {0.f, 0.f};
-      if (valid) {
-        const int64_t p = sample_pos(a, s);
-        const float R = a.tr.ret[p];
-        const float V = y[1] + b3[1];                                  // critic: no final activation (ppo_nn.h:118-122)
-        const float e = V - R;
-        dz[1] = e * a.inv_denom;                                       // d(0.5 mean e^2)/dV  (:288)
-        const float mu = act_tanh(y[0] + b3[0]);                       // ppo_nn.h:102
-        const float act = a.tr.action[p];
-        const float lp = gauss_logprob(act, mu, a.hp.inv_var, a.hp.half_log_norm);  // :140
-        const float ratio = expf(lp - a.tr.logp[p]);                   // :263
-        const float A = R - V;                                         // :274 (detached)
-        const float surr1 = ratio * A;                                 // :284
-        const float rc = fminf(fmaxf(ratio, a.hp.clip_lo), a.hp.clip_hi);
-        const float surr2 = rc * A;                                    // :285
-        const bool inside = (ratio >= a.hp.clip_lo) && (ratio <= a.hp.clip_hi);
-        float gr;                                                      // autograd of min(): ties split the gradient
-        if (surr1 < surr2) gr = A;
-        else if (surr1 > surr2) gr = inside ? A : 0.f;
-        else gr = 0.5f * A + (inside ? 0.5f * A : 0.f);
-        const float dlogp = -gr * ratio * a.inv_denom;
-        const float dmu = dlogp * (act - mu) * a.hp.inv_var;           // :20-31
-        dz[0] = dmu * (1.0f - mu * mu);
-        if (lane == 0) {
-          loss2 = fmaf(e, e, loss2);
-          loss1 -= fminf(surr1, surr2);                                // :287
-          clipped += inside ? 0.f : 1.f;
-          gb3[0] += dz[0];
-          gb3[1] += dz[1];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      y[0] += __shfl_xor_sync(0xffffffffu, y[0], o);
+      y[1] += __shfl_xor_sync(0xffffffffu, y[1], o);
+    }
+    float dz[2] = {0.f, 0.f};
+    if (valid) {
+      const int64_t p = sample_pos(a, s);
+      const float R = a.tr.ret[p];
+      const float V = y[1] + b3[1];                                  // critic: no final activation (ppo_nn.h:118-122)
+      const float e = V - R;
+      dz[1] = e * a.inv_denom;                                       // d(0.5 mean e^2)/dV  (:288)
+      const float mu = act_tanh(y[0] + b3[0]);                       // ppo_nn.h:102
+      const float act = a.tr.action[p];
+      const float lp = gauss_logprob(act, mu, a.hp.inv_var, a.hp.half_log_norm);  // :140
+      const float ratio = expf(lp - a.tr.logp[p]);                   // :263
+      const float A = R - V;                                         // :274 (detached)
+      const float surr1 = ratio * A;                                 // :284
+      const float rc = fminf(fmaxf(ratio, a.hp.clip_lo), a.hp.clip_hi);
+      const float surr2 = rc * A;                                    // :285
+      const bool inside = (ratio >= a.hp.clip_lo) && (ratio <= a.hp.clip_hi);
+      float gr;                                                      // autograd of min(): ties split the gradient
+      if (surr1 < surr2) gr = A;
+      else if (surr1 > surr2) gr = inside ? A : 0.f;
+      else gr = 0.5f * A + (inside ? 0.5f * A : 0.f);
+      const float dlogp = -gr * ratio * a.inv_denom;
+      const float dmu = dlogp * (act - mu) * a.hp.inv_var;           // :20-31
+      dz[0] = dmu * (1.0f - mu * mu);
+      if (lane == 0) {
+        loss2 = fmaf(e, e, loss2);
+        loss1 -= fminf(surr1, surr2);                                // :287
+        clipped += inside ? 0.f : 1.f;
+        gb3[0] += dz[0];
+        gb3[1] += dz[1];
+      }
+    }
+#pragma unroll
+    for (int g = 0; g < 2; g++) {
+      __align__(16) __nv_bfloat16 dh[NJ], dm[NJ];
+#pragma unroll
+      for (int i = 0; i < NJ; i++) {
+        const float dd = dz[g] * w3[g][i] * (1.0f - h[g][i] * h[g][i]);
+        gW3[g][i] = fmaf(dz[g], h[g][i], gW3[g][i]);
+        gb2[g][i] += dd;
+        tc::split_bf16(dd, dh[i], dm[i]);
+      }
+      const int64_t o = (int64_t)s * H2 + lane * NJ;
+      uint32_t* oh = reinterpret_cast<uint32_t*>(a.d2p + (g * 2 + 0) * plane + o);
+      uint32_t* om = reinterpret_cast<uint32_t*>(a.d2p + (g * 2 + 1) * plane + o);
+      if (NJ == 8) {
+        *reinterpret_cast<uint4*>(oh) = *reinterpret_cast<const uint4*>(dh);
+        *reinterpret_cast<uint4*>(om) = *reinterpret_cast<const uint4*>(dm);
+      } else {
+#pragma unroll
+        for (int i = 0; i < NJ / 2; i++) {
+          oh[i] = reinterpret_cast<const uint32_t*>(dh)[i];
+          om[i] = reinterpret_cast<const uint32_t*>(dm)[i];
         }
       }
-#pragma unroll
-      for (int g = 0; g < 2; g++)
-#pragma unroll
-        for (int i = 0; i < NJ; i++) {
-          const float dd = dz[g] * w3[g][i] * (1.0f - h[g][i] * h[g][i]);
-          gW3[g][i] = fmaf(dz[g], h[g][i], gW3[g][i]);
-          gb2[g][i] += dd;
-          __nv_bfloat16 hi, mid;
-          tc::split_bf16(dd, hi, mid);
-          const int j = i * 32 + lane;
-          const int64_t o = (int64_t)s * H2 + j;
-          a.d2p[(g * 2 + 0) * plane + o] = hi;
-          a.d2p[(g * 2 + 1) * plane + o] = mid;
-          tileH[(((g * 2 + 0) * H2 + j) * ROWW) * 2 + sl] = hi;
-          tileH[(((g * 2 + 1) * H2 + j) * ROWW) * 2 + sl] = mid;
-        }
     }
-    __syncthreads();
-    // feature-major rows: 16 words (32 samples) per (plane, j); a half-warp writes one 64-B row
-    for (int r = threadIdx.x >> 4; r < 4 * H2; r += 16) {
-      const int wl = threadIdx.x & 15;
-      uint32_t* dst = reinterpret_cast<uint32_t*>(a.d2tp + (int64_t)(r / H2) * plane + (int64_t)(r % H2) * a.cap + s0);
-      dst[wl] = tileT[r * ROWW + wl];
-    }
-    __syncthreads();
   }
 
   // block reduction of the per-lane column sums -> this block's partial row (fixed order: deterministic)
@@ -219,7 +217,7 @@ __global__ void __launch_bounds__(256) k_wide_head(const WideArgs a) {
   for (int g = 0; g < 2; g++) {
     float* r = red + (warp * 2 + g) * RW;
 #pragma unroll
-    for (int i = 0; i < NJ; i++) { r[i * 32 + lane] = gW3[g][i]; r[H2 + i * 32 + lane] = gb2[g][i]; }
+    for (int i = 0; i < NJ; i++) { r[lane * NJ + i] = gW3[g][i]; r[H2 + lane * NJ + i] = gb2[g][i]; }
     if (lane == 0) {
       r[2 * H2] = gb3[g];
       r[2 * H2 + 1] = g == 0 ? loss1 : loss2;
@@ -257,8 +255,19 @@ __global__ void __launch_bounds__(256) k_wide_dw1(const WideArgs a, int samples_
     __syncthreads();
     if (k < H1) {
       const float* dp = a.d1 + ((int64_t)g * a.cap + t0) * H1 + k;
-#pragma unroll 4
-      for (int s = 0; s < nt; s++) {
+      int s = 0;
+      for (; s + 16 <= nt; s += 16) {          // 16 independent loads in flight per thread
+        float dv[16];
+#pragma unroll
+        for (int u = 0; u < 16; u++) dv[u] = dp[(int64_t)(s + u) * H1];
+#pragma unroll
+        for (int u = 0; u < 16; u++) {
+#pragma unroll
+          for (int c = 0; c < S; c++) acc[c] = fmaf(dv[u], xs[s + u][c], acc[c]);
+          acc[S] += dv[u];
+        }
+      }
+      for (; s < nt; s++) {
         const float dv = dp[(int64_t)s * H1];
 #pragma unroll
         for (int c = 0; c < S; c++) acc[c] = fmaf(dv, xs[s][c], acc[c]);
@@ -280,71 +289,145 @@ struct ReduceArgs {
   const float *part_head, *part_dw1, *part_dw2;
   int head_blocks, head_row, dw1_blocks, splits, pstride;
   int first_chunk, last_chunk, apply_adam;
+  __nv_bfloat16 *w2p, *w2tp;   // weight planes the Adam step keeps current
+  float* bias2;
 };
 
+struct AdamCoef {
+  float fb1, f1mb1, fb2, f1mb2, sq_bc2, feps, step_size;
+};
+// libtorch adam.cpp: scalars are doubles narrowed to f32 inside the tensor kernels
+__device__ __forceinline__ AdamCoef adam_coef(const HyperDev& hp, int64_t step) {
+  const double bc1 = 1.0 - pow(hp.beta1, (double)step);
+  const double bc2 = 1.0 - pow(hp.beta2, (double)step);
+  AdamCoef c;
+  c.fb1 = (float)hp.beta1; c.f1mb1 = (float)(1.0 - hp.beta1);
+  c.fb2 = (float)hp.beta2; c.f1mb2 = (float)(1.0 - hp.beta2);
+  c.sq_bc2 = (float)sqrt(bc2); c.feps = (float)hp.eps; c.step_size = (float)(-(hp.lr / bc1));
+  return c;
+}
+// a parameter changed: keep the bf16 planes (both majors) of W2 and the bias copy in step with it
+__device__ __forceinline__ void wide_store_planes(const NetDims& d, __nv_bfloat16* w2p, __nv_bfloat16* w2tp, float* bias2,
+                                                  int p, float val) {
+  const int g = p / d.SIZE, o = p % d.SIZE;
+  if (o >= d.oW2 && o < d.ob2) {
+    const int e = o - d.oW2, j = e / d.H1, k = e % d.H1;
+    __nv_bfloat16 hi, mid;
+    tc::split_bf16(val, hi, mid);
+    const int64_t ps = (int64_t)d.H2 * d.H1;
+    w2p[(g * 2 + 0) * ps + e] = hi;
+    w2p[(g * 2 + 1) * ps + e] = mid;
+    w2tp[(g * 2 + 0) * ps + (int64_t)k * d.H2 + j] = hi;
+    w2tp[(g * 2 + 1) * ps + (int64_t)k * d.H2 + j] = mid;
+  } else if (o >= d.ob2 && o < d.oW3) {
+    bias2[g * d.H2 + (o - d.ob2)] = val;
+  }
+}
+
 // same arithmetic as ppo_update.cu adam_apply (libtorch adam.cpp order), generic parameter count
-__device__ __forceinline__ void wide_adam_apply(const UpdateArgs& a, int p, float g, int64_t step) {
-  const double bc1 = 1.0 - pow(a.hp.beta1, (double)step);
-  const double bc2 = 1.0 - pow(a.hp.beta2, (double)step);
-  const float fb1 = (float)a.hp.beta1, f1mb1 = (float)(1.0 - a.hp.beta1);
-  const float fb2 = (float)a.hp.beta2, f1mb2 = (float)(1.0 - a.hp.beta2);
-  const float sq_bc2 = (float)sqrt(bc2), feps = (float)a.hp.eps, step_size = (float)(-(a.hp.lr / bc1));
+__device__ __forceinline__ float wide_adam_apply(const UpdateArgs& a, const AdamCoef& c, int p, float g) {
   float m = a.adam_m[p], v = a.adam_v[p];
-  m = __fadd_rn(__fmul_rn(m, fb1), __fmul_rn(f1mb1, g));
-  v = __fadd_rn(__fmul_rn(v, fb2), __fmul_rn(f1mb2, __fmul_rn(g, g)));
-  const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(v), sq_bc2), feps);
+  m = __fadd_rn(__fmul_rn(m, c.fb1), __fmul_rn(c.f1mb1, g));                 // exp_avg.mul_(b1).add_(grad, 1-b1)
+  v = __fadd_rn(__fmul_rn(v, c.fb2), __fmul_rn(c.f1mb2, __fmul_rn(g, g)));   // exp_avg_sq.mul_(b2).addcmul_(g, g, 1-b2)
+  const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(v), c.sq_bc2), c.feps); // (sqrt(v)/sqrt(bc2)).add_(eps)
   a.adam_m[p] = m;
   a.adam_v[p] = v;
-  a.params[p] = __fadd_rn(a.params[p], __fmul_rn(step_size, __fdiv_rn(m, denom)));
+  const float np = __fadd_rn(a.params[p], __fmul_rn(c.step_size, __fdiv_rn(m, denom)));  // p.addcdiv_(m, denom, -step_size)
+  a.params[p] = np;
+  return np;
 }
 
 __device__ __forceinline__ void wide_loss_log(const UpdateArgs& a, int q, float sum) {
   a.loss_log[a.step_slot * 4 + q] = (q == 1 ? 0.5 : 1.0) * (double)sum / (double)a.denom;
 }
 
-// fixed-order sum of every partial that feeds parameter p (or loss scalar q); accumulates over chunks; Adam on the last
-__global__ void __launch_bounds__(128) k_wide_reduce(const ReduceArgs r) {
-  const NetDims d = r.d;
-  const int p = blockIdx.x * blockDim.x + threadIdx.x;
-  if (p >= d.P + 3) return;
-  float s = 0.f;
-  int slot;
-  if (p < d.P) {
-    slot = p;
-    const int g = p / d.SIZE, o = p % d.SIZE;
-    if (o < d.oW2) {                       // W1 [H1][S] or b1 [H1]
-      int k, c;
-      if (o < d.ob1) { k = o / S; c = o % S; } else { k = o - d.ob1; c = S; }
-      for (int b = 0; b < r.dw1_blocks; b++) s += r.part_dw1[((int64_t)b * 2 + g) * d.H1 * 8 + k * 8 + c];
-    } else if (o < d.ob2) {                // W2 [H2][H1]
-      const int e = o - d.oW2;
-      const float* base = r.part_dw2 + (int64_t)g * r.splits * d.H2 * d.H1 + e;
-      for (int sp = 0; sp < r.splits; sp++) s += base[(int64_t)sp * d.H2 * d.H1];
-    } else {                               // b2, W3, b3 from the head partial rows
-      int col;
-      if (o < d.oW3) col = d.H2 + (o - d.ob2);
-      else if (o < d.ob3) col = o - d.oW3;
-      else col = 2 * d.H2;
-      for (int b = 0; b < r.head_blocks; b++) s += r.part_head[((int64_t)b * 2 + g) * r.head_row + col];
-    }
-  } else {
-    const int q = p - d.P;                 // 0 loss1 sum, 1 sum e^2, 2 clipped count
-    slot = r.pstride - 4 + q;
-    const int g = q == 1 ? 1 : 0, col = 2 * d.H2 + (q == 2 ? 2 : 1);
-    for (int b = 0; b < r.head_blocks; b++) s += r.part_head[((int64_t)b * 2 + g) * r.head_row + col];
-  }
+// Fixed-order (bit-reproducible) sum of every partial that feeds a parameter; accumulates over chunks; Adam on the last.
+// Blocks [0, w2_blocks): one thread per W2 element, split-K partials summed 8 loads at a time.
+// Remaining blocks: one WARP per "small" parameter (W1, b1, b2, W3, b3 and the 3 loss scalars), lanes stride over the
+// per-block partial rows and a shuffle tree finishes the sum.
+__device__ __forceinline__ void wide_finish(const ReduceArgs& r, const AdamCoef& c, int p, int slot, float s) {
   if (!r.first_chunk) s += r.u.grads[slot];
   r.u.grads[slot] = s;
   if (r.last_chunk && r.apply_adam) {
-    if (p < d.P) wide_adam_apply(r.u, p, s, *r.u.adam_step);
-    else wide_loss_log(r.u, p - d.P, s);
+    if (p < r.d.P) wide_store_planes(r.d, r.w2p, r.w2tp, r.bias2, p, wide_adam_apply(r.u, c, p, s));
+    else wide_loss_log(r.u, p - r.d.P, s);
   }
 }
 
-__global__ void __launch_bounds__(128) k_wide_adam(const UpdateArgs a, int P, int pstride) {
+__global__ void __launch_bounds__(128) k_wide_reduce(const ReduceArgs r, int w2_blocks) {
+  const NetDims d = r.d;
+  const int w2n = d.H2 * d.H1;
+  __shared__ AdamCoef coef;
+  if (threadIdx.x == 0 && r.last_chunk && r.apply_adam) coef = adam_coef(r.u.hp, *r.u.adam_step);
+  __syncthreads();
+  if ((int)blockIdx.x < w2_blocks) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 2 * w2n) return;
+    const int g = i / w2n, e = i % w2n;
+    const float* base = r.part_dw2 + (int64_t)g * r.splits * w2n + e;
+    float s = 0.f;
+    int sp = 0;
+    for (; sp + 8 <= r.splits; sp += 8) {
+      float t[8];
+#pragma unroll
+      for (int u = 0; u < 8; u++) t[u] = base[(int64_t)(sp + u) * w2n];
+#pragma unroll
+      for (int u = 0; u < 8; u++) s += t[u];
+    }
+    for (; sp < r.splits; sp++) s += base[(int64_t)sp * w2n];
+    const int p = g * d.SIZE + d.oW2 + e;
+    wide_finish(r, coef, p, p, s);
+    return;
+  }
+  const int lane = threadIdx.x & 31;
+  const int per_net = d.H1 * (S + 1) + 2 * d.H2 + 1;     // W1, b1, b2, W3, b3
+  const int q = ((int)blockIdx.x - w2_blocks) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (q >= 2 * per_net + 3) return;
+  const float* src;
+  int64_t stride;
+  int rows, p, slot;
+  if (q < 2 * per_net) {
+    const int g = q / per_net, o = q % per_net;
+    if (o < d.H1 * (S + 1)) {                              // dW1aug[k][c], c == S is b1
+      const int k = o / (S + 1), c = o % (S + 1);
+      src = r.part_dw1 + (int64_t)g * d.H1 * 8 + k * 8 + c;
+      stride = (int64_t)2 * d.H1 * 8; rows = r.dw1_blocks;
+      p = g * d.SIZE + (c < S ? d.oW1 + k * S + c : d.ob1 + k);
+    } else {
+      const int o2 = o - d.H1 * (S + 1);                   // head row: [0,H2) dW3, [H2,2H2) db2, 2H2 db3
+      src = r.part_head + (int64_t)g * r.head_row + o2;
+      stride = (int64_t)2 * r.head_row; rows = r.head_blocks;
+      p = g * d.SIZE + (o2 < d.H2 ? d.oW3 + o2 : (o2 < 2 * d.H2 ? d.ob2 + (o2 - d.H2) : d.ob3));
+    }
+    slot = p;
+  } else {
+    const int l = q - 2 * per_net;                         // 0 loss1 sum, 1 sum e^2, 2 clipped count
+    const int g = l == 1 ? 1 : 0, col = 2 * d.H2 + (l == 2 ? 2 : 1);
+    src = r.part_head + (int64_t)g * r.head_row + col;
+    stride = (int64_t)2 * r.head_row; rows = r.head_blocks;
+    p = d.P + l; slot = r.pstride - 4 + l;
+  }
+  float s = 0.f;
+  for (int b0 = lane; b0 < rows; b0 += 32 * 8) {     // 8 independent loads per lane per round
+    float t[8];
+#pragma unroll
+    for (int u = 0; u < 8; u++) t[u] = (b0 + 32 * u < rows) ? src[(int64_t)(b0 + 32 * u) * stride] : 0.f;
+#pragma unroll
+    for (int u = 0; u < 8; u++) s += t[u];
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) wide_finish(r, coef, p, slot, s);
+}
+
+__global__ void __launch_bounds__(128) k_wide_adam(const UpdateArgs a, const NetDims d, int pstride, __nv_bfloat16* w2p,
+                                                   __nv_bfloat16* w2tp, float* bias2) {
+  __shared__ AdamCoef coef;
+  if (threadIdx.x == 0) coef = adam_coef(a.hp, *a.adam_step);
+  __syncthreads();
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
-  if (p < P) wide_adam_apply(a, p, a.grads[p], *a.adam_step);
-  else if (p < P + 3) wide_loss_log(a, p - P, a.grads[pstride - 4 + (p - P)]);
+  if (p < d.P) wide_store_planes(d, w2p, w2tp, bias2, p, wide_adam_apply(a, coef, p, a.grads[p]));
+  else if (p < d.P + 3) wide_loss_log(a, p - d.P, a.grads[pstride - 4 + (p - d.P)]);
 }
 
 }  // namespace
@@ -461,11 +544,11 @@ struct WideNet {
   NetDims d;
   int sm_count = 148;
   int64_t cap = 0;                 // samples per chunk, multiple of 128
-  __nv_bfloat16 *w2p = nullptr, *w2tp = nullptr, *h1p = nullptr, *h1tp = nullptr, *d2p = nullptr, *d2tp = nullptr;
+  __nv_bfloat16 *w2p = nullptr, *w2tp = nullptr, *h1p = nullptr, *d2p = nullptr;
   float *bias2 = nullptr, *h2 = nullptr, *d1 = nullptr;
   float *part_head = nullptr, *part_dw1 = nullptr, *part_dw2 = nullptr;
   int head_blocks = 0, head_row = 0, dw1_blocks = 0, splits_max = 0;
-  CUtensorMap tm_h1, tm_w2, tm_d2, tm_w2t, tm_d2t, tm_h1t;
+  CUtensorMap tm_h1, tm_w2, tm_d2, tm_w2t, tm_d2_mn, tm_h1_mn;
   int32_t* boot_idx = nullptr;
   int64_t boot_cap = 0;
   int* boot_count = nullptr;
@@ -480,7 +563,7 @@ int64_t wide_chunk_cap(const WideNet* w) { return w ? w->cap : 0; }
 
 void wide_destroy(WideNet* w) {
   if (!w) return;
-  cudaFree(w->w2p); cudaFree(w->w2tp); cudaFree(w->h1p); cudaFree(w->h1tp); cudaFree(w->d2p); cudaFree(w->d2tp);
+  cudaFree(w->w2p); cudaFree(w->w2tp); cudaFree(w->h1p); cudaFree(w->d2p);
   cudaFree(w->bias2); cudaFree(w->h2); cudaFree(w->d1);
   cudaFree(w->part_head); cudaFree(w->part_dw1); cudaFree(w->part_dw2);
   cudaFree(w->boot_idx); cudaFree(w->boot_count);
@@ -511,17 +594,13 @@ int wide_create(WideNet** out, int H1, int H2, int64_t max_chunk, int sm_count) 
   WCK(cudaMalloc(&w->w2p, bf * 4 * H2 * H1));
   WCK(cudaMalloc(&w->w2tp, bf * 4 * H2 * H1));
   WCK(cudaMalloc(&w->h1p, bf * 4 * cap * H1));
-  WCK(cudaMalloc(&w->h1tp, bf * 4 * cap * H1));
   WCK(cudaMalloc(&w->d2p, bf * 4 * cap * H2));
-  WCK(cudaMalloc(&w->d2tp, bf * 4 * cap * H2));
   WCK(cudaMalloc(&w->bias2, sizeof(float) * 2 * H2));
   WCK(cudaMalloc(&w->h2, sizeof(float) * 2 * cap * H2));
   WCK(cudaMalloc(&w->d1, sizeof(float) * 2 * cap * H1));
   // stale bits must never be NaN where a zero-weighted product could meet them
   WCK(cudaMemset(w->h1p, 0, bf * 4 * cap * H1));
-  WCK(cudaMemset(w->h1tp, 0, bf * 4 * cap * H1));
   WCK(cudaMemset(w->d2p, 0, bf * 4 * cap * H2));
-  WCK(cudaMemset(w->d2tp, 0, bf * 4 * cap * H2));
   w->head_blocks = 2 * sm_count;
   w->head_row = 2 * H2 + 4;
   w->dw1_blocks = sm_count;
@@ -538,9 +617,9 @@ int wide_create(WideNet** out, int H1, int H2, int64_t max_chunk, int sm_count) 
   if (!rc) rc = make_operand_map(&w->tm_w2, w->w2p, H1, H2, 4, H1, (uint64_t)H2 * H1, (uint32_t)H2);
   if (!rc) rc = make_operand_map(&w->tm_d2, w->d2p, H2, ucap, 4, H2, ucap * H2, 128);
   if (!rc) rc = make_operand_map(&w->tm_w2t, w->w2tp, H2, H1, 4, H2, (uint64_t)H2 * H1, (uint32_t)H1);
-  // feature-major activations: K = samples
-  if (!rc) rc = make_operand_map(&w->tm_d2t, w->d2tp, ucap, H2, 4, ucap, ucap * H2, 128);
-  if (!rc) rc = make_operand_map(&w->tm_h1t, w->h1tp, ucap, H1, 4, ucap, ucap * H1, (uint32_t)H1);
+  // the same sample-major planes read contraction-major (K = samples) by the dW2 GEMM: boxes of 64 features x 32 samples
+  if (!rc) rc = make_operand_map(&w->tm_d2_mn, w->d2p, H2, ucap, 4, H2, ucap * H2, MN_BOX_ROWS);
+  if (!rc) rc = make_operand_map(&w->tm_h1_mn, w->h1p, H1, ucap, 4, H1, ucap * H1, MN_BOX_ROWS);
   if (rc) { wide_destroy(w); return rc; }
   *out = w;
   return B2_OK;
@@ -549,7 +628,7 @@ int wide_create(WideNet** out, int H1, int H2, int64_t max_chunk, int sm_count) 
 template <int NJ>
 static cudaError_t launch_head(const WideArgs& wa, int grid, cudaStream_t st) {
   constexpr int H2 = NJ * 32;
-  const int smem = 4 * H2 * 17 * 4 + 8 * 2 * (2 * H2 + 4) * 4;
+  const int smem = 8 * 2 * (2 * H2 + 4) * 4;
   static bool attr = false;
   if (!attr) {
     cudaError_t e = cudaFuncSetAttribute(k_wide_head<NJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -566,7 +645,7 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
   WideArgs wa{};
   wa.d = d; wa.params = a.params; wa.tr = a.tr; wa.idx = a.idx; wa.cap = w->cap;
   wa.inv_denom = 1.0f / (float)a.denom; wa.hp = a.hp;
-  wa.w2p = w->w2p; wa.w2tp = w->w2tp; wa.h1p = w->h1p; wa.h1tp = w->h1tp; wa.d2p = w->d2p; wa.d2tp = w->d2tp;
+  wa.w2p = w->w2p; wa.w2tp = w->w2tp; wa.h1p = w->h1p; wa.d2p = w->d2p;
   wa.bias2 = w->bias2; wa.h2 = w->h2; wa.d1 = w->d1;
   wa.part_head = w->part_head; wa.part_dw1 = w->part_dw1; wa.head_row = w->head_row;
   cudaError_t ce;
@@ -576,16 +655,19 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
       return set_error(B2_ERR_CUDA, "wide %s: %s", what, cudaGetErrorString(ce));              \
     (*launches)++;                                                                             \
   } while (0)
-  k_wide_prep<<<128, 256, 0, st>>>(wa, a.adam_step);
-  LCK("prep");
+  if (a.step_slot == 0) {   // first optimizer step of this update: the weights may have been set from outside
+    k_wide_prep<<<128, 256, 0, st>>>(wa);
+    LCK("prep");
+  }
   const int64_t n_chunks = (a.count + w->cap - 1) / w->cap;
   for (int64_t c = 0; c < n_chunks; c++) {
     wa.first = a.first + c * w->cap;
     wa.count = (int)std::min<int64_t>(w->cap, a.count - c * w->cap);
     wa.m_pad = (wa.count + 127) / 128 * 128;
+    wa.bump_step = c == 0 ? a.adam_step : nullptr;
     const int m_tiles = wa.m_pad / 128;
     // layer 1
-    k_wide_l1<<<dim3(wa.m_pad / TILE_S, 2), 256, 0, st>>>(wa);
+    k_wide_l1<<<dim3(wa.m_pad / L1_TILE, 2), 256, 0, st>>>(wa);
     LCK("l1");
     // H2 = tanh(H1 W2^T + b2)
     GemmArgs g{};
@@ -597,7 +679,7 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     (*launches)++;
     // loss head, D2
     {
-      const int n_tiles = wa.m_pad / TILE_S;
+      const int n_tiles = wa.m_pad / 8;
       const int grid = n_tiles < w->head_blocks ? n_tiles : w->head_blocks;
       if (grid < w->head_blocks)   // rows of blocks that do not run this time must read as zero
         if ((ce = cudaMemsetAsync(w->part_head, 0, sizeof(float) * (size_t)w->head_blocks * 2 * w->head_row, st)) != cudaSuccess)
@@ -620,7 +702,7 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
       return set_error(B2_ERR_CUDA, "wide gemm bwd: %s", cudaGetErrorString(ce));
     (*launches)++;
     // dW2 partials = D2^T H1 over sample splits
-    const int kb_total = wa.m_pad / 64;
+    const int kb_total = wa.m_pad / MN_BOX_ROWS;
     const int jt = (H2 + 127) / 128;
     int splits = w->sm_count / (2 * jt);
     if (splits > kb_total) splits = kb_total;
@@ -630,9 +712,9 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     splits = (kb_total + kbps - 1) / kbps;
     g = GemmArgs{};
     g.G = 2; g.M = H2; g.N = H1; g.K = wa.m_pad; g.m_tiles = jt; g.splits = splits; g.kb_per_split = kbps;
-    g.stages = gemm_x3_stages(H1);
+    g.stages = gemm_x3_stages(H1, true); g.mn_major = 1;
     g.out = w->part_dw2; g.out_g_stride = (int64_t)splits * H2 * H1;
-    if ((ce = launch_gemm_x3(EPI_RAW, w->tm_d2t, w->tm_h1t, g, w->sm_count, st)) != cudaSuccess)
+    if ((ce = launch_gemm_x3(EPI_RAW, w->tm_d2_mn, w->tm_h1_mn, g, w->sm_count, st)) != cudaSuccess)
       return set_error(B2_ERR_CUDA, "wide gemm dW2: %s", cudaGetErrorString(ce));
     (*launches)++;
     // dW1, db1
@@ -644,8 +726,11 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     r.d = d; r.u = a; r.part_head = w->part_head; r.part_dw1 = w->part_dw1; r.part_dw2 = w->part_dw2;
     r.head_blocks = w->head_blocks; r.head_row = w->head_row; r.dw1_blocks = w->dw1_blocks; r.splits = splits;
     r.pstride = wide_pstride(H1, H2);
+    r.w2p = w->w2p; r.w2tp = w->w2tp; r.bias2 = w->bias2;
     r.first_chunk = c == 0; r.last_chunk = c == n_chunks - 1; r.apply_adam = apply_adam ? 1 : 0;
-    k_wide_reduce<<<(d.P + 3 + 127) / 128, 128, 0, st>>>(r);
+    const int w2_blocks = (2 * H2 * H1 + 127) / 128;
+    const int small = 2 * (H1 * (S + 1) + 2 * H2 + 1) + 3;
+    k_wide_reduce<<<w2_blocks + (small + 3) / 4, 128, 0, st>>>(r, w2_blocks);
     LCK("reduce");
   }
 #undef LCK
@@ -653,7 +738,7 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
 }
 
 cudaError_t launch_wide_adam(WideNet* w, const UpdateArgs& a, cudaStream_t st) {
-  k_wide_adam<<<(w->d.P + 3 + 127) / 128, 128, 0, st>>>(a, w->d.P, wide_pstride(w->d.H1, w->d.H2));
+  k_wide_adam<<<(w->d.P + 3 + 127) / 128, 128, 0, st>>>(a, w->d, wide_pstride(w->d.H1, w->d.H2), w->w2p, w->w2tp, w->bias2);
   return cudaGetLastError();
 }
 

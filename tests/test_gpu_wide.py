@@ -167,3 +167,16 @@ def test_wide_rollout_is_refused_loudly():
     with wide_engine(256, 256) as E:
         with pytest.raises(capi.B2Error):
             E.rollout(1)
+
+
+@pytest.mark.parametrize("M,N,K,splits", [(128, 256, 256, 1), (256, 256, 1000, 3), (64, 128, 96, 1), (192, 64, 4096, 5)])
+def test_gemm_bf16x3_mn_major(eng, M, N, K, splits):
+    """contraction-major operands (the dW2 = D2^T H1 layout): C = A^T B with A [K][M], B [K][N]"""
+    rng = np.random.default_rng(M + N + K)
+    A = rng.standard_normal((K, M)).astype(np.float32)
+    B = (rng.standard_normal((K, N)) / np.sqrt(K)).astype(np.float32)
+    Cm = eng.selftest_gemm(A, B, splits, mn_major=True)
+    ref = A.astype(np.float64).T @ B.astype(np.float64)
+    rel = np.linalg.norm(Cm - ref) / np.linalg.norm(ref)
+    print(f"gemm MN {M}x{N}x{K} splits {splits}: rel fro {rel:.2e}")
+    assert rel < 2e-5, rel
