@@ -4,11 +4,12 @@
 // Per optimizer step and per net the reference computes (src/ppo_nn.cpp:126-194 evaluate, :263-290 loss,
 // :301-303 backward + Adam):
 //     H1 = tanh(X W1^T + b1)        K = 6      -> FP32 FMA      (k_wide_l1)
-//     H2 = tanh(H1 W2^T + b2)       K = H1     -> tcgen05 GEMM  (k_gemm_x3<EPI_TANH>)
-//     y  = H2 W3^T + b3, loss head, D2 = dz3 (x) W3 .* (1 - H2^2)   (k_wide_head)
-//     D1 = (D2 W2) .* (1 - H1^2)    K = H2     -> tcgen05 GEMM  (k_gemm_x3<EPI_DTANH>)
-//     dW2 = D2^T H1                 K = samples-> tcgen05 GEMM  (k_gemm_x3<EPI_RAW>, split-K partials)
-//     dW1 = D1^T X, db1, db2, dW3, db3         -> FP32 FMA      (k_wide_dw1, k_wide_head)
+//     Z2 = H1 W2^T                  K = H1     -> tcgen05 GEMM  (k_gemm_x3<false>)
+//     H2 = tanh(Z2 + b2), y = H2 W3^T + b3, loss head, D2 = dz3 (x) W3 .* (1 - H2^2)   (k_wide_head)
+//     Z1 = D2 W2                    K = H2     -> tcgen05 GEMM  (k_gemm_x3<false>)
+//     dW2 = D2^T H1                 K = samples-> tcgen05 GEMM  (k_gemm_x3<true>, MN-major operands, split-K partials)
+//     D1 = Z1 .* (1 - H1^2), dW1 = D1^T X, db1 -> FP32 FMA      (k_wide_dw1, recomputes H1 from X)
+//     db2, dW3, db3                            -> FP32 FMA      (k_wide_head)
 // The three GEMMs hold 99 % of the 801,792 flop per sample-epoch.  The 1e-4 gradient gate
 // rules out single-pass BF16/TF32, so every fp32 operand is split into a (hi, mid) bf16 pair and each product
 // is issued as three bf16 MMAs hi*hi + mid*hi + hi*mid with fp32 accumulation in TMEM ("bf16x3", error
@@ -36,21 +37,18 @@ struct NetDims {
   }
 };
 
-enum { EPI_TANH = 0, EPI_DTANH = 1, EPI_RAW = 2 };
-
 struct GemmArgs {
   int G, M, N, K;                // per group g < G: C[M][N] = A[M][K] . B[N][K]^T ; K % 64 == 0, N % 16 == 0, N <= 256
   int m_tiles, splits, kb_per_split, stages;
-  int mn_major;                  // 1: C[M][N] = A[K][M]^T . B[K][N] (EPI_RAW only, K blocks of 32, K % 32 == 0, N % 64 == 0)
-  float* out;                    // EPI_TANH / EPI_DTANH: [G][out_rows][N] ; EPI_RAW: [G][splits][M][N]
-  int64_t out_g_stride;          // floats between groups
-  const float* bias;             // EPI_TANH: [G][N]
-  const __nv_bfloat16* hpl;      // EPI_DTANH: activation planes [G*2][h_rows][N] (hi, mid)
-  int64_t h_plane_stride;        // elements between planes
+  int mn_major;                  // 1: C[M][N] = A[K][M]^T . B[K][N] (K blocks of 32, K % 32 == 0, N % 64 == 0)
+                                 // output: raw fp32 accumulator tiles, TMA-stored to plane g * splits + split of tmC
+  long long* dbg;                // optional per-CTA timeline (clock64), diagnostic runs only
 };
 
-cudaError_t launch_gemm_x3(int epi, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& a, int sm_count,
-                           cudaStream_t st);
+cudaError_t launch_gemm_x3(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const GemmArgs& a,
+                           int sm_count, cudaStream_t st);
+// fp32 output tensor [planes][rows][N] the epilogue TMA-stores 32 x 32 tiles into (plane = group, or group*splits + split)
+int make_output_map(CUtensorMap* out, const void* base, uint64_t N, uint64_t rows, uint64_t planes);
 int gemm_x3_stages(int N, bool mn_major = false);
 
 // 3-D bf16 tensor map (K fastest, rows, planes) with a (64 x box_rows x 1) box and the 128-B swizzle.

@@ -1,18 +1,27 @@
-// wide_gemm.cu -- k_gemm_x3: persistent, warp-specialised tcgen05 GEMM with bf16x3 operands and fused epilogues.
+// wide_gemm.cu -- k_gemm_x3: persistent, warp-specialised tcgen05 GEMM with bf16x3 operands.
 //
 //   C[g][M][N] = A[g][M][K] . B[g][N][K]^T        (both operands K-major, fp32 values stored as (hi, mid) bf16 planes)
 //
-// One CTA per SM, 192 threads:
+// One CTA per SM, 320 threads:
 //   warp 0  : TMA producer   -- one lane streams 64-wide K blocks of A_hi, A_mid (128 rows) and B_hi, B_mid (N rows)
 //                               into a ring of shared-memory stages (cp.async.bulk.tensor, 128-B swizzle, mbarrier tx)
 //   warp 1  : MMA issuer     -- one lane issues 4 (K steps of 16) x 3 (hi*hi, mid*hi, hi*mid) tcgen05.mma per stage,
 //                               M = 128, N = whole width (<= 256), fp32 accumulator in TMEM; tcgen05.commit frees the
 //                               stage and, after the last K block, publishes the accumulator
-//   warps 2-5: epilogue      -- thread = accumulator row; tcgen05.ld 32 columns at a time, bias/tanh or tanh' or raw
-//                               store, 128 B contiguous per thread
+//   warps 2-9: epilogue      -- thread = accumulator row; tcgen05.ld 32 columns at a time, registers -> swizzled
+//                               shared tile -> TMA store of the raw fp32 accumulator.  (A direct row-per-thread store
+//                               costs the LSU 32 lines per instruction, and bias/tanh/tanh' in this epilogue were
+//                               MUFU- and load-latency-bound at 1-2x the MMA time of a tile; both measured with the
+//                               clock64 timeline of profiles/gemm_timeline.py.  The elementwise work now rides in the
+//                               memory-bound consumers: k_wide_head applies bias + tanh, k_wide_dw1 applies tanh'.)
 // TMEM holds two accumulators (2 x 256 columns) so the epilogue of tile i overlaps the MMAs of tile i+1.
 // Tiles are dealt statically: item = ((g * m_tiles) + mt) * splits + split, strided by gridDim.x.
 // Roofline: tensor (bf16 dense); algorithmic flop = 2 M N K per group, issued flop = 3x that.
+#include <stdio.h>
+#include <stdlib.h>
+
+#include <vector>
+
 #include "tc_ptx.cuh"
 #include "wide.h"
 #include "mlp.cuh"
@@ -22,10 +31,12 @@ namespace b2 {
 namespace {
 
 constexpr int BM = 128, BK = 64;
-constexpr int GEMM_THREADS = 192;
+constexpr int GEMM_THREADS = 320;              // TMA warp, MMA warp, 8 epilogue warps
 constexpr int A_PLANE_BYTES = BM * BK * 2;          // 16 KB
 constexpr int SMEM_LIMIT = 227 * 1024;
 constexpr int BAR_BYTES = 256;
+constexpr int STG_BUF = 4096;                 // one 32 x 32 fp32 output tile
+constexpr int STG_BYTES = 8 * STG_BUF;        // one staging tile per epilogue warp
 
 __host__ __device__ constexpr int stage_bytes(int N) { return 2 * A_PLANE_BYTES + 2 * N * BK * 2; }
 
@@ -36,9 +47,10 @@ __host__ __device__ constexpr int stage_bytes(int N) { return 2 * A_PLANE_BYTES 
 constexpr int BKS = 32;                       // samples per K block in MN mode
 constexpr int MNB_BYTES = BKS * 128;          // one 64-feature x 32-sample block
 
-template <int EPI, bool MN>
+template <bool MN>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
-k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmArgs a) {
+k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+          const __grid_constant__ CUtensorMap tmC, const GemmArgs a) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = tc::smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);   // 1024-B alignment for the 128-B swizzle atoms
@@ -47,7 +59,7 @@ k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
   const int SB = MN ? (4 + 2 * (N / 64)) * MNB_BYTES : stage_bytes(N);
   const int B_PLANE_BYTES = MN ? (N / 64) * MNB_BYTES : N * BK * 2;
   const int A_PLANE = MN ? 2 * MNB_BYTES : A_PLANE_BYTES;
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)stages * SB);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)stages * SB + STG_BYTES);
   uint64_t* empty = full + 8;
   uint64_t* tfull = empty + 8;
   uint64_t* tempty = tfull + 2;
@@ -59,8 +71,9 @@ k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
   if (warp == 0 && lane == 0) {
     tc::tma_prefetch_desc(&tmA);
     tc::tma_prefetch_desc(&tmB);
+    tc::tma_prefetch_desc(&tmC);
     for (int s = 0; s < stages; s++) { tc::mbar_init(&full[s], 1); tc::mbar_init(&empty[s], 1); }
-    for (int b = 0; b < 2; b++) { tc::mbar_init(&tfull[b], 1); tc::mbar_init(&tempty[b], 128); }
+    for (int b = 0; b < 2; b++) { tc::mbar_init(&tfull[b], 1); tc::mbar_init(&tempty[b], 256); }
     tc::fence_barrier_init();
   }
   if (warp == 1) tc::tmem_alloc(tmem_slot, 512);
@@ -68,6 +81,7 @@ k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (a.dbg && threadIdx.x == 0) a.dbg[(blockIdx.x * 4 + 0) * 8 + 7] = clock64();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -78,8 +92,10 @@ k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         const int g = item / (a.splits * a.m_tiles);
         const int kb0 = sp * a.kb_per_split;
         const int kb1 = min(kb0 + a.kb_per_split, kb_total);
+        if (a.dbg) a.dbg[(blockIdx.x * 4 + (item / gridDim.x)) * 8 + 0] = clock64();
         for (int kb = kb0; kb < kb1; kb++) {
           tc::mbar_wait(&empty[stage], phase ^ 1);
+          if (a.dbg && kb == kb1 - 1) a.dbg[(blockIdx.x * 4 + (item / gridDim.x)) * 8 + 1] = clock64();
           uint8_t* s = smem + (size_t)stage * SB;
           tc::mbar_arrive_expect_tx(&full[stage], (uint32_t)SB);
           if (MN) {
@@ -114,11 +130,14 @@ k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         const uint32_t bphase = (uint32_t)(it >> 1) & 1u;
         tc::mbar_wait(&tempty[buf], bphase ^ 1);       // epilogue has drained this accumulator
         tc::tc_fence_after();
+        if (a.dbg) a.dbg[(blockIdx.x * 4 + it) * 8 + 2] = clock64();
         const uint32_t d_tmem = tmem_base + (uint32_t)buf * 256u;
         uint32_t acc = 0;
         for (int kb = kb0; kb < kb1; kb++) {
           tc::mbar_wait(&full[stage], phase);
           tc::tc_fence_after();
+          if (a.dbg && kb == kb0) a.dbg[(blockIdx.x * 4 + it) * 8 + 3] = clock64();
+          if (a.dbg && kb == kb1 - 1) a.dbg[(blockIdx.x * 4 + it) * 8 + 4] = clock64();
           const uint32_t s = tc::smem_u32(smem + (size_t)stage * SB);
           if (MN) {
             const uint64_t mAh = tc::smem_desc_mn_sw128(s, MNB_BYTES), mAm = tc::smem_desc_mn_sw128(s + A_PLANE, MNB_BYTES);
@@ -156,7 +175,13 @@ k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     __syncwarp();
   } else {
     const int q = warp & 3;                             // TMEM lane quarter this warp may read
-    const int row_in_tile = q * 32 + lane;
+    // two warps share each TMEM lane quarter (and each SM sub-partition): one takes the low half of the columns, the
+    // other the high half, so one warp's tcgen05.ld / LDG / store latency hides under the other's tanh (MUFU) work
+    const int half = (warp - 2) >> 2;
+    const int n_chunks = N / 32;
+    const int c_begin = half ? ((n_chunks + 1) / 2) * 32 : 0;
+    const int c_end = half ? N : ((n_chunks + 1) / 2) * 32;
+    uint8_t* sb = smem + (size_t)stages * SB + (warp - 2) * STG_BUF;
     int it = 0;
     for (int item = blockIdx.x; item < n_items; item += gridDim.x, it++) {
       const int sp = item % a.splits;
@@ -166,53 +191,33 @@ k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
       const uint32_t bphase = (uint32_t)(it >> 1) & 1u;
       tc::mbar_wait(&tfull[buf], bphase);
       tc::tc_fence_after();
-      const int row = mt * BM + row_in_tile;
-      const bool valid = row < a.M;
+      if (a.dbg && threadIdx.x == 64 + 128) a.dbg[(blockIdx.x * 4 + it) * 8 + 5] = clock64();
+      const int row0 = mt * BM + q * 32;                 // first accumulator row of this warp
+      const int plane = g * a.splits + sp;
       const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * 256u;
-      float* orow;
-      if (EPI == EPI_RAW) orow = a.out + (int64_t)g * a.out_g_stride + ((int64_t)sp * a.M + row) * N;
-      else orow = a.out + (int64_t)g * a.out_g_stride + (int64_t)row * N;
-      for (int c = 0; c < N; c += 32) {
+      for (int c = c_begin; c < c_end; c += 32) {
         float v[32];
         tc::tmem_ld32(t0 + (uint32_t)c, v);
         tc::tmem_ld_wait();
-        if (EPI == EPI_TANH) {
-          const float4* b4 = reinterpret_cast<const float4*>(a.bias + g * N + c);
+        if (lane == 0) tc::bulk_wait_read<0>();          // the previous store has finished reading the staging tile
+        __syncwarp();
+        // registers -> shared (row = lane, 128-B swizzle: 16-B chunk i of row r sits at chunk i ^ (r & 7)) -> TMA store
 #pragma unroll
-          for (int i = 0; i < 8; i++) {
-            const float4 b = __ldg(b4 + i);
-            v[4 * i + 0] = act_tanh(v[4 * i + 0] + b.x); v[4 * i + 1] = act_tanh(v[4 * i + 1] + b.y);
-            v[4 * i + 2] = act_tanh(v[4 * i + 2] + b.z); v[4 * i + 3] = act_tanh(v[4 * i + 3] + b.w);
-          }
-        } else if (EPI == EPI_DTANH) {
-          if (valid) {
-            const __nv_bfloat16* hh = a.hpl + (int64_t)(g * 2) * a.h_plane_stride + (int64_t)row * N + c;
-            const __nv_bfloat16* hm = hh + a.h_plane_stride;
-#pragma unroll
-            for (int i = 0; i < 4; i++) {
-              const uint4 ph = __ldg(reinterpret_cast<const uint4*>(hh) + i);
-              const uint4 pm = __ldg(reinterpret_cast<const uint4*>(hm) + i);
-              const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&ph);
-              const __nv_bfloat162* m2 = reinterpret_cast<const __nv_bfloat162*>(&pm);
-#pragma unroll
-              for (int j = 0; j < 4; j++) {
-                const float2 fh = __bfloat1622float2(h2[j]), fm = __bfloat1622float2(m2[j]);
-                const float h0 = fh.x + fm.x, h1 = fh.y + fm.y;
-                v[8 * i + 2 * j] *= (1.0f - h0 * h0);
-                v[8 * i + 2 * j + 1] *= (1.0f - h1 * h1);
-              }
-            }
-          }
-        }
-        if (valid) {
-          float4* o4 = reinterpret_cast<float4*>(orow + c);
-#pragma unroll
-          for (int i = 0; i < 8; i++) o4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        for (int i = 0; i < 8; i++)
+          *reinterpret_cast<float4*>(sb + lane * 128 + ((i ^ (lane & 7)) << 4)) =
+              make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        tc::fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          tc::tma_store_3d(&tmC, sb, c, row0, plane);
+          tc::bulk_commit();
         }
       }
       tc::tc_fence_before();
       tc::mbar_arrive(&tempty[buf]);
+      if (a.dbg && threadIdx.x == 64 + 128) a.dbg[(blockIdx.x * 4 + it) * 8 + 6] = clock64();
     }
+    if (lane == 0) tc::bulk_wait_all();                  // every output tile has landed before the CTA retires
   }
 
   tc::tc_fence_before();
@@ -231,7 +236,7 @@ EncodeTiledFn g_encode = nullptr;
 }  // namespace
 
 int gemm_x3_stages(int N, bool mn_major) {
-  int s = (SMEM_LIMIT - 1024 - BAR_BYTES) / (mn_major ? (4 + 2 * (N / 64)) * MNB_BYTES : stage_bytes(N));
+  int s = (SMEM_LIMIT - 1024 - BAR_BYTES - STG_BYTES) / (mn_major ? (4 + 2 * (N / 64)) * MNB_BYTES : stage_bytes(N));
   if (s > 6) s = 6;
   return s;
 }
@@ -258,16 +263,35 @@ int make_operand_map(CUtensorMap* out, const void* base, uint64_t K, uint64_t ro
   return B2_OK;
 }
 
-cudaError_t launch_gemm_x3(int epi, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& a, int sm_count,
-                           cudaStream_t st) {
-  const int smem = a.stages * (a.mn_major ? (4 + 2 * (a.N / 64)) * MNB_BYTES : stage_bytes(a.N)) + BAR_BYTES + 1024;
+// fp32 output map: (N fastest, rows, planes), box 32 x 32 x 1, 128-B swizzle (matches the epilogue's staging tiles)
+int make_output_map(CUtensorMap* out, const void* base, uint64_t N, uint64_t rows, uint64_t planes) {
+  if (!g_encode) {
+    CUtensorMap tmp;
+    static __nv_bfloat16* dummy = nullptr;
+    if (!dummy) cudaMalloc(&dummy, 64 * 64 * 2);
+    int rc = make_operand_map(&tmp, dummy, 64, 64, 1, 64, 64 * 64, 32);   // resolves the driver entry point
+    if (rc) return rc;
+  }
+  cuuint64_t dims[3] = {N, rows, planes};
+  cuuint64_t strides[2] = {N * 4, rows * N * 4};
+  cuuint32_t box[3] = {32, 32, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_error(B2_ERR_CUDA, "cuTensorMapEncodeTiled(output) failed (%d): N=%llu rows=%llu planes=%llu", (int)r,
+                                          (unsigned long long)N, (unsigned long long)rows, (unsigned long long)planes);
+  return B2_OK;
+}
+
+cudaError_t launch_gemm_x3(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const GemmArgs& a,
+                           int sm_count, cudaStream_t st) {
+  const int smem = a.stages * (a.mn_major ? (4 + 2 * (a.N / 64)) * MNB_BYTES : stage_bytes(a.N)) + STG_BYTES + BAR_BYTES + 1024;
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e;
-    if ((e = cudaFuncSetAttribute(k_gemm_x3<EPI_TANH, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(k_gemm_x3<EPI_DTANH, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(k_gemm_x3<EPI_RAW, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(k_gemm_x3<EPI_RAW, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_gemm_x3<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_gemm_x3<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)) != cudaSuccess) return e;
     attr_set = true;
   }
   const int n_items = a.G * a.m_tiles * a.splits;
@@ -276,11 +300,9 @@ cudaError_t launch_gemm_x3(int epi, const CUtensorMap& tmA, const CUtensorMap& t
   // 1 CTA per SM is assumed by the 512-column TMEM allocation: always ask for more than half of the shared memory
   const int smem_req = smem > 120 * 1024 ? smem : 120 * 1024;
   if (a.mn_major) {
-    if (epi != EPI_RAW || (a.N % 64)) return cudaErrorInvalidValue;
-    k_gemm_x3<EPI_RAW, true><<<grid, GEMM_THREADS, smem_req, st>>>(tmA, tmB, a);
-  } else if (epi == EPI_TANH) k_gemm_x3<EPI_TANH, false><<<grid, GEMM_THREADS, smem_req, st>>>(tmA, tmB, a);
-  else if (epi == EPI_DTANH) k_gemm_x3<EPI_DTANH, false><<<grid, GEMM_THREADS, smem_req, st>>>(tmA, tmB, a);
-  else k_gemm_x3<EPI_RAW, false><<<grid, GEMM_THREADS, smem_req, st>>>(tmA, tmB, a);
+    if (a.N % 64) return cudaErrorInvalidValue;
+    k_gemm_x3<true><<<grid, GEMM_THREADS, smem_req, st>>>(tmA, tmB, tmC, a);
+  } else k_gemm_x3<false><<<grid, GEMM_THREADS, smem_req, st>>>(tmA, tmB, tmC, a);
   return cudaGetLastError();
 }
 
@@ -338,8 +360,33 @@ int wide_selftest_gemm(int M, int N, int K, const float* A_dev, const float* B_d
     GemmArgs g{};
     g.G = 1; g.M = M; g.N = N; g.K = (int)Kp; g.mn_major = mn_major ? 1 : 0;
     g.m_tiles = (M + BM - 1) / BM; g.splits = splits; g.kb_per_split = kbps; g.stages = gemm_x3_stages(N, mn_major != 0);
-    g.out = part; g.out_g_stride = 0;
-    cudaError_t e = launch_gemm_x3(EPI_RAW, tmA, tmB, g, sm_count, st);
+    CUtensorMap tmC;
+    if ((rc = make_output_map(&tmC, part, N, M, splits))) { cudaFree(pa); cudaFree(pb); cudaFree(part); return rc; }
+    long long* dbg = nullptr;
+    const char* dbg_env = getenv("B2_GEMM_DBG");
+    if (dbg_env) {
+      cudaMalloc(&dbg, sizeof(long long) * sm_count * 4 * 8);
+      cudaMemsetAsync(dbg, 0, sizeof(long long) * sm_count * 4 * 8, st);
+      g.dbg = dbg;
+    }
+    cudaError_t e = launch_gemm_x3(tmA, tmB, tmC, g, sm_count, st);
+    if (dbg_env && e == cudaSuccess) {
+      e = launch_gemm_x3(tmA, tmB, tmC, g, sm_count, st);   // second launch: warm L2
+      std::vector<long long> h((size_t)sm_count * 32);
+      cudaStreamSynchronize(st);
+      cudaMemcpy(h.data(), dbg, sizeof(long long) * h.size(), cudaMemcpyDeviceToHost);
+      for (int c : {0, 1, 73, 147}) {
+        if (c >= sm_count) continue;
+        const long long t0 = h[(size_t)c * 32 + 7];
+        for (int it = 0; it < 4; it++) {
+          const long long* r = &h[(size_t)(c * 4 + it) * 8];
+          if (!r[0] && !r[5]) continue;
+          fprintf(stderr, "cta %3d item %d: prod_first %6lld prod_last_issue %6lld | mma_start %6lld first_full %6lld last_full %6lld | epi_start %6lld epi_end %6lld (cycles after setup)\n",
+                  c, it, r[0] - t0, r[1] - t0, r[2] - t0, r[3] - t0, r[4] - t0, r[5] - t0, r[6] - t0);
+        }
+      }
+      cudaFree(dbg);
+    }
     if (e != cudaSuccess) rc = set_error(B2_ERR_CUDA, "gemm_x3: %s", cudaGetErrorString(e));
     else {
       k_sum_splits<<<256, 256, 0, st>>>(part, C_dev, (int64_t)M * N, splits);

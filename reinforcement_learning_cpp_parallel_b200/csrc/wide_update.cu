@@ -72,13 +72,15 @@ __global__ void __launch_bounds__(256) k_wide_prep(const WideArgs a) {
 // owns 8 consecutive features (their 56 weights stay in registers) and strides over the samples, so every store is a
 // 16-B vector and a warp writes 512 contiguous bytes of one row.  grid (m_pad / 128, 2 nets)
 constexpr int L1_TILE = 64;
-__global__ void __launch_bounds__(256) k_wide_l1(const WideArgs a) {
+__global__ void __launch_bounds__(256, 4) k_wide_l1(const WideArgs a) {
   __shared__ float xs[L1_TILE][S + 2];
-  __shared__ float ws[256 * (S + 1)];          // W1 [H1][S] then b1 [H1] of this net (contiguous in the parameter vector)
+  __shared__ __align__(16) float ws[32 * 52];   // per feature group of 8: 48 weights (+4 pad: conflict-free LDS.128)
+  __shared__ __align__(16) float bs[256];       // b1
   const int H1 = a.d.H1, g = blockIdx.y;
   const int s0 = blockIdx.x * L1_TILE;
   if (blockIdx.x == 0 && g == 0 && threadIdx.x == 0 && a.bump_step) *a.bump_step += 1;   // one optimizer step
-  for (int i = threadIdx.x; i < H1 * (S + 1); i += blockDim.x) ws[i] = a.params[g * a.d.SIZE + a.d.oW1 + i];
+  for (int i = threadIdx.x; i < H1 * S; i += blockDim.x) ws[(i / 48) * 52 + (i % 48)] = a.params[g * a.d.SIZE + a.d.oW1 + i];
+  for (int i = threadIdx.x; i < H1; i += blockDim.x) bs[i] = a.params[g * a.d.SIZE + a.d.ob1 + i];
   for (int i = threadIdx.x; i < L1_TILE * S; i += blockDim.x) {
     const int s = i / S, c = i % S;
     xs[s][c] = (s0 + s < a.count) ? a.tr.obs[c * a.tr.cap + sample_pos(a, s0 + s)] : 0.0f;
@@ -88,22 +90,27 @@ __global__ void __launch_bounds__(256) k_wide_l1(const WideArgs a) {
   const int groups = H1 / 8;                    // feature groups of 8
   const int kg = threadIdx.x % groups, sl = threadIdx.x / groups, sstep = blockDim.x / groups;
   if (sl >= sstep) return;                      // H1 = 192: 24 groups, 10 sample lanes, 16 idle threads
-  float w[8][S], b[8];
-#pragma unroll
-  for (int u = 0; u < 8; u++) {
-#pragma unroll
-    for (int c = 0; c < S; c++) w[u][c] = ws[(kg * 8 + u) * S + c];
-    b[u] = ws[H1 * S + kg * 8 + u];
-  }
+  const float* wg = ws + kg * 52;
   for (int s = sl; s < L1_TILE; s += sstep) {
     const bool valid = s0 + s < a.count;
     __align__(16) __nv_bfloat16 th[8], tm[8];
+    float x[S];
 #pragma unroll
-    for (int u = 0; u < 8; u++) {
-      float z = b[u];
+    for (int c = 0; c < S; c++) x[c] = xs[s][c];
 #pragma unroll
-      for (int c = 0; c < S; c++) z = fmaf(w[u][c], xs[s][c], z);
-      tc::split_bf16(valid ? act_tanh(z) : 0.0f, th[u], tm[u]);
+    for (int u4 = 0; u4 < 2; u4++) {             // 4 features at a time: 24 weights = 6 LDS.128
+      float w[24];
+#pragma unroll
+      for (int v = 0; v < 6; v++) *reinterpret_cast<float4*>(&w[4 * v]) = *reinterpret_cast<const float4*>(wg + u4 * 24 + 4 * v);
+      const float4 b4 = *reinterpret_cast<const float4*>(bs + kg * 8 + u4 * 4);
+      const float b[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        float z = b[u];
+#pragma unroll
+        for (int c = 0; c < S; c++) z = fmaf(w[u * S + c], x[c], z);
+        tc::split_bf16(valid ? act_tanh(z) : 0.0f, th[u4 * 4 + u], tm[u4 * 4 + u]);
+      }
     }
     const int64_t o = (int64_t)(s0 + s) * H1 + kg * 8;
     *reinterpret_cast<uint4*>(a.h1p + (g * 2 + 0) * plane + o) = *reinterpret_cast<const uint4*>(th);
@@ -111,22 +118,25 @@ __global__ void __launch_bounds__(256) k_wide_l1(const WideArgs a) {
   }
 }
 
-// layer 3 + loss head + D2 for both nets.  One warp per sample; lane l owns the NJ consecutive features
-// j = l*NJ .. l*NJ+NJ-1, so the H2 row is read and the D2 planes are written as contiguous vectors.  dW3, db2, db3 and
-// the loss sums are accumulated per lane over all samples of the block and written once, to this block's partial row.
+// layer 2 activation + layer 3 + loss head + D2 for both nets.  The GEMM left Z2 = H1 W2^T; here H2 = tanh(Z2 + b2).
+// One warp per sample; lane l owns the NJ consecutive features j = l*NJ .. l*NJ+NJ-1, so the Z2 row is read and the D2
+// planes are written as contiguous vectors.  The critic is finished first (its V feeds the actor's advantage, :274), so
+// only one net's activations are live at a time; W3 / b2 sit in shared memory.  dW3, db2, db3 and the loss sums are
+// accumulated per lane over all samples of the block and written once, to this block's partial row.
 template <int NJ>   // H2 / 32
-__global__ void __launch_bounds__(256) k_wide_head(const WideArgs a) {
-  extern __shared__ __align__(16) float red[];             // [8 warps][2 nets][2 * H2 + 4]
+__global__ void __launch_bounds__(256, 3) k_wide_head(const WideArgs a) {
+  extern __shared__ __align__(16) float hsm[];
   constexpr int H2 = NJ * 32;
+  float* wsm = hsm;                  // [2 nets][2][H2]: W3, b2
+  float* red = hsm + 4 * H2;         // [8 warps][2 nets][2 * H2 + 4]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const NetDims d = a.d;
-  float w3[2][NJ], b3[2];
-#pragma unroll
-  for (int g = 0; g < 2; g++) {
-#pragma unroll
-    for (int i = 0; i < NJ; i++) w3[g][i] = a.params[g * d.SIZE + d.oW3 + lane * NJ + i];
-    b3[g] = a.params[g * d.SIZE + d.ob3];
+  for (int i = threadIdx.x; i < 4 * H2; i += blockDim.x) {
+    const int g = i / (2 * H2), r = i % (2 * H2);
+    wsm[i] = a.params[g * d.SIZE + (r < H2 ? d.oW3 + r : d.ob2 + (r - H2))];
   }
+  const float b3a = a.params[d.ob3], b3c = a.params[d.SIZE + d.ob3];
+  __syncthreads();
   float gW3[2][NJ], gb2[2][NJ], gb3[2] = {0.f, 0.f};
 #pragma unroll
   for (int g = 0; g < 2; g++)
@@ -135,36 +145,73 @@ __global__ void __launch_bounds__(256) k_wide_head(const WideArgs a) {
   float loss1 = 0.f, loss2 = 0.f, clipped = 0.f;
   const int64_t plane = a.cap * H2;
 
-  for (int s = blockIdx.x * 8 + warp; s < a.m_pad; s += gridDim.x * 8) {
-    const bool valid = s < a.count;
-    float h[2][NJ], y[2] = {0.f, 0.f};
+  // one net of one sample: activation, dot with W3 (returned warp-reduced), h left in registers
+  auto forward = [&](int g, int s, bool valid, float (&h)[NJ]) {
+    const float2* zp = reinterpret_cast<const float2*>(a.h2 + ((int64_t)g * a.cap + s) * H2 + lane * NJ);
+    const float* w3 = wsm + g * 2 * H2 + lane * NJ;
+    const float* b2 = w3 + H2;
+    float y = 0.f;
 #pragma unroll
-    for (int g = 0; g < 2; g++) {
-      const float2* hp = reinterpret_cast<const float2*>(a.h2 + ((int64_t)g * a.cap + s) * H2 + lane * NJ);
+    for (int i = 0; i < NJ; i += 2) {
+      float2 t = make_float2(0.f, 0.f);
+      if (valid) {
+        t = zp[i >> 1];
+        t.x = act_tanh(t.x + b2[i]);
+        t.y = act_tanh(t.y + b2[i + 1]);
+      }
+      h[i] = t.x; h[i + 1] = t.y;
+      y = fmaf(w3[i], t.x, y);
+      y = fmaf(w3[i + 1], t.y, y);
+    }
 #pragma unroll
-      for (int i = 0; i < NJ; i += 2) {
-        const float2 t = valid ? hp[i >> 1] : make_float2(0.f, 0.f);
-        h[g][i] = t.x; h[g][i + 1] = t.y;
-        y[g] = fmaf(w3[g][i], t.x, y[g]);
-        y[g] = fmaf(w3[g][i + 1], t.y, y[g]);
+    for (int o = 16; o > 0; o >>= 1) y += __shfl_xor_sync(0xffffffffu, y, o);
+    return y;
+  };
+  // D2 = dz (x) W3 .* (1 - h^2) -> planes; column sums
+  auto backward = [&](int g, int s, float dz, const float (&h)[NJ]) {
+    const float* w3 = wsm + g * 2 * H2 + lane * NJ;
+    __align__(16) __nv_bfloat16 dh[NJ], dm[NJ];
+#pragma unroll
+    for (int i = 0; i < NJ; i++) {
+      const float dd = dz * w3[i] * (1.0f - h[i] * h[i]);
+      gW3[g][i] = fmaf(dz, h[i], gW3[g][i]);
+      gb2[g][i] += dd;
+      tc::split_bf16(dd, dh[i], dm[i]);
+    }
+    const int64_t o = (int64_t)s * H2 + lane * NJ;
+    uint32_t* oh = reinterpret_cast<uint32_t*>(a.d2p + (g * 2 + 0) * plane + o);
+    uint32_t* om = reinterpret_cast<uint32_t*>(a.d2p + (g * 2 + 1) * plane + o);
+    if (NJ == 8) {
+      *reinterpret_cast<uint4*>(oh) = *reinterpret_cast<const uint4*>(dh);
+      *reinterpret_cast<uint4*>(om) = *reinterpret_cast<const uint4*>(dm);
+    } else {
+#pragma unroll
+      for (int i = 0; i < NJ / 2; i++) {
+        oh[i] = reinterpret_cast<const uint32_t*>(dh)[i];
+        om[i] = reinterpret_cast<const uint32_t*>(dm)[i];
       }
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      y[0] += __shfl_xor_sync(0xffffffffu, y[0], o);
-      y[1] += __shfl_xor_sync(0xffffffffu, y[1], o);
-    }
-    float dz[2] = {0.f, 0.f};
+  };
+
+  for (int s = blockIdx.x * 8 + warp; s < a.m_pad; s += gridDim.x * 8) {
+    const bool valid = s < a.count;
+    float R = 0.f, act = 0.f, oldlp = 0.f;
     if (valid) {
       const int64_t p = sample_pos(a, s);
-      const float R = a.tr.ret[p];
-      const float V = y[1] + b3[1];                                  // critic: no final activation (ppo_nn.h:118-122)
-      const float e = V - R;
-      dz[1] = e * a.inv_denom;                                       // d(0.5 mean e^2)/dV  (:288)
-      const float mu = act_tanh(y[0] + b3[0]);                       // ppo_nn.h:102
-      const float act = a.tr.action[p];
+      R = a.tr.ret[p]; act = a.tr.action[p]; oldlp = a.tr.logp[p];
+    }
+    float h[NJ];
+    // ---- critic: no final activation (ppo_nn.h:118-122)
+    const float V = forward(1, s, valid, h) + b3c;
+    const float e = V - R;
+    const float dzc = valid ? e * a.inv_denom : 0.f;                 // d(0.5 mean e^2)/dV  (:288)
+    backward(1, s, dzc, h);
+    // ---- actor
+    const float mu = act_tanh(forward(0, s, valid, h) + b3a);        // ppo_nn.h:102
+    float dza = 0.f;
+    if (valid) {
       const float lp = gauss_logprob(act, mu, a.hp.inv_var, a.hp.half_log_norm);  // :140
-      const float ratio = expf(lp - a.tr.logp[p]);                   // :263
+      const float ratio = expf(lp - oldlp);                          // :263
       const float A = R - V;                                         // :274 (detached)
       const float surr1 = ratio * A;                                 // :284
       const float rc = fminf(fmaxf(ratio, a.hp.clip_lo), a.hp.clip_hi);
@@ -176,39 +223,16 @@ __global__ void __launch_bounds__(256) k_wide_head(const WideArgs a) {
       else gr = 0.5f * A + (inside ? 0.5f * A : 0.f);
       const float dlogp = -gr * ratio * a.inv_denom;
       const float dmu = dlogp * (act - mu) * a.hp.inv_var;           // :20-31
-      dz[0] = dmu * (1.0f - mu * mu);
+      dza = dmu * (1.0f - mu * mu);
       if (lane == 0) {
         loss2 = fmaf(e, e, loss2);
         loss1 -= fminf(surr1, surr2);                                // :287
         clipped += inside ? 0.f : 1.f;
-        gb3[0] += dz[0];
-        gb3[1] += dz[1];
+        gb3[0] += dza;
+        gb3[1] += dzc;
       }
     }
-#pragma unroll
-    for (int g = 0; g < 2; g++) {
-      __align__(16) __nv_bfloat16 dh[NJ], dm[NJ];
-#pragma unroll
-      for (int i = 0; i < NJ; i++) {
-        const float dd = dz[g] * w3[g][i] * (1.0f - h[g][i] * h[g][i]);
-        gW3[g][i] = fmaf(dz[g], h[g][i], gW3[g][i]);
-        gb2[g][i] += dd;
-        tc::split_bf16(dd, dh[i], dm[i]);
-      }
-      const int64_t o = (int64_t)s * H2 + lane * NJ;
-      uint32_t* oh = reinterpret_cast<uint32_t*>(a.d2p + (g * 2 + 0) * plane + o);
-      uint32_t* om = reinterpret_cast<uint32_t*>(a.d2p + (g * 2 + 1) * plane + o);
-      if (NJ == 8) {
-        *reinterpret_cast<uint4*>(oh) = *reinterpret_cast<const uint4*>(dh);
-        *reinterpret_cast<uint4*>(om) = *reinterpret_cast<const uint4*>(dm);
-      } else {
-#pragma unroll
-        for (int i = 0; i < NJ / 2; i++) {
-          oh[i] = reinterpret_cast<const uint32_t*>(dh)[i];
-          om[i] = reinterpret_cast<const uint32_t*>(dm)[i];
-        }
-      }
-    }
+    backward(0, s, dza, h);
   }
 
   // block reduction of the per-lane column sums -> this block's partial row (fixed order: deterministic)
@@ -234,26 +258,47 @@ __global__ void __launch_bounds__(256) k_wide_head(const WideArgs a) {
   }
 }
 
-// dW1aug[k][c] = sum_s D1[s][k] x[s][c] (c = 6: ones -> db1).  thread = feature k, block = contiguous sample range.
-// grid (blocks, 2 nets); partial row [blk][g][k * 8 + c]
-__global__ void __launch_bounds__(256) k_wide_dw1(const WideArgs a, int samples_per_block) {
-  __shared__ float xs[64][S + 2];
+// dW1aug[k][c] = sum_s D1[s][k] x[s][c] (c = 6: ones -> db1) with D1 = Z1 .* (1 - H1^2): the GEMM left Z1 = D2 W2 and
+// H1 is recomputed from X exactly as k_wide_l1 computes it.  thread = (sample half, feature k); a block owns a contiguous
+// sample range, its two halves are folded through shared memory at the end.  grid (blocks, 2 nets), 512 threads;
+// partial row [blk][g][k * 8 + c]
+__global__ void __launch_bounds__(512) k_wide_dw1(const WideArgs a, int samples_per_block) {
+  __shared__ float xs[2][64][S + 2];
+  __shared__ float fold[256][S + 2];
   const int H1 = a.d.H1, g = blockIdx.y;
+  const int half = threadIdx.x >> 8, k = threadIdx.x & 255, ht = threadIdx.x & 255;
   const int sb = blockIdx.x * samples_per_block;
   const int se = min(sb + samples_per_block, a.count);
+  const int len = max(se - sb, 0), hlen = (len + 1) / 2;
+  const int hb = sb + half * hlen, he = min(hb + hlen, se);      // this half's sample range
   float acc[S + 1];
 #pragma unroll
   for (int c = 0; c <= S; c++) acc[c] = 0.f;
-  const int k = threadIdx.x;
-  for (int t0 = sb; t0 < se; t0 += 64) {
-    const int nt = min(64, se - t0);
+  float w1[S], b1 = 0.f;
+#pragma unroll
+  for (int c = 0; c < S; c++) w1[c] = 0.f;
+  if (k < H1) {
+#pragma unroll
+    for (int c = 0; c < S; c++) w1[c] = a.params[g * a.d.SIZE + a.d.oW1 + k * S + c];
+    b1 = a.params[g * a.d.SIZE + a.d.ob1 + k];
+  }
+  auto d1_of = [&](float z1, const float* x) {
+    float z = b1;
+#pragma unroll
+    for (int c = 0; c < S; c++) z = fmaf(w1[c], x[c], z);
+    const float h = act_tanh(z);
+    return z1 * (1.0f - h * h);
+  };
+  for (int off = 0; off < hlen; off += 64) {                     // uniform trip count for both halves
+    const int t0 = hb + off;
+    const int nt = max(min(64, he - t0), 0);
     __syncthreads();
-    for (int i = threadIdx.x; i < nt * S; i += blockDim.x) {
+    for (int i = ht; i < nt * S; i += 256) {
       const int s = i / S, c = i % S;
-      xs[s][c] = a.tr.obs[c * a.tr.cap + sample_pos(a, t0 + s)];
+      xs[half][s][c] = a.tr.obs[c * a.tr.cap + sample_pos(a, t0 + s)];
     }
     __syncthreads();
-    if (k < H1) {
+    if (k < H1 && nt > 0) {
       const float* dp = a.d1 + ((int64_t)g * a.cap + t0) * H1 + k;
       int s = 0;
       for (; s + 16 <= nt; s += 16) {          // 16 independent loads in flight per thread
@@ -262,23 +307,29 @@ __global__ void __launch_bounds__(256) k_wide_dw1(const WideArgs a, int samples_
         for (int u = 0; u < 16; u++) dv[u] = dp[(int64_t)(s + u) * H1];
 #pragma unroll
         for (int u = 0; u < 16; u++) {
+          dv[u] = d1_of(dv[u], xs[half][s + u]);
 #pragma unroll
-          for (int c = 0; c < S; c++) acc[c] = fmaf(dv[u], xs[s + u][c], acc[c]);
+          for (int c = 0; c < S; c++) acc[c] = fmaf(dv[u], xs[half][s + u][c], acc[c]);
           acc[S] += dv[u];
         }
       }
       for (; s < nt; s++) {
-        const float dv = dp[(int64_t)s * H1];
+        const float dv = d1_of(dp[(int64_t)s * H1], xs[half][s]);
 #pragma unroll
-        for (int c = 0; c < S; c++) acc[c] = fmaf(dv, xs[s][c], acc[c]);
+        for (int c = 0; c < S; c++) acc[c] = fmaf(dv, xs[half][s][c], acc[c]);
         acc[S] += dv;
       }
     }
   }
-  if (k < H1) {
+  if (half == 1) {
+#pragma unroll
+    for (int c = 0; c <= S; c++) fold[k][c] = acc[c];
+  }
+  __syncthreads();
+  if (half == 0 && k < H1) {
     float* out = a.part_dw1 + ((int64_t)blockIdx.x * 2 + g) * H1 * 8 + k * 8;
 #pragma unroll
-    for (int c = 0; c <= S; c++) out[c] = acc[c];
+    for (int c = 0; c <= S; c++) out[c] = acc[c] + fold[k][c];
     out[S + 1] = 0.f;
   }
 }
@@ -367,12 +418,19 @@ __global__ void __launch_bounds__(128) k_wide_reduce(const ReduceArgs r, int w2_
     const float* base = r.part_dw2 + (int64_t)g * r.splits * w2n + e;
     float s = 0.f;
     int sp = 0;
-    for (; sp + 8 <= r.splits; sp += 8) {
-      float t[8];
+    for (; sp + 16 <= r.splits; sp += 16) {
+      float t[16];
 #pragma unroll
-      for (int u = 0; u < 8; u++) t[u] = base[(int64_t)(sp + u) * w2n];
+      for (int u = 0; u < 16; u++) t[u] = base[(int64_t)(sp + u) * w2n];
 #pragma unroll
-      for (int u = 0; u < 8; u++) s += t[u];
+      for (int u = 0; u < 16; u++) s += t[u];
+    }
+    for (; sp + 4 <= r.splits; sp += 4) {
+      float t[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) t[u] = base[(int64_t)(sp + u) * w2n];
+#pragma unroll
+      for (int u = 0; u < 4; u++) s += t[u];
     }
     for (; sp < r.splits; sp++) s += base[(int64_t)sp * w2n];
     const int p = g * d.SIZE + d.oW2 + e;
@@ -549,6 +607,7 @@ struct WideNet {
   float *part_head = nullptr, *part_dw1 = nullptr, *part_dw2 = nullptr;
   int head_blocks = 0, head_row = 0, dw1_blocks = 0, splits_max = 0;
   CUtensorMap tm_h1, tm_w2, tm_d2, tm_w2t, tm_d2_mn, tm_h1_mn;
+  CUtensorMap tm_out_h2, tm_out_d1, tm_out_dw2;
   int32_t* boot_idx = nullptr;
   int64_t boot_cap = 0;
   int* boot_count = nullptr;
@@ -601,7 +660,7 @@ int wide_create(WideNet** out, int H1, int H2, int64_t max_chunk, int sm_count) 
   // stale bits must never be NaN where a zero-weighted product could meet them
   WCK(cudaMemset(w->h1p, 0, bf * 4 * cap * H1));
   WCK(cudaMemset(w->d2p, 0, bf * 4 * cap * H2));
-  w->head_blocks = 2 * sm_count;
+  w->head_blocks = 3 * sm_count;
   w->head_row = 2 * H2 + 4;
   w->dw1_blocks = sm_count;
   w->splits_max = sm_count;
@@ -620,6 +679,9 @@ int wide_create(WideNet** out, int H1, int H2, int64_t max_chunk, int sm_count) 
   // the same sample-major planes read contraction-major (K = samples) by the dW2 GEMM: boxes of 64 features x 32 samples
   if (!rc) rc = make_operand_map(&w->tm_d2_mn, w->d2p, H2, ucap, 4, H2, ucap * H2, MN_BOX_ROWS);
   if (!rc) rc = make_operand_map(&w->tm_h1_mn, w->h1p, H1, ucap, 4, H1, ucap * H1, MN_BOX_ROWS);
+  if (!rc) rc = make_output_map(&w->tm_out_h2, w->h2, H2, ucap, 2);
+  if (!rc) rc = make_output_map(&w->tm_out_d1, w->d1, H1, ucap, 2);
+  if (!rc) rc = make_output_map(&w->tm_out_dw2, w->part_dw2, H1, H2, (uint64_t)2 * w->splits_max);
   if (rc) { wide_destroy(w); return rc; }
   *out = w;
   return B2_OK;
@@ -628,7 +690,7 @@ int wide_create(WideNet** out, int H1, int H2, int64_t max_chunk, int sm_count) 
 template <int NJ>
 static cudaError_t launch_head(const WideArgs& wa, int grid, cudaStream_t st) {
   constexpr int H2 = NJ * 32;
-  const int smem = 8 * 2 * (2 * H2 + 4) * 4;
+  const int smem = (4 * H2 + 8 * 2 * (2 * H2 + 4)) * 4;
   static bool attr = false;
   if (!attr) {
     cudaError_t e = cudaFuncSetAttribute(k_wide_head<NJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -673,8 +735,7 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     GemmArgs g{};
     g.G = 2; g.M = wa.count; g.N = H2; g.K = H1; g.m_tiles = m_tiles; g.splits = 1; g.kb_per_split = H1 / 64;
     g.stages = gemm_x3_stages(H2);
-    g.out = w->h2; g.out_g_stride = w->cap * H2; g.bias = w->bias2;
-    if ((ce = launch_gemm_x3(EPI_TANH, w->tm_h1, w->tm_w2, g, w->sm_count, st)) != cudaSuccess)
+    if ((ce = launch_gemm_x3(w->tm_h1, w->tm_w2, w->tm_out_h2, g, w->sm_count, st)) != cudaSuccess)
       return set_error(B2_ERR_CUDA, "wide gemm fwd: %s", cudaGetErrorString(ce));
     (*launches)++;
     // loss head, D2
@@ -697,8 +758,7 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     g = GemmArgs{};
     g.G = 2; g.M = wa.count; g.N = H1; g.K = H2; g.m_tiles = m_tiles; g.splits = 1; g.kb_per_split = H2 / 64;
     g.stages = gemm_x3_stages(H1);
-    g.out = w->d1; g.out_g_stride = w->cap * H1; g.hpl = w->h1p; g.h_plane_stride = w->cap * H1;
-    if ((ce = launch_gemm_x3(EPI_DTANH, w->tm_d2, w->tm_w2t, g, w->sm_count, st)) != cudaSuccess)
+    if ((ce = launch_gemm_x3(w->tm_d2, w->tm_w2t, w->tm_out_d1, g, w->sm_count, st)) != cudaSuccess)
       return set_error(B2_ERR_CUDA, "wide gemm bwd: %s", cudaGetErrorString(ce));
     (*launches)++;
     // dW2 partials = D2^T H1 over sample splits
@@ -713,13 +773,12 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     g = GemmArgs{};
     g.G = 2; g.M = H2; g.N = H1; g.K = wa.m_pad; g.m_tiles = jt; g.splits = splits; g.kb_per_split = kbps;
     g.stages = gemm_x3_stages(H1, true); g.mn_major = 1;
-    g.out = w->part_dw2; g.out_g_stride = (int64_t)splits * H2 * H1;
-    if ((ce = launch_gemm_x3(EPI_RAW, w->tm_d2_mn, w->tm_h1_mn, g, w->sm_count, st)) != cudaSuccess)
+    if ((ce = launch_gemm_x3(w->tm_d2_mn, w->tm_h1_mn, w->tm_out_dw2, g, w->sm_count, st)) != cudaSuccess)
       return set_error(B2_ERR_CUDA, "wide gemm dW2: %s", cudaGetErrorString(ce));
     (*launches)++;
     // dW1, db1
     const int spb = (wa.count + w->dw1_blocks - 1) / w->dw1_blocks;
-    k_wide_dw1<<<dim3(w->dw1_blocks, 2), 256, 0, st>>>(wa, spb < 1 ? 1 : spb);
+    k_wide_dw1<<<dim3(w->dw1_blocks, 2), 512, 0, st>>>(wa, spb < 1 ? 1 : spb);
     LCK("dw1");
     // reduce (+ Adam on the last chunk)
     ReduceArgs r{};

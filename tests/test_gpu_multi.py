@@ -78,3 +78,77 @@ def test_two_gpu_update_matches_one_gpu():
     assert rel(res[0][4], g1) < 1e-5, rel(res[0][4], g1)        # different reduction tree only
     assert rel(res[0][5], p1) < 1e-6, rel(res[0][5], p1)
     assert abs(res[0][6] - st.loss) < 1e-5 * abs(st.loss) and res[0][7] == st.adam_step == K
+
+
+# ---- wide nets (BASELINE configs[4]): each rank holds half of every minibatch, gradients all-reduced over NCCL ----
+WB, WK, WM = 2048, 2, 2
+
+
+def _wide_batch():
+    import ctypes as C
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import helpers as H
+    rng = np.random.default_rng(99)
+    dims = H.Dims(6, 256, 256, 1)
+    th = 0.3 * rng.standard_normal(WB)
+    obs = np.stack([rng.standard_normal(WB), rng.standard_normal(WB), rng.standard_normal(WB), th, np.cos(th), np.sin(th)],
+                   1).astype(np.float32)
+    return dims, obs, rng.standard_normal(WB).astype(np.float32), (rng.random(WB) < 0.9).astype(np.float32)
+
+
+def _wide_rank(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    import reinforcement_learning_cpp_parallel_b200 as pkg
+    from reinforcement_learning_cpp_parallel_b200 import capi, sharding
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        dims, obs, eps, reward = _wide_batch()
+        E = pkg.Engine(capi.default_config(n_envs=WB // world, horizon=1, hidden1=256, hidden2=256, k_epochs=WK,
+                                           n_minibatches=WM, device=rank))
+        E.init_params(4)
+        E.comm_init(rank, world, sharding.broadcast_comm_id(dist, pkg.Engine.comm_unique_id))
+        act, lp, _ = E.act(obs, eps)
+        # global minibatch m = records [m*B/M, (m+1)*B/M); this rank takes its half of each, keeping minibatch order
+        per = WB // WM
+        half = per // world
+        sel = np.concatenate([np.arange(m * per + rank * half, m * per + (rank + 1) * half) for m in range(WM)])
+        st = E.update(obs[sel], act[sel], lp[sel], reward[sel], np.ones(sel.size, np.uint8))
+        q.put((rank, E.get_grads(), E.get_params(), st.loss, st.adam_step))
+        E.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_gpu_wide_update_matches_one_gpu():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    import reinforcement_learning_cpp_parallel_b200 as pkg
+    from reinforcement_learning_cpp_parallel_b200 import capi
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_wide_rank, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=300) for _ in procs], key=lambda r: r[0])
+    for p in procs:
+        p.join(60)
+    dims, obs, eps, reward = _wide_batch()
+    E = pkg.Engine(capi.default_config(n_envs=WB, horizon=1, hidden1=256, hidden2=256, k_epochs=WK, n_minibatches=WM))
+    E.init_params(4)
+    act, lp, _ = E.act(obs, eps)
+    st = E.update(obs, act, lp, reward, np.ones(WB, np.uint8))
+    g1, p1 = E.get_grads(), E.get_params()
+    E.close()
+    np.testing.assert_array_equal(res[0][2], res[1][2])          # weights bit-identical across ranks
+    rel = lambda a, b: float(np.linalg.norm(a.astype(np.float64) - b) / np.linalg.norm(b.astype(np.float64)))
+    assert rel(res[0][1], g1) < 2e-5, rel(res[0][1], g1)
+    assert rel(res[0][2], p1) < 1e-6, rel(res[0][2], p1)
+    assert abs(res[0][3] - st.loss) < 1e-4 * abs(st.loss) and res[0][4] == st.adam_step == WK * WM
