@@ -151,6 +151,13 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
+def _ncu_traffic(key):
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "NCU_TRAFFIC.json"))).get(key)
+    except Exception:
+        return None
+
+
 def wide_leg(args, pkg, capi, np, rank, local, world, dist, barrier, max_over_ranks, bf16_peak, bf16_src):
     """BASELINE configs[4]: PPO update sweep, 2x256 MLPs, 4M-sample batch over 8 GPUs = 524,288 samples per GPU,
     32 minibatches x 10 epochs; weak scaling (every rank owns its own 524,288 samples, gradients all-reduced)."""
@@ -213,7 +220,8 @@ def wide_leg(args, pkg, capi, np, rank, local, world, dist, barrier, max_over_ra
             "roofline": {"kernel": "k_gemm_x3", "bound": "tensor", "achieved": ach, "peak": bf16_peak / 3.0,
                          "unit": "TFLOP/s", "frac": ach / (bf16_peak / 3.0) if bf16_peak else None,
                          "peak_source": bf16_src + " / 3 (every fp32 product is three bf16 MMAs)",
-                         "issued_bf16_tflops": 3 * ach, "flop_per_sample_epoch": FLOP_UPDATE_WIDE, "traffic": None},
+                         "issued_bf16_tflops": 3 * ach, "flop_per_sample_epoch": FLOP_UPDATE_WIDE,
+                         "traffic": _ncu_traffic("k_gemm_x3_fwd_2x16384x256x256")},
             "last_loss": st.loss}
 
 
