@@ -37,12 +37,27 @@ struct NetDims {
   }
 };
 
+// k_wide_dw1's work, carried by eight extra warps of the dW2 GEMM kernel (FP32 pipe beside the tensor pipe): per CTA a
+// contiguous slice of the chunk's samples, both nets; D1 = Z1 .* (1 - H1^2), dW1aug = D1^T [x, 1] -> part[cta][g][k*8+c]
+struct Dw1Args {
+  const float* params;      // null: no fused dw1 work
+  const float* obs;         // trajectory observations, SoA: obs[c * obs_cap + position]
+  int64_t obs_cap;
+  const int32_t* idx;
+  int64_t first;
+  int count, H1, SIZE, oW1, ob1;
+  const float* z1;          // [2][cap][H1]
+  int64_t cap;
+  float* part;              // [grid][2][H1 * 8]
+};
+
 struct GemmArgs {
   int G, M, N, K;                // per group g < G: C[M][N] = A[M][K] . B[N][K]^T ; K % 64 == 0, N % 16 == 0, N <= 256
   int m_tiles, splits, kb_per_split, stages;
   int mn_major;                  // 1: C[M][N] = A[K][M]^T . B[K][N] (K blocks of 32, K % 32 == 0, N % 64 == 0)
                                  // output: raw fp32 accumulator tiles, TMA-stored to plane g * splits + split of tmC
   long long* dbg;                // optional per-CTA timeline (clock64), diagnostic runs only
+  Dw1Args dw1;                   // MN-major kernel only
 };
 
 cudaError_t launch_gemm_x3(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const GemmArgs& a,

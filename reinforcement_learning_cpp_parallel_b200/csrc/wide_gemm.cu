@@ -47,8 +47,89 @@ __host__ __device__ constexpr int stage_bytes(int N) { return 2 * A_PLANE_BYTES 
 constexpr int BKS = 32;                       // samples per K block in MN mode
 constexpr int MNB_BYTES = BKS * 128;          // one 64-feature x 32-sample block
 
+constexpr int DW1_THREADS = 512;              // extra warps 10..25 of the MN-major kernel (fused k_wide_dw1 work)
+constexpr int DW1_SMEM = (2 * 64 * 8 + 256 * 8) * 4;   // two 64-sample observation tiles + the fold buffer
+
+// The dW1 / db1 partials of this CTA's slice of samples (see Dw1Args).  512 threads = 2 sample halves x 256 features;
+// loads of Z1 are coalesced across k and batched 16 samples deep; H1 is recomputed from x exactly as k_wide_l1 computes
+// it; the two halves are folded through shared memory in a fixed order.
+__device__ __forceinline__ void dw1_worker(const Dw1Args& w, float* sm, int t) {
+  const int spb = (w.count + (int)gridDim.x - 1) / (int)gridDim.x;
+  const int sb = min((int)blockIdx.x * spb, w.count), se = min(sb + spb, w.count);
+  const int half = t >> 8, k = t & 255;
+  const int hlen = (se - sb + 1) / 2;
+  const int hb = sb + half * hlen, he = min(hb + hlen, se);
+  float* xs = sm + half * 64 * 8;
+  float* fold = sm + 2 * 64 * 8;
+#pragma unroll 1
+  for (int g = 0; g < 2; g++) {
+    float acc[OBS + 1], w1[OBS], b1 = 0.f;
+#pragma unroll
+    for (int c = 0; c <= OBS; c++) acc[c] = 0.f;
+#pragma unroll
+    for (int c = 0; c < OBS; c++) w1[c] = 0.f;
+    if (k < w.H1) {
+#pragma unroll
+      for (int c = 0; c < OBS; c++) w1[c] = w.params[g * w.SIZE + w.oW1 + k * OBS + c];
+      b1 = w.params[g * w.SIZE + w.ob1 + k];
+    }
+    auto d1_of = [&](float z1, const float* x) {
+      float z = b1;
+#pragma unroll
+      for (int c = 0; c < OBS; c++) z = fmaf(w1[c], x[c], z);
+      const float h = act_tanh(z);
+      return z1 * (1.0f - h * h);
+    };
+    for (int off = 0; off < hlen; off += 64) {           // uniform trip count for both halves
+      const int t0 = hb + off;
+      const int nt = max(min(64, he - t0), 0);
+      asm volatile("bar.sync 1, %0;" ::"n"(DW1_THREADS) : "memory");
+      for (int i = k; i < nt * OBS; i += 256) {
+        const int s = i / OBS, c = i % OBS;
+        const int64_t p = w.first + t0 + s;
+        xs[s * 8 + c] = w.obs[c * w.obs_cap + (w.idx ? (int64_t)w.idx[p] : p)];
+      }
+      asm volatile("bar.sync 1, %0;" ::"n"(DW1_THREADS) : "memory");
+      if (k < w.H1 && nt > 0) {
+        const float* dp = w.z1 + ((int64_t)g * w.cap + t0) * w.H1 + k;
+        int s = 0;
+        for (; s + 16 <= nt; s += 16) {
+          float dv[16];
+#pragma unroll
+          for (int u = 0; u < 16; u++) dv[u] = dp[(int64_t)(s + u) * w.H1];
+#pragma unroll
+          for (int u = 0; u < 16; u++) {
+            dv[u] = d1_of(dv[u], xs + (s + u) * 8);
+#pragma unroll
+            for (int c = 0; c < OBS; c++) acc[c] = fmaf(dv[u], xs[(s + u) * 8 + c], acc[c]);
+            acc[OBS] += dv[u];
+          }
+        }
+        for (; s < nt; s++) {
+          const float dv = d1_of(dp[(int64_t)s * w.H1], xs + s * 8);
+#pragma unroll
+          for (int c = 0; c < OBS; c++) acc[c] = fmaf(dv, xs[s * 8 + c], acc[c]);
+          acc[OBS] += dv;
+        }
+      }
+    }
+    asm volatile("bar.sync 1, %0;" ::"n"(DW1_THREADS) : "memory");
+    if (half == 1) {
+#pragma unroll
+      for (int c = 0; c <= OBS; c++) fold[k * 8 + c] = acc[c];
+    }
+    asm volatile("bar.sync 1, %0;" ::"n"(DW1_THREADS) : "memory");
+    if (half == 0 && k < w.H1) {
+      float* out = w.part + ((int64_t)blockIdx.x * 2 + g) * w.H1 * 8 + k * 8;
+#pragma unroll
+      for (int c = 0; c <= OBS; c++) out[c] = acc[c] + fold[k * 8 + c];
+      out[OBS + 1] = 0.f;
+    }
+  }
+}
+
 template <bool MN>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __launch_bounds__(MN ? GEMM_THREADS + DW1_THREADS : GEMM_THREADS, 1)
 k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
           const __grid_constant__ CUtensorMap tmC, const GemmArgs a) {
   extern __shared__ uint8_t smem_raw[];
@@ -173,6 +254,9 @@ k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
       }
     }
     __syncwarp();
+  } else if (MN && warp >= GEMM_THREADS / 32) {
+    if (a.dw1.params)
+      dw1_worker(a.dw1, reinterpret_cast<float*>(smem + (size_t)stages * SB + STG_BYTES + BAR_BYTES), threadIdx.x - GEMM_THREADS);
   } else {
     const int q = warp & 3;                             // TMEM lane quarter this warp may read
     // two warps share each TMEM lane quarter (and each SM sub-partition): one takes the low half of the columns, the
@@ -236,7 +320,7 @@ EncodeTiledFn g_encode = nullptr;
 }  // namespace
 
 int gemm_x3_stages(int N, bool mn_major) {
-  int s = (SMEM_LIMIT - 1024 - BAR_BYTES - STG_BYTES) / (mn_major ? (4 + 2 * (N / 64)) * MNB_BYTES : stage_bytes(N));
+  int s = (SMEM_LIMIT - 1024 - BAR_BYTES - STG_BYTES - (mn_major ? DW1_SMEM : 0)) / (mn_major ? (4 + 2 * (N / 64)) * MNB_BYTES : stage_bytes(N));
   if (s > 6) s = 6;
   return s;
 }
@@ -286,7 +370,8 @@ int make_output_map(CUtensorMap* out, const void* base, uint64_t N, uint64_t row
 
 cudaError_t launch_gemm_x3(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const GemmArgs& a,
                            int sm_count, cudaStream_t st) {
-  const int smem = a.stages * (a.mn_major ? (4 + 2 * (a.N / 64)) * MNB_BYTES : stage_bytes(a.N)) + STG_BYTES + BAR_BYTES + 1024;
+  const int smem = a.stages * (a.mn_major ? (4 + 2 * (a.N / 64)) * MNB_BYTES : stage_bytes(a.N)) + STG_BYTES + BAR_BYTES + 1024 +
+                   (a.mn_major ? DW1_SMEM : 0);
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e;
@@ -301,7 +386,7 @@ cudaError_t launch_gemm_x3(const CUtensorMap& tmA, const CUtensorMap& tmB, const
   const int smem_req = smem > 120 * 1024 ? smem : 120 * 1024;
   if (a.mn_major) {
     if (a.N % 64) return cudaErrorInvalidValue;
-    k_gemm_x3<true><<<grid, GEMM_THREADS, smem_req, st>>>(tmA, tmB, tmC, a);
+    k_gemm_x3<true><<<grid, GEMM_THREADS + DW1_THREADS, smem_req, st>>>(tmA, tmB, tmC, a);
   } else k_gemm_x3<false><<<grid, GEMM_THREADS, smem_req, st>>>(tmA, tmB, tmC, a);
   return cudaGetLastError();
 }

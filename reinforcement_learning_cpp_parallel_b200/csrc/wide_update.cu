@@ -258,81 +258,7 @@ __global__ void __launch_bounds__(256, 3) k_wide_head(const WideArgs a) {
   }
 }
 
-// dW1aug[k][c] = sum_s D1[s][k] x[s][c] (c = 6: ones -> db1) with D1 = Z1 .* (1 - H1^2): the GEMM left Z1 = D2 W2 and
-// H1 is recomputed from X exactly as k_wide_l1 computes it.  thread = (sample half, feature k); a block owns a contiguous
-// sample range, its two halves are folded through shared memory at the end.  grid (blocks, 2 nets), 512 threads;
-// partial row [blk][g][k * 8 + c]
-__global__ void __launch_bounds__(512) k_wide_dw1(const WideArgs a, int samples_per_block) {
-  __shared__ float xs[2][64][S + 2];
-  __shared__ float fold[256][S + 2];
-  const int H1 = a.d.H1, g = blockIdx.y;
-  const int half = threadIdx.x >> 8, k = threadIdx.x & 255, ht = threadIdx.x & 255;
-  const int sb = blockIdx.x * samples_per_block;
-  const int se = min(sb + samples_per_block, a.count);
-  const int len = max(se - sb, 0), hlen = (len + 1) / 2;
-  const int hb = sb + half * hlen, he = min(hb + hlen, se);      // this half's sample range
-  float acc[S + 1];
-#pragma unroll
-  for (int c = 0; c <= S; c++) acc[c] = 0.f;
-  float w1[S], b1 = 0.f;
-#pragma unroll
-  for (int c = 0; c < S; c++) w1[c] = 0.f;
-  if (k < H1) {
-#pragma unroll
-    for (int c = 0; c < S; c++) w1[c] = a.params[g * a.d.SIZE + a.d.oW1 + k * S + c];
-    b1 = a.params[g * a.d.SIZE + a.d.ob1 + k];
-  }
-  auto d1_of = [&](float z1, const float* x) {
-    float z = b1;
-#pragma unroll
-    for (int c = 0; c < S; c++) z = fmaf(w1[c], x[c], z);
-    const float h = act_tanh(z);
-    return z1 * (1.0f - h * h);
-  };
-  for (int off = 0; off < hlen; off += 64) {                     // uniform trip count for both halves
-    const int t0 = hb + off;
-    const int nt = max(min(64, he - t0), 0);
-    __syncthreads();
-    for (int i = ht; i < nt * S; i += 256) {
-      const int s = i / S, c = i % S;
-      xs[half][s][c] = a.tr.obs[c * a.tr.cap + sample_pos(a, t0 + s)];
-    }
-    __syncthreads();
-    if (k < H1 && nt > 0) {
-      const float* dp = a.d1 + ((int64_t)g * a.cap + t0) * H1 + k;
-      int s = 0;
-      for (; s + 16 <= nt; s += 16) {          // 16 independent loads in flight per thread
-        float dv[16];
-#pragma unroll
-        for (int u = 0; u < 16; u++) dv[u] = dp[(int64_t)(s + u) * H1];
-#pragma unroll
-        for (int u = 0; u < 16; u++) {
-          dv[u] = d1_of(dv[u], xs[half][s + u]);
-#pragma unroll
-          for (int c = 0; c < S; c++) acc[c] = fmaf(dv[u], xs[half][s + u][c], acc[c]);
-          acc[S] += dv[u];
-        }
-      }
-      for (; s < nt; s++) {
-        const float dv = d1_of(dp[(int64_t)s * H1], xs[half][s]);
-#pragma unroll
-        for (int c = 0; c < S; c++) acc[c] = fmaf(dv, xs[half][s][c], acc[c]);
-        acc[S] += dv;
-      }
-    }
-  }
-  if (half == 1) {
-#pragma unroll
-    for (int c = 0; c <= S; c++) fold[k][c] = acc[c];
-  }
-  __syncthreads();
-  if (half == 0 && k < H1) {
-    float* out = a.part_dw1 + ((int64_t)blockIdx.x * 2 + g) * H1 * 8 + k * 8;
-#pragma unroll
-    for (int c = 0; c <= S; c++) out[c] = acc[c] + fold[k][c];
-    out[S + 1] = 0.f;
-  }
-}
+// (dW1 / db1: the work of the former k_wide_dw1 kernel rides in extra warps of the dW2 GEMM, wide_gemm.cu dw1_worker)
 
 struct ReduceArgs {
   NetDims d;
@@ -773,17 +699,18 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     g = GemmArgs{};
     g.G = 2; g.M = H2; g.N = H1; g.K = wa.m_pad; g.m_tiles = jt; g.splits = splits; g.kb_per_split = kbps;
     g.stages = gemm_x3_stages(H1, true); g.mn_major = 1;
+    // k_wide_dw1's work rides in eight extra warps of this kernel (FP32 pipe beside the tensor pipe)
+    g.dw1.params = a.params; g.dw1.obs = a.tr.obs; g.dw1.obs_cap = a.tr.cap; g.dw1.idx = a.idx; g.dw1.first = wa.first;
+    g.dw1.count = wa.count; g.dw1.H1 = H1; g.dw1.SIZE = d.SIZE; g.dw1.oW1 = d.oW1; g.dw1.ob1 = d.ob1;
+    g.dw1.z1 = w->d1; g.dw1.cap = w->cap; g.dw1.part = w->part_dw1;
+    const int dw2_grid = std::min(2 * jt * splits, w->sm_count);
     if ((ce = launch_gemm_x3(w->tm_d2_mn, w->tm_h1_mn, w->tm_out_dw2, g, w->sm_count, st)) != cudaSuccess)
       return set_error(B2_ERR_CUDA, "wide gemm dW2: %s", cudaGetErrorString(ce));
     (*launches)++;
-    // dW1, db1
-    const int spb = (wa.count + w->dw1_blocks - 1) / w->dw1_blocks;
-    k_wide_dw1<<<dim3(w->dw1_blocks, 2), 512, 0, st>>>(wa, spb < 1 ? 1 : spb);
-    LCK("dw1");
     // reduce (+ Adam on the last chunk)
     ReduceArgs r{};
     r.d = d; r.u = a; r.part_head = w->part_head; r.part_dw1 = w->part_dw1; r.part_dw2 = w->part_dw2;
-    r.head_blocks = w->head_blocks; r.head_row = w->head_row; r.dw1_blocks = w->dw1_blocks; r.splits = splits;
+    r.head_blocks = w->head_blocks; r.head_row = w->head_row; r.dw1_blocks = dw2_grid; r.splits = splits;
     r.pstride = wide_pstride(H1, H2);
     r.w2p = w->w2p; r.w2tp = w->w2tp; r.bias2 = w->bias2;
     r.first_chunk = c == 0; r.last_chunk = c == n_chunks - 1; r.apply_adam = apply_adam ? 1 : 0;
