@@ -178,7 +178,8 @@ int b2_host_alloc(void** p, size_t bytes);                     /* pinned host me
 int b2_host_free(void* p);
 /* diagnostic for the tensor-core path of wide nets: C[M][N] = A[M][K] . B[N][K]^T (host fp32 in/out) through the
  * bf16x3 tcgen05 GEMM that the 2x256 update uses; N % 32 == 0, N <= 256; splits > 1 exercises the split-K partials.
- * mn_major = 1: operands are given contraction-major, A[K][M] and B[K][N] (the layout of dW2 = D2^T H1), M, N % 64 == 0 */
+ * mn_major = 1: operands are given contraction-major, A[K][M] and B[K][N] (the layout of dW2 = D2^T H1), M, N % 64 == 0;
+ * mn_major = 2: A[M][K] as usual, B contraction-major B[K][N] (the layout of Z1 = D2 W2 with W2 as stored), N % 64 == 0 */
 int b2_selftest_gemm(b2_handle h, int M, int N, int K, const float* A, const float* B, float* C, int splits, int mn_major);
 
 #ifdef __cplusplus

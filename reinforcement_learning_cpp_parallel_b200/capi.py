@@ -381,7 +381,11 @@ def _selftest_gemm(self, A, B, splits=1, mn_major=False):
     GEMM of the wide-net update (diagnostic)."""
     A = np.ascontiguousarray(A, np.float32)
     B = np.ascontiguousarray(B, np.float32)
-    if mn_major:
+    if int(mn_major) == 2:      # A [M][K] as usual, B contraction-major [K][N]: C = A @ B
+        M, K = A.shape
+        N = B.shape[1]
+        assert B.shape[0] == K
+    elif mn_major:
         K, M = A.shape
         N = B.shape[1]
         assert B.shape[0] == K

@@ -24,6 +24,25 @@
 
 namespace b2 {
 
+// Programmatic dependent launch: the kernels of one optimizer step form a strict chain of 6 short launches (15-30 us
+// each), so launch latency and grid ramp-up are a visible share of the step.  Every kernel of the chain calls
+// pdl_launch_dependents() on entry (the next grid may start being scheduled as SMs free up) and pdl_wait() before its
+// first read of anything an earlier kernel wrote (blocks until ALL earlier grids have completed and flushed).
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+#endif
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // runtime layout of policy.parameters() for arbitrary hidden widths (same order as common.cuh Net<>)
 struct NetDims {
   int S, H1, H2;
@@ -54,6 +73,7 @@ struct Dw1Args {
 struct GemmArgs {
   int G, M, N, K;                // per group g < G: C[M][N] = A[M][K] . B[N][K]^T ; K % 64 == 0, N % 16 == 0, N <= 256
   int m_tiles, splits, kb_per_split, stages;
+  int b_mn;                      // K-major kernel only: B is given contraction-major [K][N] (N % 64 == 0), read as an MN-major operand
   int mn_major;                  // 1: C[M][N] = A[K][M]^T . B[K][N] (K blocks of 32, K % 32 == 0, N % 64 == 0)
                                  // output: raw fp32 accumulator tiles, TMA-stored to plane g * splits + split of tmC
   long long* dbg;                // optional per-CTA timeline (clock64), diagnostic runs only

@@ -20,6 +20,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 
+#include <algorithm>
 #include <vector>
 
 #include "tc_ptx.cuh"
@@ -133,6 +134,7 @@ __global__ void __launch_bounds__(MN ? GEMM_THREADS + DW1_THREADS : GEMM_THREADS
 k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
           const __grid_constant__ CUtensorMap tmC, const GemmArgs a) {
   extern __shared__ uint8_t smem_raw[];
+  if (a.dbg && threadIdx.x == 0) a.dbg[(blockIdx.x * 4 + 1) * 8 + 7] = clock64();   // kernel entry
   const uint32_t raw = tc::smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);   // 1024-B alignment for the 128-B swizzle atoms
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -157,7 +159,9 @@ k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     for (int b = 0; b < 2; b++) { tc::mbar_init(&tfull[b], 1); tc::mbar_init(&tempty[b], 256); }
     tc::fence_barrier_init();
   }
+  pdl_launch_dependents();
   if (warp == 1) tc::tmem_alloc(tmem_slot, 512);
+  pdl_wait();                                           // operands come from the previous kernels of the step
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
@@ -192,15 +196,22 @@ k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
           }
           tc::tma_load_3d(s, &tmA, &full[stage], kb * BK, mt * BM, g * 2 + 0);
           tc::tma_load_3d(s + A_PLANE_BYTES, &tmA, &full[stage], kb * BK, mt * BM, g * 2 + 1);
-          tc::tma_load_3d(s + 2 * A_PLANE_BYTES, &tmB, &full[stage], kb * BK, 0, g * 2 + 0);
-          tc::tma_load_3d(s + 2 * A_PLANE_BYTES + B_PLANE_BYTES, &tmB, &full[stage], kb * BK, 0, g * 2 + 1);
+          if (a.b_mn) {   // B given contraction-major ([K][N], e.g. W2 itself for Z1 = D2 W2): 64 x 64 boxes, MN-major UMMA operand
+            for (int pl = 0; pl < 2; pl++)
+              for (int fb = 0; fb < N / 64; fb++)
+                tc::tma_load_3d(s + 2 * A_PLANE_BYTES + pl * B_PLANE_BYTES + fb * (BK * 128), &tmB, &full[stage], fb * 64, kb * BK,
+                                g * 2 + pl);
+          } else {
+            tc::tma_load_3d(s + 2 * A_PLANE_BYTES, &tmB, &full[stage], kb * BK, 0, g * 2 + 0);
+            tc::tma_load_3d(s + 2 * A_PLANE_BYTES + B_PLANE_BYTES, &tmB, &full[stage], kb * BK, 0, g * 2 + 1);
+          }
           if (++stage == stages) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      const uint32_t idesc = tc::idesc_bf16_f32(BM, N) | (MN ? ((1u << 15) | (1u << 16)) : 0u);
+      const uint32_t idesc = tc::idesc_bf16_f32(BM, N) | (MN ? ((1u << 15) | (1u << 16)) : 0u) | ((!MN && a.b_mn) ? (1u << 16) : 0u);
       int stage = 0; uint32_t phase = 0;
       int it = 0;
       for (int item = blockIdx.x; item < n_items; item += gridDim.x, it++) {
@@ -237,14 +248,17 @@ k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
             continue;
           }
           const uint64_t dAh = tc::smem_desc_sw128(s), dAm = tc::smem_desc_sw128(s + A_PLANE_BYTES);
-          const uint64_t dBh = tc::smem_desc_sw128(s + 2 * A_PLANE_BYTES);
-          const uint64_t dBm = tc::smem_desc_sw128(s + 2 * A_PLANE_BYTES + B_PLANE_BYTES);
+          const uint32_t sBh = s + 2 * A_PLANE_BYTES, sBm = sBh + B_PLANE_BYTES;
+          const uint64_t dBh = a.b_mn ? tc::smem_desc_mn_sw128(sBh, BK * 128) : tc::smem_desc_sw128(sBh);
+          const uint64_t dBm = a.b_mn ? tc::smem_desc_mn_sw128(sBm, BK * 128) : tc::smem_desc_sw128(sBm);
+          const uint64_t bstep = a.b_mn ? (2048 >> 4) : (32 >> 4);   // 16 contraction rows of 128 B, or 16 bf16 along a row
 #pragma unroll
           for (int k = 0; k < BK / 16; k++) {
             const uint64_t off = (uint64_t)((k * 32) >> 4);    // 16 bf16 = 32 B along K inside the swizzle atom
-            tc::umma_bf16(d_tmem, dAm + off, dBh + off, idesc, acc);   // small terms first
-            tc::umma_bf16(d_tmem, dAh + off, dBm + off, idesc, 1u);
-            tc::umma_bf16(d_tmem, dAh + off, dBh + off, idesc, 1u);
+            const uint64_t offb = (uint64_t)k * bstep;
+            tc::umma_bf16(d_tmem, dAm + off, dBh + offb, idesc, acc);   // small terms first
+            tc::umma_bf16(d_tmem, dAh + off, dBm + offb, idesc, 1u);
+            tc::umma_bf16(d_tmem, dAh + off, dBh + offb, idesc, 1u);
             acc = 1u;
           }
           tc::umma_commit(&empty[stage]);               // stage reusable once these MMAs have read it
@@ -310,6 +324,7 @@ k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     tc::tc_fence_after();
     tc::tmem_dealloc(tmem_base, 512);
   }
+  if (a.dbg && threadIdx.x == 32) a.dbg[(blockIdx.x * 4 + 2) * 8 + 7] = clock64();   // after the TMEM release
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -386,9 +401,9 @@ cudaError_t launch_gemm_x3(const CUtensorMap& tmA, const CUtensorMap& tmB, const
   const int smem_req = smem > 120 * 1024 ? smem : 120 * 1024;
   if (a.mn_major) {
     if (a.N % 64) return cudaErrorInvalidValue;
-    k_gemm_x3<true><<<grid, GEMM_THREADS + DW1_THREADS, smem_req, st>>>(tmA, tmB, tmC, a);
-  } else k_gemm_x3<false><<<grid, GEMM_THREADS, smem_req, st>>>(tmA, tmB, tmC, a);
-  return cudaGetLastError();
+    return launch_pdl(k_gemm_x3<true>, dim3(grid), dim3(GEMM_THREADS + DW1_THREADS), (size_t)smem_req, st, tmA, tmB, tmC, a);
+  }
+  return launch_pdl(k_gemm_x3<false>, dim3(grid), dim3(GEMM_THREADS), (size_t)smem_req, st, tmA, tmB, tmC, a);
 }
 
 // ---- diagnostic GEMM: fp32 device operands -> planes -> k_gemm_x3<EPI_RAW> ----
@@ -413,7 +428,10 @@ __global__ void k_sum_splits(const float* __restrict__ part, float* __restrict__
 int wide_selftest_gemm(int M, int N, int K, const float* A_dev, const float* B_dev, float* C_dev, int splits,
                        int mn_major, int sm_count, cudaStream_t st) {
   if (M < 1 || N < 32 || N > 256 || (N % 32) || K < 1) return set_error(B2_ERR_INVALID, "selftest gemm: need N %% 32 == 0, 32 <= N <= 256");
-  if (mn_major && ((M % 64) || (N % 64))) return set_error(B2_ERR_INVALID, "selftest gemm (MN-major): need M %% 64 == 0 and N %% 64 == 0");
+  const bool mixed = mn_major == 2;        // A [M][K] K-major, B [K][N] contraction-major
+  if (mixed) mn_major = 0;
+  if ((mn_major && (M % 64)) || ((mn_major || mixed) && (N % 64)))
+    return set_error(B2_ERR_INVALID, "selftest gemm: MN-major operands need M %% 64 == 0 (mode 1) and N %% 64 == 0 (modes 1, 2)");
   const int kblk = mn_major ? BKS : BK;
   const int64_t Kp = ((int64_t)K + kblk - 1) / kblk * kblk;
   __nv_bfloat16 *pa = nullptr, *pb = nullptr;
@@ -435,6 +453,12 @@ int wide_selftest_gemm(int M, int N, int K, const float* A_dev, const float* B_d
     k_split_planes<<<256, 256, 0, st>>>(B_dev, pb, pb + (int64_t)N * Kp, K, N, N);
     rc = make_operand_map(&tmA, pa, M, Kp, 2, M, (uint64_t)M * Kp, MN_BOX_ROWS);
     if (!rc) rc = make_operand_map(&tmB, pb, N, Kp, 2, N, (uint64_t)N * Kp, MN_BOX_ROWS);
+  } else if (mixed) {
+    B2_CUDA_CHECK(cudaMemsetAsync(pb, 0, sizeof(__nv_bfloat16) * 2 * N * Kp, st));
+    k_split_planes<<<256, 256, 0, st>>>(A_dev, pa, pa + (int64_t)M * Kp, M, K, Kp);
+    k_split_planes<<<256, 256, 0, st>>>(B_dev, pb, pb + (int64_t)N * Kp, K, N, N);
+    rc = make_operand_map(&tmA, pa, Kp, M, 2, Kp, (uint64_t)M * Kp, BM);
+    if (!rc) rc = make_operand_map(&tmB, pb, N, Kp, 2, N, (uint64_t)N * Kp, BK);
   } else {
     k_split_planes<<<256, 256, 0, st>>>(A_dev, pa, pa + (int64_t)M * Kp, M, K, Kp);
     k_split_planes<<<256, 256, 0, st>>>(B_dev, pb, pb + (int64_t)N * Kp, N, K, Kp);
@@ -443,7 +467,7 @@ int wide_selftest_gemm(int M, int N, int K, const float* A_dev, const float* B_d
   }
   if (!rc) {
     GemmArgs g{};
-    g.G = 1; g.M = M; g.N = N; g.K = (int)Kp; g.mn_major = mn_major ? 1 : 0;
+    g.G = 1; g.M = M; g.N = N; g.K = (int)Kp; g.mn_major = mn_major ? 1 : 0; g.b_mn = mixed ? 1 : 0;
     g.m_tiles = (M + BM - 1) / BM; g.splits = splits; g.kb_per_split = kbps; g.stages = gemm_x3_stages(N, mn_major != 0);
     CUtensorMap tmC;
     if ((rc = make_output_map(&tmC, part, N, M, splits))) { cudaFree(pa); cudaFree(pb); cudaFree(part); return rc; }
@@ -460,6 +484,17 @@ int wide_selftest_gemm(int M, int N, int K, const float* A_dev, const float* B_d
       std::vector<long long> h((size_t)sm_count * 32);
       cudaStreamSynchronize(st);
       cudaMemcpy(h.data(), dbg, sizeof(long long) * h.size(), cudaMemcpyDeviceToHost);
+      {   // whole-grid view: setup cost (kernel entry -> roles start) and the slowest CTA
+        long long worst = 0, setup_max = 0, tot_max = 0;
+        for (int c = 0; c < sm_count; c++) {
+          const long long t0 = h[(size_t)c * 32 + 7];
+          for (int it = 0; it < 4; it++) worst = std::max(worst, h[(size_t)(c * 4 + it) * 8 + 6] - t0);
+          setup_max = std::max(setup_max, t0 - h[(size_t)(c * 4 + 1) * 8 + 7]);
+          tot_max = std::max(tot_max, h[(size_t)(c * 4 + 2) * 8 + 7] - h[(size_t)(c * 4 + 1) * 8 + 7]);
+        }
+        fprintf(stderr, "slowest CTA: last epilogue ends %lld cycles after setup; setup (entry -> roles) max %lld cycles; entry -> exit max %lld cycles\n",
+                worst, setup_max, tot_max);
+      }
       for (int c : {0, 1, 73, 147}) {
         if (c >= sm_count) continue;
         const long long t0 = h[(size_t)c * 32 + 7];

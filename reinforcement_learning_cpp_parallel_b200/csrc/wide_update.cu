@@ -4,7 +4,7 @@
 // (src/ppo_nn.cpp:126-194), the loss (:263-290), autograd backward (:301-302) and Adam::step (:303).
 //
 // Memory plan for a chunk of CAP samples (CAP % 128 == 0), g = net (0 actor, 1 critic), pl = bf16 plane (hi, mid):
-//   w2p  [g*2+pl][H2][H1]   w2tp [g*2+pl][H1][H2]   bias2 [g][H2]    (re-split every step)
+//   w2p  [g*2+pl][H2][H1]   bias2 [g][H2]                            (kept current by the Adam step)
 //   h1p  [g*2+pl][CAP][H1]                                           (layer-1 activations, sample-major)
 //   h2   [g][CAP][H2] f32                                            (layer-2 activations)
 //   d2p  [g*2+pl][CAP][H2]                                           (dL/dz2, sample-major)
@@ -26,6 +26,19 @@ namespace {
 
 constexpr int S = OBS;
 
+struct AdamCoef {
+  float fb1, f1mb1, fb2, f1mb2, sq_bc2, feps, step_size;
+};
+// libtorch adam.cpp: scalars are doubles narrowed to f32 inside the tensor kernels
+__device__ __forceinline__ AdamCoef adam_coef(const HyperDev& hp, int64_t step) {
+  const double bc1 = 1.0 - pow(hp.beta1, (double)step);
+  const double bc2 = 1.0 - pow(hp.beta2, (double)step);
+  AdamCoef c;
+  c.fb1 = (float)hp.beta1; c.f1mb1 = (float)(1.0 - hp.beta1);
+  c.fb2 = (float)hp.beta2; c.f1mb2 = (float)(1.0 - hp.beta2);
+  c.sq_bc2 = (float)sqrt(bc2); c.feps = (float)hp.eps; c.step_size = (float)(-(hp.lr / bc1));
+  return c;
+}
 struct WideArgs {
   NetDims d;
   const float* params;
@@ -36,11 +49,12 @@ struct WideArgs {
   int64_t cap;        // CAP
   float inv_denom;
   HyperDev hp;
-  __nv_bfloat16 *w2p, *w2tp, *h1p, *d2p;
+  __nv_bfloat16 *w2p, *h1p, *d2p;
   float *bias2, *h2, *d1;
   float *part_head, *part_dw1;   // [blocks][2][head_row] , [blocks][2][H1 * 8]
   int head_row;
-  int64_t* bump_step;   // non-null on the first chunk of an optimizer step: adam_step += 1
+  int64_t* bump_step;   // non-null on the first chunk of an optimizer step: adam_step += 1 ...
+  AdamCoef* coef_out;   // ... and the Adam coefficients of the new step, for k_wide_reduce / k_wide_adam at its end
 };
 
 __device__ __forceinline__ int64_t sample_pos(const WideArgs& a, int s) {
@@ -48,21 +62,20 @@ __device__ __forceinline__ int64_t sample_pos(const WideArgs& a, int s) {
   return a.idx ? (int64_t)a.idx[p] : p;
 }
 
-// weights -> bf16 planes in both majors.  Runs at the start of an update; afterwards the Adam step itself rewrites the
-// planes of every W2 element it changes (wide_store_planes), so the steady state has no conversion pass.
+// weights -> bf16 planes.  Runs at the start of an update; afterwards the Adam step itself rewrites the planes of every
+// W2 element it changes (wide_store_planes), so the steady state has no conversion pass.  One copy serves both GEMMs:
+// Z2 = H1 W2^T reads it K-major, Z1 = D2 W2 reads it as an MN-major operand.
 __global__ void __launch_bounds__(256) k_wide_prep(const WideArgs a) {
   const int H1 = a.d.H1, H2 = a.d.H2;
   const int n = 2 * H2 * H1;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const int g = i / (H2 * H1), r = i % (H2 * H1), j = r / H1, k = r % H1;
+    const int g = i / (H2 * H1), r = i % (H2 * H1);
     const float w = a.params[g * a.d.SIZE + a.d.oW2 + r];
     __nv_bfloat16 hi, mid;
     tc::split_bf16(w, hi, mid);
     const int64_t ps = (int64_t)H2 * H1;
     a.w2p[(g * 2 + 0) * ps + r] = hi;
     a.w2p[(g * 2 + 1) * ps + r] = mid;
-    a.w2tp[(g * 2 + 0) * ps + (int64_t)k * H2 + j] = hi;
-    a.w2tp[(g * 2 + 1) * ps + (int64_t)k * H2 + j] = mid;
   }
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 2 * H2; i += gridDim.x * blockDim.x)
     a.bias2[i] = a.params[(i / H2) * a.d.SIZE + a.d.ob2 + (i % H2)];
@@ -78,7 +91,13 @@ __global__ void __launch_bounds__(256, 4) k_wide_l1(const WideArgs a) {
   __shared__ __align__(16) float bs[256];       // b1
   const int H1 = a.d.H1, g = blockIdx.y;
   const int s0 = blockIdx.x * L1_TILE;
-  if (blockIdx.x == 0 && g == 0 && threadIdx.x == 0 && a.bump_step) *a.bump_step += 1;   // one optimizer step
+  pdl_launch_dependents();
+  pdl_wait();                                   // the weights come from the previous step's Adam
+  if (blockIdx.x == 0 && g == 0 && threadIdx.x == 0 && a.bump_step) {   // one optimizer step
+    const int64_t step = *a.bump_step + 1;
+    *a.bump_step = step;
+    *a.coef_out = adam_coef(a.hp, step);   // two fp64 pow() on one thread here instead of a barrier in every reduce block
+  }
   for (int i = threadIdx.x; i < H1 * S; i += blockDim.x) ws[(i / 48) * 52 + (i % 48)] = a.params[g * a.d.SIZE + a.d.oW1 + i];
   for (int i = threadIdx.x; i < H1; i += blockDim.x) bs[i] = a.params[g * a.d.SIZE + a.d.ob1 + i];
   for (int i = threadIdx.x; i < L1_TILE * S; i += blockDim.x) {
@@ -131,6 +150,8 @@ __global__ void __launch_bounds__(256, 3) k_wide_head(const WideArgs a) {
   float* red = hsm + 4 * H2;         // [8 warps][2 nets][2 * H2 + 4]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const NetDims d = a.d;
+  pdl_launch_dependents();
+  pdl_wait();
   for (int i = threadIdx.x; i < 4 * H2; i += blockDim.x) {
     const int g = i / (2 * H2), r = i % (2 * H2);
     wsm[i] = a.params[g * d.SIZE + (r < H2 ? d.oW3 + r : d.ob2 + (r - H2))];
@@ -266,36 +287,22 @@ struct ReduceArgs {
   const float *part_head, *part_dw1, *part_dw2;
   int head_blocks, head_row, dw1_blocks, splits, pstride;
   int first_chunk, last_chunk, apply_adam;
-  __nv_bfloat16 *w2p, *w2tp;   // weight planes the Adam step keeps current
+  __nv_bfloat16* w2p;          // weight planes the Adam step keeps current
   float* bias2;
+  const AdamCoef* coef;        // written by k_wide_l1 at the start of this optimizer step
 };
 
-struct AdamCoef {
-  float fb1, f1mb1, fb2, f1mb2, sq_bc2, feps, step_size;
-};
-// libtorch adam.cpp: scalars are doubles narrowed to f32 inside the tensor kernels
-__device__ __forceinline__ AdamCoef adam_coef(const HyperDev& hp, int64_t step) {
-  const double bc1 = 1.0 - pow(hp.beta1, (double)step);
-  const double bc2 = 1.0 - pow(hp.beta2, (double)step);
-  AdamCoef c;
-  c.fb1 = (float)hp.beta1; c.f1mb1 = (float)(1.0 - hp.beta1);
-  c.fb2 = (float)hp.beta2; c.f1mb2 = (float)(1.0 - hp.beta2);
-  c.sq_bc2 = (float)sqrt(bc2); c.feps = (float)hp.eps; c.step_size = (float)(-(hp.lr / bc1));
-  return c;
-}
 // a parameter changed: keep the bf16 planes (both majors) of W2 and the bias copy in step with it
-__device__ __forceinline__ void wide_store_planes(const NetDims& d, __nv_bfloat16* w2p, __nv_bfloat16* w2tp, float* bias2,
+__device__ __forceinline__ void wide_store_planes(const NetDims& d, __nv_bfloat16* w2p, float* bias2,
                                                   int p, float val) {
   const int g = p / d.SIZE, o = p % d.SIZE;
   if (o >= d.oW2 && o < d.ob2) {
-    const int e = o - d.oW2, j = e / d.H1, k = e % d.H1;
+    const int e = o - d.oW2;
     __nv_bfloat16 hi, mid;
     tc::split_bf16(val, hi, mid);
     const int64_t ps = (int64_t)d.H2 * d.H1;
     w2p[(g * 2 + 0) * ps + e] = hi;
     w2p[(g * 2 + 1) * ps + e] = mid;
-    w2tp[(g * 2 + 0) * ps + (int64_t)k * d.H2 + j] = hi;
-    w2tp[(g * 2 + 1) * ps + (int64_t)k * d.H2 + j] = mid;
   } else if (o >= d.ob2 && o < d.oW3) {
     bias2[g * d.H2 + (o - d.ob2)] = val;
   }
@@ -326,7 +333,7 @@ __device__ __forceinline__ void wide_finish(const ReduceArgs& r, const AdamCoef&
   if (!r.first_chunk) s += r.u.grads[slot];
   r.u.grads[slot] = s;
   if (r.last_chunk && r.apply_adam) {
-    if (p < r.d.P) wide_store_planes(r.d, r.w2p, r.w2tp, r.bias2, p, wide_adam_apply(r.u, c, p, s));
+    if (p < r.d.P) wide_store_planes(r.d, r.w2p, r.bias2, p, wide_adam_apply(r.u, c, p, s));
     else wide_loss_log(r.u, p - r.d.P, s);
   }
 }
@@ -334,9 +341,9 @@ __device__ __forceinline__ void wide_finish(const ReduceArgs& r, const AdamCoef&
 __global__ void __launch_bounds__(128) k_wide_reduce(const ReduceArgs r, int w2_blocks) {
   const NetDims d = r.d;
   const int w2n = d.H2 * d.H1;
-  __shared__ AdamCoef coef;
-  if (threadIdx.x == 0 && r.last_chunk && r.apply_adam) coef = adam_coef(r.u.hp, *r.u.adam_step);
-  __syncthreads();
+  pdl_launch_dependents();
+  pdl_wait();
+  const AdamCoef coef = *r.coef;
   if ((int)blockIdx.x < w2_blocks) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= 2 * w2n) return;
@@ -344,6 +351,14 @@ __global__ void __launch_bounds__(128) k_wide_reduce(const ReduceArgs r, int w2_
     const float* base = r.part_dw2 + (int64_t)g * r.splits * w2n + e;
     float s = 0.f;
     int sp = 0;
+    if (r.splits <= 40) {                      // the usual case: every partial of this element in flight at once
+      float t[40];
+#pragma unroll
+      for (int u = 0; u < 40; u++) t[u] = (u < r.splits) ? base[(int64_t)u * w2n] : 0.f;
+#pragma unroll
+      for (int u = 0; u < 40; u++) s += t[u];  // adding the zero padding does not change the sum
+      sp = r.splits;
+    }
     for (; sp + 16 <= r.splits; sp += 16) {
       float t[16];
 #pragma unroll
@@ -405,12 +420,10 @@ __global__ void __launch_bounds__(128) k_wide_reduce(const ReduceArgs r, int w2_
 }
 
 __global__ void __launch_bounds__(128) k_wide_adam(const UpdateArgs a, const NetDims d, int pstride, __nv_bfloat16* w2p,
-                                                   __nv_bfloat16* w2tp, float* bias2) {
-  __shared__ AdamCoef coef;
-  if (threadIdx.x == 0) coef = adam_coef(a.hp, *a.adam_step);
-  __syncthreads();
+                                                   float* bias2, const AdamCoef* coef_p) {
+  const AdamCoef coef = *coef_p;
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
-  if (p < d.P) wide_store_planes(d, w2p, w2tp, bias2, p, wide_adam_apply(a, coef, p, a.grads[p]));
+  if (p < d.P) wide_store_planes(d, w2p, bias2, p, wide_adam_apply(a, coef, p, a.grads[p]));
   else if (p < d.P + 3) wide_loss_log(a, p - d.P, a.grads[pstride - 4 + (p - d.P)]);
 }
 
@@ -528,8 +541,9 @@ struct WideNet {
   NetDims d;
   int sm_count = 148;
   int64_t cap = 0;                 // samples per chunk, multiple of 128
-  __nv_bfloat16 *w2p = nullptr, *w2tp = nullptr, *h1p = nullptr, *d2p = nullptr;
+  __nv_bfloat16 *w2p = nullptr, *h1p = nullptr, *d2p = nullptr;
   float *bias2 = nullptr, *h2 = nullptr, *d1 = nullptr;
+  AdamCoef* coef = nullptr;
   float *part_head = nullptr, *part_dw1 = nullptr, *part_dw2 = nullptr;
   int head_blocks = 0, head_row = 0, dw1_blocks = 0, splits_max = 0;
   CUtensorMap tm_h1, tm_w2, tm_d2, tm_w2t, tm_d2_mn, tm_h1_mn;
@@ -548,8 +562,8 @@ int64_t wide_chunk_cap(const WideNet* w) { return w ? w->cap : 0; }
 
 void wide_destroy(WideNet* w) {
   if (!w) return;
-  cudaFree(w->w2p); cudaFree(w->w2tp); cudaFree(w->h1p); cudaFree(w->d2p);
-  cudaFree(w->bias2); cudaFree(w->h2); cudaFree(w->d1);
+  cudaFree(w->w2p); cudaFree(w->h1p); cudaFree(w->d2p);
+  cudaFree(w->bias2); cudaFree(w->h2); cudaFree(w->d1); cudaFree(w->coef);
   cudaFree(w->part_head); cudaFree(w->part_dw1); cudaFree(w->part_dw2);
   cudaFree(w->boot_idx); cudaFree(w->boot_count);
   delete w;
@@ -577,10 +591,10 @@ int wide_create(WideNet** out, int H1, int H2, int64_t max_chunk, int sm_count) 
     }                                                                                                        \
   } while (0)
   WCK(cudaMalloc(&w->w2p, bf * 4 * H2 * H1));
-  WCK(cudaMalloc(&w->w2tp, bf * 4 * H2 * H1));
   WCK(cudaMalloc(&w->h1p, bf * 4 * cap * H1));
   WCK(cudaMalloc(&w->d2p, bf * 4 * cap * H2));
   WCK(cudaMalloc(&w->bias2, sizeof(float) * 2 * H2));
+  WCK(cudaMalloc(&w->coef, sizeof(AdamCoef)));
   WCK(cudaMalloc(&w->h2, sizeof(float) * 2 * cap * H2));
   WCK(cudaMalloc(&w->d1, sizeof(float) * 2 * cap * H1));
   // stale bits must never be NaN where a zero-weighted product could meet them
@@ -601,7 +615,7 @@ int wide_create(WideNet** out, int H1, int H2, int64_t max_chunk, int sm_count) 
   if (!rc) rc = make_operand_map(&w->tm_h1, w->h1p, H1, ucap, 4, H1, ucap * H1, 128);
   if (!rc) rc = make_operand_map(&w->tm_w2, w->w2p, H1, H2, 4, H1, (uint64_t)H2 * H1, (uint32_t)H2);
   if (!rc) rc = make_operand_map(&w->tm_d2, w->d2p, H2, ucap, 4, H2, ucap * H2, 128);
-  if (!rc) rc = make_operand_map(&w->tm_w2t, w->w2tp, H2, H1, 4, H2, (uint64_t)H2 * H1, (uint32_t)H1);
+  if (!rc) rc = make_operand_map(&w->tm_w2t, w->w2p, H1, H2, 4, H1, (uint64_t)H2 * H1, 64);   // W2 as [K = j][N = k] boxes
   // the same sample-major planes read contraction-major (K = samples) by the dW2 GEMM: boxes of 64 features x 32 samples
   if (!rc) rc = make_operand_map(&w->tm_d2_mn, w->d2p, H2, ucap, 4, H2, ucap * H2, MN_BOX_ROWS);
   if (!rc) rc = make_operand_map(&w->tm_h1_mn, w->h1p, H1, ucap, 4, H1, ucap * H1, MN_BOX_ROWS);
@@ -623,8 +637,7 @@ static cudaError_t launch_head(const WideArgs& wa, int grid, cudaStream_t st) {
     if (e != cudaSuccess) return e;
     attr = true;
   }
-  k_wide_head<NJ><<<grid, 256, smem, st>>>(wa);
-  return cudaGetLastError();
+  return launch_pdl(k_wide_head<NJ>, dim3(grid), dim3(256), (size_t)smem, st, wa);
 }
 
 int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st, int64_t* launches) {
@@ -633,7 +646,7 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
   WideArgs wa{};
   wa.d = d; wa.params = a.params; wa.tr = a.tr; wa.idx = a.idx; wa.cap = w->cap;
   wa.inv_denom = 1.0f / (float)a.denom; wa.hp = a.hp;
-  wa.w2p = w->w2p; wa.w2tp = w->w2tp; wa.h1p = w->h1p; wa.d2p = w->d2p;
+  wa.w2p = w->w2p; wa.h1p = w->h1p; wa.d2p = w->d2p;
   wa.bias2 = w->bias2; wa.h2 = w->h2; wa.d1 = w->d1;
   wa.part_head = w->part_head; wa.part_dw1 = w->part_dw1; wa.head_row = w->head_row;
   cudaError_t ce;
@@ -653,10 +666,12 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     wa.count = (int)std::min<int64_t>(w->cap, a.count - c * w->cap);
     wa.m_pad = (wa.count + 127) / 128 * 128;
     wa.bump_step = c == 0 ? a.adam_step : nullptr;
+    wa.coef_out = w->coef;
     const int m_tiles = wa.m_pad / 128;
     // layer 1
-    k_wide_l1<<<dim3(wa.m_pad / L1_TILE, 2), 256, 0, st>>>(wa);
-    LCK("l1");
+    if ((ce = launch_pdl(k_wide_l1, dim3(wa.m_pad / L1_TILE, 2), dim3(256), 0, st, wa)) != cudaSuccess)
+      return set_error(B2_ERR_CUDA, "wide l1: %s", cudaGetErrorString(ce));
+    (*launches)++;
     // H2 = tanh(H1 W2^T + b2)
     GemmArgs g{};
     g.G = 2; g.M = wa.count; g.N = H2; g.K = H1; g.m_tiles = m_tiles; g.splits = 1; g.kb_per_split = H1 / 64;
@@ -683,7 +698,7 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     // D1 = (D2 W2) .* (1 - H1^2)
     g = GemmArgs{};
     g.G = 2; g.M = wa.count; g.N = H1; g.K = H2; g.m_tiles = m_tiles; g.splits = 1; g.kb_per_split = H2 / 64;
-    g.stages = gemm_x3_stages(H1);
+    g.stages = gemm_x3_stages(H1); g.b_mn = 1;   // B = W2 as stored ([j][k]), read as an MN-major operand
     if ((ce = launch_gemm_x3(w->tm_d2, w->tm_w2t, w->tm_out_d1, g, w->sm_count, st)) != cudaSuccess)
       return set_error(B2_ERR_CUDA, "wide gemm bwd: %s", cudaGetErrorString(ce));
     (*launches)++;
@@ -712,19 +727,20 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     r.d = d; r.u = a; r.part_head = w->part_head; r.part_dw1 = w->part_dw1; r.part_dw2 = w->part_dw2;
     r.head_blocks = w->head_blocks; r.head_row = w->head_row; r.dw1_blocks = dw2_grid; r.splits = splits;
     r.pstride = wide_pstride(H1, H2);
-    r.w2p = w->w2p; r.w2tp = w->w2tp; r.bias2 = w->bias2;
+    r.w2p = w->w2p; r.bias2 = w->bias2; r.coef = w->coef;
     r.first_chunk = c == 0; r.last_chunk = c == n_chunks - 1; r.apply_adam = apply_adam ? 1 : 0;
     const int w2_blocks = (2 * H2 * H1 + 127) / 128;
     const int small = 2 * (H1 * (S + 1) + 2 * H2 + 1) + 3;
-    k_wide_reduce<<<w2_blocks + (small + 3) / 4, 128, 0, st>>>(r, w2_blocks);
-    LCK("reduce");
+    if ((ce = launch_pdl(k_wide_reduce, dim3(w2_blocks + (small + 3) / 4), dim3(128), 0, st, r, w2_blocks)) != cudaSuccess)
+      return set_error(B2_ERR_CUDA, "wide reduce: %s", cudaGetErrorString(ce));
+    (*launches)++;
   }
 #undef LCK
   return B2_OK;
 }
 
 cudaError_t launch_wide_adam(WideNet* w, const UpdateArgs& a, cudaStream_t st) {
-  k_wide_adam<<<(w->d.P + 3 + 127) / 128, 128, 0, st>>>(a, w->d, wide_pstride(w->d.H1, w->d.H2), w->w2p, w->w2tp, w->bias2);
+  k_wide_adam<<<(w->d.P + 3 + 127) / 128, 128, 0, st>>>(a, w->d, wide_pstride(w->d.H1, w->d.H2), w->w2p, w->bias2, w->coef);
   return cudaGetLastError();
 }
 

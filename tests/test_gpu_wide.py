@@ -180,3 +180,16 @@ def test_gemm_bf16x3_mn_major(eng, M, N, K, splits):
     rel = np.linalg.norm(Cm - ref) / np.linalg.norm(ref)
     print(f"gemm MN {M}x{N}x{K} splits {splits}: rel fro {rel:.2e}")
     assert rel < 2e-5, rel
+
+
+@pytest.mark.parametrize("M,N,K,splits", [(128, 256, 256, 1), (300, 128, 192, 1), (1000, 256, 64, 1), (64, 64, 640, 3)])
+def test_gemm_bf16x3_mixed_major(eng, M, N, K, splits):
+    """A row-major [M][K], B contraction-major [K][N] (Z1 = D2 W2 reads W2 as stored): C = A B"""
+    rng = np.random.default_rng(3 * M + N + K)
+    A = rng.standard_normal((M, K)).astype(np.float32)
+    B = (rng.standard_normal((K, N)) / np.sqrt(K)).astype(np.float32)
+    Cm = eng.selftest_gemm(A, B, splits, mn_major=2)
+    ref = A.astype(np.float64) @ B.astype(np.float64)
+    rel = np.linalg.norm(Cm - ref) / np.linalg.norm(ref)
+    print(f"gemm mixed {M}x{N}x{K} splits {splits}: rel fro {rel:.2e}")
+    assert rel < 2e-5, rel
