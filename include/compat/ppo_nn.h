@@ -7,8 +7,9 @@
 // libtorch, no CPU fallback: constructing a PPO without a CUDA device throws.
 //
 // Differences from the reference that a caller can observe (all deliberate):
-//   * MemoryNN's tensor vectors (include/ppo_nn.h:22) are flat float vectors: states holds 6 floats per
-//     record, actions/logprobs one float per record.  Method-level compatibility, not field-level.
+//   * MemoryNN's tensor vectors (include/ppo_nn.h:22) are flat float stores: actions/logprobs one float per
+//     record, states a StateStore (state_dim floats per record) whose size() counts RECORDS like the vector of
+//     tensors it replaces, so the size guard of src/main.cpp:281-285 compiles and holds unmodified.
 //   * errors are std::runtime_error carrying b2_last_error() instead of prints / exit(1) / torch exceptions.
 //   * nothing is printed (the reference prints every tensor it touches, e.g. src/ppo_nn.cpp:68,292-297).
 //   * action noise comes from the engine's Philox stream, not torch's mt19937.
@@ -25,6 +26,21 @@
 
 enum TRAIN_STATUS { NORMAL = 0, TERMINATE, TIMEUP, START };  // include/ppo_nn.h:15
 
+// Conveniences src/main.cpp gets transitively from <torch/torch.h> and uses unqualified: isnan() in the global
+// namespace (src/main.cpp:50) and stream output of std::vector (c10/util/Logging.h puts one in namespace std;
+// src/main.cpp:52,176).  Provided here so that the reference's driver compiles unmodified against this header.
+#include <cmath>
+#include <iomanip>   // std::setprecision at src/main.cpp:142, also reached through torch upstream
+#include <iostream>
+using std::isnan;
+namespace std {
+template <class T>
+ostream& operator<<(ostream& os, const vector<T>& v) {
+  for (size_t i = 0; i < v.size(); i++) os << (i ? " " : "") << v[i];
+  return os;
+}
+}  // namespace std
+
 namespace b2compat {
 inline void check(int rc, const char* what) {
   if (rc != B2_OK) throw std::runtime_error(std::string(what) + ": " + b2_last_error());
@@ -33,6 +49,16 @@ struct Handle {  // shared by every copy of a PPO, like the reference's module s
   b2_handle h = nullptr;
   ~Handle() { if (h) b2_destroy(h); }
 };
+// observations of the recorded transitions, `dim` floats each; size() == number of records
+struct StateStore {
+  std::vector<float> data;
+  size_t dim = 6;
+  size_t size() const { return dim ? data.size() / dim : 0; }
+  bool empty() const { return data.empty(); }
+  void clear() { data.clear(); }
+  void append(const float* p, size_t n_floats) { data.insert(data.end(), p, p + n_floats); }
+  void append(const StateStore& o) { data.insert(data.end(), o.data.begin(), o.data.end()); }
+};
 }  // namespace b2compat
 
 // Trajectory store, one record per chosen action: states/actions/logprobs are appended when
@@ -40,7 +66,8 @@ struct Handle {  // shared by every copy of a PPO, like the reference's module s
 // (src/main.cpp:256-262).
 class MemoryNN {
  public:
-  std::vector<float> actions, states, logprobs;  // [n], [n][6], [n]
+  std::vector<float> actions, logprobs;  // [n]
+  b2compat::StateStore states;           // [n][state_dim]
   std::vector<double> rewards;
   std::vector<bool> is_terminals;
   std::vector<bool> is_timeups;
@@ -51,7 +78,7 @@ class MemoryNN {
   }
   void merge(MemoryNN& r) {  // src/ppo_nn.cpp:74-88: append r's records after ours, r is left untouched
     actions.insert(actions.end(), r.actions.begin(), r.actions.end());
-    states.insert(states.end(), r.states.begin(), r.states.end());
+    states.append(r.states);
     logprobs.insert(logprobs.end(), r.logprobs.begin(), r.logprobs.end());
     rewards.insert(rewards.end(), r.rewards.begin(), r.rewards.end());
     is_terminals.insert(is_terminals.end(), r.is_terminals.begin(), r.is_terminals.end());
@@ -95,7 +122,8 @@ class PPO {
     if ((int64_t)state.size() != state_dim) throw std::runtime_error("select_action: observation size != state_dim");
     float a = 0.f, lp = 0.f;
     b2compat::check(b2_act(engine->h, state.data(), 1, nullptr, &a, &lp, nullptr), "select_action");
-    memory.states.insert(memory.states.end(), state.begin(), state.end());
+    memory.states.dim = (size_t)state_dim;
+    memory.states.append(state.data(), state.size());
     memory.actions.push_back(a);
     memory.logprobs.push_back(lp);
     return {std::vector<float>{a}, lp};
@@ -119,7 +147,7 @@ class PPO {
   void update(MemoryNN memory) {
     const size_t n = memory.rewards.size();
     if (n == 0) return;
-    if (memory.actions.size() != n || memory.logprobs.size() != n || memory.states.size() != n * (size_t)state_dim ||
+    if (memory.actions.size() != n || memory.logprobs.size() != n || memory.states.data.size() != n * (size_t)state_dim ||
         memory.is_terminals.size() != n || memory.is_timeups.size() != n)
       throw std::runtime_error("PPO::update: MemoryNN fields have inconsistent sizes (cf. src/main.cpp:281-289)");
     std::vector<float> reward(n);
@@ -131,7 +159,7 @@ class PPO {
     b2_batch b;
     b.n_envs = 1;  // the merged memory is one flat sequence (src/main.cpp:290-303)
     b.horizon = (int64_t)n;
-    b.obs = memory.states.data();
+    b.obs = memory.states.data.data();
     b.action = memory.actions.data();
     b.logp = memory.logprobs.data();
     b.reward = reward.data();

@@ -54,7 +54,7 @@ int main(int argc, char** argv) {
     MemoryNN memNN[2], merged;
     for (size_t k = 0; k < B; k++) {
       MemoryNN& m = memNN[k < B / 2 ? 0 : 1];
-      m.states.insert(m.states.end(), obs.begin() + 6 * k, obs.begin() + 6 * (k + 1));
+      m.states.append(obs.data() + 6 * k, 6);
       m.actions.push_back(act[k]);
       m.logprobs.push_back(lp[k]);
       m.push_reward(rew[k], term[k] != 0, tup[k] != 0);
@@ -74,7 +74,7 @@ int main(int argc, char** argv) {
       auto [action, logprob] = getAction(o0, 1, ppo, live);
       act_ok = act_ok && action.size() == 1 && std::isfinite(action[0]) && std::isfinite(logprob);
     }
-    act_ok = act_ok && live.actions.size() == 3 && live.states.size() == 18 && live.logprobs.size() == 3;
+    act_ok = act_ok && live.actions.size() == 3 && live.states.size() == 3 && live.states.data.size() == 18 && live.logprobs.size() == 3;
 
     // ---------------- CartPole, as env_run does (src/main.cpp:20-79), against the header's own known answers
     double err_state = 0, err_obs = 0;
