@@ -47,6 +47,7 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-update", action="store_true")
     ap.add_argument("--no-wide", action="store_true", help="skip the configs[4] leg (2x256 MLP update sweep on tensor cores)")
+    ap.add_argument("--no-wide-whole", action="store_true", help="skip the whole-4M-batch-on-one-GPU variant of the configs[4] leg")
     ap.add_argument("--wide-samples", type=int, default=524288, help="samples per GPU of the configs[4] leg (4M over 8 GPUs)")
     return ap.parse_args()
 
@@ -210,6 +211,34 @@ def wide_leg(args, pkg, capi, np, rank, local, world, dist, barrier, max_over_ra
     mine = sum(ms) / len(ms)
     ach = FLOP_UPDATE_WIDE * B * K / (mine * 1e-3) / 1e12
     E.close()
+    # the same sweep with the WHOLE 4M-sample batch on one GPU (131,072-sample minibatches: 2,048 GEMM tiles per launch
+    # instead of 256): shows the kernels away from the launch-latency regime of the 8-GPU share.  One GPU only.
+    whole = None
+    if world == 1 and not args.no_wide_whole:
+        Bw = 8 * B
+        Nw = Bw // T
+        Ew = pkg.Engine(capi.default_config(n_envs=Nw, horizon=T, hidden1=256, hidden2=256, k_epochs=K, n_minibatches=M,
+                                            seed=0x5EED, device=local))
+        Ew.init_params(0)
+        rep8 = lambda a: np.ascontiguousarray(np.tile(a, (8,) + (1,) * (a.ndim - 1)))
+        obs_w = rep8(obs)
+        a_w, l_w, _ = Ew.act(obs_w)
+        fl_w = np.zeros((T, Nw), np.uint8)
+        fl_w[99] = 2
+        fl_w[T - 1] = 4
+        Ew.update(obs_w, a_w, l_w, rep8(reward), fl_w.reshape(-1), n_envs=Nw, horizon=T)
+        Ew.set_params(w0)
+        msw = []
+        for _ in range(max(2, min(args.steps, 3))):
+            Ew.timer_start()
+            Ew.update_resident()
+            msw.append(Ew.timer_stop_ms())
+        mw = sum(msw) / len(msw)
+        aw = FLOP_UPDATE_WIDE * Bw * K / (mw * 1e-3) / 1e12
+        whole = {"value": Bw * K / (mw * 1e-3), "unit": "sample-epochs/s", "ms_per_update": mw, "samples": Bw,
+                 "minibatch": Bw // M, "roofline": {"bound": "tensor", "achieved": aw, "peak": bf16_peak / 3.0,
+                                                    "unit": "TFLOP/s", "frac": aw / (bf16_peak / 3.0) if bf16_peak else None}}
+        Ew.close()
     return {"value": value, "unit": "sample-epochs/s", "ms_per_update": tot / args.steps,
             "config": {"workload": "BASELINE configs[4]: PPO update sweep, 2x256 MLP, 4M-sample batch / 8 GPUs = 524,288 "
                                    "samples per GPU, 32 minibatches x 10 epochs", "samples_per_gpu": B, "minibatches": M,
@@ -222,7 +251,7 @@ def wide_leg(args, pkg, capi, np, rank, local, world, dist, barrier, max_over_ra
                          "peak_source": bf16_src + " / 3 (every fp32 product is three bf16 MMAs)",
                          "issued_bf16_tflops": 3 * ach, "flop_per_sample_epoch": FLOP_UPDATE_WIDE,
                          "traffic": _ncu_traffic("k_gemm_x3_fwd_2x16384x256x256")},
-            "last_loss": st.loss}
+            "whole_batch_one_gpu": whole, "last_loss": st.loss}
 
 
 def main():
