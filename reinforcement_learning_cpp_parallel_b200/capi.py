@@ -381,10 +381,14 @@ def _selftest_gemm(self, A, B, splits=1, mn_major=False):
     GEMM of the wide-net update (diagnostic)."""
     A = np.ascontiguousarray(A, np.float32)
     B = np.ascontiguousarray(B, np.float32)
-    if int(mn_major) == 2:      # A [M][K] as usual, B contraction-major [K][N]: C = A @ B
+    if int(mn_major) in (2, 4):  # A [M][K] as usual, B contraction-major [K][N]: C = A @ B (4: on the CTA-pair kernel)
         M, K = A.shape
         N = B.shape[1]
         assert B.shape[0] == K
+    elif int(mn_major) == 3:    # the CTA-pair kernel, usual operand layouts
+        M, K = A.shape
+        N = B.shape[0]
+        assert B.shape[1] == K
     elif mn_major:
         K, M = A.shape
         N = B.shape[1]

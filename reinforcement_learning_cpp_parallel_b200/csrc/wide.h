@@ -80,6 +80,18 @@ struct GemmArgs {
   Dw1Args dw1;                   // MN-major kernel only
 };
 
+// the CTA-pair, weights-resident GEMM of wide_gemm2.cu (layer-2 forward and dX): C[g][M][N] = A[g][M][K] . B[g]
+struct Gemm2Args {
+  int G, M, N, K;      // K, N <= 256, multiples of 64 (N % 128 == 0 when B is contraction-major)
+  int stages;          // A stages in shared memory (gemm2_stages)
+};
+int gemm2_stages(int N, int K);
+bool gemm2_supported(int N, int K, bool bmn);
+// tmA: operand map with 128-row boxes; tmB: K-major weights with (N/2)-row boxes, or (bmn) 64 x 64 boxes of [K][N];
+// tmC: fp32 output map, plane = g
+cudaError_t launch_gemm2(bool bmn, const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const Gemm2Args& a,
+                         int sm_count, cudaStream_t st);
+
 cudaError_t launch_gemm_x3(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const GemmArgs& a,
                            int sm_count, cudaStream_t st);
 // fp32 output tensor [planes][rows][N] the epilogue TMA-stores 32 x 32 tiles into (plane = group, or group*splits + split)

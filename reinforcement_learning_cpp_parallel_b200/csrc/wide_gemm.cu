@@ -428,8 +428,11 @@ __global__ void k_sum_splits(const float* __restrict__ part, float* __restrict__
 int wide_selftest_gemm(int M, int N, int K, const float* A_dev, const float* B_dev, float* C_dev, int splits,
                        int mn_major, int sm_count, cudaStream_t st) {
   if (M < 1 || N < 32 || N > 256 || (N % 32) || K < 1) return set_error(B2_ERR_INVALID, "selftest gemm: need N %% 32 == 0, 32 <= N <= 256");
-  const bool mixed = mn_major == 2;        // A [M][K] K-major, B [K][N] contraction-major
-  if (mixed) mn_major = 0;
+  const bool pair = mn_major == 3 || mn_major == 4;   // the CTA-pair weights-resident kernel (wide_gemm2.cu); 4: B is [K][N]
+  const bool mixed = mn_major == 2 || mn_major == 4;  // A [M][K] K-major, B [K][N] contraction-major
+  if (mixed || pair) mn_major = 0;
+  if (pair && (splits > 1 || !gemm2_supported(N, (int)(((int64_t)K + BK - 1) / BK * BK), mixed)))
+    return set_error(B2_ERR_INVALID, "selftest gemm (CTA pair): needs splits = 1, N %% 64 == 0 (128 for [K][N] weights), K <= 256");
   if ((mn_major && (M % 64)) || ((mn_major || mixed) && (N % 64)))
     return set_error(B2_ERR_INVALID, "selftest gemm: MN-major operands need M %% 64 == 0 (mode 1) and N %% 64 == 0 (modes 1, 2)");
   const int kblk = mn_major ? BKS : BK;
@@ -459,6 +462,11 @@ int wide_selftest_gemm(int M, int N, int K, const float* A_dev, const float* B_d
     k_split_planes<<<256, 256, 0, st>>>(B_dev, pb, pb + (int64_t)N * Kp, K, N, N);
     rc = make_operand_map(&tmA, pa, Kp, M, 2, Kp, (uint64_t)M * Kp, BM);
     if (!rc) rc = make_operand_map(&tmB, pb, N, Kp, 2, N, (uint64_t)N * Kp, BK);
+  } else if (pair) {
+    k_split_planes<<<256, 256, 0, st>>>(A_dev, pa, pa + (int64_t)M * Kp, M, K, Kp);
+    k_split_planes<<<256, 256, 0, st>>>(B_dev, pb, pb + (int64_t)N * Kp, N, K, Kp);
+    rc = make_operand_map(&tmA, pa, Kp, M, 2, Kp, (uint64_t)M * Kp, BM);
+    if (!rc) rc = make_operand_map(&tmB, pb, Kp, N, 2, Kp, (uint64_t)N * Kp, (uint32_t)(N / 2));
   } else {
     k_split_planes<<<256, 256, 0, st>>>(A_dev, pa, pa + (int64_t)M * Kp, M, K, Kp);
     k_split_planes<<<256, 256, 0, st>>>(B_dev, pb, pb + (int64_t)N * Kp, N, K, Kp);
@@ -471,6 +479,17 @@ int wide_selftest_gemm(int M, int N, int K, const float* A_dev, const float* B_d
     g.m_tiles = (M + BM - 1) / BM; g.splits = splits; g.kb_per_split = kbps; g.stages = gemm_x3_stages(N, mn_major != 0);
     CUtensorMap tmC;
     if ((rc = make_output_map(&tmC, part, N, M, splits))) { cudaFree(pa); cudaFree(pb); cudaFree(part); return rc; }
+    if (pair) {
+      Gemm2Args g2{1, M, N, (int)Kp, gemm2_stages(N, (int)Kp)};
+      cudaError_t e2 = launch_gemm2(mixed, tmA, tmB, tmC, g2, sm_count, st);
+      if (e2 == cudaSuccess) {
+        k_sum_splits<<<256, 256, 0, st>>>(part, C_dev, (int64_t)M * N, 1);
+        e2 = cudaStreamSynchronize(st);
+      }
+      if (e2 != cudaSuccess) rc = set_error(B2_ERR_CUDA, "gemm2: %s", cudaGetErrorString(e2));
+      cudaFree(pa); cudaFree(pb); cudaFree(part);
+      return rc;
+    }
     long long* dbg = nullptr;
     const char* dbg_env = getenv("B2_GEMM_DBG");
     if (dbg_env) {

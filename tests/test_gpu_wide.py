@@ -193,3 +193,21 @@ def test_gemm_bf16x3_mixed_major(eng, M, N, K, splits):
     rel = np.linalg.norm(Cm - ref) / np.linalg.norm(ref)
     print(f"gemm mixed {M}x{N}x{K} splits {splits}: rel fro {rel:.2e}")
     assert rel < 2e-5, rel
+
+
+@pytest.mark.parametrize("M,N,K,mode", [(256, 256, 256, 3), (1000, 256, 256, 3), (40000, 256, 256, 3), (512, 128, 192, 3), (300, 64, 64, 3),
+                                        (256, 256, 256, 4), (5000, 256, 128, 4), (777, 128, 256, 4)])
+def test_gemm_cta_pair_weights_resident(eng, M, N, K, mode):
+    """k_gemm2_ws (cta_group::2, resident weight halves): mode 3 = weights K-major [N][K], mode 4 = weights as [K][N]"""
+    rng = np.random.default_rng(M + 5 * N + K + mode)
+    A = rng.standard_normal((M, K)).astype(np.float32)
+    if mode == 3:
+        B = (rng.standard_normal((N, K)) / np.sqrt(K)).astype(np.float32)
+        ref = A.astype(np.float64) @ B.astype(np.float64).T
+    else:
+        B = (rng.standard_normal((K, N)) / np.sqrt(K)).astype(np.float32)
+        ref = A.astype(np.float64) @ B.astype(np.float64)
+    Cm = eng.selftest_gemm(A, B, 1, mn_major=mode)
+    rel = np.linalg.norm(Cm - ref) / np.linalg.norm(ref)
+    print(f"gemm2 mode {mode} {M}x{N}x{K}: rel fro {rel:.2e}")
+    assert rel < 2e-5, rel
