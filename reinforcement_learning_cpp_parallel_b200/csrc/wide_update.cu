@@ -548,6 +548,8 @@ struct WideNet {
   int head_blocks = 0, head_row = 0, dw1_blocks = 0, splits_max = 0;
   CUtensorMap tm_h1, tm_w2, tm_d2, tm_w2t, tm_d2_mn, tm_h1_mn;
   CUtensorMap tm_out_h2, tm_out_d1, tm_out_dw2;
+  CUtensorMap tm_w2_half;          // K-major weights in (H2/2)-row boxes: the resident halves of the CTA-pair GEMM
+  bool pair_fwd = false, pair_bwd = false;
   int32_t* boot_idx = nullptr;
   int64_t boot_cap = 0;
   int* boot_count = nullptr;
@@ -619,6 +621,9 @@ int wide_create(WideNet** out, int H1, int H2, int64_t max_chunk, int sm_count) 
   // the same sample-major planes read contraction-major (K = samples) by the dW2 GEMM: boxes of 64 features x 32 samples
   if (!rc) rc = make_operand_map(&w->tm_d2_mn, w->d2p, H2, ucap, 4, H2, ucap * H2, MN_BOX_ROWS);
   if (!rc) rc = make_operand_map(&w->tm_h1_mn, w->h1p, H1, ucap, 4, H1, ucap * H1, MN_BOX_ROWS);
+  w->pair_fwd = gemm2_supported(H2, H1, false);
+  w->pair_bwd = gemm2_supported(H1, H2, true);
+  if (!rc && w->pair_fwd) rc = make_operand_map(&w->tm_w2_half, w->w2p, H1, H2, 4, H1, (uint64_t)H2 * H1, (uint32_t)(H2 / 2));
   if (!rc) rc = make_output_map(&w->tm_out_h2, w->h2, H2, ucap, 2);
   if (!rc) rc = make_output_map(&w->tm_out_d1, w->d1, H1, ucap, 2);
   if (!rc) rc = make_output_map(&w->tm_out_dw2, w->part_dw2, H1, H2, (uint64_t)2 * w->splits_max);
@@ -676,8 +681,13 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     GemmArgs g{};
     g.G = 2; g.M = wa.count; g.N = H2; g.K = H1; g.m_tiles = m_tiles; g.splits = 1; g.kb_per_split = H1 / 64;
     g.stages = gemm_x3_stages(H2);
-    if ((ce = launch_gemm_x3(w->tm_h1, w->tm_w2, w->tm_out_h2, g, w->sm_count, st)) != cudaSuccess)
-      return set_error(B2_ERR_CUDA, "wide gemm fwd: %s", cudaGetErrorString(ce));
+    if (w->pair_fwd) {   // CTA pairs with the weight halves resident (wide_gemm2.cu)
+      const Gemm2Args g2{2, wa.count, H2, H1, gemm2_stages(H2, H1)};
+      ce = launch_gemm2(false, w->tm_h1, w->tm_w2_half, w->tm_out_h2, g2, w->sm_count, st);
+    } else {
+      ce = launch_gemm_x3(w->tm_h1, w->tm_w2, w->tm_out_h2, g, w->sm_count, st);
+    }
+    if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "wide gemm fwd: %s", cudaGetErrorString(ce));
     (*launches)++;
     // loss head, D2
     {
@@ -699,8 +709,13 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     g = GemmArgs{};
     g.G = 2; g.M = wa.count; g.N = H1; g.K = H2; g.m_tiles = m_tiles; g.splits = 1; g.kb_per_split = H2 / 64;
     g.stages = gemm_x3_stages(H1); g.b_mn = 1;   // B = W2 as stored ([j][k]), read as an MN-major operand
-    if ((ce = launch_gemm_x3(w->tm_d2, w->tm_w2t, w->tm_out_d1, g, w->sm_count, st)) != cudaSuccess)
-      return set_error(B2_ERR_CUDA, "wide gemm bwd: %s", cudaGetErrorString(ce));
+    if (w->pair_bwd) {
+      const Gemm2Args g2{2, wa.count, H1, H2, gemm2_stages(H1, H2)};
+      ce = launch_gemm2(true, w->tm_d2, w->tm_w2t, w->tm_out_d1, g2, w->sm_count, st);
+    } else {
+      ce = launch_gemm_x3(w->tm_d2, w->tm_w2t, w->tm_out_d1, g, w->sm_count, st);
+    }
+    if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "wide gemm bwd: %s", cudaGetErrorString(ce));
     (*launches)++;
     // dW2 partials = D2^T H1 over sample splits
     const int kb_total = wa.m_pad / MN_BOX_ROWS;
