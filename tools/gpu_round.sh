@@ -20,7 +20,7 @@ timeout 600 ncu --set full --clock-control none --import-source on -k regex:k_pp
 timeout 300 python profiles/profile_wide.py > gpurun_out/wide_timing.log 2>&1
 timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/wide_launches.csv \
   python profiles/profile_wide.py 524288 32 1 1 > gpurun_out/wide_ncu.log 2>&1
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:k_gemm_x3 -s 3 -c 3 -f -o gpurun_out/prof_wide_gemm \
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:k_gemm -s 3 -c 3 -f -o gpurun_out/prof_wide_gemm \
   python profiles/profile_wide.py 524288 32 1 1 > gpurun_out/wide_ncu2.log 2>&1
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:"k_wide_l1|k_wide_head|k_wide_dw1|k_wide_reduce" -s 8 -c 4 -f \
   -o gpurun_out/prof_wide_side python profiles/profile_wide.py 524288 32 1 1 > gpurun_out/wide_ncu3.log 2>&1
