@@ -43,6 +43,19 @@ typedef enum {
 #define B2_PREC_F64 0 /* double state + double Diff: the parity-gated path (reference is double) */
 #define B2_PREC_F32 1 /* float everything: throughput path, drift vs reference is reported, not gated */
 
+/* environment variants the reference header documents but ships disabled (opt-in; 0 = the shipped cart-pole):
+ *   B2_ENV_SWINGUP      the `#if SWINGUP` branches: Diff include/cart_pole.h:154-159, getReward :136-139,
+ *                       is_over :100-101, reset range +-0.1 :80-81
+ *   B2_ENV_RANDOM_INIT  reset draws u ~ U(-r, r)^4, r = 0.05 (0.1 with SWINGUP): the commented-out line :85, live in
+ *                       archived/single_environment/cart_pole.h:87.  Philox stream keyed by (seed, global env id, step)
+ *                       instead of the reference's std::random_device, so runs are reproducible and shard-invariant
+ *   B2_ENV_EARLY_TERM   advance() stops after the substep at which is_over() holds and returns 1 (commented-out :115,
+ *                       live in the archived header :119); the record gets B2_FLAG_TERMINAL (src/main.cpp:81-85)
+ * Variants run the double-precision physics with the reference's own operation order (B2_PREC_F64 only). */
+#define B2_ENV_SWINGUP 1
+#define B2_ENV_RANDOM_INIT 2
+#define B2_ENV_EARLY_TERM 4
+
 typedef struct b2_engine* b2_handle;
 
 typedef struct {
@@ -65,7 +78,8 @@ typedef struct {
   uint64_t seed;          /* Philox key */
   uint64_t env_offset;    /* global id of local env 0: same global seed => same trajectories for any sharding */
   int device;             /* CUDA ordinal */
-  int reserved[7];
+  int env_flags;          /* B2_ENV_* (0 = the shipped environment) */
+  int reserved[6];
 } b2_config;
 
 /* One trajectory batch in host memory: what MemoryNN holds (include/ppo_nn.h:20-29).
@@ -146,6 +160,8 @@ int b2_rollout(b2_handle h, int T, const float* forced_action);
  * env: x, xdot, thetadot, theta, cos, sin) and getReward (:135-147).  Either output may be NULL. */
 int b2_env_step(b2_handle h, const double* force, int64_t n);
 int b2_env_observe(b2_handle h, double* obs, double* reward, int64_t n);
+/* what advance() returned for every env in the last b2_env_step (always 0 without B2_ENV_EARLY_TERM, cart_pole.h:117) */
+int b2_env_terminated(b2_handle h, uint8_t* terminated, int64_t n);
 /* b2_rollout whose trajectory lands in HOST buffers (what MemoryNN holds after a collection phase): the horizon is
  * simulated in n_chunks launches and each finished chunk is copied out on a second stream while the next one is
  * being simulated.  Fields of `out` may be NULL (skipped); `returns` is ignored (no returns exist yet).  Pinned

@@ -22,6 +22,21 @@
 
 #include "../b200ppo.h"
 
+// The reference selects its environment variant at compile time (`#define SWINGUP 0`, include/cart_pole.h:17) and keeps
+// the random initial state (:85) and the early exit of advance() (:115) as commented-out lines.  Same switches here,
+// defined before including this header: SWINGUP 1, B2_CARTPOLE_RANDOM_INIT 1, B2_CARTPOLE_EARLY_TERM 1.
+#ifndef SWINGUP
+#define SWINGUP 0
+#endif
+#ifndef B2_CARTPOLE_RANDOM_INIT
+#define B2_CARTPOLE_RANDOM_INIT 0
+#endif
+#ifndef B2_CARTPOLE_EARLY_TERM
+#define B2_CARTPOLE_EARLY_TERM 0
+#endif
+#define B2_CARTPOLE_ENV_FLAGS \
+  ((SWINGUP ? B2_ENV_SWINGUP : 0) | (B2_CARTPOLE_RANDOM_INIT ? B2_ENV_RANDOM_INIT : 0) | (B2_CARTPOLE_EARLY_TERM ? B2_ENV_EARLY_TERM : 0))
+
 // include/cart_pole.h:47-61 -- plain 4-vector: y1 = x, y2 = xdot, y3 = theta, y4 = thetadot
 struct Vec4 {
   double y1, y2, y3, y4;
@@ -32,13 +47,17 @@ struct Vec4 {
 
 class CartPoleBatch {
  public:
-  explicit CartPoleBatch(int64_t n, int device = 0, int precision = B2_PREC_F64) : n_(n) {
+  explicit CartPoleBatch(int64_t n, int device = 0, int precision = B2_PREC_F64, int env_flags = B2_CARTPOLE_ENV_FLAGS,
+                         uint64_t seed = 0x5EED)
+      : n_(n) {
     b2_config c;
     ck(b2_config_default(&c), "b2_config_default");
     c.n_envs = n;
     c.horizon = 1;
     c.device = device;
     c.precision = precision;
+    c.env_flags = env_flags;
+    c.seed = seed;
     ck(b2_create(&c, &h_), "CartPoleBatch");
   }
   ~CartPoleBatch() { if (h_) b2_destroy(h_); }
@@ -61,6 +80,11 @@ class CartPoleBatch {
     ck(b2_env_observe(h_, nullptr, r.data(), n_), "getReward");
     return r;
   }
+  std::vector<uint8_t> terminated() {                                                      // advance()'s return value per env
+    std::vector<uint8_t> t((size_t)n_);
+    ck(b2_env_terminated(h_, t.data(), n_), "terminated");
+    return t;
+  }
   std::vector<Vec4> state() {
     std::vector<double> u((size_t)4 * n_);
     ck(b2_env_get_state(h_, u.data(), nullptr, n_), "state");
@@ -68,13 +92,14 @@ class CartPoleBatch {
     for (int64_t e = 0; e < n_; e++) out[(size_t)e] = Vec4(u[4 * e], u[4 * e + 1], u[4 * e + 2], u[4 * e + 3]);
     return out;
   }
-  void set_state(const std::vector<Vec4>& s) {
+  void set_state(const std::vector<Vec4>& s, const std::vector<int32_t>* steps = nullptr) {
     if ((int64_t)s.size() != n_) throw std::runtime_error("set_state: one state per environment expected");
+    if (steps && (int64_t)steps->size() != n_) throw std::runtime_error("set_state: one step counter per environment expected");
     std::vector<double> u((size_t)4 * n_);
     for (int64_t e = 0; e < n_; e++) {
       u[4 * e] = s[(size_t)e].y1; u[4 * e + 1] = s[(size_t)e].y2; u[4 * e + 2] = s[(size_t)e].y3; u[4 * e + 3] = s[(size_t)e].y4;
     }
-    ck(b2_env_set_state(h_, u.data(), nullptr, n_), "set_state");
+    ck(b2_env_set_state(h_, u.data(), steps ? steps->data() : nullptr, n_), "set_state");
   }
   b2_handle handle() const { return h_; }
 
@@ -96,21 +121,27 @@ class CartPole {
 
   explicit CartPole(int device = 0) : sim_(1, device) {}
 
-  void reset() {  // :77-90 (the random initial state is commented out upstream: exact zero state)
+  void reset() {  // :77-90 (upstream the random initial state is commented out: exact zero state unless B2_CARTPOLE_RANDOM_INIT)
     sim_.reset();
-    u = Vec4(0.0, 0.0, 0.0, 0.0);
+    u = sim_.state()[0];
     step = 0; F = 0; t = 0;
   }
-  bool is_failed() const { return std::fabs(u.y1) > 2.4 || std::fabs(u.y3) > M_PI / 15; }  // :92-98
-  bool is_over() const { return is_failed(); }                                             // :99-105
-  int advance(std::vector<double> action) {  // :107-118; always returns 0 (the early exit is commented out)
+#if SWINGUP
+  bool is_failed() const { return std::fabs(u.y1) > 2.4; }                                 // :93-94
+  bool is_over() const { return step >= 500 || std::fabs(u.y1) > 2.4; }                    // :100-101
+#else
+  bool is_failed() const { return std::fabs(u.y1) > 2.4 || std::fabs(u.y3) > M_PI / 15; }  // :96
+  bool is_over() const { return is_failed(); }                                             // :103
+#endif
+  int advance(std::vector<double> action) {  // :107-118; returns 0 unless B2_CARTPOLE_EARLY_TERM (the early exit, :115)
     F = action.at(0);
+    const std::vector<int32_t> before{step};
     step++;
-    sim_.set_state({u});  // `u` is a public field upstream: honour a caller that wrote to it
+    sim_.set_state({u}, &before);  // `u` and `step` are public fields upstream: honour a caller that wrote to them
     sim_.advance({F});
     u = sim_.state()[0];
     t += dt * nsteps;
-    return 0;
+    return sim_.terminated()[0];
   }
   std::vector<double> getobs(const int size = 6) {  // :120-133
     assert(size == 4 || size == 6);

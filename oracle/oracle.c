@@ -74,6 +74,61 @@ double orc_cartpole_reward(const double u[4]) {
   return 1 - (fabs(u[2]) > M_PI / 15 || fabs(u[0]) > 2.4); /* :142 */
 }
 
+/* ---- variants (documented in the header, disabled in the shipped build) ---- */
+void orc_cartpole_diff_v(int fl, const double u[4], double F, double du[4]) {
+  if (!(fl & ORC_ENV_SWINGUP)) { orc_cartpole_diff(u, F, du); return; }
+  const double cosy = cos(u[2]), siny = sin(u[2]); /* :152 */
+  const double w = u[3];
+  const double fac1 = 1 / (MC + MP * siny * siny);                                   /* :155 */
+  const double fac2 = fac1 / LEN;                                                    /* :156 */
+  du[1] = fac1 * (F + MP * siny * (LEN * w * w + GRAV * cosy));                      /* :157 */
+  du[3] = fac2 * (-F * cosy - MP * LEN * w * w * cosy * siny - (MC + MP) * GRAV * siny); /* :158-159 */
+  du[0] = u[1];
+  du[2] = u[3];
+}
+
+int orc_cartpole_is_over(int fl, const double u[4], int step) {
+  if (fl & ORC_ENV_SWINGUP) return step >= 500 || fabs(u[0]) > 2.4;                  /* :101 */
+  return fabs(u[0]) > 2.4 || fabs(u[2]) > M_PI / 15;                                 /* :103 */
+}
+
+int orc_cartpole_advance_v(int fl, double u[4], int step, double F) {
+  static const double a[6] = {0.000000000000,  -0.737101392796, -1.634740794341,
+                              -0.744739003780, -1.469897351522, -2.813971388035};
+  static const double b[6] = {0.032918605146, 0.823256998200, 0.381530948900,
+                              0.200092213184, 1.718581042715, 0.270000000000};
+  for (int s = 0; s < NSUB; s++) {
+    double w[4] = {0, 0, 0, 0};
+    for (int i = 0; i < 6; i++) {
+      double d[4];
+      orc_cartpole_diff_v(fl, u, F, d);
+      for (int j = 0; j < 4; j++) {
+        w[j] = w[j] * a[i] + d[j] * DT;
+        u[j] = u[j] + w[j] * b[i];
+      }
+    }
+    if ((fl & ORC_ENV_EARLY_TERM) && orc_cartpole_is_over(fl, u, step)) return 1;    /* :115 */
+  }
+  return 0;
+}
+
+double orc_cartpole_reward_v(int fl, const double u[4]) {
+  if (!(fl & ORC_ENV_SWINGUP)) return orc_cartpole_reward(u);
+  double angle = fmod(u[2], 2 * M_PI);                                               /* :137 */
+  angle = angle < 0 ? angle + 2 * M_PI : angle;                                      /* :138 */
+  return fabs(angle - M_PI) < M_PI / 6 ? 1 : 0;                                      /* :139 */
+}
+
+void orc_cartpole_init_state(int fl, uint64_t seed, uint64_t env, uint64_t tick, double u[4]) {
+  if (!(fl & ORC_ENV_RANDOM_INIT)) { u[0] = u[1] = u[2] = u[3] = 0; return; }        /* :86 */
+  const double r = (fl & ORC_ENV_SWINGUP) ? 0.1 : 0.05;                              /* :81, :83 */
+  uint32_t ctr[4] = {(uint32_t)env, (uint32_t)(env >> 32), (uint32_t)tick, (uint32_t)(tick >> 32)};
+  uint32_t key[2] = {(uint32_t)seed ^ 0x494E4954u, (uint32_t)(seed >> 32)};          /* a stream of its own: "INIT" */
+  uint32_t x[4];
+  orc_philox4x32_10(ctr, key, x);
+  for (int j = 0; j < 4; j++) u[j] = (((double)x[j] + 0.5) * (1.0 / 4294967296.0) * 2 - 1) * r;
+}
+
 double orc_scale_action(float a) {
   /* src/main.cpp:57-60: float + int in float, then double arithmetic, stored to float; :69 widen */
   const double hi = 10, lo = -10; /* :18 */
@@ -330,6 +385,47 @@ float orc_gauss(uint64_t seed, uint64_t env, uint64_t step) {
 }
 
 /* ----------------------------------------------------------------- rollout */
+void orc_rollout_v(const orc_dims* d, const float* params, long N, int T, int n_timestep, double sigma,
+                   uint64_t seed, uint64_t env0, uint64_t step0, const float* forced_action, int env_flags,
+                   double* state, int* ep_step, double* ep_ret, float* obs, float* action,
+                   float* logp, float* mu, float* reward, uint8_t* flags, double* state_trace) {
+#pragma omp parallel for schedule(static)
+  for (long e = 0; e < N; e++) {
+    double u[4] = {state[4 * e], state[4 * e + 1], state[4 * e + 2], state[4 * e + 3]};
+    int es = ep_step[e];
+    double er = ep_ret ? ep_ret[e] : 0;
+    for (int t = 0; t < T; t++) {
+      long k = (long)t * N + e;
+      float o[6], m, a;
+      orc_cartpole_obs(u, o);
+      orc_mlp_forward(d, params, d->A, 1, o, NULL, NULL, &m);
+      if (forced_action) a = forced_action[k];
+      else a = (float)((double)m + sigma * (double)orc_gauss(seed, env0 + e, step0 + t));
+      float lp = orc_logprob(a, m, sigma);
+      es += 1;                                                                   /* cart_pole.h:109 */
+      int term = orc_cartpole_advance_v(env_flags, u, es, orc_scale_action(a));
+      double r = orc_cartpole_reward_v(env_flags, u);
+      er += r;
+      int timeup = !term && (es == n_timestep);                                  /* src/main.cpp:81-88 */
+      uint8_t f = (uint8_t)(term ? 1 : (timeup ? 2 : (t == T - 1 ? 4 : 0)));
+      if (obs) memcpy(obs + k * 6, o, sizeof o);
+      if (action) action[k] = a;
+      if (logp) logp[k] = lp;
+      if (mu) mu[k] = m;
+      if (reward) reward[k] = (float)r;
+      if (flags) flags[k] = f;
+      if (state_trace) memcpy(state_trace + k * 4, u, sizeof u);
+      if (term || timeup) {
+        orc_cartpole_init_state(env_flags, seed, env0 + e, step0 + (uint64_t)t + 1, u);
+        es = 0; er = 0;
+      }
+    }
+    memcpy(state + 4 * e, u, sizeof u);
+    ep_step[e] = es;
+    if (ep_ret) ep_ret[e] = er;
+  }
+}
+
 void orc_rollout(const orc_dims* d, const float* params, long N, int T, int n_timestep, double sigma,
                  uint64_t seed, uint64_t env0, uint64_t step0, const float* forced_action,
                  double* state, int* ep_step, double* ep_ret, float* obs, float* action,

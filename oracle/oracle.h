@@ -31,6 +31,24 @@ void orc_cartpole_obs(const double u[4], float obs[6]);              /* :120-133
 double orc_cartpole_reward(const double u[4]);                       /* :135-147              */
 double orc_scale_action(float a);                                    /* src/main.cpp:57-60,69 */
 
+/* ---- environment variants the header documents but ships disabled, opt-in:
+ *   ORC_ENV_SWINGUP      the `#if SWINGUP` branches: Diff :154-159, getReward :136-139, is_over :100-101,
+ *                        reset range +-0.1 :80-81
+ *   ORC_ENV_RANDOM_INIT  reset draws u ~ U(-r, r)^4, r = 0.05 (0.1 SWINGUP): the commented-out line :85
+ *                        (live in archived/single_environment/cart_pole.h:87).  The reference seeds mt19937 from
+ *                        std::random_device (not reproducible); here the draw is Philox, keyed like orc_gauss.
+ *   ORC_ENV_EARLY_TERM   advance returns 1 as soon as is_over() holds after a substep: the commented-out
+ *                        line :115 (live in archived/.../cart_pole.h:119); env_run turns it into TERMINATE
+ *                        (src/main.cpp:81-85) and the learner restarts the return there (src/ppo_nn.cpp:229-230) */
+#define ORC_ENV_SWINGUP 1
+#define ORC_ENV_RANDOM_INIT 2
+#define ORC_ENV_EARLY_TERM 4
+void orc_cartpole_diff_v(int env_flags, const double u[4], double F, double du[4]);
+int orc_cartpole_is_over(int env_flags, const double u[4], int step);             /* :99-105 */
+int orc_cartpole_advance_v(int env_flags, double u[4], int step, double F);       /* step = value after step++ (:109) */
+double orc_cartpole_reward_v(int env_flags, const double u[4]);
+void orc_cartpole_init_state(int env_flags, uint64_t seed, uint64_t env, uint64_t tick, double u[4]);
+
 /* ---- policy: src/ppo_nn.cpp ---- */
 /* one net forward; h1/h2 may be NULL.  final_tanh=1 for the actor (ppo_nn.h:98-102). */
 void orc_mlp_forward(const orc_dims* d, const float* net, int out, int final_tanh, const float* obs,
@@ -80,6 +98,13 @@ void orc_rollout(const orc_dims* d, const float* params, long N, int T, int n_ti
                  uint64_t seed, uint64_t env0, uint64_t step0, const float* forced_action,
                  double* state, int* ep_step, double* ep_ret, float* obs, float* action,
                  float* logp, float* mu, float* reward, uint8_t* flags, double* state_trace);
+
+/* orc_rollout with the env variants above.  TERMINATE takes precedence over TIMEUP (src/main.cpp:81-88); after either
+ * the env is reset (zero state, or orc_cartpole_init_state(.., env0 + e, step0 + t + 1) with RANDOM_INIT). */
+void orc_rollout_v(const orc_dims* d, const float* params, long N, int T, int n_timestep, double sigma,
+                   uint64_t seed, uint64_t env0, uint64_t step0, const float* forced_action, int env_flags,
+                   double* state, int* ep_step, double* ep_ret, float* obs, float* action,
+                   float* logp, float* mu, float* reward, uint8_t* flags, double* state_trace);
 
 #ifdef __cplusplus
 }

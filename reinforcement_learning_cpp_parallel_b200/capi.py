@@ -13,6 +13,7 @@ def lib_path():
 
 FLAG_TERMINAL, FLAG_TIMEUP, FLAG_TRUNC = 1, 2, 4
 PREC_F64, PREC_F32 = 0, 1
+ENV_SWINGUP, ENV_RANDOM_INIT, ENV_EARLY_TERM = 1, 2, 4
 COMM_ID_BYTES = 128
 
 
@@ -31,7 +32,7 @@ class Config(C.Structure):
                 ("k_epochs", C.c_int), ("hidden1", C.c_int), ("hidden2", C.c_int),
                 ("n_envs", C.c_int64), ("horizon", C.c_int), ("n_minibatches", C.c_int),
                 ("precision", C.c_int), ("seed", C.c_uint64), ("env_offset", C.c_uint64),
-                ("device", C.c_int), ("reserved", C.c_int * 7)]
+                ("device", C.c_int), ("env_flags", C.c_int), ("reserved", C.c_int * 6)]
 
 
 class Batch(C.Structure):
@@ -83,6 +84,7 @@ SYMBOLS = {
     "b2_rollout_host": (C.c_int, [_H, C.c_int, C.c_int, _P(BatchOut)]),
     "b2_env_step": (C.c_int, [_H, C.c_void_p, C.c_int64]),
     "b2_env_observe": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_int64]),
+    "b2_env_terminated": (C.c_int, [_H, C.c_void_p, C.c_int64]),
     "b2_update_resident": (C.c_int, [_H, _P(UpdateStats)]),
     "b2_train_iteration": (C.c_int, [_H, C.c_int, _P(UpdateStats)]),
     "b2_traj_download": (C.c_int, [_H, _P(BatchOut), C.c_void_p]),
@@ -287,6 +289,13 @@ class Engine:
         r = np.empty(n, np.float64)
         _ck(self.L.b2_env_observe(self.h, _vp(o), _vp(r), n))
         return o, r
+
+    def env_terminated(self):
+        """what advance() returned per env in the last env_step (include/cart_pole.h:115,117)."""
+        n = int(self.cfg.n_envs)
+        t = np.empty(n, np.uint8)
+        _ck(self.L.b2_env_terminated(self.h, _vp(t), n))
+        return t
 
     def set_state_trace(self, on=True):
         _ck(self.L.b2_set_state_trace(self.h, int(on)))

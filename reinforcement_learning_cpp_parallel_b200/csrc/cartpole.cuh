@@ -19,6 +19,7 @@
 //   * the RK accumulator is kept as W = w / dt and b_i dt is folded into one constant.
 // Measured against the unmodified header: <= 1e-12 relative per env step (tests/test_gpu_parity.py).
 #pragma once
+#include "../../include/b200ppo.h"
 #include "common.cuh"
 
 namespace b2 {
@@ -195,6 +196,77 @@ struct CartPoleDyn<float> {
     float s, c;
     sincosf(u[2], &s, &c);
     o[0] = u[0]; o[1] = u[1]; o[2] = u[3]; o[3] = u[2]; o[4] = c; o[5] = s;
+  }
+};
+
+// ---------------------------------------------------------------------------------------- variants
+// The branches the reference header documents but ships disabled (b200ppo.h B2_ENV_*): SWINGUP dynamics / reward /
+// is_over, early termination inside advance(), random initial state.  Opt-in and never on the benchmark path, so the
+// physics is written reference-shaped (sincos + true divisions per stage, include/cart_pole.h:149-170) rather than
+// with the carried-rotation stage above; double only.  Out of line: one copy per kernel.
+struct CartPoleVar {
+  static __device__ __forceinline__ bool is_over(int fl, const double (&u)[4], int step) {   // :99-105
+    if (fl & B2_ENV_SWINGUP) return step >= 500 || fabs(u[0]) > 2.4;
+    return fabs(u[0]) > 2.4 || fabs(u[2]) > CPC::PI_15;
+  }
+  // advance (:107-118) with line :115 live when B2_ENV_EARLY_TERM is set; step = the value after step++ (:109)
+  struct Adv { double4 u; int term; };   // by value in and out (see substep_exact)
+  static __device__ __noinline__ Adv advance(double4 u4, double F, int fl, int step) {
+    constexpr double a[6] = B2_RK_A;
+    constexpr double b[6] = B2_RK_B;
+    double u[4] = {u4.x, u4.y, u4.z, u4.w};
+    int term = 0;
+#pragma unroll 1
+    for (int sub = 0; sub < CPC::nsteps && !term; sub++) {
+      double w[4] = {0, 0, 0, 0};
+#pragma unroll 1
+      for (int i = 0; i < 6; i++) {
+        double s, c, dd2, dd4;
+        sincos(u[2], &s, &c);
+        const double om = u[3];
+        if (fl & B2_ENV_SWINGUP) {                                                              // :155-159
+          const double fac1 = 1.0 / (CPC::mc + CPC::mp * s * s);
+          const double fac2 = fac1 / CPC::l;
+          dd2 = fac1 * (F + CPC::mp * s * (CPC::l * om * om + CPC::g * c));
+          dd4 = fac2 * (-F * c - CPC::mp * CPC::l * om * om * c * s - (CPC::mc + CPC::mp) * CPC::g * s);
+        } else {                                                                                // :161-165
+          const double tot = CPC::mp + CPC::mc;
+          const double fac2 = CPC::l * (4.0 / 3 - (CPC::mp * c * c) / tot);
+          const double F1 = F + CPC::mp * CPC::l * om * om * s;
+          dd4 = (CPC::g * s - F1 * c / tot) / fac2;
+          dd2 = (F1 - CPC::mp * CPC::l * dd4 * c) / tot;
+        }
+        const double d[4] = {u[1], dd2, om, dd4};
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          w[j] = w[j] * a[i] + d[j] * CPC::dt;
+          u[j] = u[j] + w[j] * b[i];
+        }
+      }
+      if ((fl & B2_ENV_EARLY_TERM) && is_over(fl, u, step)) term = 1;                           // :115
+    }
+    Adv r;
+    r.u = make_double4(u[0], u[1], u[2], u[3]);
+    r.term = term;
+    return r;
+  }
+  static __device__ __forceinline__ float reward(int fl, const double (&u)[4]) {                // :135-147
+    if (!(fl & B2_ENV_SWINGUP)) return CartPoleDyn<double>::reward(u);
+    double angle = fmod(u[2], 2 * 3.14159265358979323846);
+    angle = angle < 0 ? angle + 2 * 3.14159265358979323846 : angle;
+    return fabs(angle - 3.14159265358979323846) < 3.14159265358979323846 / 6 ? 1.0f : 0.0f;
+  }
+  // reset (:77-90): zero state, or (B2_ENV_RANDOM_INIT) U(-r, r)^4 from a Philox stream of its own, counter
+  // (global env id, tick) (the CPU checker restates the same draw)
+  static __device__ __forceinline__ void init_state(int fl, uint64_t seed, uint64_t env, uint64_t tick, double (&u)[4]) {
+    if (!(fl & B2_ENV_RANDOM_INIT)) { u[0] = u[1] = u[2] = u[3] = 0.0; return; }
+    const double r = (fl & B2_ENV_SWINGUP) ? 0.1 : 0.05;
+    uint32_t xs[4];
+    philox4x32_10((uint32_t)env, (uint32_t)(env >> 32), (uint32_t)tick, (uint32_t)(tick >> 32),
+                  (uint32_t)seed ^ 0x494E4954u, (uint32_t)(seed >> 32), xs);
+#pragma unroll
+    for (int j = 0; j < 4; j++)
+      u[j] = __dmul_rn(__dadd_rn(__dmul_rn(__dmul_rn(__dadd_rn((double)xs[j], 0.5), 1.0 / 4294967296.0), 2.0), -1.0), r);
   }
 };
 

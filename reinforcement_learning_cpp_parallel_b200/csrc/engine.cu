@@ -82,6 +82,8 @@ struct b2_engine {
   // env state
   double* state = nullptr;
   int32_t *ep_step = nullptr, *ep_count = nullptr;
+  uint8_t* env_term = nullptr;   // [n_envs] what advance() returned in the last b2_env_step
+  uint64_t reset_calls = 0;      // tick of the random initial state drawn by b2_env_reset
   float *ep_ret = nullptr, *ep_log = nullptr;
   int* progress = nullptr;
   int max_eps = 0;
@@ -320,6 +322,8 @@ int b2_create(const b2_config* cfg, b2_handle* out) {
     return set_error(B2_ERR_INVALID, "hidden widths %dx%d not built: 64x32 (reference) or both in {64,128,192,256}", cfg->hidden1, cfg->hidden2);
   if (cfg->n_envs < 1 || cfg->horizon < 1 || cfg->n_timestep < 1) return set_error(B2_ERR_INVALID, "n_envs, horizon, n_timestep must be >= 1");
   if (cfg->precision != B2_PREC_F64 && cfg->precision != B2_PREC_F32) return set_error(B2_ERR_INVALID, "unknown precision %d", cfg->precision);
+  if (cfg->env_flags & ~(B2_ENV_SWINGUP | B2_ENV_RANDOM_INIT | B2_ENV_EARLY_TERM)) return set_error(B2_ERR_INVALID, "unknown env_flags 0x%x", cfg->env_flags);
+  if (cfg->env_flags && cfg->precision != B2_PREC_F64) return set_error(B2_ERR_INVALID, "env variants (env_flags 0x%x) run the double-precision physics only", cfg->env_flags);
   if (cfg->k_epochs < 1 || cfg->n_minibatches < 1) return set_error(B2_ERR_INVALID, "k_epochs and n_minibatches must be >= 1");
   if (!(cfg->action_std > 0)) return set_error(B2_ERR_INVALID, "action_std must be > 0");
   int ndev = b2_device_count();
@@ -353,7 +357,10 @@ int b2_create(const b2_config* cfg, b2_handle* out) {
   CK(cudaMemset(E->grads, 0, sizeof(float) * E->pstride));
   CK(cudaMemset(E->adam_step, 0, sizeof(int64_t)));
   CK(cudaMemset(E->status, 0, sizeof(int)));
-  E->max_eps = cfg->horizon / cfg->n_timestep + 2;
+  // episodes one env can finish inside one rollout: TIMEUP every n_timestep steps; with early termination every step
+  E->max_eps = (cfg->env_flags & B2_ENV_EARLY_TERM) ? cfg->horizon + 1 : cfg->horizon / cfg->n_timestep + 2;
+  CK(cudaMalloc(&E->env_term, (size_t)cfg->n_envs));
+  CK(cudaMemset(E->env_term, 0, (size_t)cfg->n_envs));
   CK(cudaMalloc(&E->state, sizeof(double) * 4 * NE));
   CK(cudaMalloc(&E->ep_step, sizeof(int32_t) * NE));
   CK(cudaMalloc(&E->ep_count, sizeof(int32_t) * NE));
@@ -361,6 +368,11 @@ int b2_create(const b2_config* cfg, b2_handle* out) {
   CK(cudaMalloc(&E->ep_log, sizeof(float) * NE * E->max_eps));
   CK(cudaMalloc(&E->progress, sizeof(int) * ((NE + 31) / 32)));
   CK(cudaMemset(E->state, 0, sizeof(double) * 4 * NE));   // CartPole::reset: u = 0 (cart_pole.h:86)
+  if (cfg->env_flags & B2_ENV_RANDOM_INIT) {
+    cudaError_t ce = launch_env_init(E->state, NE, cfg->env_flags, cfg->seed, cfg->env_offset, 0, E->stream);
+    if (ce != cudaSuccess) { b2_destroy(E); return set_error(B2_ERR_CUDA, "env init: %s", cudaGetErrorString(ce)); }
+    E->launches += 1;
+  }
   CK(cudaMemset(E->ep_step, 0, sizeof(int32_t) * NE));
   CK(cudaMemset(E->ep_count, 0, sizeof(int32_t) * NE));
   CK(cudaMemset(E->ep_ret, 0, sizeof(float) * NE));
@@ -387,7 +399,7 @@ int b2_destroy(b2_handle E) {
   void* ptrs[] = {E->params, E->adam_m, E->adam_v, E->grads, E->partials, E->adam_step, E->loss_log, E->state,
                   E->ep_step, E->ep_count, E->ep_ret, E->ep_log, t.obs, t.action, t.logp, t.mu, t.reward, t.ret,
                   t.vboot, t.vcur, t.flags, t.state_trace, E->forced, E->stage, E->stage_u8, E->status, E->flush_buf,
-                  E->progress};
+                  E->progress, E->env_term};
   for (void* p : ptrs) cudaFree(p);
   if (E->status_host) cudaFreeHost(E->status_host);
   if (E->copy_stream) {
@@ -608,6 +620,14 @@ int b2_env_reset(b2_handle E) {
   CK(cudaSetDevice(E->cfg.device));
   const int64_t NE = E->cfg.n_envs;
   CK(cudaMemsetAsync(E->state, 0, sizeof(double) * 4 * NE, E->stream));
+  if (E->cfg.env_flags & B2_ENV_RANDOM_INIT) {   // a fresh draw per reset call; ticks >= 2^63 never collide with in-rollout resets
+    E->reset_calls += 1;
+    cudaError_t ce = launch_env_init(E->state, NE, E->cfg.env_flags, E->cfg.seed, E->cfg.env_offset,
+                                     (1ull << 63) | E->reset_calls, E->stream);
+    if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "env init: %s", cudaGetErrorString(ce));
+    E->launches += 1;
+  }
+  CK(cudaMemsetAsync(E->env_term, 0, (size_t)NE, E->stream));
   CK(cudaMemsetAsync(E->ep_step, 0, sizeof(int32_t) * NE, E->stream));
   CK(cudaMemsetAsync(E->ep_ret, 0, sizeof(float) * NE, E->stream));
   CK(cudaMemsetAsync(E->ep_count, 0, sizeof(int32_t) * NE, E->stream));
@@ -648,7 +668,7 @@ int b2_env_step(b2_handle E, const double* force, int64_t n) {
   if (rc) return rc;
   double* d_force = reinterpret_cast<double*>(E->stage);
   CK(cudaMemcpyAsync(d_force, force, sizeof(double) * n, cudaMemcpyHostToDevice, E->stream));
-  cudaError_t ce = launch_env_step(E->state, E->ep_step, d_force, n, E->cfg.precision, E->stream);
+  cudaError_t ce = launch_env_step(E->state, E->ep_step, d_force, n, E->cfg.precision, E->cfg.env_flags, E->env_term, E->stream);
   if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "env_step: %s", cudaGetErrorString(ce));
   E->launches += 1;
   E->total_env_steps += n;
@@ -665,11 +685,20 @@ int b2_env_observe(b2_handle E, double* obs, double* reward, int64_t n) {
   if (rc) return rc;
   double* d_obs = reinterpret_cast<double*>(E->stage) + n;
   double* d_rew = d_obs + 6 * n;
-  cudaError_t ce = launch_env_observe(E->state, obs ? d_obs : nullptr, reward ? d_rew : nullptr, n, E->stream);
+  cudaError_t ce = launch_env_observe(E->state, obs ? d_obs : nullptr, reward ? d_rew : nullptr, n, E->cfg.env_flags, E->stream);
   if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "env_observe: %s", cudaGetErrorString(ce));
   E->launches += 1;
   if (obs) CK(cudaMemcpyAsync(obs, d_obs, sizeof(double) * 6 * n, cudaMemcpyDeviceToHost, E->stream));
   if (reward) CK(cudaMemcpyAsync(reward, d_rew, sizeof(double) * n, cudaMemcpyDeviceToHost, E->stream));
+  CK(cudaStreamSynchronize(E->stream));
+  return B2_OK;
+}
+
+int b2_env_terminated(b2_handle E, uint8_t* terminated, int64_t n) {
+  NEED(E);
+  if (!terminated || n != E->cfg.n_envs) return set_error(B2_ERR_INVALID, "env_terminated: expected %lld envs", (long long)E->cfg.n_envs);
+  CK(cudaSetDevice(E->cfg.device));
+  CK(cudaMemcpyAsync(terminated, E->env_term, (size_t)n, cudaMemcpyDeviceToHost, E->stream));
   CK(cudaStreamSynchronize(E->stream));
   return B2_OK;
 }
@@ -689,7 +718,7 @@ static int rollout_window(b2_engine* E, int T, int t_begin, int t_end, bool forc
   a.forced_action = forced ? E->forced : nullptr;
   a.n_envs = E->cfg.n_envs; a.T = T; a.t_begin = t_begin; a.t_end = t_end; a.n_timestep = E->cfg.n_timestep;
   a.seed = E->cfg.seed; a.env_offset = E->cfg.env_offset; a.step0 = E->global_step;
-  a.hp = E->hp; a.status = E->status; a.progress = E->progress;
+  a.hp = E->hp; a.status = E->status; a.progress = E->progress; a.env_flags = E->cfg.env_flags;
   cudaError_t ce = launch_rollout(a, E->cfg.precision, E->trace, E->sm_count, E->stream, E->cfg.hidden1, E->cfg.hidden2);
   if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "rollout: %s", cudaGetErrorString(ce));
   E->launches += 1;

@@ -57,6 +57,7 @@ struct RolloutArgs {
   uint64_t seed, env_offset, step0;
   HyperDev hp;
   int* status;          // bit0: non-finite action seen
+  int env_flags;        // B2_ENV_* (0: the shipped environment, hot kernels)
   int* progress;        // [ceil(n_envs/32)] steps of this rollout already published per env group (hand-off word)
 };
 
@@ -94,8 +95,10 @@ cudaError_t launch_ppo_grad(const UpdateArgs& a, cudaStream_t st);
 cudaError_t launch_reduce(const UpdateArgs& a, bool apply_adam, cudaStream_t st);
 cudaError_t launch_adam(const UpdateArgs& a, cudaStream_t st);
 cudaError_t launch_env_step(double* state, int32_t* ep_step, const double* force, int64_t n, int precision,
+                            int env_flags, uint8_t* terminated, cudaStream_t st);
+cudaError_t launch_env_observe(const double* state, double* obs, double* reward, int64_t n, int env_flags, cudaStream_t st);
+cudaError_t launch_env_init(double* state, int64_t n, int env_flags, uint64_t seed, uint64_t env_offset, uint64_t tick,
                             cudaStream_t st);
-cudaError_t launch_env_observe(const double* state, double* obs, double* reward, int64_t n, cudaStream_t st);
 cudaError_t launch_flush(float* buf, int64_t n, cudaStream_t st);
 cudaError_t measure_fma_peak(bool fp64, int sm_count, cudaStream_t st, double* tflops);
 

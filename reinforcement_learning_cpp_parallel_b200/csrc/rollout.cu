@@ -46,7 +46,9 @@ __device__ __forceinline__ void st_release(int* p, int v) {
 }
 
 // Advance group g (envs 32 g .. 32 g + 31) over steps [t0, t1) of this LAUNCH (absolute step = t_begin + t).
-template <typename Real, class N, bool TRACE>
+// VAR: the opt-in env variants of b200ppo.h B2_ENV_* (a.env_flags), double physics in the reference's operation order;
+// a separate instantiation, so the shipped-env kernels are untouched by it.
+template <typename Real, class N, bool TRACE, bool VAR>
 __device__ __forceinline__ void rollout_segment(const RolloutArgs& a, const float* sm, float* hs, int64_t g, int t0,
                                                 int t1) {
   using Dyn = CartPoleDyn<Real>;
@@ -84,12 +86,24 @@ __device__ __forceinline__ void rollout_segment(const RolloutArgs& a, const floa
     const float lp = gauss_logprob(act, mu, a.hp.inv_var, a.hp.half_log_norm);   // :115
     bad |= !isfinite(act);                                               // src/main.cpp:50-55
 
-    Dyn::advance(u, (Real)scale_action(act));                            // src/main.cpp:57-71
-    const float r = Dyn::reward(u);                                      // :73
+    bool terminal = false;
+    float r;
+    if constexpr (VAR) {
+      const CartPoleVar::Adv adv = CartPoleVar::advance(make_double4((double)u[0], (double)u[1], (double)u[2], (double)u[3]),
+                                                        scale_action(act), a.env_flags, es + 1);
+      u[0] = (Real)adv.u.x; u[1] = (Real)adv.u.y; u[2] = (Real)adv.u.z; u[3] = (Real)adv.u.w;
+      terminal = adv.term != 0;                                          // src/main.cpp:81-85
+      const double ud[4] = {adv.u.x, adv.u.y, adv.u.z, adv.u.w};
+      r = CartPoleVar::reward(a.env_flags, ud);
+    } else {
+      Dyn::advance(u, (Real)scale_action(act));                          // src/main.cpp:57-71
+      r = Dyn::reward(u);                                                // :73
+    }
     es += 1;
     er += r;
-    const bool timeup = (es == a.n_timestep);                            // :86-88 (TERMINATE never fires, Q1)
-    const uint8_t fl = timeup ? (uint8_t)B2_FLAG_TIMEUP : ((t == a.T - 1) ? (uint8_t)B2_FLAG_TRUNC : (uint8_t)0);
+    const bool timeup = !terminal && (es == a.n_timestep);               // :86-88 (TERMINATE never fires in the shipped env, Q1)
+    const uint8_t fl = terminal ? (uint8_t)B2_FLAG_TERMINAL
+                                : (timeup ? (uint8_t)B2_FLAG_TIMEUP : ((t == a.T - 1) ? (uint8_t)B2_FLAG_TRUNC : (uint8_t)0));
 
 #pragma unroll
     for (int c = 0; c < 6; c++) __stcs(a.tr.obs + c * cap + k, o[c]);   // streaming: written once, read by K3 later
@@ -102,10 +116,16 @@ __device__ __forceinline__ void rollout_segment(const RolloutArgs& a, const floa
       double4 s4 = make_double4((double)u[0], (double)u[1], (double)u[2], (double)u[3]);
       *reinterpret_cast<double4*>(a.tr.state_trace + 4 * k) = s4;
     }
-    if (timeup) {                                                        // :137-142 log, :27 reset
+    if (timeup || terminal) {                                            // :137-142 log, :27 reset
       if (ecount < a.max_eps) a.ep_log[(int64_t)ecount * NE + e] = er;
       ecount++;
-      u[0] = u[1] = u[2] = u[3] = (Real)0;                               // cart_pole.h:86
+      if constexpr (VAR) {
+        double u0[4];
+        CartPoleVar::init_state(a.env_flags, a.seed, a.env_offset + (uint64_t)e, a.step0 + (uint64_t)t + 1, u0);
+        u[0] = (Real)u0[0]; u[1] = (Real)u0[1]; u[2] = (Real)u0[2]; u[3] = (Real)u0[3];
+      } else {
+        u[0] = u[1] = u[2] = u[3] = (Real)0;                             // cart_pole.h:86
+      }
       es = 0;
       er = 0.0f;
     }
@@ -118,7 +138,7 @@ __device__ __forceinline__ void rollout_segment(const RolloutArgs& a, const floa
   if (bad) atomicOr(a.status, 1);
 }
 
-template <typename Real, class N, bool TRACE>
+template <typename Real, class N, bool TRACE, bool VAR = false>
 __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_CTAS_PER_SM) k_rollout(const RolloutArgs a) {
   extern __shared__ __align__(16) float sm[];
   float* hs = sm + NetSmem<N>::FLOATS;  // hidden-1 scratch, one column per thread
@@ -141,7 +161,7 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_CTAS_PER_SM) k_rollout(
     const int64_t lo = g * T, hi = lo + T;
     const int t0 = (int)((u0 > lo ? u0 : lo) - lo);
     const int t1 = (int)((u1 < hi ? u1 : hi) - lo);
-    rollout_segment<Real, N, TRACE>(a, sm, hs, g, t0, t1);
+    rollout_segment<Real, N, TRACE, VAR>(a, sm, hs, g, t0, t1);
     if (t1 < (int)T) {  // publish: every lane's stores, then the progress word
       __threadfence();
       __syncwarp();
@@ -150,10 +170,10 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_CTAS_PER_SM) k_rollout(
   }
 }
 
-template <typename Real, bool TRACE>
+template <typename Real, bool TRACE, bool VAR = false>
 static cudaError_t launch_t(const RolloutArgs& a, int sm_count, cudaStream_t st) {
   using N = NetDefault;
-  auto kern = k_rollout<Real, N, TRACE>;
+  auto kern = k_rollout<Real, N, TRACE, VAR>;
   const int smem = mlp_smem_bytes<N>(ROLLOUT_BLOCK);
   static int per_sm = 0;  // per instantiation
   if (per_sm == 0) {
@@ -187,6 +207,10 @@ static cudaError_t launch_t(const RolloutArgs& a, int sm_count, cudaStream_t st)
 cudaError_t launch_rollout(const RolloutArgs& a, int precision, bool trace, int sm_count, cudaStream_t st, int h1,
                            int h2) {
   if (h1 != NetDefault::H1 || h2 != NetDefault::H2) return cudaErrorInvalidValue;
+  if (a.env_flags) {   // opt-in env variants: double physics only (b2_create refuses B2_PREC_F32 with env_flags)
+    if (precision != B2_PREC_F64) return cudaErrorInvalidValue;
+    return trace ? launch_t<double, true, true>(a, sm_count, st) : launch_t<double, false, true>(a, sm_count, st);
+  }
   if (precision == B2_PREC_F64)
     return trace ? launch_t<double, true>(a, sm_count, st) : launch_t<double, false>(a, sm_count, st);
   return trace ? launch_t<float, true>(a, sm_count, st) : launch_t<float, false>(a, sm_count, st);

@@ -77,6 +77,13 @@ def oracle():
     L.orc_gauss.restype = C.c_float
     L.orc_rollout.argtypes = [P(Dims), _f, C.c_long, C.c_int, C.c_int, C.c_double, C.c_uint64,
                               C.c_uint64, C.c_uint64, C.c_void_p, _d, _i32, C.c_void_p] + [C.c_void_p] * 7
+    L.orc_cartpole_advance_v.argtypes = [C.c_int, _d, C.c_int, C.c_double]
+    L.orc_cartpole_reward_v.argtypes = [C.c_int, _d]
+    L.orc_cartpole_reward_v.restype = C.c_double
+    L.orc_cartpole_is_over.argtypes = [C.c_int, _d, C.c_int]
+    L.orc_cartpole_init_state.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_uint64, _d]
+    L.orc_rollout_v.argtypes = [P(Dims), _f, C.c_long, C.c_int, C.c_int, C.c_double, C.c_uint64,
+                                C.c_uint64, C.c_uint64, C.c_void_p, C.c_int, _d, _i32, C.c_void_p] + [C.c_void_p] * 7
     _oracle = L
     return L
 
@@ -116,6 +123,28 @@ def oracle_rollout(params, N, T, n_timestep=100, seed=0x5EED, env0=0, step0=0, f
                   ptr(forced), state, ep_step, ptr(ep_ret), ptr(out["obs"]), ptr(out["action"]),
                   ptr(out["logp"]), ptr(out["mu"]), ptr(out["reward"]), ptr(out["flags"]),
                   ptr(out["state_trace"]))
+    out.update(state=state, ep_step=ep_step, ep_ret=ep_ret)
+    return out
+
+
+ENV_SWINGUP, ENV_RANDOM_INIT, ENV_EARLY_TERM = 1, 2, 4  # oracle.h ORC_ENV_* == b200ppo.h B2_ENV_*
+
+
+def oracle_rollout_v(params, N, T, env_flags, n_timestep=100, seed=0x5EED, env0=0, step0=0, forced=None,
+                     state=None, ep_step=None, dims=DEFAULT_DIMS, sigma=SIGMA):
+    """orc_rollout_v: the rollout with the opt-in env variants (SWINGUP / random init / early termination)."""
+    L = oracle()
+    state = np.zeros((N, 4), np.float64) if state is None else state.copy()
+    ep_step = np.zeros(N, np.int32) if ep_step is None else ep_step.copy()
+    ep_ret = np.zeros(N, np.float64)
+    out = dict(obs=np.zeros((T, N, 6), np.float32), action=np.zeros((T, N), np.float32),
+               logp=np.zeros((T, N), np.float32), mu=np.zeros((T, N), np.float32),
+               reward=np.zeros((T, N), np.float32), flags=np.zeros((T, N), np.uint8),
+               state_trace=np.zeros((T, N, 4), np.float64))
+    L.orc_rollout_v(C.byref(dims), params, N, T, n_timestep, sigma, seed, env0, step0,
+                    ptr(forced), env_flags, state, ep_step, ptr(ep_ret), ptr(out["obs"]), ptr(out["action"]),
+                    ptr(out["logp"]), ptr(out["mu"]), ptr(out["reward"]), ptr(out["flags"]),
+                    ptr(out["state_trace"]))
     out.update(state=state, ep_step=ep_step, ep_ret=ep_ret)
     return out
 

@@ -206,3 +206,67 @@ def test_oracle_wide_nets_match_torch_golden(H1, H2):
     gg = H.gold(f"{tag}_grads.f32")
     for name, sl in H.param_slices(dims):
         assert H.relerr(g[sl], gg[sl]) < 1e-4, name
+
+
+# ---- env variants: SWINGUP branches, early termination, scripted re-initialisation ----
+# KATs minted from the reference's own headers by oracle/ref_env_variants.cpp (make -C oracle golden_variants):
+# [E][T][8] = F, y1..y4, reward, terminate, step.
+@pytest.mark.parametrize("name,fl", [("swingup", H.ENV_SWINGUP), ("early", H.ENV_EARLY_TERM),
+                                     ("early_swingup", H.ENV_EARLY_TERM | H.ENV_SWINGUP)])
+def test_env_variant_kat(name, fl):
+    L = H.oracle()
+    kat = H.gold(f"envvar_{name}.f64").reshape(8, 620, 8)
+    init = H.gold(f"envvar_{name}_init.f64").reshape(8, 64, 4)
+    n_term = 0
+    for e in range(kat.shape[0]):
+        u = init[e, 0].copy()
+        slot, step = 0, 0
+        for t in range(kat.shape[1]):
+            F, ref_u, ref_r, ref_term, ref_step = kat[e, t, 0], kat[e, t, 1:5], kat[e, t, 5], kat[e, t, 6], kat[e, t, 7]
+            step += 1
+            term = L.orc_cartpole_advance_v(fl, u, step, F)
+            assert step == int(ref_step)
+            assert term == int(ref_term), (name, e, t)
+            # same operations in the same order, no contraction: bit-identical to the reference header
+            assert np.array_equal(u, ref_u), (name, e, t, u, ref_u)
+            assert L.orc_cartpole_reward_v(fl, u) == ref_r
+            if term:
+                n_term += 1
+                slot = (slot + 1) % 64
+                u = init[e, slot].copy()
+                step = 0
+    if fl & H.ENV_EARLY_TERM:
+        assert n_term > 10
+    else:
+        assert n_term == 0  # the shipped advance() never terminates (include/cart_pole.h:115,117)
+
+
+def test_env_variant_default_flags_equal_shipped_env():
+    """flags = 0 must be the shipped environment bit for bit."""
+    L = H.oracle()
+    rng = np.random.default_rng(3)
+    for _ in range(20):
+        u = rng.uniform(-0.05, 0.05, 4)
+        F = float(rng.uniform(-10, 10))
+        a, b = u.copy(), u.copy()
+        L.orc_cartpole_advance(a, F)
+        assert L.orc_cartpole_advance_v(0, b, 1, F) == 0
+        assert np.array_equal(a, b)
+        assert L.orc_cartpole_reward(a) == L.orc_cartpole_reward_v(0, b)
+
+
+def test_env_variant_init_state_range_and_streams():
+    L = H.oracle()
+    u = np.zeros(4)
+    L.orc_cartpole_init_state(0, 1, 2, 3, u)
+    assert np.all(u == 0)  # shipped reset: zero state (include/cart_pole.h:86)
+    seen = []
+    for fl, r in ((H.ENV_RANDOM_INIT, 0.05), (H.ENV_RANDOM_INIT | H.ENV_SWINGUP, 0.1)):
+        draws = np.zeros((2000, 4))
+        for i in range(2000):
+            L.orc_cartpole_init_state(fl, 0x5EED, i % 50, i // 50, u)
+            draws[i] = u
+        assert np.all(np.abs(draws) < r) and np.abs(draws).max() > 0.95 * r      # :81-84 ranges
+        assert abs(draws.mean()) < 0.05 * r and len(np.unique(draws)) == draws.size
+        seen.append(draws)
+    assert np.allclose(seen[1], 2 * seen[0])  # same stream, scaled range

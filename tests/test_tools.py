@@ -55,6 +55,15 @@ def test_compat_shims_match_reference_goldens(tools):
 
 
 @pytest.mark.gpu
+def test_compat_cartpole_with_the_reference_compile_time_switches(tools):
+    """include/compat/cart_pole.h built with -DSWINGUP=1 -DB2_CARTPOLE_EARLY_TERM=1 replays the KAT minted from the
+    reference's archived header with SWINGUP 1 (advance() return value, is_over, reward, step, states)."""
+    r = _run([os.path.join(tools, "compat_variants_check"), GOLD])
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    assert r.returncode == 0 and out["ok"] and out["terminations"] > 0, out
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("envs,records", [(1, 2000), (3, 2100)])
 def test_b2_train_driver_semantics(tools, tmp_path, envs, records):
     """Batch sizes of the reference's update trigger and its per-env log format."""
