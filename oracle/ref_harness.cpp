@@ -84,11 +84,15 @@ void adam_of(PPO& p, std::vector<float>& m, std::vector<float>& v, std::vector<i
   }
 }
 
+// observation width: 6 (config:2, the shipped default) or 4 (getobs(4), include/cart_pole.h:120-127 -- the cos/sin
+// pair is dropped and the nets are built with state_dim 4); only the golden_obs4 command changes it
+static int g_obs_dim = 6;
+
 PPO make_ppo(uint64_t seed, int64_t K) {
   torch::manual_seed(seed);
   Quiet q;
   // hyper-parameters: src/main.cpp:196-206
-  return PPO(6, 1, 0.5, 0.0003, std::make_tuple(0.9, 0.999), 0.99, K, 0.2);
+  return PPO(g_obs_dim, 1, 0.5, 0.0003, std::make_tuple(0.9, 0.999), 0.99, K, 0.2);
 }
 
 // One recorded transition (SURVEY 3.6 record alignment).
@@ -112,7 +116,7 @@ MemoryNN rollout(PPO& ppo, int nenv, int episodes, int n_timestep,
     std::vector<double> epr(nenv, 0.0);
     for (int e = 0; e < nenv; e++) {
       env[e].reset();                                   // src/main.cpp:27
-      auto raw = env[e].getobs();                       // :29
+      auto raw = env[e].getobs(g_obs_dim);              // :29
       obs[e] = std::vector<float>(raw.begin(), raw.end());  // :34  (START message, no reward pushed :256)
     }
     for (int j = 0; j < n_timestep; j++) {
@@ -122,7 +126,7 @@ MemoryNN rollout(PPO& ppo, int nenv, int episodes, int n_timestep,
         auto [act, lp] = getAction(obs[e], 1, ppo, mem[e]);
         {
           torch::NoGradGuard ng;
-          auto st = torch::from_blob(obs[e].data(), {1, 6}, torch::kFloat32).clone();
+          auto st = torch::from_blob(obs[e].data(), {1, g_obs_dim}, torch::kFloat32).clone();
           T.mu.push_back(ppo.policy.actor->forward(st).item<float>());
           T.value.push_back(ppo.policy.critic->forward(st).item<float>());
         }
@@ -136,7 +140,7 @@ MemoryNN rollout(PPO& ppo, int nenv, int episodes, int n_timestep,
         T.force.push_back(action[0]);
         std::vector<double> action_double(action.begin(), action.end());  // :69
         bool terminate = env[e].advance(action_double);                    // :71
-        auto raw = env[e].getobs();                                        // :72
+        auto raw = env[e].getobs(g_obs_dim);                               // :72
         double reward = env[e].getReward();                                // :73
         epr[e] += reward;
         obs[e] = std::vector<float>(raw.begin(), raw.end());               // :79
@@ -338,6 +342,21 @@ int cmd_golden(const std::string& dir) {
   return 0;
 }
 
+// ---- the 4-observation configuration (obs_vars = 4): PPO(4, ...) + getobs(4), 1 env x 10 episodes x 100 steps ----
+int cmd_golden_obs4(const std::string& dir) {
+  g_obs_dim = 4;
+  const uint64_t seed = 0;
+  { PPO p = make_ppo(seed, 1); wr(dir, "o4_init_params.f32", params_of(p)); }
+  PPO p = make_ppo(seed, 1);
+  std::vector<Trace> tr; MemoryNN mem;
+  { Quiet q; torch::manual_seed(4321); mem = rollout(p, 1, 10, 100, tr, nullptr); }
+  dump_traces(dir, "o4", tr);
+  wr(dir, "o4_returns.f32", flat(returns_of(p, mem)));
+  dump_update(dir, "o4_k1", seed, 1, mem);
+  dump_update(dir, "o4_k5", seed, 5, mem);
+  return 0;
+}
+
 // ---- timing of the reference's own CPU path (bench.py --impl reference) ----
 int cmd_bench(int nenv, int episodes, int K, int threads, int updates) {
   if (threads > 0) torch::set_num_threads(threads);
@@ -368,8 +387,9 @@ int cmd_bench(int nenv, int episodes, int K, int threads, int updates) {
 
 int main(int argc, char** argv) {
   if (argc >= 3 && std::string(argv[1]) == "golden") return cmd_golden(argv[2]);
+  if (argc >= 3 && std::string(argv[1]) == "golden_obs4") return cmd_golden_obs4(argv[2]);
   if (argc >= 7 && std::string(argv[1]) == "bench")
     return cmd_bench(atoi(argv[2]), atoi(argv[3]), atoi(argv[4]), atoi(argv[5]), atoi(argv[6]));
-  fprintf(stderr, "usage: %s golden <outdir> | bench <nenv> <episodes> <K> <threads> <updates>\n", argv[0]);
+  fprintf(stderr, "usage: %s golden <outdir> | golden_obs4 <outdir> | bench <nenv> <episodes> <K> <threads> <updates>\n", argv[0]);
   return 1;
 }

@@ -219,7 +219,7 @@ class Engine:
     # ---- ppo_nn.h-shaped calls
     def act(self, obs, eps=None, out=None):
         """getAction on n observations (src/ppo_nn.cpp:308-331): returns (action, logp, mu)."""
-        obs = _f32(obs).reshape(-1, 6)
+        obs = _f32(obs).reshape(-1, int(self.cfg.obs_vars))
         n = obs.shape[0]
         eps = _f32(eps)
         a, lp, mu = out if out is not None else (np.empty(n, np.float32), np.empty(n, np.float32),
@@ -228,7 +228,7 @@ class Engine:
         return a, lp, mu
 
     def value(self, obs):
-        obs = _f32(obs).reshape(-1, 6)
+        obs = _f32(obs).reshape(-1, int(self.cfg.obs_vars))
         v = np.empty(obs.shape[0], np.float32)
         _ck(self.L.b2_value(self.h, _vp(obs), obs.shape[0], _vp(v)))
         return v
@@ -326,7 +326,7 @@ class Engine:
     def traj_download(self, T, fields=("obs", "action", "logp", "mu", "reward", "flags"), state_trace=False,
                       out=None):
         n = int(self.cfg.n_envs)
-        shp = {"obs": ((T, n, 6), np.float32), "flags": ((T, n), np.uint8)}
+        shp = {"obs": ((T, n, int(self.cfg.obs_vars)), np.float32), "flags": ((T, n), np.uint8)}
         res = out if out is not None else {}
         for f in fields:
             if f not in res:

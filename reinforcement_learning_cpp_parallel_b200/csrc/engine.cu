@@ -69,6 +69,11 @@ constexpr int B2_MAX_CHUNKS = 32;
 struct b2_engine {
   b2_config cfg;
   int P = 0, pstride = 0, sm_count = 148;
+  // obs_vars = 4 (getobs(4), include/cart_pole.h:120-127): the caller's nets are S = 4 wide; on the device they live
+  // inside the S = 6 layout with the two extra W1 columns, their Adam state and the stored cos/sin planes all exactly
+  // zero -- 0 * x adds nothing to any FMA chain and a zero gradient leaves Adam's m, v and p untouched, so every
+  // kernel computes the S = 4 net bit for bit.  S_ext / P_ext are the shapes at the C ABI.
+  int S_ext = OBS, P_ext = 0;
   cudaStream_t stream = nullptr, copy_stream = nullptr;
   cudaEvent_t chunk_ev[B2_MAX_CHUNKS] = {}, copy_done = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -278,6 +283,67 @@ int run_update(b2_engine* E, b2_update_stats* stats) {
   return B2_OK;
 }
 
+// host [n][S_ext] -> device AoS [n][6] (zero-filled tail when S_ext = 4) and back
+int h2d_obs(b2_engine* E, float* dst, const float* src, int64_t n, cudaStream_t st) {
+  if (E->S_ext == OBS) {
+    CK(cudaMemcpyAsync(dst, src, sizeof(float) * OBS * n, cudaMemcpyHostToDevice, st));
+  } else {
+    CK(cudaMemsetAsync(dst, 0, sizeof(float) * OBS * n, st));
+    CK(cudaMemcpy2DAsync(dst, sizeof(float) * OBS, src, sizeof(float) * E->S_ext, sizeof(float) * E->S_ext, (size_t)n,
+                         cudaMemcpyHostToDevice, st));
+  }
+  return B2_OK;
+}
+int d2h_obs(b2_engine* E, float* dst, const float* src, int64_t n, cudaStream_t st) {
+  if (E->S_ext == OBS) {
+    CK(cudaMemcpyAsync(dst, src, sizeof(float) * OBS * n, cudaMemcpyDeviceToHost, st));
+  } else {
+    CK(cudaMemcpy2DAsync(dst, sizeof(float) * E->S_ext, src, sizeof(float) * OBS, sizeof(float) * E->S_ext, (size_t)n,
+                         cudaMemcpyDeviceToHost, st));
+  }
+  return B2_OK;
+}
+// parameter-shaped vectors (weights, Adam m / v, gradients): caller layout (S_ext) <-> device layout (S = 6)
+void widen_params(const b2_engine* E, const float* ext, float* in) {
+  const NetDims de = NetDims::make(E->S_ext, E->dims.H1, E->dims.H2), &di = E->dims;
+  for (int net = 0; net < 2; net++) {
+    const float* e = ext + (size_t)net * de.SIZE;
+    float* d = in + (size_t)net * di.SIZE;
+    for (int j = 0; j < di.H1; j++)
+      for (int c = 0; c < di.S; c++) d[di.oW1 + j * di.S + c] = c < de.S ? e[de.oW1 + j * de.S + c] : 0.0f;
+    memcpy(d + di.ob1, e + de.ob1, sizeof(float) * (size_t)(di.SIZE - di.ob1));
+  }
+}
+void narrow_params(const b2_engine* E, const float* in, float* ext) {
+  const NetDims de = NetDims::make(E->S_ext, E->dims.H1, E->dims.H2), &di = E->dims;
+  for (int net = 0; net < 2; net++) {
+    float* e = ext + (size_t)net * de.SIZE;
+    const float* d = in + (size_t)net * di.SIZE;
+    for (int j = 0; j < di.H1; j++)
+      for (int c = 0; c < de.S; c++) e[de.oW1 + j * de.S + c] = d[di.oW1 + j * di.S + c];
+    memcpy(e + de.ob1, d + di.ob1, sizeof(float) * (size_t)(di.SIZE - di.ob1));
+  }
+}
+int put_vec(b2_engine* E, float* dev, const float* host) {
+  std::vector<float> tmp;
+  if (E->S_ext != OBS) { tmp.resize((size_t)E->P); widen_params(E, host, tmp.data()); host = tmp.data(); }
+  CK(cudaMemcpyAsync(dev, host, sizeof(float) * E->P, cudaMemcpyHostToDevice, E->stream));
+  CK(cudaStreamSynchronize(E->stream));
+  return B2_OK;
+}
+int get_vec(b2_engine* E, float* host, const float* dev) {
+  if (E->S_ext == OBS) {
+    CK(cudaMemcpyAsync(host, dev, sizeof(float) * E->P, cudaMemcpyDeviceToHost, E->stream));
+    CK(cudaStreamSynchronize(E->stream));
+    return B2_OK;
+  }
+  std::vector<float> tmp((size_t)E->P);
+  CK(cudaMemcpyAsync(tmp.data(), dev, sizeof(float) * E->P, cudaMemcpyDeviceToHost, E->stream));
+  CK(cudaStreamSynchronize(E->stream));
+  narrow_params(E, tmp.data(), host);
+  return B2_OK;
+}
+
 int upload_batch(b2_engine* E, const b2_batch* b) {
   if (!b || !b->obs || !b->reward || !b->flags) return set_error(B2_ERR_INVALID, "batch: null field");
   const int64_t B = b->n_envs * b->horizon;
@@ -286,7 +352,7 @@ int upload_batch(b2_engine* E, const b2_batch* b) {
   if (rc) return rc;
   if ((rc = ensure_stage(E, B * OBS, 0))) return rc;
   Traj& t = E->tr;
-  CK(cudaMemcpyAsync(E->stage, b->obs, sizeof(float) * OBS * B, cudaMemcpyHostToDevice, E->stream));
+  if ((rc = h2d_obs(E, E->stage, b->obs, B, E->stream))) return rc;
   cudaError_t ce = launch_aos_to_soa(E->stage, t.obs, t.cap, B, E->stream);
   if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "aos_to_soa: %s", cudaGetErrorString(ce));
   E->launches += 1;
@@ -316,7 +382,7 @@ int b2_create(const b2_config* cfg, b2_handle* out) {
   if (!cfg || !out) return set_error(B2_ERR_INVALID, "b2_create: null argument");
   *out = nullptr;
   if (cfg->control_vars != 1) return set_error(B2_ERR_INVALID, "control_vars must be 1 (src/ppo_nn.cpp:107)");
-  if (cfg->obs_vars != 6) return set_error(B2_ERR_INVALID, "obs_vars must be 6 (include/cart_pole.h:120-131)");
+  if (cfg->obs_vars != 6 && cfg->obs_vars != 4) return set_error(B2_ERR_INVALID, "obs_vars must be 6 or 4 (include/cart_pole.h:120-131)");
   const bool is_default_net = cfg->hidden1 == NetDefault::H1 && cfg->hidden2 == NetDefault::H2;
   if (!is_default_net && (cfg->hidden1 < 64 || cfg->hidden2 < 64 || cfg->hidden1 > 256 || cfg->hidden2 > 256 || cfg->hidden1 % 64 || cfg->hidden2 % 64))
     return set_error(B2_ERR_INVALID, "hidden widths %dx%d not built: 64x32 (reference) or both in {64,128,192,256}", cfg->hidden1, cfg->hidden2);
@@ -335,6 +401,8 @@ int b2_create(const b2_config* cfg, b2_handle* out) {
   E->cfg = *cfg;
   E->dims = NetDims::make(OBS, cfg->hidden1, cfg->hidden2);
   E->P = E->dims.P;
+  E->S_ext = cfg->obs_vars;
+  E->P_ext = NetDims::make(E->S_ext, cfg->hidden1, cfg->hidden2).P;
   E->pstride = is_default_net ? update_partial_stride() : wide_pstride(cfg->hidden1, cfg->hidden2);
   cudaDeviceProp prop;
   CK(cudaGetDeviceProperties(&prop, cfg->device));
@@ -422,15 +490,15 @@ int b2_get_config(b2_handle E, b2_config* out) {
   return B2_OK;
 }
 
-int64_t b2_n_params(b2_handle E) { return E ? E->P : 0; }
+int64_t b2_n_params(b2_handle E) { return E ? E->P_ext : 0; }
 
 int b2_init_params(b2_handle E, uint64_t seed) {
   NEED(E);
   // torch::nn::Linear::reset_parameters: kaiming_uniform(a=sqrt(5)) on W and U(+-1/sqrt(fan_in)) on b,
   // both = U(-1/sqrt(fan_in), 1/sqrt(fan_in)).  Drawn host-side from Philox (init is not a hot path;
   // parity runs import the reference's weights through b2_set_params instead).
-  const NetDims& N = E->dims;
-  std::vector<float> p((size_t)E->P);
+  const NetDims N = NetDims::make(E->S_ext, E->dims.H1, E->dims.H2);
+  std::vector<float> p((size_t)E->P_ext);
   uint64_t ctr = 0;
   auto fill = [&](int off, int n, int fan_in) {
     const float bound = 1.0f / sqrtf((float)fan_in);
@@ -447,64 +515,59 @@ int b2_init_params(b2_handle E, uint64_t seed) {
     fill(o + N.oW2, N.H2 * N.H1, N.H1); fill(o + N.ob2, N.H2, N.H1);
     fill(o + N.oW3, N.H2, N.H2); fill(o + N.ob3, 1, N.H2);
   }
-  return b2_set_params(E, p.data(), E->P);
+  return b2_set_params(E, p.data(), E->P_ext);
 }
 
 int b2_set_params(b2_handle E, const float* p, int64_t n) {
   NEED(E);
-  if (!p || n != E->P) return set_error(B2_ERR_INVALID, "set_params: expected %d floats, got %lld", E->P, (long long)n);
-  CK(cudaMemcpyAsync(E->params, p, sizeof(float) * n, cudaMemcpyHostToDevice, E->stream));
-  CK(cudaStreamSynchronize(E->stream));
-  return B2_OK;
+  if (!p || n != E->P_ext) return set_error(B2_ERR_INVALID, "set_params: expected %d floats, got %lld", E->P_ext, (long long)n);
+  return put_vec(E, E->params, p);
 }
 int b2_get_params(b2_handle E, float* p, int64_t n) {
   NEED(E);
-  if (!p || n != E->P) return set_error(B2_ERR_INVALID, "get_params: expected %d floats", E->P);
-  CK(cudaMemcpyAsync(p, E->params, sizeof(float) * n, cudaMemcpyDeviceToHost, E->stream));
-  CK(cudaStreamSynchronize(E->stream));
-  return B2_OK;
+  if (!p || n != E->P_ext) return set_error(B2_ERR_INVALID, "get_params: expected %d floats", E->P_ext);
+  return get_vec(E, p, E->params);
 }
 int b2_set_adam_state(b2_handle E, const float* m, const float* v, int64_t n, int64_t step) {
   NEED(E);
-  if (!m || !v || n != E->P || step < 0) return set_error(B2_ERR_INVALID, "set_adam_state: bad arguments");
-  CK(cudaMemcpyAsync(E->adam_m, m, sizeof(float) * n, cudaMemcpyHostToDevice, E->stream));
-  CK(cudaMemcpyAsync(E->adam_v, v, sizeof(float) * n, cudaMemcpyHostToDevice, E->stream));
+  if (!m || !v || n != E->P_ext || step < 0) return set_error(B2_ERR_INVALID, "set_adam_state: bad arguments");
+  int rc = put_vec(E, E->adam_m, m);
+  if (rc || (rc = put_vec(E, E->adam_v, v))) return rc;
   CK(cudaMemcpyAsync(E->adam_step, &step, sizeof(int64_t), cudaMemcpyHostToDevice, E->stream));
   CK(cudaStreamSynchronize(E->stream));
   return B2_OK;
 }
 int b2_get_adam_state(b2_handle E, float* m, float* v, int64_t n, int64_t* step) {
   NEED(E);
-  if (n != E->P) return set_error(B2_ERR_INVALID, "get_adam_state: expected %d floats", E->P);
-  if (m) CK(cudaMemcpyAsync(m, E->adam_m, sizeof(float) * n, cudaMemcpyDeviceToHost, E->stream));
-  if (v) CK(cudaMemcpyAsync(v, E->adam_v, sizeof(float) * n, cudaMemcpyDeviceToHost, E->stream));
+  if (n != E->P_ext) return set_error(B2_ERR_INVALID, "get_adam_state: expected %d floats", E->P_ext);
+  int rc;
+  if (m && (rc = get_vec(E, m, E->adam_m))) return rc;
+  if (v && (rc = get_vec(E, v, E->adam_v))) return rc;
   if (step) CK(cudaMemcpyAsync(step, E->adam_step, sizeof(int64_t), cudaMemcpyDeviceToHost, E->stream));
   CK(cudaStreamSynchronize(E->stream));
   return B2_OK;
 }
 int b2_get_grads(b2_handle E, float* g, int64_t n) {
   NEED(E);
-  if (!g || n != E->P) return set_error(B2_ERR_INVALID, "get_grads: expected %d floats", E->P);
-  CK(cudaMemcpyAsync(g, E->grads, sizeof(float) * n, cudaMemcpyDeviceToHost, E->stream));
-  CK(cudaStreamSynchronize(E->stream));
-  return B2_OK;
+  if (!g || n != E->P_ext) return set_error(B2_ERR_INVALID, "get_grads: expected %d floats", E->P_ext);
+  return get_vec(E, g, E->grads);
 }
 
 // checkpoint: "B2CK" | version | P | step | params | m | v   (the reference has none)
 int b2_save_checkpoint(b2_handle E, const char* path) {
   NEED(E);
   if (!path) return set_error(B2_ERR_INVALID, "null path");
-  std::vector<float> p(E->P), m(E->P), v(E->P);
+  std::vector<float> p(E->P_ext), m(E->P_ext), v(E->P_ext);
   int64_t step = 0;
-  int rc = b2_get_params(E, p.data(), E->P);
+  int rc = b2_get_params(E, p.data(), E->P_ext);
   if (rc) return rc;
-  if ((rc = b2_get_adam_state(E, m.data(), v.data(), E->P, &step))) return rc;
+  if ((rc = b2_get_adam_state(E, m.data(), v.data(), E->P_ext, &step))) return rc;
   FILE* f = fopen(path, "wb");
   if (!f) return set_error(B2_ERR_IO, "cannot open %s for writing", path);
-  int32_t hdr[2] = {1, E->P};
+  int32_t hdr[2] = {1, E->P_ext};
   bool ok = fwrite("B2CK", 1, 4, f) == 4 && fwrite(hdr, sizeof hdr, 1, f) == 1 && fwrite(&step, sizeof step, 1, f) == 1 &&
-            fwrite(p.data(), sizeof(float), E->P, f) == (size_t)E->P && fwrite(m.data(), sizeof(float), E->P, f) == (size_t)E->P &&
-            fwrite(v.data(), sizeof(float), E->P, f) == (size_t)E->P;
+            fwrite(p.data(), sizeof(float), E->P_ext, f) == (size_t)E->P_ext && fwrite(m.data(), sizeof(float), E->P_ext, f) == (size_t)E->P_ext &&
+            fwrite(v.data(), sizeof(float), E->P_ext, f) == (size_t)E->P_ext;
   ok = (fclose(f) == 0) && ok;
   return ok ? B2_OK : set_error(B2_ERR_IO, "short write to %s", path);
 }
@@ -516,16 +579,16 @@ int b2_load_checkpoint(b2_handle E, const char* path) {
   char magic[4];
   int32_t hdr[2];
   int64_t step = 0;
-  std::vector<float> p(E->P), m(E->P), v(E->P);
+  std::vector<float> p(E->P_ext), m(E->P_ext), v(E->P_ext);
   bool ok = fread(magic, 1, 4, f) == 4 && memcmp(magic, "B2CK", 4) == 0 && fread(hdr, sizeof hdr, 1, f) == 1 &&
-            hdr[0] == 1 && hdr[1] == E->P && fread(&step, sizeof step, 1, f) == 1 &&
-            fread(p.data(), sizeof(float), E->P, f) == (size_t)E->P && fread(m.data(), sizeof(float), E->P, f) == (size_t)E->P &&
-            fread(v.data(), sizeof(float), E->P, f) == (size_t)E->P;
+            hdr[0] == 1 && hdr[1] == E->P_ext && fread(&step, sizeof step, 1, f) == 1 &&
+            fread(p.data(), sizeof(float), E->P_ext, f) == (size_t)E->P_ext && fread(m.data(), sizeof(float), E->P_ext, f) == (size_t)E->P_ext &&
+            fread(v.data(), sizeof(float), E->P_ext, f) == (size_t)E->P_ext;
   fclose(f);
   if (!ok) return set_error(B2_ERR_IO, "%s is not a matching b200ppo checkpoint", path);
-  int rc = b2_set_params(E, p.data(), E->P);
+  int rc = b2_set_params(E, p.data(), E->P_ext);
   if (rc) return rc;
-  return b2_set_adam_state(E, m.data(), v.data(), E->P, step);
+  return b2_set_adam_state(E, m.data(), v.data(), E->P_ext, step);
 }
 
 int b2_act(b2_handle E, const float* obs, int64_t n, const float* eps, float* action, float* logp, float* mu) {
@@ -541,7 +604,7 @@ int b2_act(b2_handle E, const float* obs, int64_t n, const float* eps, float* ac
   float* d_act = d_eps + n;
   float* d_lp = d_act + n;
   float* d_mu = d_lp + n;
-  CK(cudaMemcpyAsync(d_obs, obs, sizeof(float) * OBS * n, cudaMemcpyHostToDevice, E->stream));
+  if ((rc = h2d_obs(E, d_obs, obs, n, E->stream))) return rc;
   if (eps) CK(cudaMemcpyAsync(d_eps, eps, sizeof(float) * n, cudaMemcpyHostToDevice, E->stream));
   cudaError_t ce;
   if (E->wide) {
@@ -569,7 +632,7 @@ int b2_value(b2_handle E, const float* obs, int64_t n, float* value) {
   if (rc) return rc;
   float* d_obs = E->stage;
   float* d_v = d_obs + n * OBS;
-  CK(cudaMemcpyAsync(d_obs, obs, sizeof(float) * OBS * n, cudaMemcpyHostToDevice, E->stream));
+  if ((rc = h2d_obs(E, d_obs, obs, n, E->stream))) return rc;
   cudaError_t ce = E->wide ? launch_wide_forward(E->dims, E->params + E->dims.SIZE, d_obs, 1, OBS, nullptr, n, 0, d_v, E->stream)
                            : launch_value(E->params, d_obs, n, d_v, E->stream);
   if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "value: %s", cudaGetErrorString(ce));
@@ -722,6 +785,10 @@ static int rollout_window(b2_engine* E, int T, int t_begin, int t_end, bool forc
   cudaError_t ce = launch_rollout(a, E->cfg.precision, E->trace, E->sm_count, E->stream, E->cfg.hidden1, E->cfg.hidden2);
   if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "rollout: %s", cudaGetErrorString(ce));
   E->launches += 1;
+  if (E->S_ext != OBS) {   // getobs(4): the stored cos/sin planes must be exact zeros (see S_ext above)
+    const int64_t k0 = (int64_t)t_begin * E->cfg.n_envs, n = (int64_t)(t_end - t_begin) * E->cfg.n_envs;
+    for (int c = E->S_ext; c < OBS; c++) CK(cudaMemsetAsync(E->tr.obs + (size_t)c * E->tr.cap + k0, 0, sizeof(float) * n, E->stream));
+  }
   return B2_OK;
 }
 
@@ -790,7 +857,7 @@ int b2_rollout_host(b2_handle E, int T, int n_chunks, const b2_batch_out* out) {
       cudaError_t ce = launch_soa_to_aos(t.obs + k0, E->stage + k0 * OBS, t.cap, n, E->copy_stream);
       if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "soa_to_aos: %s", cudaGetErrorString(ce));
       E->launches += 1;
-      CK(cudaMemcpyAsync(out->obs + k0 * OBS, E->stage + k0 * OBS, sizeof(float) * OBS * n, cudaMemcpyDeviceToHost, E->copy_stream));
+      if ((rc = d2h_obs(E, out->obs + k0 * E->S_ext, E->stage + k0 * OBS, n, E->copy_stream))) return rc;
     }
     if (out->action) CK(cudaMemcpyAsync(out->action + k0, t.action + k0, sizeof(float) * n, cudaMemcpyDeviceToHost, E->copy_stream));
     if (out->logp) CK(cudaMemcpyAsync(out->logp + k0, t.logp + k0, sizeof(float) * n, cudaMemcpyDeviceToHost, E->copy_stream));
@@ -834,7 +901,7 @@ int b2_traj_download(b2_handle E, b2_batch_out* out, double* state_trace) {
     cudaError_t ce = launch_soa_to_aos(t.obs, E->stage, t.cap, B, E->stream);
     if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "soa_to_aos: %s", cudaGetErrorString(ce));
     E->launches += 1;
-    CK(cudaMemcpyAsync(out->obs, E->stage, sizeof(float) * OBS * B, cudaMemcpyDeviceToHost, E->stream));
+    if ((rc = d2h_obs(E, out->obs, E->stage, B, E->stream))) return rc;
   }
   if (out->action) CK(cudaMemcpyAsync(out->action, t.action, sizeof(float) * B, cudaMemcpyDeviceToHost, E->stream));
   if (out->logp) CK(cudaMemcpyAsync(out->logp, t.logp, sizeof(float) * B, cudaMemcpyDeviceToHost, E->stream));

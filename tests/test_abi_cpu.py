@@ -84,7 +84,7 @@ def test_no_cpu_fallback(capi):
 
 
 def test_argument_validation_happens_before_device_use(capi):
-    for kw in (dict(control_vars=2), dict(obs_vars=4), dict(hidden1=100, hidden2=256), dict(hidden1=512, hidden2=64), dict(n_envs=0),
+    for kw in (dict(control_vars=2), dict(obs_vars=5), dict(hidden1=100, hidden2=256), dict(hidden1=512, hidden2=64), dict(n_envs=0),
                dict(precision=7), dict(k_epochs=0), dict(action_std=0.0), dict(env_flags=8),
                dict(env_flags=capi.ENV_SWINGUP, precision=capi.PREC_F32)):
         with pytest.raises(capi.B2Error) as ei:

@@ -181,3 +181,63 @@ def test_variants_refuse_f32_physics(pkg):
     with pytest.raises(capi.B2Error) as ei:
         make_engine(pkg, n_envs=32, horizon=4, env_flags=SW, precision=pkg.PREC_F32)
     assert ei.value.code == -1
+
+
+# ---- obs_vars = 4: PPO(state_dim = 4) + getobs(4) (include/cart_pole.h:120-127).  Goldens o4_* come from the unmodified
+# reference built with state_dim 4 (oracle/ref_harness.cpp golden_obs4). ----
+def test_obs4_act_value_update_match_reference(pkg):
+    p0 = gold("o4_init_params.f32")
+    obs = gold("o4_obs.f32").reshape(-1, 4)
+    B = obs.shape[0]
+    act, lp_old, rew, fl = gold("o4_action.f32"), gold("o4_logp.f32"), gold("o4_reward.f32"), H.flags_of("o4")
+    for K in (1, 5):
+        E = make_engine(pkg, obs_vars=4, n_envs=1, horizon=B, k_epochs=K)
+        assert E.P == 4866 == p0.size
+        E.set_params(p0)
+        np.testing.assert_array_equal(E.get_params(), p0)
+        eps = ((act.astype(np.float64) - gold("o4_mu.f32")) / H.SIGMA).astype(np.float32)
+        a, lp, mu = E.act(obs, eps=eps)
+        np.testing.assert_allclose(mu, gold("o4_mu.f32"), rtol=0, atol=1e-6)
+        np.testing.assert_allclose(E.value(obs), gold("o4_value.f32"), rtol=1e-6, atol=1e-6)
+        R = E.returns(obs, rew, fl, n_envs=1, horizon=B)
+        assert relerr(R, gold("o4_returns.f32")) < 1e-5
+        st = E.update(obs, act, lp_old, rew, fl, n_envs=1, horizon=B)
+        assert st.adam_step == K
+        assert relerr(E.get_grads(), gold(f"o4_k{K}_grads.f32")) < 1e-4
+        assert relerr(E.get_params(), gold(f"o4_k{K}_params.f32")) < 1e-5
+        m, v, step = E.get_adam_state()
+        assert relerr(m, gold(f"o4_k{K}_adam_m.f32")) < 1e-4 and relerr(v, gold(f"o4_k{K}_adam_v.f32")) < 1e-4
+        l = E.last_update_losses(K)
+        np.testing.assert_allclose(l[3], gold(f"o4_k{K}_loss.f64"), rtol=1e-4)
+        E.close()
+
+
+def test_obs4_rollout_replays_reference_episode(pkg):
+    """fused rollout with 4-wide observations: replay the reference's recorded actions from the zero state; the stored
+    observations are getobs(4) of the reference, mu/logp those of its state_dim-4 actor."""
+    p0 = gold("o4_init_params.f32")
+    T = 100
+    obs = gold("o4_obs.f32").reshape(-1, 4)[:T]
+    E = make_engine(pkg, obs_vars=4, n_envs=1, horizon=T, n_timestep=100)
+    E.set_params(p0)
+    E.set_state_trace(True)
+    E.rollout(T, forced_action=gold("o4_action.f32")[:T])
+    out = E.traj_download(T, state_trace=True)
+    assert out["obs"].shape == (T, 1, 4)
+    st = gold("o4_state.f64").reshape(-1, 4)[:T]
+    assert relerr(out["state_trace"][:, 0], st) < 1e-9
+    np.testing.assert_allclose(out["obs"][:, 0], obs, rtol=1e-6, atol=1e-7)
+    np.testing.assert_allclose(out["mu"][:, 0], gold("o4_mu.f32")[:T], rtol=0, atol=2e-6)
+    np.testing.assert_allclose(out["logp"][:, 0], gold("o4_logp.f32")[:T], rtol=0, atol=2e-5)
+    np.testing.assert_array_equal(out["reward"][:, 0], gold("o4_reward.f32")[:T])
+    np.testing.assert_array_equal(out["flags"][:, 0], H.flags_of("o4")[:T])
+    # resident update on that trajectory == host update on the same records (the padded columns stay exactly zero)
+    E.update_resident()
+    g_res = E.get_grads()
+    E2 = make_engine(pkg, obs_vars=4, n_envs=1, horizon=T)
+    E2.set_params(p0)
+    E2.update(out["obs"].reshape(T, 4), out["action"].ravel(), out["logp"].ravel(), out["reward"].ravel(),
+              out["flags"].ravel(), n_envs=1, horizon=T)
+    assert relerr(g_res, E2.get_grads()) < 1e-6
+    E.close()
+    E2.close()

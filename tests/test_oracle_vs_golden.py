@@ -270,3 +270,39 @@ def test_env_variant_init_state_range_and_streams():
         assert abs(draws.mean()) < 0.05 * r and len(np.unique(draws)) == draws.size
         seen.append(draws)
     assert np.allclose(seen[1], 2 * seen[0])  # same stream, scaled range
+
+
+# ---- obs_vars = 4 (getobs(4), include/cart_pole.h:120-127; PPO(state_dim = 4)): goldens from the unmodified reference
+# built with state_dim 4 (oracle/ref_harness.cpp golden_obs4) ----
+D4 = H.Dims(4, 64, 32, 1)
+
+
+def test_obs4_forward_returns_and_update_match_reference():
+    L = oracle()
+    p0 = gold("o4_init_params.f32")
+    assert p0.size == L.orc_n_params(C.byref(D4)) == 4866
+    obs = gold("o4_obs.f32").reshape(-1, 4)
+    B = obs.shape[0]
+    act, lp_old, rew = gold("o4_action.f32"), gold("o4_logp.f32"), gold("o4_reward.f32")
+    fl = flags_of("o4")
+    # the 4-vector is getobs' first four entries: x, xdot, thetadot, theta of the PREVIOUS post-step state
+    st = gold("o4_state.f64").reshape(-1, 4)
+    np.testing.assert_array_equal(obs[1:100], st[0:99][:, [0, 1, 3, 2]].astype(np.float32))
+    mu, a2, lp = np.zeros(B, np.float32), np.zeros(B, np.float32), np.zeros(B, np.float32)
+    eps = ((act.astype(np.float64) - gold("o4_mu.f32")) / SIGMA).astype(np.float32)
+    L.orc_act(C.byref(D4), p0, obs, B, eps.ctypes.data_as(C.c_void_p), SIGMA, mu, a2, lp)
+    np.testing.assert_allclose(mu, gold("o4_mu.f32"), rtol=0, atol=1e-6)
+    v = np.zeros(B, np.float32)
+    L.orc_value(C.byref(D4), p0, obs, B, v)
+    np.testing.assert_allclose(v, gold("o4_value.f32"), rtol=1e-6, atol=1e-6)
+    lp2 = np.array([L.orc_logprob(float(a), float(m), SIGMA) for a, m in zip(act, gold("o4_mu.f32"))], np.float32)
+    np.testing.assert_allclose(lp2, lp_old, rtol=0, atol=2e-6)
+    z = np.zeros_like(p0)
+    for K in (1, 5):
+        p, m, vv, step, losses, g, R = H.oracle_update(p0, z, z, 0, obs, act, lp_old, rew, fl, K, dims=D4)
+        assert relerr(R, gold("o4_returns.f32")) < 1e-6
+        assert step == K == int(gold(f"o4_k{K}_adam_step.i64")[0])
+        assert relerr(g, gold(f"o4_k{K}_grads.f32")) < 1e-4
+        assert relerr(p, gold(f"o4_k{K}_params.f32")) < 1e-6
+        assert relerr(m, gold(f"o4_k{K}_adam_m.f32")) < 1e-4 and relerr(vv, gold(f"o4_k{K}_adam_v.f32")) < 1e-4
+        np.testing.assert_allclose([l.loss for l in losses], gold(f"o4_k{K}_loss.f64"), rtol=1e-5)
