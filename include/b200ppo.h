@@ -181,6 +181,10 @@ int64_t b2_total_env_steps(b2_handle h);
 int b2_comm_unique_id(char id[B2_COMM_ID_BYTES]);              /* rank 0 makes it, the caller broadcasts it */
 int b2_comm_init(b2_handle h, int rank, int world, const char id[B2_COMM_ID_BYTES]);
 int b2_comm_world(b2_handle h);
+/* how gradients travel between ranks: 0 single GPU; 1 ncclAllReduce + Adam launch (default); 2 NVLink peer memory --
+ * each rank publishes its gradient in a buffer its peers have mapped (cudaIpc) and the Adam kernel itself pulls and sums
+ * all copies in rank order.  2 is opt-in (B2_COMM_P2P=1 in the environment) and needs every rank to map every peer. */
+int b2_comm_mode(b2_handle h);
 
 /* ---- measurement helpers (CUDA events on the handle's stream) */
 int b2_sync(b2_handle h);

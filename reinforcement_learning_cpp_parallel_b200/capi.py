@@ -94,6 +94,7 @@ SYMBOLS = {
     "b2_comm_unique_id": (C.c_int, [C.c_void_p]),
     "b2_comm_init": (C.c_int, [_H, C.c_int, C.c_int, C.c_void_p]),
     "b2_comm_world": (C.c_int, [_H]),
+    "b2_comm_mode": (C.c_int, [_H]),
     "b2_sync": (C.c_int, [_H]),
     "b2_timer_start": (C.c_int, [_H]),
     "b2_timer_stop_ms": (C.c_int, [_H, _P(C.c_float)]),
@@ -360,6 +361,10 @@ class Engine:
     def comm_init(self, rank, world, uid):
         buf = (C.c_char * COMM_ID_BYTES).from_buffer_copy(uid)
         _ck(self.L.b2_comm_init(self.h, rank, world, buf))
+
+    def comm_mode(self):
+        """0 single GPU, 1 ncclAllReduce, 2 NVLink peer-memory exchange fused into the Adam kernel."""
+        return int(self.L.b2_comm_mode(self.h))
 
     # ---- measurement
     def sync(self):

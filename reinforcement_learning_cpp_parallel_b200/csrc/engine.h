@@ -61,7 +61,30 @@ struct RolloutArgs {
   int* progress;        // [ceil(n_envs/32)] steps of this rollout already published per env group (hand-off word)
 };
 
+// Gradient exchange over NVLink peer memory (multi-GPU, one process per GPU; opt-in alternative to ncclAllReduce, see
+// DESIGN.md s5 for the measurements that decided the default).  Every rank owns, in memory its peers have mapped
+// (cudaIpc),   buf[2][pstride] floats | flag | counter.
+// Step e (parity e & 1): the REDUCE kernel writes this rank's gradient into buf[e & 1] (plain local stores; it is simply
+// given that buffer as its output) and its last block (device counter) publishes flag = e with ONE system-scope fence.
+// The ADAM kernel waits until every rank's flag >= e (acquire loads over NVLink), PULLS the world copies of each of its
+// elements straight out of the peers' memory and adds them in RANK ORDER -- every rank forms the identical sum, so the
+// weights stay bit-identical without a broadcast -- and applies Adam.  Two parities are enough: a rank writes
+// buf[(e+1) & 1] only after its Adam(e) saw every peer's flag e, i.e. after every peer's Adam(e-1), the last reader of
+// that parity, has ended.
+constexpr int B2_MAX_PEERS = 8;
+struct PeerXchg {
+  int world = 0, rank = 0;      // world <= 1: single GPU, nothing below is used
+  int epoch = 0;                // this optimizer step (1-based, same on every rank)
+  int64_t par_off = 0;          // (epoch & 1) * pstride
+  const float* buf[B2_MAX_PEERS] = {};   // rank r's buffer (own entry: local pointer)
+  int* flag[B2_MAX_PEERS] = {};          // rank r's flag word
+  int* counter = nullptr;       // local: blocks of the reduce kernel that have finished
+  float* out = nullptr;         // summed gradient (pstride floats, local): what b2_get_grads returns
+  int* status = nullptr;        // bit1: a peer never arrived (bounded wait expired)
+};
+
 struct UpdateArgs {
+  PeerXchg px;
   float* params;
   float* adam_m;
   float* adam_v;
@@ -77,6 +100,50 @@ struct UpdateArgs {
   int grid;
   HyperDev hp;
 };
+
+#ifdef __CUDACC__
+// reduce side, called by EVERY thread of EVERY block after its last gradient store (no early returns before it)
+__device__ __forceinline__ void px_publish(const PeerXchg& x) {
+  __threadfence();                 // this thread's stores are visible device-wide before the block counts itself done
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const int done = atomicAdd(x.counter, 1);
+    if (done == (int)gridDim.x - 1) {      // last block: every block's stores precede (counter + fences); one system fence
+      *x.counter = 0;
+      __threadfence_system();
+      asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(x.flag[x.rank]), "r"(x.epoch) : "memory");
+    }
+  }
+}
+// Adam side: every block waits until every rank (itself included) has published step e
+__device__ __forceinline__ void px_wait(const PeerXchg& x) {
+  if (threadIdx.x < x.world) {
+    const int* f = x.flag[threadIdx.x];
+    long long spins = 0;
+    while (true) {
+      int v;
+      asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+      if (v - x.epoch >= 0) break;
+      __nanosleep(64);
+      if (++spins > (1ll << 23)) { atomicOr(x.status, 2); break; }   // ~2 s: surface a lost peer instead of hanging the GPU
+    }
+  }
+  __syncthreads();
+}
+// element i of the all-rank sum, pulled from every rank's buffer, added in rank order (loads bypass L1)
+__device__ __forceinline__ float px_sum(const PeerXchg& x, int i) {
+  float v[B2_MAX_PEERS];
+#pragma unroll
+  for (int r = 0; r < B2_MAX_PEERS; r++)
+    if (r < x.world) asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v[r]) : "l"(x.buf[r] + x.par_off + i));
+  float s = v[0];
+#pragma unroll
+  for (int r = 1; r < B2_MAX_PEERS; r++)
+    if (r < x.world) s = __fadd_rn(s, v[r]);
+  x.out[i] = s;
+  return s;
+}
+#endif
 
 // ---- launchers (each returns cudaGetLastError()) ----
 cudaError_t launch_rollout(const RolloutArgs& a, int precision, bool trace, int sm_count, cudaStream_t st, int hidden1,

@@ -329,25 +329,19 @@ __device__ __forceinline__ void wide_loss_log(const UpdateArgs& a, int q, float 
 // Blocks [0, w2_blocks): one thread per W2 element, split-K partials summed 8 loads at a time.
 // Remaining blocks: one WARP per "small" parameter (W1, b1, b2, W3, b3 and the 3 loss scalars), lanes stride over the
 // per-block partial rows and a shuffle tree finishes the sum.
-__device__ __forceinline__ void wide_finish(const ReduceArgs& r, const AdamCoef& c, int p, int slot, float s) {
-  if (!r.first_chunk) s += r.u.grads[slot];
-  r.u.grads[slot] = s;
-  if (r.last_chunk && r.apply_adam) {
-    if (p < r.d.P) wide_store_planes(r.d, r.w2p, r.bias2, p, wide_adam_apply(r.u, c, p, s));
-    else wide_loss_log(r.u, p - r.d.P, s);
-  }
-}
+// One finished element of the reduce: p = parameter index (or d.P + l for the loss scalars), slot = its place in grads.
+struct ReduceElem { bool valid; int p, slot; float s; };
 
-__global__ void __launch_bounds__(128) k_wide_reduce(const ReduceArgs r, int w2_blocks) {
+// vb: the virtual block (128 elements of W2, or 4 small parameters) this call works on; sum = false: indices only
+__device__ __forceinline__ ReduceElem wide_reduce_body(const ReduceArgs& r, int w2_blocks, int vb, bool sum) {
   const NetDims d = r.d;
+  const ReduceElem none{false, 0, 0, 0.f};
   const int w2n = d.H2 * d.H1;
-  pdl_launch_dependents();
-  pdl_wait();
-  const AdamCoef coef = *r.coef;
-  if ((int)blockIdx.x < w2_blocks) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= 2 * w2n) return;
+  if (vb < w2_blocks) {
+    const int i = vb * blockDim.x + threadIdx.x;
+    if (i >= 2 * w2n) return none;
     const int g = i / w2n, e = i % w2n;
+    if (!sum) return ReduceElem{true, g * d.SIZE + d.oW2 + e, g * d.SIZE + d.oW2 + e, 0.f};
     const float* base = r.part_dw2 + (int64_t)g * r.splits * w2n + e;
     float s = 0.f;
     int sp = 0;
@@ -375,13 +369,12 @@ __global__ void __launch_bounds__(128) k_wide_reduce(const ReduceArgs r, int w2_
     }
     for (; sp < r.splits; sp++) s += base[(int64_t)sp * w2n];
     const int p = g * d.SIZE + d.oW2 + e;
-    wide_finish(r, coef, p, p, s);
-    return;
+    return ReduceElem{true, p, p, s};
   }
   const int lane = threadIdx.x & 31;
   const int per_net = d.H1 * (S + 1) + 2 * d.H2 + 1;     // W1, b1, b2, W3, b3
-  const int q = ((int)blockIdx.x - w2_blocks) * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (q >= 2 * per_net + 3) return;
+  const int q = (vb - w2_blocks) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (q >= 2 * per_net + 3) return none;
   const float* src;
   int64_t stride;
   int rows, p, slot;
@@ -406,6 +399,7 @@ __global__ void __launch_bounds__(128) k_wide_reduce(const ReduceArgs r, int w2_
     stride = (int64_t)2 * r.head_row; rows = r.head_blocks;
     p = d.P + l; slot = r.pstride - 4 + l;
   }
+  if (!sum) return ReduceElem{lane == 0, p, slot, 0.f};
   float s = 0.f;
   for (int b0 = lane; b0 < rows; b0 += 32 * 8) {     // 8 independent loads per lane per round
     float t[8];
@@ -416,15 +410,37 @@ __global__ void __launch_bounds__(128) k_wide_reduce(const ReduceArgs r, int w2_
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-  if (lane == 0) wide_finish(r, coef, p, slot, s);
+  return ReduceElem{lane == 0, p, slot, s};
+}
+
+__global__ void __launch_bounds__(128) k_wide_reduce(const ReduceArgs r, int w2_blocks) {
+  pdl_launch_dependents();
+  pdl_wait();
+  ReduceElem e = wide_reduce_body(r, w2_blocks, (int)blockIdx.x, true);   // fixed-order sum of the local partials of one element
+  if (e.valid) {
+    if (!r.first_chunk) e.s += r.u.grads[e.slot];             // chunked gradient accumulation
+    r.u.grads[e.slot] = e.s;
+    if (r.last_chunk && r.apply_adam) {
+      if (e.p < r.d.P) wide_store_planes(r.d, r.w2p, r.bias2, e.p, wide_adam_apply(r.u, *r.coef, e.p, e.s));
+      else wide_loss_log(r.u, e.p - r.d.P, e.s);
+    }
+  }
+  if (r.last_chunk && r.u.px.world > 1) px_publish(r.u.px);   // r.u.grads is this step's exchange buffer (engine.h PeerXchg)
 }
 
 __global__ void __launch_bounds__(128) k_wide_adam(const UpdateArgs a, const NetDims d, int pstride, __nv_bfloat16* w2p,
                                                    float* bias2, const AdamCoef* coef_p) {
+  pdl_launch_dependents();
+  pdl_wait();                          // (a no-op unless launched with the programmatic-serialization attribute)
   const AdamCoef coef = *coef_p;
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
-  if (p < d.P) wide_store_planes(d, w2p, bias2, p, wide_adam_apply(a, coef, p, a.grads[p]));
-  else if (p < d.P + 3) wide_loss_log(a, p - d.P, a.grads[pstride - 4 + (p - d.P)]);
+  const bool peers = a.px.world > 1;   // peer-memory exchange fused in; otherwise a.grads already holds the all-reduced sum
+  if (peers) px_wait(a.px);
+  if (p < d.P) wide_store_planes(d, w2p, bias2, p, wide_adam_apply(a, coef, p, peers ? px_sum(a.px, p) : a.grads[p]));
+  else if (p < d.P + 3) {
+    const int i = pstride - 4 + (p - d.P);
+    wide_loss_log(a, p - d.P, peers ? px_sum(a.px, i) : a.grads[i]);
+  }
 }
 
 }  // namespace
@@ -755,7 +771,11 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
 }
 
 cudaError_t launch_wide_adam(WideNet* w, const UpdateArgs& a, cudaStream_t st) {
-  k_wide_adam<<<(w->d.P + 3 + 127) / 128, 128, 0, st>>>(a, w->d, wide_pstride(w->d.H1, w->d.H2), w->w2p, w->bias2, w->coef);
+  const int grid = (w->d.P + 3 + 127) / 128;
+  if (a.px.world > 1)   // follows k_wide_reduce directly: launch latency hidden behind it
+    return launch_pdl(k_wide_adam, dim3(grid), dim3(128), 0, st, a, w->d, wide_pstride(w->d.H1, w->d.H2), w->w2p, w->bias2,
+                      (const AdamCoef*)w->coef);
+  k_wide_adam<<<grid, 128, 0, st>>>(a, w->d, wide_pstride(w->d.H1, w->d.H2), w->w2p, w->bias2, w->coef);
   return cudaGetLastError();
 }
 

@@ -37,7 +37,7 @@ def _rank(rank, world, port, q):
         E.rollout(T)
         traj = E.traj_download(T, fields=("obs", "action", "reward", "flags"))
         st = E.update_resident()
-        q.put((rank, off, n_local, traj, E.get_grads(), E.get_params(), st.loss, st.adam_step))
+        q.put((rank, off, n_local, traj, E.get_grads(), E.get_params(), st.loss, st.adam_step, E.comm_mode()))
         E.close()
     finally:
         dist.destroy_process_group()
@@ -68,6 +68,7 @@ def test_two_gpu_update_matches_one_gpu():
     g1, p1 = E.get_grads(), E.get_params()
     E.close()
     # identical trajectories for any sharding (Philox keyed by the global env id)
+    assert res[0][8] == res[1][8] == (2 if os.environ.get("B2_COMM_P2P") == "1" else 1)   # NCCL unless the peer-memory exchange is opted in
     for rank, off, n, traj, *_ in res:
         for k in traj:
             np.testing.assert_array_equal(traj[k], full[k][:, off:off + n], err_msg=k)
@@ -78,6 +79,33 @@ def test_two_gpu_update_matches_one_gpu():
     assert rel(res[0][4], g1) < 1e-5, rel(res[0][4], g1)        # different reduction tree only
     assert rel(res[0][5], p1) < 1e-6, rel(res[0][5], p1)
     assert abs(res[0][6] - st.loss) < 1e-5 * abs(st.loss) and res[0][7] == st.adam_step == K
+
+
+def test_peer_memory_exchange_equals_nccl_allreduce(monkeypatch):
+    """The gradient exchange fused into the Adam kernel (NVLink peer memory, rank-order sum) and the ncclAllReduce
+    fallback give the same weights bit for bit at world = 2 (a + b is the same sum in either order)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    out = {}
+    for mode in ("1", "0"):
+        monkeypatch.setenv("B2_COMM_P2P", mode)       # spawned ranks inherit the environment
+        ctx = mp.get_context("spawn")
+        q = ctx.Queue()
+        port = _free_port()
+        procs = [ctx.Process(target=_rank, args=(r, 2, port, q)) for r in range(2)]
+        for p in procs:
+            p.start()
+        res = sorted([q.get(timeout=300) for _ in procs], key=lambda r: r[0])
+        for p in procs:
+            p.join(60)
+        assert res[0][8] == res[1][8] == (2 if mode == "1" else 1)
+        np.testing.assert_array_equal(res[0][5], res[1][5])
+        out[mode] = res[0]
+    np.testing.assert_array_equal(out["1"][4], out["0"][4])    # gradients of the last step
+    np.testing.assert_array_equal(out["1"][5], out["0"][5])    # weights after K epochs
+    assert out["1"][7] == out["0"][7] == K
 
 
 # ---- wide nets (BASELINE configs[4]): each rank holds half of every minibatch, gradients all-reduced over NCCL ----
