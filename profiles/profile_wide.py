@@ -32,7 +32,10 @@ print("first update (incl. upload) %.1f ms, loss %.5f" % (1e3 * (time.perf_count
 for _ in range(reps):
     l0 = E.kernel_launches()
     E.timer_start()
-    st = E.update_resident()
+    try:
+        st = E.update_resident()
+    except capi.B2Error as e:       # B2_WIDE_SKIP diagnostic runs compute garbage (non-finite loss): timing still valid
+        print("  (", e, ")")
     ms = E.timer_stop_ms()
     se = B * K / (ms * 1e-3)
     print("update_resident %.2f ms  %.3e sample-epochs/s  %.1f TFLOP/s algorithmic (x3 issued)  loss %.5f  launches %d"

@@ -76,6 +76,10 @@ struct GemmArgs {
   int b_mn;                      // K-major kernel only: B is given contraction-major [K][N] (N % 64 == 0), read as an MN-major operand
   int mn_major;                  // 1: C[M][N] = A[K][M]^T . B[K][N] (K blocks of 32, K % 32 == 0, N % 64 == 0)
                                  // output: raw fp32 accumulator tiles, TMA-stored to plane g * splits + split of tmC
+  int fuse_m;                    // MN-major kernel, m_tiles == 2 only: one CTA owns BOTH 128-row halves of the output (two TMEM
+                                 // accumulators fed from one copy of the B block), so B is streamed once instead of twice
+  int reduce_add;                // split-K: every split ADDS its tile into plane g (TMA reduce, fp32 adds in L2) instead of
+                                 // storing to plane g * splits + split; the output must be zero before the launch
   long long* dbg;                // optional per-CTA timeline (clock64), diagnostic runs only
   Dw1Args dw1;                   // MN-major kernel only
 };
@@ -96,7 +100,7 @@ cudaError_t launch_gemm_x3(const CUtensorMap& tmA, const CUtensorMap& tmB, const
                            int sm_count, cudaStream_t st);
 // fp32 output tensor [planes][rows][N] the epilogue TMA-stores 32 x 32 tiles into (plane = group, or group*splits + split)
 int make_output_map(CUtensorMap* out, const void* base, uint64_t N, uint64_t rows, uint64_t planes);
-int gemm_x3_stages(int N, bool mn_major = false);
+int gemm_x3_stages(int N, bool mn_major = false, bool fuse_m = false);
 
 // 3-D bf16 tensor map (K fastest, rows, planes) with a (64 x box_rows x 1) box and the 128-B swizzle.
 // Returns 0 on success; the driver entry point is resolved through the runtime (no -lcuda link dependency).

@@ -139,9 +139,11 @@ k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
   uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);   // 1024-B alignment for the 128-B swizzle atoms
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int N = a.N, stages = a.stages;
-  const int SB = MN ? (4 + 2 * (N / 64)) * MNB_BYTES : stage_bytes(N);
+  const bool FUSE = MN && a.fuse_m;                    // both 128-row output halves in this CTA (GemmArgs::fuse_m)
+  const int AFB = FUSE ? 4 : 2;                        // 64-feature blocks of A per plane and stage (MN mode)
+  const int SB = MN ? (2 * AFB + 2 * (N / 64)) * MNB_BYTES : stage_bytes(N);
   const int B_PLANE_BYTES = MN ? (N / 64) * MNB_BYTES : N * BK * 2;
-  const int A_PLANE = MN ? 2 * MNB_BYTES : A_PLANE_BYTES;
+  const int A_PLANE = MN ? AFB * MNB_BYTES : A_PLANE_BYTES;
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)stages * SB + STG_BYTES);
   uint64_t* empty = full + 8;
   uint64_t* tfull = empty + 8;
@@ -149,7 +151,8 @@ k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
   const int kb_total = a.K / (MN ? BKS : BK);
-  const int n_items = a.G * a.m_tiles * a.splits;
+  const int mt_n = FUSE ? 1 : a.m_tiles;               // output row tiles an item enumerates
+  const int n_items = a.G * mt_n * a.splits;
 
   if (warp == 0 && lane == 0) {
     tc::tma_prefetch_desc(&tmA);
@@ -169,28 +172,33 @@ k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
   if (a.dbg && threadIdx.x == 0) a.dbg[(blockIdx.x * 4 + 0) * 8 + 7] = clock64();
 
   if (warp == 0) {
-    if (lane == 0) {
+    // K-major: one lane issues the 4 big boxes of a stage.  MN-major: a stage is 12-16 boxes of 4 KB; issued by one
+    // thread they cost ~1,400 cycles per stage (the loop was issue-bound, gemm_timeline.py mn), so every box gets a lane.
+    if (lane == 0 || MN) {
       int stage = 0; uint32_t phase = 0;
       for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
         const int sp = item % a.splits;
-        const int mt = (item / a.splits) % a.m_tiles;
-        const int g = item / (a.splits * a.m_tiles);
+        const int mt = (item / a.splits) % mt_n;
+        const int g = item / (a.splits * mt_n);
         const int kb0 = sp * a.kb_per_split;
         const int kb1 = min(kb0 + a.kb_per_split, kb_total);
-        if (a.dbg) a.dbg[(blockIdx.x * 4 + (item / gridDim.x)) * 8 + 0] = clock64();
+        if (a.dbg && lane == 0) a.dbg[(blockIdx.x * 4 + (item / gridDim.x)) * 8 + 0] = clock64();
         for (int kb = kb0; kb < kb1; kb++) {
           tc::mbar_wait(&empty[stage], phase ^ 1);
-          if (a.dbg && kb == kb1 - 1) a.dbg[(blockIdx.x * 4 + (item / gridDim.x)) * 8 + 1] = clock64();
+          if (a.dbg && lane == 0 && kb == kb1 - 1) a.dbg[(blockIdx.x * 4 + (item / gridDim.x)) * 8 + 1] = clock64();
           uint8_t* s = smem + (size_t)stage * SB;
-          tc::mbar_arrive_expect_tx(&full[stage], (uint32_t)SB);
+          if (lane == 0) tc::mbar_arrive_expect_tx(&full[stage], (uint32_t)SB);
           if (MN) {
-            for (int pl = 0; pl < 2; pl++) {
-              for (int fb = 0; fb < 2; fb++)
-                tc::tma_load_3d(s + pl * A_PLANE + fb * MNB_BYTES, &tmA, &full[stage], (mt * 2 + fb) * 64, kb * BKS, g * 2 + pl);
-              for (int fb = 0; fb < N / 64; fb++)
-                tc::tma_load_3d(s + 2 * A_PLANE + pl * B_PLANE_BYTES + fb * MNB_BYTES, &tmB, &full[stage], fb * 64, kb * BKS,
-                                g * 2 + pl);
+            const int per = AFB + N / 64;              // boxes per plane: A feature blocks, then B feature blocks
+            if (lane < 2 * per) {
+              const int pl = lane / per, j = lane % per;
+              if (j < AFB)
+                tc::tma_load_3d(s + pl * A_PLANE + j * MNB_BYTES, &tmA, &full[stage], (mt * 2 + j) * 64, kb * BKS, g * 2 + pl);
+              else
+                tc::tma_load_3d(s + 2 * A_PLANE + pl * B_PLANE_BYTES + (j - AFB) * MNB_BYTES, &tmB, &full[stage], (j - AFB) * 64,
+                                kb * BKS, g * 2 + pl);
             }
+            __syncwarp();
             if (++stage == stages) { stage = 0; phase ^= 1; }
             continue;
           }
@@ -218,9 +226,10 @@ k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         const int sp = item % a.splits;
         const int kb0 = sp * a.kb_per_split;
         const int kb1 = min(kb0 + a.kb_per_split, kb_total);
-        const int buf = it & 1;
-        const uint32_t bphase = (uint32_t)(it >> 1) & 1u;
+        const int buf = FUSE ? 0 : (it & 1);
+        const uint32_t bphase = FUSE ? ((uint32_t)it & 1u) : ((uint32_t)(it >> 1) & 1u);
         tc::mbar_wait(&tempty[buf], bphase ^ 1);       // epilogue has drained this accumulator
+        if (FUSE) tc::mbar_wait(&tempty[1], bphase ^ 1);   // ... and the second half's
         tc::tc_fence_after();
         if (a.dbg) a.dbg[(blockIdx.x * 4 + it) * 8 + 2] = clock64();
         const uint32_t d_tmem = tmem_base + (uint32_t)buf * 256u;
@@ -241,6 +250,12 @@ k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
               tc::umma_bf16(d_tmem, mAm + off, mBh + off, idesc, acc);
               tc::umma_bf16(d_tmem, mAh + off, mBm + off, idesc, 1u);
               tc::umma_bf16(d_tmem, mAh + off, mBh + off, idesc, 1u);
+              if (FUSE) {   // rows 128..255: feature blocks 2, 3 of the same A planes, second accumulator, same B block
+                const uint64_t up = (uint64_t)((2 * MNB_BYTES) >> 4);
+                tc::umma_bf16(d_tmem + 256u, mAm + up + off, mBh + off, idesc, acc);
+                tc::umma_bf16(d_tmem + 256u, mAh + up + off, mBm + off, idesc, 1u);
+                tc::umma_bf16(d_tmem + 256u, mAh + up + off, mBh + off, idesc, 1u);
+              }
               acc = 1u;
             }
             tc::umma_commit(&empty[stage]);
@@ -265,6 +280,7 @@ k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
           if (++stage == stages) { stage = 0; phase ^= 1; }
         }
         tc::umma_commit(&tfull[buf]);                   // accumulator complete
+        if (FUSE) tc::umma_commit(&tfull[1]);
       }
     }
     __syncwarp();
@@ -283,15 +299,16 @@ k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     int it = 0;
     for (int item = blockIdx.x; item < n_items; item += gridDim.x, it++) {
       const int sp = item % a.splits;
-      const int mt = (item / a.splits) % a.m_tiles;
-      const int g = item / (a.splits * a.m_tiles);
-      const int buf = it & 1;
-      const uint32_t bphase = (uint32_t)(it >> 1) & 1u;
+      const int g = item / (a.splits * mt_n);
+      for (int mh = 0; mh < (FUSE ? 2 : 1); mh++) {      // FUSE: this item owns both accumulators (rows 0..127, 128..255)
+      const int mt = FUSE ? mh : (item / a.splits) % mt_n;
+      const int buf = FUSE ? mh : (it & 1);
+      const uint32_t bphase = FUSE ? ((uint32_t)it & 1u) : ((uint32_t)(it >> 1) & 1u);
       tc::mbar_wait(&tfull[buf], bphase);
       tc::tc_fence_after();
       if (a.dbg && threadIdx.x == 64 + 128) a.dbg[(blockIdx.x * 4 + it) * 8 + 5] = clock64();
       const int row0 = mt * BM + q * 32;                 // first accumulator row of this warp
-      const int plane = g * a.splits + sp;
+      const int plane = a.reduce_add ? g : g * a.splits + sp;
       const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * 256u;
       for (int c = c_begin; c < c_end; c += 32) {
         float v[32];
@@ -307,12 +324,14 @@ k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         tc::fence_proxy_async();
         __syncwarp();
         if (lane == 0) {
-          tc::tma_store_3d(&tmC, sb, c, row0, plane);
+          if (a.reduce_add) tc::tma_reduce_add_3d(&tmC, sb, c, row0, plane);
+          else tc::tma_store_3d(&tmC, sb, c, row0, plane);
           tc::bulk_commit();
         }
       }
       tc::tc_fence_before();
       tc::mbar_arrive(&tempty[buf]);
+      }
       if (a.dbg && threadIdx.x == 64 + 128) a.dbg[(blockIdx.x * 4 + it) * 8 + 6] = clock64();
     }
     if (lane == 0) tc::bulk_wait_all();                  // every output tile has landed before the CTA retires
@@ -334,8 +353,9 @@ EncodeTiledFn g_encode = nullptr;
 
 }  // namespace
 
-int gemm_x3_stages(int N, bool mn_major) {
-  int s = (SMEM_LIMIT - 1024 - BAR_BYTES - STG_BYTES - (mn_major ? DW1_SMEM : 0)) / (mn_major ? (4 + 2 * (N / 64)) * MNB_BYTES : stage_bytes(N));
+int gemm_x3_stages(int N, bool mn_major, bool fuse_m) {
+  int s = (SMEM_LIMIT - 1024 - BAR_BYTES - STG_BYTES - (mn_major ? DW1_SMEM : 0)) /
+          (mn_major ? ((fuse_m ? 8 : 4) + 2 * (N / 64)) * MNB_BYTES : stage_bytes(N));
   if (s > 6) s = 6;
   return s;
 }
@@ -385,8 +405,9 @@ int make_output_map(CUtensorMap* out, const void* base, uint64_t N, uint64_t row
 
 cudaError_t launch_gemm_x3(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const GemmArgs& a,
                            int sm_count, cudaStream_t st) {
-  const int smem = a.stages * (a.mn_major ? (4 + 2 * (a.N / 64)) * MNB_BYTES : stage_bytes(a.N)) + STG_BYTES + BAR_BYTES + 1024 +
-                   (a.mn_major ? DW1_SMEM : 0);
+  if (a.fuse_m && !(a.mn_major && a.m_tiles == 2 && a.stages >= 2)) return cudaErrorInvalidValue;
+  const int smem = a.stages * (a.mn_major ? ((a.fuse_m ? 8 : 4) + 2 * (a.N / 64)) * MNB_BYTES : stage_bytes(a.N)) + STG_BYTES + BAR_BYTES +
+                   1024 + (a.mn_major ? DW1_SMEM : 0);
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e;
@@ -394,7 +415,7 @@ cudaError_t launch_gemm_x3(const CUtensorMap& tmA, const CUtensorMap& tmB, const
     if ((e = cudaFuncSetAttribute(k_gemm_x3<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)) != cudaSuccess) return e;
     attr_set = true;
   }
-  const int n_items = a.G * a.m_tiles * a.splits;
+  const int n_items = a.G * (a.fuse_m ? 1 : a.m_tiles) * a.splits;
   int grid = n_items < sm_count ? n_items : sm_count;
   if (grid < 1) return cudaSuccess;
   // 1 CTA per SM is assumed by the 512-column TMEM allocation: always ask for more than half of the shared memory

@@ -284,7 +284,9 @@ __global__ void __launch_bounds__(256, 3) k_wide_head(const WideArgs a) {
 struct ReduceArgs {
   NetDims d;
   UpdateArgs u;
-  const float *part_head, *part_dw1, *part_dw2;
+  const float *part_head, *part_dw1;
+  float* part_dw2;
+  int dw2_added;        // the dW2 GEMM added its split-K tiles into ONE plane per net (TMA reduce): read it, then zero it
   int head_blocks, head_row, dw1_blocks, splits, pstride;
   int first_chunk, last_chunk, apply_adam;
   __nv_bfloat16* w2p;          // weight planes the Adam step keeps current
@@ -333,6 +335,7 @@ __device__ __forceinline__ void wide_loss_log(const UpdateArgs& a, int q, float 
 struct ReduceElem { bool valid; int p, slot; float s; };
 
 // vb: the virtual block (128 elements of W2, or 4 small parameters) this call works on; sum = false: indices only
+template <bool ADDED>   // ADDED: r.dw2_added known at compile time (drops the 40-partial path: 72 -> <= 32 registers, one wave)
 __device__ __forceinline__ ReduceElem wide_reduce_body(const ReduceArgs& r, int w2_blocks, int vb, bool sum) {
   const NetDims d = r.d;
   const ReduceElem none{false, 0, 0, 0.f};
@@ -342,6 +345,13 @@ __device__ __forceinline__ ReduceElem wide_reduce_body(const ReduceArgs& r, int 
     if (i >= 2 * w2n) return none;
     const int g = i / w2n, e = i % w2n;
     if (!sum) return ReduceElem{true, g * d.SIZE + d.oW2 + e, g * d.SIZE + d.oW2 + e, 0.f};
+    if (ADDED) {                               // already summed by the L2; leave zeros behind for the next step's adds
+      float* one = r.part_dw2 + (int64_t)g * w2n + e;
+      const float s1 = *one;
+      *one = 0.f;
+      const int p1 = g * d.SIZE + d.oW2 + e;
+      return ReduceElem{true, p1, p1, s1};
+    }
     const float* base = r.part_dw2 + (int64_t)g * r.splits * w2n + e;
     float s = 0.f;
     int sp = 0;
@@ -413,10 +423,12 @@ __device__ __forceinline__ ReduceElem wide_reduce_body(const ReduceArgs& r, int 
   return ReduceElem{lane == 0, p, slot, s};
 }
 
+template <bool ADDED>
 __global__ void __launch_bounds__(128) k_wide_reduce(const ReduceArgs r, int w2_blocks) {
   pdl_launch_dependents();
   pdl_wait();
-  ReduceElem e = wide_reduce_body(r, w2_blocks, (int)blockIdx.x, true);   // fixed-order sum of the local partials of one element
+  const int vb = (int)blockIdx.x;   // (dispatching the latency-bound small-parameter blocks first was measured slower: 37.6 vs 36.3 ms)
+  ReduceElem e = wide_reduce_body<ADDED>(r, w2_blocks, vb, true);   // fixed-order sum of the local partials of one element
   if (e.valid) {
     if (!r.first_chunk) e.s += r.u.grads[e.slot];             // chunked gradient accumulation
     r.u.grads[e.slot] = e.s;
@@ -562,6 +574,7 @@ struct WideNet {
   AdamCoef* coef = nullptr;
   float *part_head = nullptr, *part_dw1 = nullptr, *part_dw2 = nullptr;
   int head_blocks = 0, head_row = 0, dw1_blocks = 0, splits_max = 0;
+  bool dw2_add = true;   // split-K of dW2 through TMA reduce-add (default); B2_WIDE_DETERMINISTIC=1: partial planes, fixed-order sum
   CUtensorMap tm_h1, tm_w2, tm_d2, tm_w2t, tm_d2_mn, tm_h1_mn;
   CUtensorMap tm_out_h2, tm_out_d1, tm_out_dw2;
   CUtensorMap tm_w2_half;          // K-major weights in (H2/2)-row boxes: the resident halves of the CTA-pair GEMM
@@ -625,6 +638,8 @@ int wide_create(WideNet** out, int H1, int H2, int64_t max_chunk, int sm_count) 
   WCK(cudaMalloc(&w->part_head, sizeof(float) * (size_t)w->head_blocks * 2 * w->head_row));
   WCK(cudaMalloc(&w->part_dw1, sizeof(float) * (size_t)w->dw1_blocks * 2 * H1 * 8));
   WCK(cudaMalloc(&w->part_dw2, sizeof(float) * (size_t)2 * w->splits_max * H2 * H1));
+  WCK(cudaMemset(w->part_dw2, 0, sizeof(float) * (size_t)2 * w->splits_max * H2 * H1));
+  { const char* e = getenv("B2_WIDE_DETERMINISTIC"); w->dw2_add = !(e && e[0] == '1'); }
   WCK(cudaMalloc(&w->boot_count, sizeof(int)));
 #undef WCK
   int rc = 0;
@@ -681,6 +696,9 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     k_wide_prep<<<128, 256, 0, st>>>(wa);
     LCK("prep");
   }
+  // diagnostic only (profiles/wide_marginal.sh): B2_WIDE_SKIP = bit mask of step kernels to leave out (1 l1, 2 fwd GEMM,
+  // 4 head, 8 dX GEMM, 16 dW2 GEMM + dw1, 32 reduce) -- results are garbage, the timing shows each kernel's marginal cost
+  static const int skip = [] { const char* e = getenv("B2_WIDE_SKIP"); return e ? atoi(e) : 0; }();
   const int64_t n_chunks = (a.count + w->cap - 1) / w->cap;
   for (int64_t c = 0; c < n_chunks; c++) {
     wa.first = a.first + c * w->cap;
@@ -690,6 +708,7 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     wa.coef_out = w->coef;
     const int m_tiles = wa.m_pad / 128;
     // layer 1
+    if (!(skip & 1))
     if ((ce = launch_pdl(k_wide_l1, dim3(wa.m_pad / L1_TILE, 2), dim3(256), 0, st, wa)) != cudaSuccess)
       return set_error(B2_ERR_CUDA, "wide l1: %s", cudaGetErrorString(ce));
     (*launches)++;
@@ -697,7 +716,8 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     GemmArgs g{};
     g.G = 2; g.M = wa.count; g.N = H2; g.K = H1; g.m_tiles = m_tiles; g.splits = 1; g.kb_per_split = H1 / 64;
     g.stages = gemm_x3_stages(H2);
-    if (w->pair_fwd) {   // CTA pairs with the weight halves resident (wide_gemm2.cu)
+    if (skip & 2) ce = cudaSuccess;
+    else if (w->pair_fwd) {   // CTA pairs with the weight halves resident (wide_gemm2.cu)
       const Gemm2Args g2{2, wa.count, H2, H1, gemm2_stages(H2, H1)};
       ce = launch_gemm2(false, w->tm_h1, w->tm_w2_half, w->tm_out_h2, g2, w->sm_count, st);
     } else {
@@ -712,7 +732,8 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
       if (grid < w->head_blocks)   // rows of blocks that do not run this time must read as zero
         if ((ce = cudaMemsetAsync(w->part_head, 0, sizeof(float) * (size_t)w->head_blocks * 2 * w->head_row, st)) != cudaSuccess)
           return set_error(B2_ERR_CUDA, "wide memset: %s", cudaGetErrorString(ce));
-      switch (H2 / 32) {
+      if (skip & 4) ce = cudaSuccess;
+      else switch (H2 / 32) {
         case 2: ce = launch_head<2>(wa, grid, st); break;
         case 4: ce = launch_head<4>(wa, grid, st); break;
         case 6: ce = launch_head<6>(wa, grid, st); break;
@@ -725,7 +746,8 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     g = GemmArgs{};
     g.G = 2; g.M = wa.count; g.N = H1; g.K = H2; g.m_tiles = m_tiles; g.splits = 1; g.kb_per_split = H2 / 64;
     g.stages = gemm_x3_stages(H1); g.b_mn = 1;   // B = W2 as stored ([j][k]), read as an MN-major operand
-    if (w->pair_bwd) {
+    if (skip & 8) ce = cudaSuccess;
+    else if (w->pair_bwd) {
       const Gemm2Args g2{2, wa.count, H1, H2, gemm2_stages(H1, H2)};
       ce = launch_gemm2(true, w->tm_d2, w->tm_w2t, w->tm_out_d1, g2, w->sm_count, st);
     } else {
@@ -736,7 +758,10 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     // dW2 partials = D2^T H1 over sample splits
     const int kb_total = wa.m_pad / MN_BOX_ROWS;
     const int jt = (H2 + 127) / 128;
-    int splits = w->sm_count / (2 * jt);
+    // H2 = 256: one CTA owns both 128-row halves of dW2 (two TMEM accumulators), so the H1 block it streams feeds both
+    // -- the kernel is L2-bandwidth bound (100 MB of operand reads per step with separate halves, 67 MB fused)
+    const bool fuse_m = jt == 2 && gemm_x3_stages(H1, true, true) >= 2 && getenv("B2_WIDE_FUSE_M") != nullptr;   // opt-in: measured equal to two CTAs per net half (36.3 ms), see DESIGN.md s3b
+    int splits = w->sm_count / (2 * (fuse_m ? 1 : jt));
     if (splits > kb_total) splits = kb_total;
     if (splits > w->splits_max) splits = w->splits_max;
     if (splits < 1) splits = 1;
@@ -744,12 +769,14 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     splits = (kb_total + kbps - 1) / kbps;
     g = GemmArgs{};
     g.G = 2; g.M = H2; g.N = H1; g.K = wa.m_pad; g.m_tiles = jt; g.splits = splits; g.kb_per_split = kbps;
-    g.stages = gemm_x3_stages(H1, true); g.mn_major = 1;
+    g.stages = gemm_x3_stages(H1, true, fuse_m); g.mn_major = 1; g.reduce_add = w->dw2_add ? 1 : 0; g.fuse_m = fuse_m ? 1 : 0;
     // k_wide_dw1's work rides in eight extra warps of this kernel (FP32 pipe beside the tensor pipe)
-    g.dw1.params = a.params; g.dw1.obs = a.tr.obs; g.dw1.obs_cap = a.tr.cap; g.dw1.idx = a.idx; g.dw1.first = wa.first;
+    g.dw1.params = (skip & 64) ? nullptr : a.params;   // (diagnostic bit 64: the GEMM without the dw1 warps' work)
+    g.dw1.obs = a.tr.obs; g.dw1.obs_cap = a.tr.cap; g.dw1.idx = a.idx; g.dw1.first = wa.first;
     g.dw1.count = wa.count; g.dw1.H1 = H1; g.dw1.SIZE = d.SIZE; g.dw1.oW1 = d.oW1; g.dw1.ob1 = d.ob1;
     g.dw1.z1 = w->d1; g.dw1.cap = w->cap; g.dw1.part = w->part_dw1;
-    const int dw2_grid = std::min(2 * jt * splits, w->sm_count);
+    const int dw2_grid = std::min(2 * (fuse_m ? 1 : jt) * splits, w->sm_count);
+    if (!(skip & 16))
     if ((ce = launch_gemm_x3(w->tm_d2_mn, w->tm_h1_mn, w->tm_out_dw2, g, w->sm_count, st)) != cudaSuccess)
       return set_error(B2_ERR_CUDA, "wide gemm dW2: %s", cudaGetErrorString(ce));
     (*launches)++;
@@ -757,12 +784,15 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     ReduceArgs r{};
     r.d = d; r.u = a; r.part_head = w->part_head; r.part_dw1 = w->part_dw1; r.part_dw2 = w->part_dw2;
     r.head_blocks = w->head_blocks; r.head_row = w->head_row; r.dw1_blocks = dw2_grid; r.splits = splits;
+    r.dw2_added = w->dw2_add ? 1 : 0;
     r.pstride = wide_pstride(H1, H2);
     r.w2p = w->w2p; r.bias2 = w->bias2; r.coef = w->coef;
     r.first_chunk = c == 0; r.last_chunk = c == n_chunks - 1; r.apply_adam = apply_adam ? 1 : 0;
     const int w2_blocks = (2 * H2 * H1 + 127) / 128;
     const int small = 2 * (H1 * (S + 1) + 2 * H2 + 1) + 3;
-    if ((ce = launch_pdl(k_wide_reduce, dim3(w2_blocks + (small + 3) / 4), dim3(128), 0, st, r, w2_blocks)) != cudaSuccess)
+    if (!(skip & 32))
+    if ((ce = (w->dw2_add ? launch_pdl(k_wide_reduce<true>, dim3(w2_blocks + (small + 3) / 4), dim3(128), 0, st, r, w2_blocks)
+                          : launch_pdl(k_wide_reduce<false>, dim3(w2_blocks + (small + 3) / 4), dim3(128), 0, st, r, w2_blocks))) != cudaSuccess)
       return set_error(B2_ERR_CUDA, "wide reduce: %s", cudaGetErrorString(ce));
     (*launches)++;
   }
