@@ -181,9 +181,10 @@ int64_t b2_total_env_steps(b2_handle h);
 int b2_comm_unique_id(char id[B2_COMM_ID_BYTES]);              /* rank 0 makes it, the caller broadcasts it */
 int b2_comm_init(b2_handle h, int rank, int world, const char id[B2_COMM_ID_BYTES]);
 int b2_comm_world(b2_handle h);
-/* how gradients travel between ranks: 0 single GPU; 1 ncclAllReduce + Adam launch (default); 2 NVLink peer memory --
- * each rank publishes its gradient in a buffer its peers have mapped (cudaIpc) and the Adam kernel itself pulls and sums
- * all copies in rank order.  2 is opt-in (B2_COMM_P2P=1 in the environment) and needs every rank to map every peer. */
+/* how gradients travel between ranks: 0 single GPU; 1 reduce -> ncclAllReduce -> Adam (three launches); 2 NVLink peer
+ * memory: the reduce + Adam kernel itself stores every finished gradient element, tagged with the step number, into a
+ * buffer of every peer (mapped with cudaIpc), waits for the peers' copies of the same element and adds them in rank order.
+ * 2 is chosen when every rank could map every peer; B2_COMM_P2P=0 in the environment forces 1. */
 int b2_comm_mode(b2_handle h);
 
 /* ---- measurement helpers (CUDA events on the handle's stream) */

@@ -119,7 +119,7 @@ struct b2_engine {
   int rank = 0, world = 1;
   // gradient exchange over NVLink peer memory (engine.h PeerXchg); NCCL stays the fallback when the mapping fails
   bool p2p = false;
-  char* xchg = nullptr;                    // buf[2][pstride] | flag | counter, mapped by every peer (cudaIpc)
+  char* xchg = nullptr;                    // slots[2][world][pstride] of {value, epoch}, mapped by every peer (cudaIpc)
   void* peer_base[B2_MAX_PEERS] = {};      // cudaIpcOpenMemHandle results (own entry: xchg)
   int px_epoch = 0;
   // wide hidden layers (tensor-core update path, wide.h); null for the reference's 64/32 nets
@@ -215,7 +215,7 @@ int run_returns(b2_engine* E) {
 int setup_peer_exchange(b2_engine* E);
 void next_peer_step(b2_engine* E, UpdateArgs& a);
 inline size_t xchg_slot_bytes(const b2_engine* E) {
-  return ((sizeof(float) * 2 * (size_t)E->pstride + 255) / 256) * 256;
+  return ((sizeof(uint2) * 2 * (size_t)E->world * (size_t)E->pstride + 255) / 256) * 256;
 }
 
 // K2 + K optimizer steps on whatever E->tr currently holds.
@@ -259,32 +259,26 @@ int run_update(b2_engine* E, b2_update_stats* stats) {
       // rank's copy over NVLink peer memory (engine.h PeerXchg); ncclAllReduce only if the peer mapping was refused
       if (E->world > 1 && E->p2p) next_peer_step(E, a);
       if (E->wide) {
-        int rc = wide_step(E->wide, a, E->world == 1, E->stream, &E->launches);
+        int rc = wide_step(E->wide, a, E->world == 1 || E->p2p, E->stream, &E->launches);
         if (rc) return rc;
-        if (E->world > 1) {
-          if (!E->p2p) {
-            int ne = g_nccl.AllReduce(E->grads, E->grads, (size_t)E->pstride, NCCL_FLOAT32, NCCL_SUM, E->comm, E->stream);
-            if (ne != 0) return set_error(B2_ERR_COMM, "ncclAllReduce: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(ne) : "?");
-            E->launches += 1;
-          }
+        if (E->world > 1 && !E->p2p) {
+          int ne = g_nccl.AllReduce(E->grads, E->grads, (size_t)E->pstride, NCCL_FLOAT32, NCCL_SUM, E->comm, E->stream);
+          if (ne != 0) return set_error(B2_ERR_COMM, "ncclAllReduce: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(ne) : "?");
           if ((ce = launch_wide_adam(E->wide, a, E->stream)) != cudaSuccess) return set_error(B2_ERR_CUDA, "adam: %s", cudaGetErrorString(ce));
-          E->launches += 1;
+          E->launches += 2;
         }
         continue;
       }
       if ((ce = launch_ppo_grad(a, E->stream)) != cudaSuccess) return set_error(B2_ERR_CUDA, "ppo_grad: %s", cudaGetErrorString(ce));
-      if (E->world == 1) {
+      if (E->world == 1 || E->p2p) {   // one kernel: reduce (+ peer-memory exchange) + Adam
         if ((ce = launch_reduce(a, true, E->stream)) != cudaSuccess) return set_error(B2_ERR_CUDA, "reduce: %s", cudaGetErrorString(ce));
         E->launches += 2;
       } else {
         if ((ce = launch_reduce(a, false, E->stream)) != cudaSuccess) return set_error(B2_ERR_CUDA, "reduce: %s", cudaGetErrorString(ce));
-        if (!E->p2p) {
-          int ne = g_nccl.AllReduce(E->grads, E->grads, (size_t)E->pstride, NCCL_FLOAT32, NCCL_SUM, E->comm, E->stream);
-          if (ne != 0) return set_error(B2_ERR_COMM, "ncclAllReduce: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(ne) : "?");
-          E->launches += 1;
-        }
+        int ne = g_nccl.AllReduce(E->grads, E->grads, (size_t)E->pstride, NCCL_FLOAT32, NCCL_SUM, E->comm, E->stream);
+        if (ne != 0) return set_error(B2_ERR_COMM, "ncclAllReduce: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(ne) : "?");
         if ((ce = launch_adam(a, E->stream)) != cudaSuccess) return set_error(B2_ERR_CUDA, "adam: %s", cudaGetErrorString(ce));
-        E->launches += 2;
+        E->launches += 3;
       }
     }
   }
@@ -315,12 +309,12 @@ int run_update(b2_engine* E, b2_update_stats* stats) {
 // Map every peer's exchange buffer (engine.h PeerXchg).  The 64-byte cudaIpc handles travel through one ncclAllGather
 // on the communicator that was just created; ranks then agree (all-reduce of a success flag) on whether EVERY mapping
 // worked, so either all of them exchange gradients over peer memory or all of them keep calling ncclAllReduce.
-// Opt-in (B2_COMM_P2P=1 in the environment): measured on 2 x B200 (NV18) the best peer-memory variant ties with
-// ncclAllReduce + Adam (41.1 vs 40.2 ms per configs[4] update), so NCCL stays the default.
+// Default when every rank can map every peer; B2_COMM_P2P=0 in the environment forces ncclAllReduce (A/B measurements).
+// Measured: 43.7 vs 47.1 ms per configs[4] update on 8 x B200, 40.1 vs 41.0 on 2.
 int setup_peer_exchange(b2_engine* E) {
   E->p2p = false;
   const char* env = getenv("B2_COMM_P2P");
-  const bool want = env && env[0] == '1' && E->world <= B2_MAX_PEERS && g_nccl.AllGather;
+  const bool want = !(env && env[0] == '0') && E->world <= B2_MAX_PEERS && g_nccl.AllGather;
   const size_t buf_bytes = xchg_slot_bytes(E);
   CK(cudaMalloc(&E->xchg, buf_bytes + 256));
   CK(cudaMemset(E->xchg, 0, buf_bytes + 256));
@@ -367,22 +361,15 @@ int setup_peer_exchange(b2_engine* E) {
   return B2_OK;
 }
 
-// the PeerXchg of the next optimizer step (layout: buf[2][pstride] | flag | counter); the reduce kernels' output is
-// redirected into this step's buffer
+// the PeerXchg of the next optimizer step (layout: slots[2][world][pstride] of {value, epoch})
 void next_peer_step(b2_engine* E, UpdateArgs& a) {
-  const size_t buf_bytes = xchg_slot_bytes(E);
   PeerXchg& x = a.px;
-  x.world = E->world; x.rank = E->rank;
-  x.epoch = ++E->px_epoch;
-  x.par_off = (int64_t)(x.epoch & 1) * E->pstride;
-  for (int r = 0; r < E->world; r++) {
-    x.buf[r] = reinterpret_cast<const float*>(E->peer_base[r]);
-    x.flag[r] = reinterpret_cast<int*>(static_cast<char*>(E->peer_base[r]) + buf_bytes);
-  }
-  x.counter = reinterpret_cast<int*>(E->xchg + buf_bytes) + 32;
+  x.world = E->world; x.rank = E->rank; x.pstride = E->pstride;
+  x.epoch = (unsigned)++E->px_epoch;
+  x.par_off = (int64_t)(x.epoch & 1u) * E->world * E->pstride;
+  for (int r = 0; r < E->world; r++) x.slots[r] = reinterpret_cast<uint2*>(E->peer_base[r]);
   x.out = E->grads;
   x.status = E->status;
-  a.grads = reinterpret_cast<float*>(E->xchg) + x.par_off;
 }
 
 // host [n][S_ext] -> device AoS [n][6] (zero-filled tail when S_ext = 4) and back

@@ -61,24 +61,26 @@ struct RolloutArgs {
   int* progress;        // [ceil(n_envs/32)] steps of this rollout already published per env group (hand-off word)
 };
 
-// Gradient exchange over NVLink peer memory (multi-GPU, one process per GPU; opt-in alternative to ncclAllReduce, see
-// DESIGN.md s5 for the measurements that decided the default).  Every rank owns, in memory its peers have mapped
-// (cudaIpc),   buf[2][pstride] floats | flag | counter.
-// Step e (parity e & 1): the REDUCE kernel writes this rank's gradient into buf[e & 1] (plain local stores; it is simply
-// given that buffer as its output) and its last block (device counter) publishes flag = e with ONE system-scope fence.
-// The ADAM kernel waits until every rank's flag >= e (acquire loads over NVLink), PULLS the world copies of each of its
-// elements straight out of the peers' memory and adds them in RANK ORDER -- every rank forms the identical sum, so the
-// weights stay bit-identical without a broadcast -- and applies Adam.  Two parities are enough: a rank writes
-// buf[(e+1) & 1] only after its Adam(e) saw every peer's flag e, i.e. after every peer's Adam(e-1), the last reader of
-// that parity, has ended.
+// Gradient exchange over NVLink peer memory, fused into the reduce + Adam kernel (multi-GPU, one process per GPU; opt-in
+// alternative to reduce -> ncclAllReduce -> Adam, see DESIGN.md s5 for the measurements).  Flag-in-data protocol (what
+// NCCL calls LL): every rank owns, in memory its peers have mapped (cudaIpc),
+//     slots[2][world][pstride] of {value, epoch} pairs (8 bytes, written and read as ONE 8-byte access).
+// Step e (parity e & 1), every thread that finishes a gradient element i:
+//   1. stores {g_i, e} into slot[rank][i] of EVERY rank -- posted NVLink stores, no fence, no flag, no counter;
+//   2. polls its OWN copies slot[r][i] (local memory) until their tag is e, for r = 0..world-1;
+//   3. adds the values in RANK ORDER (identical sum on every rank: weights stay bit-identical without a broadcast) and
+//      applies Adam to element i.
+// A thread waits only for the SAME thread of its peers, which pushes before it waits, so there is no circular wait as
+// long as blocks are dispatched in index order; every wait is bounded (status bit 1 instead of a hung GPU).  Two parities
+// are enough: a rank pushes step e+2 only after its step e+1 kernel ended, i.e. after every peer pushed e+1, i.e. after
+// every peer's step-e kernel -- the last reader of that parity -- ended.
 constexpr int B2_MAX_PEERS = 8;
 struct PeerXchg {
   int world = 0, rank = 0;      // world <= 1: single GPU, nothing below is used
-  int epoch = 0;                // this optimizer step (1-based, same on every rank)
-  int64_t par_off = 0;          // (epoch & 1) * pstride
-  const float* buf[B2_MAX_PEERS] = {};   // rank r's buffer (own entry: local pointer)
-  int* flag[B2_MAX_PEERS] = {};          // rank r's flag word
-  int* counter = nullptr;       // local: blocks of the reduce kernel that have finished
+  unsigned epoch = 0;           // this optimizer step (1-based, same on every rank)
+  int pstride = 0;
+  int64_t par_off = 0;          // (epoch & 1) * world * pstride
+  uint2* slots[B2_MAX_PEERS] = {};       // rank r's slot array (own entry: local pointer)
   float* out = nullptr;         // summed gradient (pstride floats, local): what b2_get_grads returns
   int* status = nullptr;        // bit1: a peer never arrived (bounded wait expired)
 };
@@ -102,44 +104,24 @@ struct UpdateArgs {
 };
 
 #ifdef __CUDACC__
-// reduce side, called by EVERY thread of EVERY block after its last gradient store (no early returns before it)
-__device__ __forceinline__ void px_publish(const PeerXchg& x) {
-  __threadfence();                 // this thread's stores are visible device-wide before the block counts itself done
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    const int done = atomicAdd(x.counter, 1);
-    if (done == (int)gridDim.x - 1) {      // last block: every block's stores precede (counter + fences); one system fence
-      *x.counter = 0;
-      __threadfence_system();
-      asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(x.flag[x.rank]), "r"(x.epoch) : "memory");
-    }
-  }
-}
-// Adam side: every block waits until every rank (itself included) has published step e
-__device__ __forceinline__ void px_wait(const PeerXchg& x) {
-  if (threadIdx.x < x.world) {
-    const int* f = x.flag[threadIdx.x];
+// steps 1-3 of PeerXchg for gradient element i with rank-local value v: returns the all-rank sum
+__device__ __forceinline__ float px_allreduce_elem(const PeerXchg& x, int i, float v) {
+  const int64_t mine = x.par_off + (int64_t)x.rank * x.pstride + i;
+  for (int r = 0; r < x.world; r++)
+    asm volatile("st.relaxed.sys.global.v2.b32 [%0], {%1, %2};" ::"l"(x.slots[r] + mine), "r"(__float_as_uint(v)), "r"(x.epoch)
+                 : "memory");
+  const uint2* base = x.slots[x.rank] + x.par_off + i;
+  float s = 0.f;
+  for (int r = 0; r < x.world; r++) {
+    unsigned val, tag;
     long long spins = 0;
     while (true) {
-      int v;
-      asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
-      if (v - x.epoch >= 0) break;
-      __nanosleep(64);
-      if (++spins > (1ll << 23)) { atomicOr(x.status, 2); break; }   // ~2 s: surface a lost peer instead of hanging the GPU
+      asm volatile("ld.relaxed.sys.global.v2.b32 {%0, %1}, [%2];" : "=r"(val), "=r"(tag) : "l"(base + (int64_t)r * x.pstride) : "memory");
+      if (tag == x.epoch) break;
+      if (++spins > (1ll << 26)) { atomicOr(x.status, 2); break; }   // ~2 s: surface a lost peer instead of hanging the GPU
     }
+    s = r == 0 ? __uint_as_float(val) : __fadd_rn(s, __uint_as_float(val));
   }
-  __syncthreads();
-}
-// element i of the all-rank sum, pulled from every rank's buffer, added in rank order (loads bypass L1)
-__device__ __forceinline__ float px_sum(const PeerXchg& x, int i) {
-  float v[B2_MAX_PEERS];
-#pragma unroll
-  for (int r = 0; r < B2_MAX_PEERS; r++)
-    if (r < x.world) asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v[r]) : "l"(x.buf[r] + x.par_off + i));
-  float s = v[0];
-#pragma unroll
-  for (int r = 1; r < B2_MAX_PEERS; r++)
-    if (r < x.world) s = __fadd_rn(s, v[r]);
   x.out[i] = s;
   return s;
 }

@@ -425,34 +425,28 @@ __device__ __forceinline__ void adam_apply(const UpdateArgs& a, int p, float g, 
 
 __global__ void __launch_bounds__(128) k_reduce(const UpdateArgs a, int apply_adam) {
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
-  if (p < N::P + 3) {
-    float g = 0.f;
-    for (int c = 0; c < a.grid; c++) g += a.partials[(int64_t)c * PSTRIDE + p];
-    if (p < N::P) {
-      a.grads[p] = g;
-      if (apply_adam) adam_apply(a, p, g, *a.adam_step);
-    } else {
-      // loss1 mean, 0.5 * mean e^2, clipped fraction -- local sums; the host (or the exchange) finishes them
-      a.grads[PSTRIDE - 4 + (p - N::P)] = g;
-      if (apply_adam) {
-        const double d = (double)a.denom;
-        const int q = p - N::P;
-        a.loss_log[a.step_slot * 4 + q] = (q == 1 ? 0.5 : 1.0) * (double)g / d;
-      }
-    }
+  if (p >= N::P + 3) return;
+  const bool peers = a.px.world > 1;   // several GPUs: exchange over peer memory inside this kernel (engine.h PeerXchg)
+  const int slot = p < N::P ? p : PSTRIDE - 4 + (p - N::P);   // loss1 sum, sum e^2, clipped count ride in the tail
+  float g = 0.f;
+  for (int c = 0; c < a.grid; c++) g += a.partials[(int64_t)c * PSTRIDE + p];
+  a.grads[slot] = g;
+  if (peers) g = px_allreduce_elem(a.px, slot, g);
+  if (!(apply_adam || peers)) return;
+  if (p < N::P) adam_apply(a, p, g, *a.adam_step);
+  else {
+    const int q = p - N::P;
+    a.loss_log[a.step_slot * 4 + q] = (q == 1 ? 0.5 : 1.0) * (double)g / (double)a.denom;
   }
-  if (a.px.world > 1) px_publish(a.px);   // a.grads is this step's exchange buffer (engine.h PeerXchg)
 }
 
+// Adam after an ncclAllReduce of a.grads (the default multi-GPU path)
 __global__ void __launch_bounds__(128) k_adam(const UpdateArgs a) {
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
-  const bool peers = a.px.world > 1;   // peer-memory exchange fused in; otherwise a.grads already holds the all-reduced sum
-  if (peers) px_wait(a.px);
-  if (p < N::P) adam_apply(a, p, peers ? px_sum(a.px, p) : a.grads[p], *a.adam_step);
+  if (p < N::P) adam_apply(a, p, a.grads[p], *a.adam_step);
   else if (p < N::P + 3) {
     const int q = p - N::P;
-    const float g = peers ? px_sum(a.px, PSTRIDE - 4 + q) : a.grads[PSTRIDE - 4 + q];
-    a.loss_log[a.step_slot * 4 + q] = (q == 1 ? 0.5 : 1.0) * (double)g / (double)a.denom;
+    a.loss_log[a.step_slot * 4 + q] = (q == 1 ? 0.5 : 1.0) * (double)a.grads[PSTRIDE - 4 + q] / (double)a.denom;
   }
 }
 

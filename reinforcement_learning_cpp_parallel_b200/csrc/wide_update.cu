@@ -432,12 +432,13 @@ __global__ void __launch_bounds__(128) k_wide_reduce(const ReduceArgs r, int w2_
   if (e.valid) {
     if (!r.first_chunk) e.s += r.u.grads[e.slot];             // chunked gradient accumulation
     r.u.grads[e.slot] = e.s;
-    if (r.last_chunk && r.apply_adam) {
+    const bool peers = r.u.px.world > 1;   // several GPUs: exchange over NVLink peer memory right here (engine.h PeerXchg)
+    if (r.last_chunk && peers) e.s = px_allreduce_elem(r.u.px, e.slot, e.s);
+    if (r.last_chunk && (r.apply_adam || peers)) {
       if (e.p < r.d.P) wide_store_planes(r.d, r.w2p, r.bias2, e.p, wide_adam_apply(r.u, *r.coef, e.p, e.s));
       else wide_loss_log(r.u, e.p - r.d.P, e.s);
     }
   }
-  if (r.last_chunk && r.u.px.world > 1) px_publish(r.u.px);   // r.u.grads is this step's exchange buffer (engine.h PeerXchg)
 }
 
 __global__ void __launch_bounds__(128) k_wide_adam(const UpdateArgs a, const NetDims d, int pstride, __nv_bfloat16* w2p,
@@ -446,13 +447,9 @@ __global__ void __launch_bounds__(128) k_wide_adam(const UpdateArgs a, const Net
   pdl_wait();                          // (a no-op unless launched with the programmatic-serialization attribute)
   const AdamCoef coef = *coef_p;
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
-  const bool peers = a.px.world > 1;   // peer-memory exchange fused in; otherwise a.grads already holds the all-reduced sum
-  if (peers) px_wait(a.px);
-  if (p < d.P) wide_store_planes(d, w2p, bias2, p, wide_adam_apply(a, coef, p, peers ? px_sum(a.px, p) : a.grads[p]));
-  else if (p < d.P + 3) {
-    const int i = pstride - 4 + (p - d.P);
-    wide_loss_log(a, p - d.P, peers ? px_sum(a.px, i) : a.grads[i]);
-  }
+  // (after an ncclAllReduce of a.grads: the default multi-GPU path)
+  if (p < d.P) wide_store_planes(d, w2p, bias2, p, wide_adam_apply(a, coef, p, a.grads[p]));
+  else if (p < d.P + 3) wide_loss_log(a, p - d.P, a.grads[pstride - 4 + (p - d.P)]);
 }
 
 }  // namespace
@@ -802,9 +799,6 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
 
 cudaError_t launch_wide_adam(WideNet* w, const UpdateArgs& a, cudaStream_t st) {
   const int grid = (w->d.P + 3 + 127) / 128;
-  if (a.px.world > 1)   // follows k_wide_reduce directly: launch latency hidden behind it
-    return launch_pdl(k_wide_adam, dim3(grid), dim3(128), 0, st, a, w->d, wide_pstride(w->d.H1, w->d.H2), w->w2p, w->bias2,
-                      (const AdamCoef*)w->coef);
   k_wide_adam<<<grid, 128, 0, st>>>(a, w->d, wide_pstride(w->d.H1, w->d.H2), w->w2p, w->bias2, w->coef);
   return cudaGetLastError();
 }

@@ -68,7 +68,7 @@ def test_two_gpu_update_matches_one_gpu():
     g1, p1 = E.get_grads(), E.get_params()
     E.close()
     # identical trajectories for any sharding (Philox keyed by the global env id)
-    assert res[0][8] == res[1][8] == (2 if os.environ.get("B2_COMM_P2P") == "1" else 1)   # NCCL unless the peer-memory exchange is opted in
+    assert res[0][8] == res[1][8] == (1 if os.environ.get("B2_COMM_P2P") == "0" else 2)   # the fused peer-memory exchange by default
     for rank, off, n, traj, *_ in res:
         for k in traj:
             np.testing.assert_array_equal(traj[k], full[k][:, off:off + n], err_msg=k)
