@@ -171,6 +171,7 @@ def wide_leg(args, pkg, capi, np, rank, local, world, dist, barrier, max_over_ra
         uid = [pkg.Engine.comm_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)
         E.comm_init(rank, world, uid[0])
+    comm_mode = {0: "single GPU", 1: "ncclAllReduce + Adam launch", 2: "NVLink peer-memory exchange fused into reduce + Adam"}[E.comm_mode()]
     rng = np.random.default_rng(1234 + rank)
     th = 0.3 * rng.standard_normal(B)
     obs = capi.pinned_empty((B, 6), np.float32)
@@ -246,11 +247,13 @@ def wide_leg(args, pkg, capi, np, rank, local, world, dist, barrier, max_over_ra
             "gpu_launches": int(launches),
             "e2e": {"value": B * K * args.steps * world / dt, "unit": "sample-epochs/s", "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": 4 * 8 * K * M, "api": "b2_update on pinned host buffers (PPO::update(MemoryNN))"},
-            "roofline": {"kernel": "k_gemm_x3", "bound": "tensor", "achieved": ach, "peak": bf16_peak / 3.0,
+            "roofline": {"kernel": "whole optimizer step: k_gemm2_ws x2 + k_gemm_x3<MN> on tcgen05, 3 FP32 side kernels",
+                         "bound": "tensor", "achieved": ach, "peak": bf16_peak / 3.0,
                          "unit": "TFLOP/s", "frac": ach / (bf16_peak / 3.0) if bf16_peak else None,
                          "peak_source": bf16_src + " / 3 (every fp32 product is three bf16 MMAs)",
                          "issued_bf16_tflops": 3 * ach, "flop_per_sample_epoch": FLOP_UPDATE_WIDE,
-                         "traffic": _ncu_traffic("k_gemm_x3_fwd_2x16384x256x256")},
+                         "traffic": _ncu_traffic("k_gemm2_ws_fwd_2x16384x256x256"),
+                         "comm_mode": comm_mode},
             "whole_batch_one_gpu": whole, "last_loss": st.loss}
 
 
