@@ -70,6 +70,26 @@ struct Dw1Args {
   float* part;              // [grid][2][H1 * 8]
 };
 
+// Adam coefficients of the current optimizer step (computed once per step by k_wide_l1)
+struct AdamCoef {
+  float fb1, f1mb1, fb2, f1mb2, sq_bc2, feps, step_size;
+};
+
+// arguments of the reduce + Adam stage (wide_reduce.cuh)
+struct ReduceArgs {
+  NetDims d;
+  UpdateArgs u;
+  const float *part_head, *part_dw1;
+  float* part_dw2;
+  int dw2_added;        // the dW2 GEMM added its split-K tiles into ONE plane per net (TMA reduce): read it, then zero it
+  int head_blocks, head_row, dw1_blocks, splits, pstride;
+  int first_chunk, last_chunk, apply_adam;
+  __nv_bfloat16* w2p;          // weight planes the Adam step keeps current
+  float* bias2;
+  const AdamCoef* coef;        // written by k_wide_l1 at the start of this optimizer step
+};
+
+
 struct GemmArgs {
   int G, M, N, K;                // per group g < G: C[M][N] = A[M][K] . B[N][K]^T ; K % 64 == 0, N % 16 == 0, N <= 256
   int m_tiles, splits, kb_per_split, stages;
@@ -82,6 +102,12 @@ struct GemmArgs {
                                  // storing to plane g * splits + split; the output must be zero before the launch
   long long* dbg;                // optional per-CTA timeline (clock64), diagnostic runs only
   Dw1Args dw1;                   // MN-major kernel only
+  // MN-major kernel only: the reduce + Adam stage of the step runs in the tail of this kernel, behind a grid barrier
+  // (every CTA is resident: grid <= SM count, one CTA per SM), instead of in a launch of its own.  red.part_dw2 == nullptr: off
+  ReduceArgs red;
+  int red_w2_blocks, red_vblocks;   // virtual blocks of blockDim.x elements (W2 part) / blockDim.x / 32 small parameters
+  int* bar_counter;                 // device counter, monotonically increasing across launches
+  int bar_target;                   // value it reaches when every CTA of THIS launch has arrived
 };
 
 // the CTA-pair, weights-resident GEMM of wide_gemm2.cu (layer-2 forward and dX): C[g][M][N] = A[g][M][K] . B[g]

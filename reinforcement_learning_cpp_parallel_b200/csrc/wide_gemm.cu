@@ -26,6 +26,7 @@
 #include "tc_ptx.cuh"
 #include "wide.h"
 #include "mlp.cuh"
+#include "wide_reduce.cuh"
 
 namespace b2 {
 
@@ -344,6 +345,26 @@ k_gemm_x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     tc::tmem_dealloc(tmem_base, 512);
   }
   if (a.dbg && threadIdx.x == 32) a.dbg[(blockIdx.x * 4 + 2) * 8 + 7] = clock64();   // after the TMEM release
+  if (MN && a.red.part_dw2) {
+    // ---- reduce + Adam in the tail (GemmArgs::red).  Every CTA's dW2 tiles have landed (bulk_wait_all in the epilogue
+    // warps) and its dW1 rows are stored; the __syncthreads above orders them before thread 0's fence.  Grid barrier:
+    // all CTAs are resident (grid <= SMs, one CTA per SM), so spinning on the counter cannot starve anyone.
+    if (threadIdx.x == 0) {
+      __threadfence();
+      atomicAdd(a.bar_counter, 1);
+      long long spins = 0;
+      while (true) {
+        int v;
+        asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(a.bar_counter) : "memory");
+        if (v - a.bar_target >= 0) break;
+        __nanosleep(40);
+        if (++spins > (1ll << 25)) __trap();               // ~2 s: a CUDA error, never a hung GPU
+      }
+    }
+    __syncthreads();
+    for (int vb = blockIdx.x; vb < a.red_vblocks; vb += gridDim.x)
+      wide_reduce_finish(a.red, wide_reduce_body<true>(a.red, a.red_w2_blocks, vb, true));
+  }
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,

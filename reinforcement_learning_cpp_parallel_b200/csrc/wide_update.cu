@@ -19,26 +19,13 @@
 #include "tc_ptx.cuh"
 #include "wide.h"
 #include "mlp.cuh"
+#include "wide_reduce.cuh"
 
 namespace b2 {
 
 namespace {
 
-constexpr int S = OBS;
 
-struct AdamCoef {
-  float fb1, f1mb1, fb2, f1mb2, sq_bc2, feps, step_size;
-};
-// libtorch adam.cpp: scalars are doubles narrowed to f32 inside the tensor kernels
-__device__ __forceinline__ AdamCoef adam_coef(const HyperDev& hp, int64_t step) {
-  const double bc1 = 1.0 - pow(hp.beta1, (double)step);
-  const double bc2 = 1.0 - pow(hp.beta2, (double)step);
-  AdamCoef c;
-  c.fb1 = (float)hp.beta1; c.f1mb1 = (float)(1.0 - hp.beta1);
-  c.fb2 = (float)hp.beta2; c.f1mb2 = (float)(1.0 - hp.beta2);
-  c.sq_bc2 = (float)sqrt(bc2); c.feps = (float)hp.eps; c.step_size = (float)(-(hp.lr / bc1));
-  return c;
-}
 struct WideArgs {
   NetDims d;
   const float* params;
@@ -281,164 +268,11 @@ __global__ void __launch_bounds__(256, 3) k_wide_head(const WideArgs a) {
 
 // (dW1 / db1: the work of the former k_wide_dw1 kernel rides in extra warps of the dW2 GEMM, wide_gemm.cu dw1_worker)
 
-struct ReduceArgs {
-  NetDims d;
-  UpdateArgs u;
-  const float *part_head, *part_dw1;
-  float* part_dw2;
-  int dw2_added;        // the dW2 GEMM added its split-K tiles into ONE plane per net (TMA reduce): read it, then zero it
-  int head_blocks, head_row, dw1_blocks, splits, pstride;
-  int first_chunk, last_chunk, apply_adam;
-  __nv_bfloat16* w2p;          // weight planes the Adam step keeps current
-  float* bias2;
-  const AdamCoef* coef;        // written by k_wide_l1 at the start of this optimizer step
-};
-
-// a parameter changed: keep the bf16 planes (both majors) of W2 and the bias copy in step with it
-__device__ __forceinline__ void wide_store_planes(const NetDims& d, __nv_bfloat16* w2p, float* bias2,
-                                                  int p, float val) {
-  const int g = p / d.SIZE, o = p % d.SIZE;
-  if (o >= d.oW2 && o < d.ob2) {
-    const int e = o - d.oW2;
-    __nv_bfloat16 hi, mid;
-    tc::split_bf16(val, hi, mid);
-    const int64_t ps = (int64_t)d.H2 * d.H1;
-    w2p[(g * 2 + 0) * ps + e] = hi;
-    w2p[(g * 2 + 1) * ps + e] = mid;
-  } else if (o >= d.ob2 && o < d.oW3) {
-    bias2[g * d.H2 + (o - d.ob2)] = val;
-  }
-}
-
-// same arithmetic as ppo_update.cu adam_apply (libtorch adam.cpp order), generic parameter count
-__device__ __forceinline__ float wide_adam_apply(const UpdateArgs& a, const AdamCoef& c, int p, float g) {
-  float m = a.adam_m[p], v = a.adam_v[p];
-  m = __fadd_rn(__fmul_rn(m, c.fb1), __fmul_rn(c.f1mb1, g));                 // exp_avg.mul_(b1).add_(grad, 1-b1)
-  v = __fadd_rn(__fmul_rn(v, c.fb2), __fmul_rn(c.f1mb2, __fmul_rn(g, g)));   // exp_avg_sq.mul_(b2).addcmul_(g, g, 1-b2)
-  const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(v), c.sq_bc2), c.feps); // (sqrt(v)/sqrt(bc2)).add_(eps)
-  a.adam_m[p] = m;
-  a.adam_v[p] = v;
-  const float np = __fadd_rn(a.params[p], __fmul_rn(c.step_size, __fdiv_rn(m, denom)));  // p.addcdiv_(m, denom, -step_size)
-  a.params[p] = np;
-  return np;
-}
-
-__device__ __forceinline__ void wide_loss_log(const UpdateArgs& a, int q, float sum) {
-  a.loss_log[a.step_slot * 4 + q] = (q == 1 ? 0.5 : 1.0) * (double)sum / (double)a.denom;
-}
-
-// Fixed-order (bit-reproducible) sum of every partial that feeds a parameter; accumulates over chunks; Adam on the last.
-// Blocks [0, w2_blocks): one thread per W2 element, split-K partials summed 8 loads at a time.
-// Remaining blocks: one WARP per "small" parameter (W1, b1, b2, W3, b3 and the 3 loss scalars), lanes stride over the
-// per-block partial rows and a shuffle tree finishes the sum.
-// One finished element of the reduce: p = parameter index (or d.P + l for the loss scalars), slot = its place in grads.
-struct ReduceElem { bool valid; int p, slot; float s; };
-
-// vb: the virtual block (128 elements of W2, or 4 small parameters) this call works on; sum = false: indices only
-template <bool ADDED>   // ADDED: r.dw2_added known at compile time (drops the 40-partial path: 72 -> <= 32 registers, one wave)
-__device__ __forceinline__ ReduceElem wide_reduce_body(const ReduceArgs& r, int w2_blocks, int vb, bool sum) {
-  const NetDims d = r.d;
-  const ReduceElem none{false, 0, 0, 0.f};
-  const int w2n = d.H2 * d.H1;
-  if (vb < w2_blocks) {
-    const int i = vb * blockDim.x + threadIdx.x;
-    if (i >= 2 * w2n) return none;
-    const int g = i / w2n, e = i % w2n;
-    if (!sum) return ReduceElem{true, g * d.SIZE + d.oW2 + e, g * d.SIZE + d.oW2 + e, 0.f};
-    if (ADDED) {                               // already summed by the L2; leave zeros behind for the next step's adds
-      float* one = r.part_dw2 + (int64_t)g * w2n + e;
-      const float s1 = *one;
-      *one = 0.f;
-      const int p1 = g * d.SIZE + d.oW2 + e;
-      return ReduceElem{true, p1, p1, s1};
-    }
-    const float* base = r.part_dw2 + (int64_t)g * r.splits * w2n + e;
-    float s = 0.f;
-    int sp = 0;
-    if (r.splits <= 40) {                      // the usual case: every partial of this element in flight at once
-      float t[40];
-#pragma unroll
-      for (int u = 0; u < 40; u++) t[u] = (u < r.splits) ? base[(int64_t)u * w2n] : 0.f;
-#pragma unroll
-      for (int u = 0; u < 40; u++) s += t[u];  // adding the zero padding does not change the sum
-      sp = r.splits;
-    }
-    for (; sp + 16 <= r.splits; sp += 16) {
-      float t[16];
-#pragma unroll
-      for (int u = 0; u < 16; u++) t[u] = base[(int64_t)(sp + u) * w2n];
-#pragma unroll
-      for (int u = 0; u < 16; u++) s += t[u];
-    }
-    for (; sp + 4 <= r.splits; sp += 4) {
-      float t[4];
-#pragma unroll
-      for (int u = 0; u < 4; u++) t[u] = base[(int64_t)(sp + u) * w2n];
-#pragma unroll
-      for (int u = 0; u < 4; u++) s += t[u];
-    }
-    for (; sp < r.splits; sp++) s += base[(int64_t)sp * w2n];
-    const int p = g * d.SIZE + d.oW2 + e;
-    return ReduceElem{true, p, p, s};
-  }
-  const int lane = threadIdx.x & 31;
-  const int per_net = d.H1 * (S + 1) + 2 * d.H2 + 1;     // W1, b1, b2, W3, b3
-  const int q = (vb - w2_blocks) * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (q >= 2 * per_net + 3) return none;
-  const float* src;
-  int64_t stride;
-  int rows, p, slot;
-  if (q < 2 * per_net) {
-    const int g = q / per_net, o = q % per_net;
-    if (o < d.H1 * (S + 1)) {                              // dW1aug[k][c], c == S is b1
-      const int k = o / (S + 1), c = o % (S + 1);
-      src = r.part_dw1 + (int64_t)g * d.H1 * 8 + k * 8 + c;
-      stride = (int64_t)2 * d.H1 * 8; rows = r.dw1_blocks;
-      p = g * d.SIZE + (c < S ? d.oW1 + k * S + c : d.ob1 + k);
-    } else {
-      const int o2 = o - d.H1 * (S + 1);                   // head row: [0,H2) dW3, [H2,2H2) db2, 2H2 db3
-      src = r.part_head + (int64_t)g * r.head_row + o2;
-      stride = (int64_t)2 * r.head_row; rows = r.head_blocks;
-      p = g * d.SIZE + (o2 < d.H2 ? d.oW3 + o2 : (o2 < 2 * d.H2 ? d.ob2 + (o2 - d.H2) : d.ob3));
-    }
-    slot = p;
-  } else {
-    const int l = q - 2 * per_net;                         // 0 loss1 sum, 1 sum e^2, 2 clipped count
-    const int g = l == 1 ? 1 : 0, col = 2 * d.H2 + (l == 2 ? 2 : 1);
-    src = r.part_head + (int64_t)g * r.head_row + col;
-    stride = (int64_t)2 * r.head_row; rows = r.head_blocks;
-    p = d.P + l; slot = r.pstride - 4 + l;
-  }
-  if (!sum) return ReduceElem{lane == 0, p, slot, 0.f};
-  float s = 0.f;
-  for (int b0 = lane; b0 < rows; b0 += 32 * 8) {     // 8 independent loads per lane per round
-    float t[8];
-#pragma unroll
-    for (int u = 0; u < 8; u++) t[u] = (b0 + 32 * u < rows) ? src[(int64_t)(b0 + 32 * u) * stride] : 0.f;
-#pragma unroll
-    for (int u = 0; u < 8; u++) s += t[u];
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-  return ReduceElem{lane == 0, p, slot, s};
-}
-
 template <bool ADDED>
 __global__ void __launch_bounds__(128) k_wide_reduce(const ReduceArgs r, int w2_blocks) {
   pdl_launch_dependents();
   pdl_wait();
-  const int vb = (int)blockIdx.x;   // (dispatching the latency-bound small-parameter blocks first was measured slower: 37.6 vs 36.3 ms)
-  ReduceElem e = wide_reduce_body<ADDED>(r, w2_blocks, vb, true);   // fixed-order sum of the local partials of one element
-  if (e.valid) {
-    if (!r.first_chunk) e.s += r.u.grads[e.slot];             // chunked gradient accumulation
-    r.u.grads[e.slot] = e.s;
-    const bool peers = r.u.px.world > 1;   // several GPUs: exchange over NVLink peer memory right here (engine.h PeerXchg)
-    if (r.last_chunk && peers) e.s = px_allreduce_elem(r.u.px, e.slot, e.s);
-    if (r.last_chunk && (r.apply_adam || peers)) {
-      if (e.p < r.d.P) wide_store_planes(r.d, r.w2p, r.bias2, e.p, wide_adam_apply(r.u, *r.coef, e.p, e.s));
-      else wide_loss_log(r.u, e.p - r.d.P, e.s);
-    }
-  }
+  wide_reduce_finish(r, wide_reduce_body<ADDED>(r, w2_blocks, (int)blockIdx.x, true));
 }
 
 __global__ void __launch_bounds__(128) k_wide_adam(const UpdateArgs a, const NetDims d, int pstride, __nv_bfloat16* w2p,
@@ -571,6 +405,11 @@ struct WideNet {
   AdamCoef* coef = nullptr;
   float *part_head = nullptr, *part_dw1 = nullptr, *part_dw2 = nullptr;
   int head_blocks = 0, head_row = 0, dw1_blocks = 0, splits_max = 0;
+  int* bar_counter = nullptr;   // grid barrier of the dW2 kernel's fused reduce tail (device, monotonically increasing)
+  int bar_count = 0;            // host mirror: value after every launch so far
+  bool fuse_reduce = false;     // B2_WIDE_FUSE_REDUCE=1: reduce + Adam in the tail of the dW2 GEMM kernel behind a grid barrier (needs
+                                // dw2_add).  Opt-in: measured 38.3 vs 36.5 ms per configs[4] update -- the barrier and the 2-3 serial
+                                // rounds of latency-bound partial sums per CTA cost more than the launch they save
   bool dw2_add = true;   // split-K of dW2 through TMA reduce-add (default); B2_WIDE_DETERMINISTIC=1: partial planes, fixed-order sum
   CUtensorMap tm_h1, tm_w2, tm_d2, tm_w2t, tm_d2_mn, tm_h1_mn;
   CUtensorMap tm_out_h2, tm_out_d1, tm_out_dw2;
@@ -592,7 +431,7 @@ void wide_destroy(WideNet* w) {
   if (!w) return;
   cudaFree(w->w2p); cudaFree(w->h1p); cudaFree(w->d2p);
   cudaFree(w->bias2); cudaFree(w->h2); cudaFree(w->d1); cudaFree(w->coef);
-  cudaFree(w->part_head); cudaFree(w->part_dw1); cudaFree(w->part_dw2);
+  cudaFree(w->part_head); cudaFree(w->part_dw1); cudaFree(w->part_dw2); cudaFree(w->bar_counter);
   cudaFree(w->boot_idx); cudaFree(w->boot_count);
   delete w;
 }
@@ -637,6 +476,9 @@ int wide_create(WideNet** out, int H1, int H2, int64_t max_chunk, int sm_count) 
   WCK(cudaMalloc(&w->part_dw2, sizeof(float) * (size_t)2 * w->splits_max * H2 * H1));
   WCK(cudaMemset(w->part_dw2, 0, sizeof(float) * (size_t)2 * w->splits_max * H2 * H1));
   { const char* e = getenv("B2_WIDE_DETERMINISTIC"); w->dw2_add = !(e && e[0] == '1'); }
+  w->fuse_reduce = w->dw2_add && getenv("B2_WIDE_FUSE_REDUCE") != nullptr;
+  WCK(cudaMalloc(&w->bar_counter, sizeof(int)));
+  WCK(cudaMemset(w->bar_counter, 0, sizeof(int)));
   WCK(cudaMalloc(&w->boot_count, sizeof(int)));
 #undef WCK
   int rc = 0;
@@ -773,11 +615,7 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     g.dw1.count = wa.count; g.dw1.H1 = H1; g.dw1.SIZE = d.SIZE; g.dw1.oW1 = d.oW1; g.dw1.ob1 = d.ob1;
     g.dw1.z1 = w->d1; g.dw1.cap = w->cap; g.dw1.part = w->part_dw1;
     const int dw2_grid = std::min(2 * (fuse_m ? 1 : jt) * splits, w->sm_count);
-    if (!(skip & 16))
-    if ((ce = launch_gemm_x3(w->tm_d2_mn, w->tm_h1_mn, w->tm_out_dw2, g, w->sm_count, st)) != cudaSuccess)
-      return set_error(B2_ERR_CUDA, "wide gemm dW2: %s", cudaGetErrorString(ce));
-    (*launches)++;
-    // reduce (+ Adam on the last chunk)
+    // reduce (+ Adam on the last chunk): in the tail of the dW2 kernel behind a grid barrier, or as a launch of its own
     ReduceArgs r{};
     r.d = d; r.u = a; r.part_head = w->part_head; r.part_dw1 = w->part_dw1; r.part_dw2 = w->part_dw2;
     r.head_blocks = w->head_blocks; r.head_row = w->head_row; r.dw1_blocks = dw2_grid; r.splits = splits;
@@ -785,8 +623,23 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     r.pstride = wide_pstride(H1, H2);
     r.w2p = w->w2p; r.bias2 = w->bias2; r.coef = w->coef;
     r.first_chunk = c == 0; r.last_chunk = c == n_chunks - 1; r.apply_adam = apply_adam ? 1 : 0;
-    const int w2_blocks = (2 * H2 * H1 + 127) / 128;
     const int small = 2 * (H1 * (S + 1) + 2 * H2 + 1) + 3;
+    const bool fused_tail = w->fuse_reduce && !(skip & (16 | 32));
+    if (fused_tail) {
+      const int bd = 320 + 512;                         // threads of the MN-major GEMM kernel (GEMM roles + dw1 warps)
+      g.red = r;
+      g.red_w2_blocks = (2 * H2 * H1 + bd - 1) / bd;
+      g.red_vblocks = g.red_w2_blocks + (small + bd / 32 - 1) / (bd / 32);
+      g.bar_counter = w->bar_counter;
+      w->bar_count += dw2_grid;
+      g.bar_target = w->bar_count;
+    }
+    if (!(skip & 16))
+    if ((ce = launch_gemm_x3(w->tm_d2_mn, w->tm_h1_mn, w->tm_out_dw2, g, w->sm_count, st)) != cudaSuccess)
+      return set_error(B2_ERR_CUDA, "wide gemm dW2: %s", cudaGetErrorString(ce));
+    (*launches)++;
+    if (fused_tail) continue;
+    const int w2_blocks = (2 * H2 * H1 + 127) / 128;
     if (!(skip & 32))
     if ((ce = (w->dw2_add ? launch_pdl(k_wide_reduce<true>, dim3(w2_blocks + (small + 3) / 4), dim3(128), 0, st, r, w2_blocks)
                           : launch_pdl(k_wide_reduce<false>, dim3(w2_blocks + (small + 3) / 4), dim3(128), 0, st, r, w2_blocks))) != cudaSuccess)
