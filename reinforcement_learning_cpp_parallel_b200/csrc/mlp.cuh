@@ -8,6 +8,10 @@
 #pragma once
 #include "common.cuh"
 
+#ifndef B2_MLP_FFMA2
+#define B2_MLP_FFMA2 1
+#endif
+
 namespace b2 {
 
 // smem image of one net, k-major:  W1T[S][H1] b1[H1] W2T[H1][H2] b2[H2] W3[H2] b3[1](+pad)
@@ -84,6 +88,29 @@ __device__ __forceinline__ float mlp_row(const float* __restrict__ sm, float* __
   }
   // ---- layer 2: accumulators in registers, rolled over k ----
   float h2[N::H2];
+#if B2_MLP_FFMA2
+  // packed FP32 FMA (FFMA2, sm_100): the two halves of an LDS.128 are register pairs already, so a k step costs
+  // H2/2 issue slots instead of H2.  Same IEEE fma per element as the scalar form: results are bit-identical.
+  float2 acc[N::H2 / 2];
+#pragma unroll
+  for (int j = 0; j < N::H2; j += 4) {
+    const float4 b = *reinterpret_cast<const float4*>(sm + L::ob2 + j);
+    acc[j / 2] = make_float2(b.x, b.y); acc[j / 2 + 1] = make_float2(b.z, b.w);
+  }
+#pragma unroll 4
+  for (int k = 0; k < N::H1; k++) {
+    const float hk = hcol[k * BS];
+    const float2 hk2 = make_float2(hk, hk);
+#pragma unroll
+    for (int j = 0; j < N::H2; j += 4) {
+      const float4 w = *reinterpret_cast<const float4*>(sm + L::oW2T + k * N::H2 + j);
+      acc[j / 2] = __ffma2_rn(make_float2(w.x, w.y), hk2, acc[j / 2]);
+      acc[j / 2 + 1] = __ffma2_rn(make_float2(w.z, w.w), hk2, acc[j / 2 + 1]);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < N::H2; j += 2) { h2[j] = acc[j / 2].x; h2[j + 1] = acc[j / 2].y; }
+#else
 #pragma unroll
   for (int j = 0; j < N::H2; j += 4) {
     const float4 b = *reinterpret_cast<const float4*>(sm + L::ob2 + j);
@@ -101,6 +128,7 @@ __device__ __forceinline__ float mlp_row(const float* __restrict__ sm, float* __
       h2[j + 3] = fmaf(w.w, hk, h2[j + 3]);
     }
   }
+#endif
   // ---- layer 3 ----
   float y = sm[L::ob3];
 #pragma unroll

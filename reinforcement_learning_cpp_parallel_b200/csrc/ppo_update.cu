@@ -85,6 +85,24 @@ __device__ __forceinline__ void stage_weights(float* sm, const float* __restrict
     sm[oW3 + i] = (i < H2) ? g[N::oW3 + i] : (i == H2 ? g[N::ob3] : 0.0f);
 }
 
+#ifndef B2_GRAD_FFMA2
+#define B2_GRAD_FFMA2 1
+#endif
+#if B2_GRAD_FFMA2
+// 4 x 4 rank-1 update with packed FP32 FMA (FFMA2, sm_100): 8 issue slots instead of 16; the column pairs of `a` are the
+// halves of an LDS.128 and the accumulator rows live in aligned register pairs.  Same IEEE fma per element.
+__device__ __forceinline__ void fma44(float (&acc)[4][4], const float4& b, const float4& a) {
+  const float2 a01 = make_float2(a.x, a.y), a23 = make_float2(a.z, a.w);
+  const float bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const float2 bb = make_float2(bv[i], bv[i]);
+    const float2 r0 = __ffma2_rn(bb, a01, make_float2(acc[i][0], acc[i][1]));
+    const float2 r1 = __ffma2_rn(bb, a23, make_float2(acc[i][2], acc[i][3]));
+    acc[i][0] = r0.x; acc[i][1] = r0.y; acc[i][2] = r1.x; acc[i][3] = r1.y;
+  }
+}
+#else
 __device__ __forceinline__ void fma44(float (&acc)[4][4], const float4& b, const float4& a) {
   acc[0][0] = fmaf(b.x, a.x, acc[0][0]); acc[0][1] = fmaf(b.x, a.y, acc[0][1]);
   acc[0][2] = fmaf(b.x, a.z, acc[0][2]); acc[0][3] = fmaf(b.x, a.w, acc[0][3]);
@@ -95,6 +113,7 @@ __device__ __forceinline__ void fma44(float (&acc)[4][4], const float4& b, const
   acc[3][0] = fmaf(b.w, a.x, acc[3][0]); acc[3][1] = fmaf(b.w, a.y, acc[3][1]);
   acc[3][2] = fmaf(b.w, a.z, acc[3][2]); acc[3][3] = fmaf(b.w, a.w, acc[3][3]);
 }
+#endif
 __device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
 __device__ __forceinline__ void st4(float* p, float a, float b, float c, float d) {
   *reinterpret_cast<float4*>(p) = make_float4(a, b, c, d);
