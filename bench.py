@@ -378,7 +378,8 @@ def main():
         dt = max_over_ranks(time.perf_counter() - t0)
         d2h = sum(a.nbytes for a in out.values())
         e2e = {"value": steps_all / dt, "unit": "env-steps/s", "h2d_bytes_per_step": int(hp.nbytes),
-               "d2h_bytes_per_step": int(d2h), "api": f"b2_set_params + b2_rollout_host (pinned host buffers, {args.chunks} chunks: D2H overlaps simulation)"}
+               "d2h_bytes_per_step": int(d2h), "api": "b2_set_params + b2_rollout_host (pinned host buffers: the rollout kernel stores every field straight into "
+                      "host memory over PCIe while it simulates; B2_ROLLOUT_HOST_DIRECT=0 selects the chunked copy-engine pipeline)"}
 
     update_wide = None
     if not args.no_wide:

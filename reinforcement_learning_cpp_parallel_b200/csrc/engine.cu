@@ -865,12 +865,15 @@ int b2_set_state_trace(b2_handle E, int enable) {
 }
 
 // one k_rollout launch covering steps [t_begin, t_end) of a T-step rollout that started at E->global_step
-static int rollout_window(b2_engine* E, int T, int t_begin, int t_end, bool forced) {
+static int rollout_window(b2_engine* E, int T, int t_begin, int t_end, bool forced, float* obs_aos = nullptr,
+                          const b2_batch_out* host = nullptr) {
   RolloutArgs a{};
   a.params = E->params; a.state = E->state; a.ep_step = E->ep_step; a.ep_ret = E->ep_ret;
   a.ep_count = E->ep_count; a.ep_log = E->ep_log; a.max_eps = E->max_eps;
   a.tr = E->tr;
   a.forced_action = forced ? E->forced : nullptr;
+  a.obs_aos = obs_aos;
+  if (host) { a.h_action = host->action; a.h_logp = host->logp; a.h_mu = host->mu; a.h_reward = host->reward; a.h_flags = host->flags; }
   a.n_envs = E->cfg.n_envs; a.T = T; a.t_begin = t_begin; a.t_end = t_end; a.n_timestep = E->cfg.n_timestep;
   a.seed = E->cfg.seed; a.env_offset = E->cfg.env_offset; a.step0 = E->global_step;
   a.hp = E->hp; a.status = E->status; a.progress = E->progress; a.env_flags = E->cfg.env_flags;
@@ -933,6 +936,29 @@ int b2_rollout_host(b2_handle E, int T, int n_chunks, const b2_batch_out* out) {
   if (n_chunks > B2_MAX_CHUNKS) n_chunks = B2_MAX_CHUNKS;
   const int64_t NE = E->cfg.n_envs;
   Traj& t = E->tr;
+  // Pinned destinations (b2_host_alloc / cudaHostAlloc) and 6-wide observations: ONE launch whose stores go to the device
+  // trajectory AND straight into the host buffers (posted PCIe writes, the observations transposed in the warp so that
+  // every store is a whole 128-B line).  Measured at the reference shape (tools/e2e_probe.py): 7.1-7.2 ms -- SM-issued
+  // writes sustain ~44 GB/s and 37 B per record need 49 GB/s to hide completely behind the 6.3 ms of simulation; the
+  // chunked copy-engine pipeline below takes 7.3-7.4 ms; splitting the fields between the two (small fields direct,
+  // observations by DMA) 9.3 ms: SM writes and DMA contend for the link.  B2_ROLLOUT_HOST_DIRECT=0 forces the pipeline,
+  // which pageable buffers and 4-wide observations always take.
+  {
+    auto pinned = [](const void* p) {
+      if (!p) return true;
+      cudaPointerAttributes at;
+      if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+      return at.type == cudaMemoryTypeHost;
+    };
+    const char* env = getenv("B2_ROLLOUT_HOST_DIRECT");
+    const bool direct_ok = !(env && env[0] == '0') && E->S_ext == OBS && pinned(out->obs) && pinned(out->action) &&
+                           pinned(out->logp) && pinned(out->mu) && pinned(out->reward) && pinned(out->flags);
+    if (direct_ok) {
+      if ((rc = rollout_window(E, T, 0, T, false, out->obs, out))) return rc;
+      rollout_finish(E, T);
+      return check_status(E, "rollout");    // synchronises the stream: the host buffers are complete
+    }
+  }
   if (out->obs && (rc = ensure_stage(E, NE * T * OBS, 0))) return rc;
   if (!E->copy_stream) {
     CK(cudaStreamCreateWithFlags(&E->copy_stream, cudaStreamNonBlocking));
@@ -957,9 +983,12 @@ int b2_rollout_host(b2_handle E, int T, int n_chunks, const b2_batch_out* out) {
   }
   for (int c = 0; c < nb; c++) {
     const int t0 = bounds[c], t1 = bounds[c + 1];
-    if ((rc = rollout_window(E, T, t0, t1, false))) return rc;
+    // 6-wide observations leave the kernel record-major as well (RolloutArgs::obs_aos): no transpose between the
+    // simulation and the copy.  4-wide ones (S_ext = 4) keep the transpose: their stored cos/sin planes are zeroed first.
+    const bool direct = out->obs && E->S_ext == OBS;
+    if ((rc = rollout_window(E, T, t0, t1, false, direct ? E->stage : nullptr))) return rc;
     const int64_t k0 = (int64_t)t0 * NE, n = (int64_t)(t1 - t0) * NE;
-    if (out->obs) {
+    if (out->obs && !direct) {
       // The [c][k] -> [k][c] transpose runs on the MAIN stream, between two rollout launches: the persistent rollout
       // kernel owns every register file while it runs, so a transpose queued on the copy stream could only start
       // after the NEXT chunk's simulation had finished, delaying two thirds of the chunk's bytes by one chunk.

@@ -51,6 +51,12 @@ struct RolloutArgs {
   int max_eps;
   Traj tr;
   const float* forced_action;  // [T][N] or null
+  // b2_rollout_host with PINNED destination buffers: the kernel also stores every field straight into host memory (posted
+  // PCIe writes, 37 B per record ~ 49 GB/s at the reference shape), so the trajectory is on the host when the kernel ends
+  float *h_action, *h_logp, *h_mu, *h_reward;   // each null or [T][N] in pinned host memory
+  uint8_t* h_flags;
+  float* obs_aos;              // null, or [T][N][6] (device staging or pinned host): the observations ALSO as records (what MemoryNN holds) for b2_rollout_host,
+                               // so that no transpose kernel sits between the simulation and the D2H copy
   int64_t n_envs;
   int T, n_timestep;    // T: horizon of the whole rollout (trajectory index and TRUNC flag use absolute t)
   int t_begin, t_end;   // this launch advances steps [t_begin, t_end) of it

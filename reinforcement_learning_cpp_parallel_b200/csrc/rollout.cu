@@ -60,7 +60,8 @@ __device__ __forceinline__ void rollout_segment(const RolloutArgs& a, const floa
       while (ld_acquire(a.progress + g) < t0) __nanosleep(200);
     __syncwarp();
   }
-  if (e >= NE) return;  // ragged last group (no warp-level sync below this line)
+  if (e >= NE) return;  // ragged last group (no warp-level sync below this line, except under full_group)
+  const bool full_group = g * 32 + 32 <= NE;
 
   Real u[4];
 #pragma unroll
@@ -107,11 +108,37 @@ __device__ __forceinline__ void rollout_segment(const RolloutArgs& a, const floa
 
 #pragma unroll
     for (int c = 0; c < 6; c++) __stcs(a.tr.obs + c * cap + k, o[c]);   // streaming: written once, read by K3 later
+    if (a.obs_aos) {                                                     // host-bound copy, record-major (b2_rollout_host)
+      if (full_group) {
+        // the warp's 32 records are 768 contiguous bytes: transpose through shuffles so that each of the 6 stores is one
+        // fully coalesced 128-B line (PCIe writes of whole lines when the destination is pinned host memory)
+        float* blk = a.obs_aos + 6 * ((int64_t)t * NE + g * 32);
+#pragma unroll
+        for (int i = 0; i < 6; i++) {
+          const int idx = i * 32 + lane, src = idx / 6, c = idx - 6 * src;
+          float v = __shfl_sync(0xffffffffu, o[0], src);
+#pragma unroll
+          for (int cc = 1; cc < 6; cc++) {
+            const float w = __shfl_sync(0xffffffffu, o[cc], src);
+            v = (c == cc) ? w : v;
+          }
+          __stcs(blk + idx, v);
+        }
+      } else {
+        float2* rec = reinterpret_cast<float2*>(a.obs_aos + 6 * k);
+        __stcs(rec, make_float2(o[0], o[1])); __stcs(rec + 1, make_float2(o[2], o[3])); __stcs(rec + 2, make_float2(o[4], o[5]));
+      }
+    }
     __stcs(a.tr.action + k, act);
     __stcs(a.tr.logp + k, lp);
     __stcs(a.tr.mu + k, mu);
     __stcs(a.tr.reward + k, r);
     a.tr.flags[k] = fl;
+    if (a.h_action) __stcs(a.h_action + k, act);                         // host-resident copies (b2_rollout_host, pinned buffers)
+    if (a.h_logp) __stcs(a.h_logp + k, lp);
+    if (a.h_mu) __stcs(a.h_mu + k, mu);
+    if (a.h_reward) __stcs(a.h_reward + k, r);
+    if (a.h_flags) a.h_flags[k] = fl;
     if (TRACE) {
       double4 s4 = make_double4((double)u[0], (double)u[1], (double)u[2], (double)u[3]);
       *reinterpret_cast<double4*>(a.tr.state_trace + 4 * k) = s4;
