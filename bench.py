@@ -257,6 +257,25 @@ def wide_leg(args, pkg, capi, np, rank, local, world, dist, barrier, max_over_ra
             "whole_batch_one_gpu": whole, "last_loss": st.loss}
 
 
+def _bind_to_gpu_numa_node(local):
+    """Pin this process to the CPUs NVML reports as local to GPU `local`: first-touch then places the pinned host buffers
+    of the e2e leg on the GPU's own NUMA node (on a two-socket box half of the ranks would otherwise write across the
+    socket link).  Host-side placement only; returns a short description for the JSON line, None if NVML is unavailable."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = [64 * w + b for w, word in enumerate(words) for b in range(64) if (word >> b) & 1]
+        allowed = sorted(set(cpus) & set(os.sched_getaffinity(0)))
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+            return f"{len(allowed)} cpus ({allowed[0]}-{allowed[-1]})"
+    except Exception:
+        pass
+    return None
+
+
 def main():
     args = parse()
     rank = int(os.environ.get("RANK", "0"))
@@ -277,6 +296,7 @@ def main():
         ge.build(oracle=False)
 
     torch.cuda.set_device(local)
+    numa = _bind_to_gpu_numa_node(local)       # pinned host buffers are then allocated next to this rank's GPU
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -378,7 +398,7 @@ def main():
         dt = max_over_ranks(time.perf_counter() - t0)
         d2h = sum(a.nbytes for a in out.values())
         e2e = {"value": steps_all / dt, "unit": "env-steps/s", "h2d_bytes_per_step": int(hp.nbytes),
-               "d2h_bytes_per_step": int(d2h), "api": "b2_set_params + b2_rollout_host (pinned host buffers: the rollout kernel stores every field straight into "
+               "d2h_bytes_per_step": int(d2h), "host_numa_binding": numa, "api": "b2_set_params + b2_rollout_host (pinned host buffers: the rollout kernel stores every field straight into "
                       "host memory over PCIe while it simulates; B2_ROLLOUT_HOST_DIRECT=0 selects the chunked copy-engine pipeline)"}
 
     update_wide = None

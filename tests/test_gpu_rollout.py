@@ -194,10 +194,14 @@ def test_training_learns_cartpole(pkg):
     E.close()
 
 
-def test_rollout_host_pipelined_equals_resident_rollout(pkg):
+@pytest.mark.parametrize("pinned", [True, False])
+def test_rollout_host_pipelined_equals_resident_rollout(pkg, pinned):
+    """b2_rollout_host delivers exactly what b2_rollout + b2_traj_download deliver and carries env state on: with pinned
+    buffers the kernel stores straight into host memory (one launch; 200 envs = 6 full warps + a ragged one, so both
+    observation store paths run); with pageable buffers the chunked launches + copy-engine pipeline, for chunk counts
+    that do and do not divide the horizon."""
     from reinforcement_learning_cpp_parallel_b200 import capi
-    """b2_rollout_host (chunked launches + overlapped D2H into host buffers) delivers exactly what b2_rollout +
-    b2_traj_download deliver, for chunk counts that do and do not divide the horizon, and carries env state on."""
+    alloc = capi.pinned_empty if pinned else (lambda shape, dt: np.empty(shape, dt))
     N, T = 200, 37
     ref = make_engine(pkg, n_envs=N, horizon=T, seed=5)
     ref.init_params(3)
@@ -208,9 +212,8 @@ def test_rollout_host_pipelined_equals_resident_rollout(pkg):
     for chunks in (1, 4, 37):
         E = make_engine(pkg, n_envs=N, horizon=T, seed=5)
         E.init_params(3)
-        out = {"obs": capi.pinned_empty((T, N, 6), np.float32), "action": capi.pinned_empty((T, N), np.float32),
-               "logp": capi.pinned_empty((T, N), np.float32), "reward": capi.pinned_empty((T, N), np.float32),
-               "flags": capi.pinned_empty((T, N), np.uint8)}
+        out = {"obs": alloc((T, N, 6), np.float32), "action": alloc((T, N), np.float32), "logp": alloc((T, N), np.float32),
+               "mu": alloc((T, N), np.float32), "reward": alloc((T, N), np.float32), "flags": alloc((T, N), np.uint8)}
         E.rollout_host(T, out, n_chunks=chunks)
         for k in out:
             np.testing.assert_array_equal(out[k], a[k], err_msg=f"{k} chunks={chunks}")
@@ -220,3 +223,22 @@ def test_rollout_host_pipelined_equals_resident_rollout(pkg):
         np.testing.assert_array_equal(E.env_get_state()[0], ref.env_get_state()[0])
         E.close()
     ref.close()
+
+
+def test_rollout_host_four_wide_observations(pkg):
+    """obs_vars = 4 takes the copy-engine pipeline (the stored cos/sin planes are zeroed before the transpose)."""
+    from reinforcement_learning_cpp_parallel_b200 import capi
+    N, T = 96, 20
+    ref = make_engine(pkg, n_envs=N, horizon=T, seed=8, obs_vars=4)
+    ref.init_params(2)
+    ref.rollout(T)
+    a = ref.traj_download(T)
+    ref.close()
+    E = make_engine(pkg, n_envs=N, horizon=T, seed=8, obs_vars=4)
+    E.init_params(2)
+    out = {"obs": capi.pinned_empty((T, N, 4), np.float32), "action": capi.pinned_empty((T, N), np.float32),
+           "flags": capi.pinned_empty((T, N), np.uint8)}
+    E.rollout_host(T, out, n_chunks=4)
+    for k in out:
+        np.testing.assert_array_equal(out[k], a[k], err_msg=k)
+    E.close()
