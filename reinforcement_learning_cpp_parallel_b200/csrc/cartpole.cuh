@@ -165,6 +165,8 @@ struct CartPoleDyn<float> {
     constexpr double b[6] = B2_RK_B;
     constexpr float dt = (float)CPC::dt, A0 = (float)CPC::A0, A1 = (float)CPC::A1, mpl = (float)CPC::mpl,
                     inv_tot = (float)CPC::inv_tot, g = (float)CPC::g;
+    // (the RK update on packed FP32 -- FFMA2 / FMUL2 on the (x, xdot), (theta, thetadot) pairs, 12 -> 6 instructions per
+    // stage -- was measured SLOWER, 4.25 vs 3.93 ms: the stage is one dependency chain and the packed ops lengthen it)
 #pragma unroll 1
     for (int sub = 0; sub < CPC::nsteps; sub++) {
       float w0, w1, w2, w3;
