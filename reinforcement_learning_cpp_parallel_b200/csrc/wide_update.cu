@@ -79,6 +79,11 @@ __global__ void __launch_bounds__(256, 4) k_wide_l1(const WideArgs a) {
   const int H1 = a.d.H1, g = blockIdx.y;
   const int s0 = blockIdx.x * L1_TILE;
   pdl_launch_dependents();
+  // the observations are constant during an update: fetch this block's tile while the previous step's reduce still runs
+  for (int i = threadIdx.x; i < L1_TILE * S; i += blockDim.x) {
+    const int s = i / S, c = i % S;
+    xs[s][c] = (s0 + s < a.count) ? a.tr.obs[c * a.tr.cap + sample_pos(a, s0 + s)] : 0.0f;
+  }
   pdl_wait();                                   // the weights come from the previous step's Adam
   if (blockIdx.x == 0 && g == 0 && threadIdx.x == 0 && a.bump_step) {   // one optimizer step
     const int64_t step = *a.bump_step + 1;
@@ -87,10 +92,6 @@ __global__ void __launch_bounds__(256, 4) k_wide_l1(const WideArgs a) {
   }
   for (int i = threadIdx.x; i < H1 * S; i += blockDim.x) ws[(i / 48) * 52 + (i % 48)] = a.params[g * a.d.SIZE + a.d.oW1 + i];
   for (int i = threadIdx.x; i < H1; i += blockDim.x) bs[i] = a.params[g * a.d.SIZE + a.d.ob1 + i];
-  for (int i = threadIdx.x; i < L1_TILE * S; i += blockDim.x) {
-    const int s = i / S, c = i % S;
-    xs[s][c] = (s0 + s < a.count) ? a.tr.obs[c * a.tr.cap + sample_pos(a, s0 + s)] : 0.0f;
-  }
   __syncthreads();
   const int64_t plane = a.cap * H1;
   const int groups = H1 / 8;                    // feature groups of 8
