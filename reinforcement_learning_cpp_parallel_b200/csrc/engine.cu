@@ -255,8 +255,8 @@ int run_update(b2_engine* E, b2_update_stats* stats) {
       a.denom = a.count * E->world;       // every rank holds an equal shard of the global minibatch
       a.grid = update_grid_for(a.count, E->sm_count);
       a.step_slot = slot;
-      // several GPUs: the rank-local gradient goes into this step's exchange buffer and the Adam kernel sums every
-      // rank's copy over NVLink peer memory (engine.h PeerXchg); ncclAllReduce only if the peer mapping was refused
+      // several GPUs: the reduce + Adam kernel exchanges every gradient element with its peers over NVLink peer memory
+      // (engine.h PeerXchg); reduce -> ncclAllReduce -> Adam only if the peer mapping was refused or switched off
       if (E->world > 1 && E->p2p) next_peer_step(E, a);
       if (E->wide) {
         int rc = wide_step(E->wide, a, E->world == 1 || E->p2p, E->stream, &E->launches);
