@@ -110,12 +110,16 @@ struct UpdateArgs {
 };
 
 #ifdef __CUDACC__
-// steps 1-3 of PeerXchg for gradient element i with rank-local value v: returns the all-rank sum
-__device__ __forceinline__ float px_allreduce_elem(const PeerXchg& x, int i, float v) {
+// steps 1-3 of PeerXchg for gradient element i with rank-local value v, in two halves so that a thread that owns several
+// elements can push them all before it waits for any: px_push stores {v, epoch} into this rank's slot on every rank,
+// px_pull waits for every rank's slot of element i and returns the rank-order sum
+__device__ __forceinline__ void px_push(const PeerXchg& x, int i, float v) {
   const int64_t mine = x.par_off + (int64_t)x.rank * x.pstride + i;
   for (int r = 0; r < x.world; r++)
     asm volatile("st.relaxed.sys.global.v2.b32 [%0], {%1, %2};" ::"l"(x.slots[r] + mine), "r"(__float_as_uint(v)), "r"(x.epoch)
                  : "memory");
+}
+__device__ __forceinline__ float px_pull(const PeerXchg& x, int i) {
   const uint2* base = x.slots[x.rank] + x.par_off + i;
   float s = 0.f;
   for (int r = 0; r < x.world; r++) {
@@ -130,6 +134,10 @@ __device__ __forceinline__ float px_allreduce_elem(const PeerXchg& x, int i, flo
   }
   x.out[i] = s;
   return s;
+}
+__device__ __forceinline__ float px_allreduce_elem(const PeerXchg& x, int i, float v) {
+  px_push(x, i, v);
+  return px_pull(x, i);
 }
 #endif
 

@@ -39,14 +39,17 @@ __device__ __forceinline__ void wide_store_planes(const NetDims& d, __nv_bfloat1
 }
 
 // same arithmetic as ppo_update.cu adam_apply (libtorch adam.cpp order), generic parameter count
-__device__ __forceinline__ float wide_adam_apply(const UpdateArgs& a, const AdamCoef& c, int p, float g) {
-  float m = a.adam_m[p], v = a.adam_v[p];
+__device__ __forceinline__ float wide_adam_math(const AdamCoef& c, float g, float& m, float& v, float w) {
   m = __fadd_rn(__fmul_rn(m, c.fb1), __fmul_rn(c.f1mb1, g));                 // exp_avg.mul_(b1).add_(grad, 1-b1)
   v = __fadd_rn(__fmul_rn(v, c.fb2), __fmul_rn(c.f1mb2, __fmul_rn(g, g)));   // exp_avg_sq.mul_(b2).addcmul_(g, g, 1-b2)
   const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(v), c.sq_bc2), c.feps); // (sqrt(v)/sqrt(bc2)).add_(eps)
+  return __fadd_rn(w, __fmul_rn(c.step_size, __fdiv_rn(m, denom)));          // p.addcdiv_(m, denom, -step_size)
+}
+__device__ __forceinline__ float wide_adam_apply(const UpdateArgs& a, const AdamCoef& c, int p, float g) {
+  float m = a.adam_m[p], v = a.adam_v[p];
+  const float np = wide_adam_math(c, g, m, v, a.params[p]);
   a.adam_m[p] = m;
   a.adam_v[p] = v;
-  const float np = __fadd_rn(a.params[p], __fmul_rn(c.step_size, __fdiv_rn(m, denom)));  // p.addcdiv_(m, denom, -step_size)
   a.params[p] = np;
   return np;
 }
@@ -162,6 +165,107 @@ __device__ __forceinline__ void wide_reduce_finish(const ReduceArgs& r, ReduceEl
   if (!(r.apply_adam || peers)) return;
   if (e.p < r.d.P) wide_store_planes(r.d, r.w2p, r.bias2, e.p, wide_adam_apply(r.u, *r.coef, e.p, e.s));
   else wide_loss_log(r.u, e.p - r.d.P, e.s);
+}
+
+// ---- k_wide_reduce's own paths (one wave of 128-thread blocks; the fused GEMM tail keeps wide_reduce_body) ----------
+
+// Two finished W2 elements of one thread: every load of both is in flight before the first dependent instruction, and
+// both exchange slots are pushed before either is awaited.
+__device__ __forceinline__ void wide_reduce_finish2(const ReduceArgs& r, int p0, int p1, float s0, float s1) {
+  if (!r.first_chunk) {
+    const float g0 = r.u.grads[p0], g1 = r.u.grads[p1];
+    s0 += g0; s1 += g1;
+  }
+  r.u.grads[p0] = s0;
+  r.u.grads[p1] = s1;
+  if (!r.last_chunk) return;
+  const bool peers = r.u.px.world > 1;
+  if (peers) {
+    px_push(r.u.px, p0, s0);
+    px_push(r.u.px, p1, s1);
+    s0 = px_pull(r.u.px, p0);
+    s1 = px_pull(r.u.px, p1);
+  }
+  if (!(r.apply_adam || peers)) return;
+  const AdamCoef c = *r.coef;
+  float m0 = r.u.adam_m[p0], m1 = r.u.adam_m[p1], v0 = r.u.adam_v[p0], v1 = r.u.adam_v[p1];
+  const float w0 = r.u.params[p0], w1 = r.u.params[p1];
+  const float n0 = wide_adam_math(c, s0, m0, v0, w0), n1 = wide_adam_math(c, s1, m1, v1, w1);
+  r.u.adam_m[p0] = m0; r.u.adam_m[p1] = m1;
+  r.u.adam_v[p0] = v0; r.u.adam_v[p1] = v1;
+  r.u.params[p0] = n0; r.u.params[p1] = n1;
+  wide_store_planes(r.d, r.w2p, r.bias2, p0, n0);
+  wide_store_planes(r.d, r.w2p, r.bias2, p1, n1);
+}
+
+constexpr int RED_THREADS = 128, RED_RG = 8, RED_COLS = 16, RED_INFLIGHT = 28;
+
+// Fixed-order sum of one column of `rows` partial rows (`stride` floats apart), coalesced: the block is 8 row groups x
+// 16 adjacent columns, so every half-warp reads 64 contiguous bytes of one row; a row group adds rows rg, rg + 8, ..
+// (28 loads in flight), the groups are folded in order through shared memory.  The total is returned to row group 0.
+__device__ __forceinline__ float wide_colsum(const float* __restrict__ src, bool live, int rows, int64_t stride,
+                                             float* red) {
+  const int rg = threadIdx.x / RED_COLS, cx = threadIdx.x % RED_COLS;
+  float s = 0.f;
+  for (int b0 = rg; b0 < rows; b0 += RED_RG * RED_INFLIGHT) {
+    float t[RED_INFLIGHT];
+#pragma unroll
+    for (int u = 0; u < RED_INFLIGHT; u++) {
+      const int b = b0 + RED_RG * u;
+      t[u] = (live && b < rows) ? src[(int64_t)b * stride] : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < RED_INFLIGHT; u++) s += t[u];
+  }
+  red[rg * RED_COLS + cx] = s;
+  __syncthreads();
+  float tot = 0.f;
+  if (rg == 0) {
+#pragma unroll
+    for (int j = 0; j < RED_RG; j++) tot += red[j * RED_COLS + cx];
+  }
+  return tot;
+}
+
+__host__ __device__ inline int wide_reduce_dw1_blocks(const NetDims& d) { return (2 * d.H1 * 8 + RED_COLS - 1) / RED_COLS; }
+__host__ __device__ inline int wide_reduce_head_blocks(const NetDims& d) { return 2 * ((2 * d.H2 + 3 + RED_COLS - 1) / RED_COLS); }
+
+// block sb of the small-parameter part: [0, dw1 blocks) the dW1aug partial rows of the dW2 kernel's CTAs,
+// then the head rows (dW3, db2, db3 and the three loss sums) of k_wide_head's blocks
+__device__ __forceinline__ void wide_reduce_small(const ReduceArgs& r, int sb, float* red) {
+  const NetDims d = r.d;
+  const int cx = threadIdx.x % RED_COLS;
+  const bool lead = threadIdx.x < RED_COLS;
+  const int dw1b = wide_reduce_dw1_blocks(d);
+  if (sb < dw1b) {
+    const int x = sb * RED_COLS + cx;                      // flat [g][k][8] index inside a partial row
+    const bool live = x < 2 * d.H1 * 8;
+    const float s = wide_colsum(r.part_dw1 + x, live, r.dw1_blocks, (int64_t)2 * d.H1 * 8, red);
+    const int c = x & 7, k = (x >> 3) % d.H1, g = x / (d.H1 * 8);
+    if (!lead || !live || c > S) return;
+    const int p = g * d.SIZE + (c < S ? d.oW1 + k * S + c : d.ob1 + k);
+    wide_reduce_finish(r, ReduceElem{true, p, p, s});
+    return;
+  }
+  const int ncol = 2 * d.H2 + 3;                           // [0,H2) dW3, [H2,2H2) db2, 2H2 db3, then the loss columns
+  const int bpg = (ncol + RED_COLS - 1) / RED_COLS;
+  const int hb = sb - dw1b, g = hb / bpg, col = (hb % bpg) * RED_COLS + cx;
+  if (g >= 2) return;                                      // (whole block: no barrier is skipped by part of a block)
+  const bool live = col < ncol;
+  const float s = wide_colsum(r.part_head + (int64_t)g * r.head_row + col, live, r.head_blocks, (int64_t)2 * r.head_row, red);
+  if (!lead || !live) return;
+  int p, slot;
+  if (col <= 2 * d.H2) {
+    p = g * d.SIZE + (col < d.H2 ? d.oW3 + col : (col < 2 * d.H2 ? d.ob2 + (col - d.H2) : d.ob3));
+    slot = p;
+  } else {
+    int l;                                                  // 0 loss1 sum (actor), 1 sum e^2 (critic), 2 clipped count (actor)
+    if (col == 2 * d.H2 + 1) l = g == 0 ? 0 : 1;
+    else if (g == 0) l = 2;
+    else return;
+    p = d.P + l; slot = r.pstride - 4 + l;
+  }
+  wide_reduce_finish(r, ReduceElem{true, p, slot, s});
 }
 
 }  // namespace

@@ -269,11 +269,32 @@ __global__ void __launch_bounds__(256, 3) k_wide_head(const WideArgs a) {
 
 // (dW1 / db1: the work of the former k_wide_dw1 kernel rides in extra warps of the dW2 GEMM, wide_gemm.cu dw1_worker)
 
+// Blocks [0, w2_blocks): W2 -- with the L2 having added the split-K partials already (ADDED), two elements per thread;
+// the rest: the small parameters and the loss sums, coalesced column sums (wide_reduce.cuh wide_reduce_small).
+// 834 blocks for 2 x 256 nets: one wave (the former warp-per-parameter layout needed 2,178 blocks = two waves at 56
+// registers, and its strided 4-byte reads cost 14 of the kernel's 19 us).
 template <bool ADDED>
-__global__ void __launch_bounds__(128) k_wide_reduce(const ReduceArgs r, int w2_blocks) {
+__global__ void __launch_bounds__(RED_THREADS) k_wide_reduce(const ReduceArgs r, int w2_blocks) {
+  __shared__ float red[RED_RG * RED_COLS];
   pdl_launch_dependents();
   pdl_wait();
-  wide_reduce_finish(r, wide_reduce_body<ADDED>(r, w2_blocks, (int)blockIdx.x, true));
+  const int vb = (int)blockIdx.x;
+  if (vb >= w2_blocks) {
+    wide_reduce_small(r, vb - w2_blocks, red);
+    return;
+  }
+  if (ADDED) {
+    const int w2n = r.d.H2 * r.d.H1;
+    const int i = (vb * RED_THREADS + (int)threadIdx.x) * 2;
+    if (i >= 2 * w2n) return;
+    float2* two = reinterpret_cast<float2*>(r.part_dw2 + i);   // [net][H2 * H1], already summed; zeroed for the next step's adds
+    const float2 s = *two;
+    *two = make_float2(0.f, 0.f);
+    auto pidx = [&](int j) { return (j / w2n) * r.d.SIZE + r.d.oW2 + (j % w2n); };
+    wide_reduce_finish2(r, pidx(i), pidx(i + 1), s.x, s.y);
+  } else {
+    wide_reduce_finish(r, wide_reduce_body<false>(r, w2_blocks, vb, true));
+  }
 }
 
 __global__ void __launch_bounds__(128) k_wide_adam(const UpdateArgs a, const NetDims d, int pstride, __nv_bfloat16* w2p,
@@ -640,10 +661,11 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
       return set_error(B2_ERR_CUDA, "wide gemm dW2: %s", cudaGetErrorString(ce));
     (*launches)++;
     if (fused_tail) continue;
-    const int w2_blocks = (2 * H2 * H1 + 127) / 128;
+    const int w2_blocks = w->dw2_add ? (2 * H2 * H1 + 2 * RED_THREADS - 1) / (2 * RED_THREADS) : (2 * H2 * H1 + RED_THREADS - 1) / RED_THREADS;
+    const int rgrid = w2_blocks + wide_reduce_dw1_blocks(d) + wide_reduce_head_blocks(d);
     if (!(skip & 32))
-    if ((ce = (w->dw2_add ? launch_pdl(k_wide_reduce<true>, dim3(w2_blocks + (small + 3) / 4), dim3(128), 0, st, r, w2_blocks)
-                          : launch_pdl(k_wide_reduce<false>, dim3(w2_blocks + (small + 3) / 4), dim3(128), 0, st, r, w2_blocks))) != cudaSuccess)
+    if ((ce = (w->dw2_add ? launch_pdl(k_wide_reduce<true>, dim3(rgrid), dim3(RED_THREADS), 0, st, r, w2_blocks)
+                          : launch_pdl(k_wide_reduce<false>, dim3(rgrid), dim3(RED_THREADS), 0, st, r, w2_blocks))) != cudaSuccess)
       return set_error(B2_ERR_CUDA, "wide reduce: %s", cudaGetErrorString(ce));
     (*launches)++;
   }
