@@ -130,8 +130,12 @@ __global__ void __launch_bounds__(256, 4) k_wide_l1(const WideArgs a) {
 // planes are written as contiguous vectors.  The critic is finished first (its V feeds the actor's advantage, :274), so
 // only one net's activations are live at a time; W3 / b2 sit in shared memory.  dW3, db2, db3 and the loss sums are
 // accumulated per lane over all samples of the block and written once, to this block's partial row.
+// A warp walks ~7 samples; the rows and scalars of its NEXT sample are fetched before the current one is worked on
+// (one exposed memory round trip per warp instead of two per sample), which is what the 128-register budget of
+// HEAD_CTAS = 2 blocks per SM pays for.
+constexpr int HEAD_CTAS = 2;
 template <int NJ>   // H2 / 32
-__global__ void __launch_bounds__(256, 3) k_wide_head(const WideArgs a) {
+__global__ void __launch_bounds__(256, HEAD_CTAS) k_wide_head(const WideArgs a) {
   extern __shared__ __align__(16) float hsm[];
   constexpr int H2 = NJ * 32;
   float* wsm = hsm;                  // [2 nets][2][H2]: W3, b2
@@ -154,9 +158,26 @@ __global__ void __launch_bounds__(256, 3) k_wide_head(const WideArgs a) {
   float loss1 = 0.f, loss2 = 0.f, clipped = 0.f;
   const int64_t plane = a.cap * H2;
 
+  // what a warp needs of one sample: both Z2 rows (this lane's NJ features) and the three trajectory scalars
+  struct Fetched { float2 z[2][NJ / 2]; float R, act, oldlp; };
+  auto fetch = [&](int s, Fetched& q) {
+    q.R = 0.f; q.act = 0.f; q.oldlp = 0.f;
+#pragma unroll
+    for (int g = 0; g < 2; g++)
+#pragma unroll
+      for (int i = 0; i < NJ / 2; i++) q.z[g][i] = make_float2(0.f, 0.f);
+    if (s >= a.count) return;                    // padding rows of the last tile: all-zero activations and deltas
+    const int64_t p = sample_pos(a, s);
+    q.R = a.tr.ret[p]; q.act = a.tr.action[p]; q.oldlp = a.tr.logp[p];
+#pragma unroll
+    for (int g = 0; g < 2; g++) {
+      const float2* zp = reinterpret_cast<const float2*>(a.h2 + ((int64_t)g * a.cap + s) * H2 + lane * NJ);
+#pragma unroll
+      for (int i = 0; i < NJ / 2; i++) q.z[g][i] = zp[i];
+    }
+  };
   // one net of one sample: activation, dot with W3 (returned warp-reduced), h left in registers
-  auto forward = [&](int g, int s, bool valid, float (&h)[NJ]) {
-    const float2* zp = reinterpret_cast<const float2*>(a.h2 + ((int64_t)g * a.cap + s) * H2 + lane * NJ);
+  auto forward = [&](int g, const float2 (&z)[NJ / 2], bool valid, float (&h)[NJ]) {
     const float* w3 = wsm + g * 2 * H2 + lane * NJ;
     const float* b2 = w3 + H2;
     float y = 0.f;
@@ -164,9 +185,8 @@ __global__ void __launch_bounds__(256, 3) k_wide_head(const WideArgs a) {
     for (int i = 0; i < NJ; i += 2) {
       float2 t = make_float2(0.f, 0.f);
       if (valid) {
-        t = zp[i >> 1];
-        t.x = act_tanh(t.x + b2[i]);
-        t.y = act_tanh(t.y + b2[i + 1]);
+        t.x = act_tanh(z[i >> 1].x + b2[i]);
+        t.y = act_tanh(z[i >> 1].y + b2[i + 1]);
       }
       h[i] = t.x; h[i + 1] = t.y;
       y = fmaf(w3[i], t.x, y);
@@ -202,21 +222,21 @@ __global__ void __launch_bounds__(256, 3) k_wide_head(const WideArgs a) {
     }
   };
 
-  for (int s = blockIdx.x * 8 + warp; s < a.m_pad; s += gridDim.x * 8) {
+  const int sstride = (int)gridDim.x * 8;
+  Fetched cur, nxt;
+  if ((int)blockIdx.x * 8 + warp < a.m_pad) fetch(blockIdx.x * 8 + warp, cur);
+  for (int s = blockIdx.x * 8 + warp; s < a.m_pad; s += sstride, cur = nxt) {
+    if (s + sstride < a.m_pad) fetch(s + sstride, nxt);   // in flight while this sample is worked on
     const bool valid = s < a.count;
-    float R = 0.f, act = 0.f, oldlp = 0.f;
-    if (valid) {
-      const int64_t p = sample_pos(a, s);
-      R = a.tr.ret[p]; act = a.tr.action[p]; oldlp = a.tr.logp[p];
-    }
+    const float R = cur.R, act = cur.act, oldlp = cur.oldlp;
     float h[NJ];
     // ---- critic: no final activation (ppo_nn.h:118-122)
-    const float V = forward(1, s, valid, h) + b3c;
+    const float V = forward(1, cur.z[1], valid, h) + b3c;
     const float e = V - R;
     const float dzc = valid ? e * a.inv_denom : 0.f;                 // d(0.5 mean e^2)/dV  (:288)
     backward(1, s, dzc, h);
     // ---- actor
-    const float mu = act_tanh(forward(0, s, valid, h) + b3a);        // ppo_nn.h:102
+    const float mu = act_tanh(forward(0, cur.z[0], valid, h) + b3a);   // ppo_nn.h:102
     float dza = 0.f;
     if (valid) {
       const float lp = gauss_logprob(act, mu, a.hp.inv_var, a.hp.half_log_norm);  // :140
@@ -489,7 +509,7 @@ int wide_create(WideNet** out, int H1, int H2, int64_t max_chunk, int sm_count) 
   // stale bits must never be NaN where a zero-weighted product could meet them
   WCK(cudaMemset(w->h1p, 0, bf * 4 * cap * H1));
   WCK(cudaMemset(w->d2p, 0, bf * 4 * cap * H2));
-  w->head_blocks = 3 * sm_count;
+  w->head_blocks = HEAD_CTAS * sm_count;
   w->head_row = 2 * H2 + 4;
   w->dw1_blocks = sm_count;
   w->splits_max = sm_count;
