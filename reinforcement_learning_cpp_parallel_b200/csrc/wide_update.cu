@@ -68,60 +68,68 @@ __global__ void __launch_bounds__(256) k_wide_prep(const WideArgs a) {
     a.bias2[i] = a.params[(i / H2) * a.d.SIZE + a.d.ob2 + (i % H2)];
 }
 
-// layer 1: H1 = tanh(W1 x + b1) -> (hi, mid) bf16 planes, sample-major.  A block walks a tile of 128 samples; a thread
-// owns 8 consecutive features (their 56 weights stay in registers) and strides over the samples, so every store is a
-// 16-B vector and a warp writes 512 contiguous bytes of one row.  grid (m_pad / 128, 2 nets)
+// layer 1: H1 = tanh(W1 x + b1) -> (hi, mid) bf16 planes, sample-major.  grid (blocks, 2 nets); a block owns an equal
+// share of the m_pad rows of one net (balanced to a row: L1_CTAS resident blocks on every SM, one wave) and walks it in
+// tiles of 64 samples.  A thread owns 4 consecutive features -- their 24 weights and 4 biases live in registers for the
+// whole block, so the inner loop reads only the 6 observation values (a shared-memory broadcast) -- and strides over the
+// samples; a warp's stores are 256 contiguous bytes of one row per plane.
 constexpr int L1_TILE = 64;
-__global__ void __launch_bounds__(256, 4) k_wide_l1(const WideArgs a) {
+constexpr int L1_CTAS = 4;
+__global__ void __launch_bounds__(256, L1_CTAS) k_wide_l1(const WideArgs a) {
   __shared__ float xs[L1_TILE][S + 2];
-  __shared__ __align__(16) float ws[32 * 52];   // per feature group of 8: 48 weights (+4 pad: conflict-free LDS.128)
-  __shared__ __align__(16) float bs[256];       // b1
+  __shared__ __align__(16) float ws[64 * 28];   // per feature group of 4: 24 weights + 4 biases (28: conflict-free LDS.128)
   const int H1 = a.d.H1, g = blockIdx.y;
-  const int s0 = blockIdx.x * L1_TILE;
+  const int lo = (int)((int64_t)blockIdx.x * a.m_pad / gridDim.x), hi = (int)((int64_t)(blockIdx.x + 1) * a.m_pad / gridDim.x);
+  auto load_tile = [&](int r0) {
+    const int n = min(L1_TILE, hi - r0);
+    for (int i = threadIdx.x; i < n * S; i += blockDim.x) {
+      const int r = i / S, c = i % S;
+      xs[r][c] = (r0 + r < a.count) ? a.tr.obs[c * a.tr.cap + sample_pos(a, r0 + r)] : 0.0f;
+    }
+  };
   pdl_launch_dependents();
-  // the observations are constant during an update: fetch this block's tile while the previous step's reduce still runs
-  for (int i = threadIdx.x; i < L1_TILE * S; i += blockDim.x) {
-    const int s = i / S, c = i % S;
-    xs[s][c] = (s0 + s < a.count) ? a.tr.obs[c * a.tr.cap + sample_pos(a, s0 + s)] : 0.0f;
-  }
+  load_tile(lo);   // the observations are constant during an update: fetched while the previous step's reduce still runs
   pdl_wait();                                   // the weights come from the previous step's Adam
   if (blockIdx.x == 0 && g == 0 && threadIdx.x == 0 && a.bump_step) {   // one optimizer step
     const int64_t step = *a.bump_step + 1;
     *a.bump_step = step;
     *a.coef_out = adam_coef(a.hp, step);   // two fp64 pow() on one thread here instead of a barrier in every reduce block
   }
-  for (int i = threadIdx.x; i < H1 * S; i += blockDim.x) ws[(i / 48) * 52 + (i % 48)] = a.params[g * a.d.SIZE + a.d.oW1 + i];
-  for (int i = threadIdx.x; i < H1; i += blockDim.x) bs[i] = a.params[g * a.d.SIZE + a.d.ob1 + i];
+  for (int i = threadIdx.x; i < H1 * S; i += blockDim.x) ws[(i / 24) * 28 + (i % 24)] = a.params[g * a.d.SIZE + a.d.oW1 + i];
+  for (int i = threadIdx.x; i < H1; i += blockDim.x) ws[(i / 4) * 28 + 24 + (i % 4)] = a.params[g * a.d.SIZE + a.d.ob1 + i];
   __syncthreads();
   const int64_t plane = a.cap * H1;
-  const int groups = H1 / 8;                    // feature groups of 8
+  const int groups = H1 / 4;                    // feature groups of 4
   const int kg = threadIdx.x % groups, sl = threadIdx.x / groups, sstep = blockDim.x / groups;
-  if (sl >= sstep) return;                      // H1 = 192: 24 groups, 10 sample lanes, 16 idle threads
-  const float* wg = ws + kg * 52;
-  for (int s = sl; s < L1_TILE; s += sstep) {
-    const bool valid = s0 + s < a.count;
-    __align__(16) __nv_bfloat16 th[8], tm[8];
-    float x[S];
+  const bool worker = sl < sstep;               // H1 = 192: 48 groups, 5 sample lanes, 16 idle threads
+  float w[24], b[4];
 #pragma unroll
-    for (int c = 0; c < S; c++) x[c] = xs[s][c];
+  for (int v = 0; v < 6; v++) *reinterpret_cast<float4*>(&w[4 * v]) = *reinterpret_cast<const float4*>(ws + kg * 28 + 4 * v);
+  *reinterpret_cast<float4*>(b) = *reinterpret_cast<const float4*>(ws + kg * 28 + 24);
+  for (int r0 = lo; r0 < hi; r0 += L1_TILE) {
+    if (r0 != lo) {
+      __syncthreads();                          // the previous tile's readers are done
+      load_tile(r0);
+      __syncthreads();
+    }
+    const int n = min(L1_TILE, hi - r0);
+    for (int r = sl; worker && r < n; r += sstep) {
+      const bool valid = r0 + r < a.count;
+      __align__(8) __nv_bfloat16 th[4], tm[4];
+      float x[S];
 #pragma unroll
-    for (int u4 = 0; u4 < 2; u4++) {             // 4 features at a time: 24 weights = 6 LDS.128
-      float w[24];
-#pragma unroll
-      for (int v = 0; v < 6; v++) *reinterpret_cast<float4*>(&w[4 * v]) = *reinterpret_cast<const float4*>(wg + u4 * 24 + 4 * v);
-      const float4 b4 = *reinterpret_cast<const float4*>(bs + kg * 8 + u4 * 4);
-      const float b[4] = {b4.x, b4.y, b4.z, b4.w};
+      for (int c = 0; c < S; c++) x[c] = xs[r][c];
 #pragma unroll
       for (int u = 0; u < 4; u++) {
         float z = b[u];
 #pragma unroll
         for (int c = 0; c < S; c++) z = fmaf(w[u * S + c], x[c], z);
-        tc::split_bf16(valid ? act_tanh(z) : 0.0f, th[u4 * 4 + u], tm[u4 * 4 + u]);
+        tc::split_bf16(valid ? act_tanh(z) : 0.0f, th[u], tm[u]);
       }
+      const int64_t o = (int64_t)(r0 + r) * H1 + kg * 4;
+      *reinterpret_cast<uint2*>(a.h1p + (g * 2 + 0) * plane + o) = *reinterpret_cast<const uint2*>(th);
+      *reinterpret_cast<uint2*>(a.h1p + (g * 2 + 1) * plane + o) = *reinterpret_cast<const uint2*>(tm);
     }
-    const int64_t o = (int64_t)(s0 + s) * H1 + kg * 8;
-    *reinterpret_cast<uint4*>(a.h1p + (g * 2 + 0) * plane + o) = *reinterpret_cast<const uint4*>(th);
-    *reinterpret_cast<uint4*>(a.h1p + (g * 2 + 1) * plane + o) = *reinterpret_cast<const uint4*>(tm);
   }
 }
 
@@ -589,8 +597,9 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     wa.coef_out = w->coef;
     const int m_tiles = wa.m_pad / 128;
     // layer 1
+    const int l1_grid = std::max(1, std::min(w->sm_count * L1_CTAS / 2, wa.m_pad / 16));
     if (!(skip & 1))
-    if ((ce = launch_pdl(k_wide_l1, dim3(wa.m_pad / L1_TILE, 2), dim3(256), 0, st, wa)) != cudaSuccess)
+    if ((ce = launch_pdl(k_wide_l1, dim3(l1_grid, 2), dim3(256), 0, st, wa)) != cudaSuccess)
       return set_error(B2_ERR_CUDA, "wide l1: %s", cudaGetErrorString(ce));
     (*launches)++;
     // H2 = tanh(H1 W2^T + b2)
