@@ -121,16 +121,26 @@ __device__ __forceinline__ void px_push(const PeerXchg& x, int i, float v) {
 }
 __device__ __forceinline__ float px_pull(const PeerXchg& x, int i) {
   const uint2* base = x.slots[x.rank] + x.par_off + i;
+  // every rank's slot is read at once (one L2 round trip when the peers are ahead, not `world` of them); a slot whose
+  // tag is not this step's yet is re-read until it is
+  unsigned val[B2_MAX_PEERS], tag[B2_MAX_PEERS];
+#pragma unroll
+  for (int r = 0; r < B2_MAX_PEERS; r++) {
+    val[r] = 0u; tag[r] = x.epoch;
+    if (r < x.world)
+      asm volatile("ld.relaxed.sys.global.v2.b32 {%0, %1}, [%2];" : "=r"(val[r]), "=r"(tag[r]) : "l"(base + (int64_t)r * x.pstride) : "memory");
+  }
+  long long spins = 0;
   float s = 0.f;
-  for (int r = 0; r < x.world; r++) {
-    unsigned val, tag;
-    long long spins = 0;
-    while (true) {
-      asm volatile("ld.relaxed.sys.global.v2.b32 {%0, %1}, [%2];" : "=r"(val), "=r"(tag) : "l"(base + (int64_t)r * x.pstride) : "memory");
-      if (tag == x.epoch) break;
-      if (++spins > (1ll << 26)) { atomicOr(x.status, 2); break; }   // ~2 s: surface a lost peer instead of hanging the GPU
+#pragma unroll
+  for (int r = 0; r < B2_MAX_PEERS; r++) {
+    if (r < x.world) {
+      while (tag[r] != x.epoch) {
+        if (++spins > (1ll << 26)) { atomicOr(x.status, 2); break; }   // ~2 s: surface a lost peer instead of hanging the GPU
+        asm volatile("ld.relaxed.sys.global.v2.b32 {%0, %1}, [%2];" : "=r"(val[r]), "=r"(tag[r]) : "l"(base + (int64_t)r * x.pstride) : "memory");
+      }
+      s = r == 0 ? __uint_as_float(val[r]) : __fadd_rn(s, __uint_as_float(val[r]));
     }
-    s = r == 0 ? __uint_as_float(val) : __fadd_rn(s, __uint_as_float(val));
   }
   x.out[i] = s;
   return s;
