@@ -21,6 +21,7 @@
 #include <stdlib.h>
 
 #include <algorithm>
+#include <type_traits>
 #include <vector>
 
 #include "tc_ptx.cuh"
@@ -93,26 +94,29 @@ __device__ __forceinline__ void dw1_worker(const Dw1Args& w, float* sm, int t) {
       }
       asm volatile("bar.sync 1, %0;" ::"n"(DW1_THREADS) : "memory");
       if (k < w.H1 && nt > 0) {
+        // batches of 16 loads in flight, then 8 / 4 / 2 / 1 for the remainder: an L2 round trip is ~2,000 cycles beside
+        // the GEMM's operand stream, and a one-sample-at-a-time tail (8 of them for 56 samples) made these warps outlast
+        // the GEMM by 5 us per step (clock64 stamps: 49k cycles against the epilogue's 40k).  Same order of adds.
         const float* dp = w.z1 + ((int64_t)g * w.cap + t0) * w.H1 + k;
-        int s = 0;
-        for (; s + 16 <= nt; s += 16) {
-          float dv[16];
+        auto batch = [&](auto bc, int s) {
+          constexpr int B = decltype(bc)::value;
+          float dv[B];
 #pragma unroll
-          for (int u = 0; u < 16; u++) dv[u] = dp[(int64_t)(s + u) * w.H1];
+          for (int u = 0; u < B; u++) dv[u] = dp[(int64_t)(s + u) * w.H1];
 #pragma unroll
-          for (int u = 0; u < 16; u++) {
+          for (int u = 0; u < B; u++) {
             dv[u] = d1_of(dv[u], xs + (s + u) * 8);
 #pragma unroll
             for (int c = 0; c < OBS; c++) acc[c] = fmaf(dv[u], xs[(s + u) * 8 + c], acc[c]);
             acc[OBS] += dv[u];
           }
-        }
-        for (; s < nt; s++) {
-          const float dv = d1_of(dp[(int64_t)s * w.H1], xs + s * 8);
-#pragma unroll
-          for (int c = 0; c < OBS; c++) acc[c] = fmaf(dv, xs[s * 8 + c], acc[c]);
-          acc[OBS] += dv;
-        }
+        };
+        int s = 0;
+        for (; s + 16 <= nt; s += 16) batch(std::integral_constant<int, 16>{}, s);
+        if (s + 8 <= nt) { batch(std::integral_constant<int, 8>{}, s); s += 8; }
+        if (s + 4 <= nt) { batch(std::integral_constant<int, 4>{}, s); s += 4; }
+        if (s + 2 <= nt) { batch(std::integral_constant<int, 2>{}, s); s += 2; }
+        if (s < nt) batch(std::integral_constant<int, 1>{}, s);
       }
     }
     asm volatile("bar.sync 1, %0;" ::"n"(DW1_THREADS) : "memory");
