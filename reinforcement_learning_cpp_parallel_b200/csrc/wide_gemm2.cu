@@ -55,7 +55,7 @@ k_gemm2_ws(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
   uint64_t* tfull = empty + 4;
   uint64_t* tempty = tfull + 2;
   uint64_t* bfull = tempty + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bfull + 1);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bfull + 4);   // bfull[kb]: one barrier per K block of the weights (K <= 256)
 
   // schedule: the pairs are split evenly between the G groups; a pair walks the 256-row tiles of its group
   const int n_pairs = gridDim.x / 2, pair = blockIdx.x / 2;
@@ -69,7 +69,7 @@ k_gemm2_ws(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
     tc::tma_prefetch_desc(&tmC);
     for (int s = 0; s < stages; s++) { tc::mbar_init(&full[s], 1); tc::mbar_init(&empty[s], 1); }
     for (int b = 0; b < 2; b++) { tc::mbar_init(&tfull[b], 1); tc::mbar_init(&tempty[b], 512); }
-    tc::mbar_init(bfull, 1);
+    for (int kb = 0; kb < 4; kb++) tc::mbar_init(&bfull[kb], 1);
     tc::fence_barrier_init();
   }
   pdl_launch_dependents();
@@ -82,23 +82,27 @@ k_gemm2_ws(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
 
   if (warp == 0) {
     if (lane == 0) {
-      // ---- resident weights: this CTA's N/2 rows (or columns), every K block, hi and mid
-      if (rank == 0) tc::mbar_arrive_expect_tx(bfull, (uint32_t)(2 * B_BYTES));
-      for (int kb = 0; kb < KB; kb++)
+      // ---- resident weights: this CTA's N/2 rows (or columns), hi and mid, one barrier per K block, issued in front of
+      // the first tile's A stage of the same K block: the first MMA waits for a quarter of the weights, not all 128 KB
+      auto load_weights = [&](int kb) {
+        if (rank == 0) tc::mbar_arrive_expect_tx(&bfull[kb], (uint32_t)(4 * B_KBLOCK));   // 2 planes x 2 CTAs
         for (int pl = 0; pl < 2; pl++) {
           uint8_t* dst = sB + (size_t)(kb * 2 + pl) * B_KBLOCK;
           if (BMN) {
             for (int fb = 0; fb < NH / 64; fb++)
-              tc::tma_load_3d_2sm(dst + fb * (BK * 128), &tmB, bfull, (int)rank * NH + fb * 64, kb * BK, g * 2 + pl);
+              tc::tma_load_3d_2sm(dst + fb * (BK * 128), &tmB, &bfull[kb], (int)rank * NH + fb * 64, kb * BK, g * 2 + pl);
           } else {
-            tc::tma_load_3d_2sm(dst, &tmB, bfull, kb * BK, (int)rank * NH, g * 2 + pl);
+            tc::tma_load_3d_2sm(dst, &tmB, &bfull[kb], kb * BK, (int)rank * NH, g * 2 + pl);
           }
         }
+      };
       // ---- A: this CTA's 128 rows of every tile of the pair
       int stage = 0; uint32_t phase = 0;
-      for (int t = p_local; t < tiles; t += ppg) {
+      bool first_tile = true;
+      for (int t = p_local; t < tiles; t += ppg, first_tile = false) {
         const int row0 = t * 2 * BM + (int)rank * BM;
         for (int kb = 0; kb < KB; kb++) {
+          if (first_tile) load_weights(kb);
           tc::mbar_wait(&empty[stage], phase ^ 1);
           if (rank == 0) tc::mbar_arrive_expect_tx(&full[stage], (uint32_t)(2 * A_STAGE));
           uint8_t* s = sA + (size_t)stage * A_STAGE;
@@ -111,8 +115,6 @@ k_gemm2_ws(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
   } else if (warp == 1) {
     if (lane == 0 && rank == 0) {
       const uint32_t idesc = tc::idesc_bf16_f32(2 * BM, N) | (BMN ? (1u << 16) : 0u);
-      tc::mbar_wait(bfull, 0);
-      tc::tc_fence_after();
       int stage = 0; uint32_t phase = 0;
       int it = 0;
       for (int t = p_local; t < tiles; t += ppg, it++) {
@@ -123,6 +125,7 @@ k_gemm2_ws(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
         const uint32_t d_tmem = tmem_base + (uint32_t)buf * 256u;
         uint32_t acc = 0;
         for (int kb = 0; kb < KB; kb++) {
+          if (it == 0) tc::mbar_wait(&bfull[kb], 0);         // this K block of the resident weights has landed
           tc::mbar_wait(&full[stage], phase);
           tc::tc_fence_after();
           const uint32_t sa = tc::smem_u32(sA + (size_t)stage * A_STAGE);
