@@ -124,9 +124,10 @@ class ClockSampler:
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.rows, self.p = index, [], None
+        self.index, self.rows, self.p, self.t0 = index, [], None, None
 
     def start(self):
+        """Started before the warm-up: nvidia-smi needs ~0.3 s before its first row, longer than a short timed region."""
         try:
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
                                        "--format=csv,noheader,nounits", "-lms", "20"],
@@ -137,19 +138,30 @@ class ClockSampler:
 
     def _read(self):
         for line in self.p.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            self.rows.append((time.time(), [x.strip() for x in line.split(",")]))
+
+    def mark(self):
+        """The timed region starts here: only rows sampled from now until stop() are reported."""
+        self.t0 = time.time()
 
     def stop(self):
+        t1 = time.time()
         if self.p:
             self.p.terminate()
-        sm = sorted(int(float(r[0])) for r in self.rows if r and r[0].replace(".", "").isdigit())
-        mx = [int(float(r[1])) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        t0 = self.t0 if self.t0 is not None else 0.0
+        rows = [r for t, r in self.rows if t0 <= t <= t1]
+        window = "timed region"
+        if not rows:   # a region shorter than one sampling period: the same workload's warm-up steps just before it
+            rows = [r for t, r in self.rows if t <= t1][-8:]
+            window = "warm-up steps before the timed region (region shorter than one sample)"
+        sm = sorted(int(float(r[0])) for r in rows if r and r[0].replace(".", "").isdigit())
+        mx = [int(float(r[1])) for r in rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
+        reasons = sorted({names[i] for r in rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
         # the kernel keeps the SMs busy for most samples; take the median of the upper half as "under load"
         load = sm[len(sm) // 2:] if sm else []
         return {"sm_mhz": (load[len(load) // 2] if load else None), "sm_max_mhz": (max(mx) if mx else None),
-                "reasons": reasons, "samples": len(sm)}
+                "reasons": reasons, "samples": len(sm), "window": window}
 
 
 def _ncu_traffic(key):
@@ -344,6 +356,9 @@ def main():
     bf16_src = ("MEASURED_PEAKS.json bf16_tflops_sustained" if "bf16_tflops_sustained" in peaks else
                 "fallback 1590 TFLOP/s (B200_PROFILING.md)")
 
+    cs = ClockSampler(local)
+    if rank == 0:
+        cs.start()
     # ---------------- warm-up ----------------
     for _ in range(max(args.warmup, 3)):
         E.rollout(T)
@@ -354,12 +369,10 @@ def main():
     # ---------------- timed: rollout leg and update leg, K steps ----------------
     # inputs: the 344 MB trajectory buffer written by each rollout is larger than the 126 MB L2, and the
     # update streams the whole buffer every epoch -> no explicit flush needed ("inputs larger than L2").
-    cs = ClockSampler(local)
-    if rank == 0:
-        cs.start()
     l0 = E.kernel_launches()
     roll_ms, upd_ms = [], []
     barrier()
+    cs.mark()
     t_wall0 = time.time()
     for _ in range(args.steps):
         E.timer_start()
