@@ -162,6 +162,33 @@ def test_wide_update_chunked_and_minibatched():
         assert H.relerr(E.get_params(), p) < 1e-5
 
 
+@pytest.mark.parametrize("env", [{"B2_WIDE_DETERMINISTIC": "1"}, {"B2_WIDE_FUSE_REDUCE": "1"}, {"B2_WIDE_FUSE_M": "1"}],
+                         ids=["deterministic", "fused_reduce_tail", "fuse_m"])
+def test_wide_update_opt_in_modes_match_oracle(env, monkeypatch):
+    """the opt-in variants of the step (read from the environment when the engine is created / the step is launched) are
+    held to the same oracle gates as the default; the fixed-order mode must also be bit-identical run to run"""
+    H1, H2, B, K = 256, 256, 1000, 3
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    dims = H.Dims(6, H1, H2, 1)
+    params, obs, act, oldlp, reward, flags = synth_batch(dims, B, 4242)
+    z = np.zeros_like(params)
+    po, mo, vo, so, losses, go, Ro = H.oracle_update(params, z, z, 0, obs, act, oldlp, reward, flags, K, dims=dims)
+    runs = []
+    for _ in range(2):
+        with wide_engine(H1, H2, k_epochs=K) as E:
+            E.set_params(params)
+            E.update(obs, act, oldlp, reward, flags)
+            p = E.get_params()
+            m, v, step = E.get_adam_state()
+            assert step == so == K
+            assert H.relerr(E.get_grads(), go) < 1e-4
+            assert H.relerr(p, po) < 1e-5 and H.relerr(m, mo) < 1e-4 and H.relerr(v, vo) < 2e-4
+            runs.append(p.copy())
+    if "B2_WIDE_DETERMINISTIC" in env:
+        assert np.array_equal(runs[0], runs[1])
+
+
 def test_wide_rollout_is_refused_loudly():
     from reinforcement_learning_cpp_parallel_b200 import capi
     with wide_engine(256, 256) as E:
