@@ -1,7 +1,11 @@
 // wide_reduce.cuh -- the last stage of a wide-net optimizer step: fixed-order sums of the partial rows, the multi-GPU
-// gradient exchange, Adam (libtorch operation order) and the refresh of the bf16 weight planes.  Device code shared by
-// k_wide_reduce (wide_update.cu) and the tail of the dW2 GEMM kernel (wide_gemm.cu), which runs the same work behind a
-// grid barrier so that the step needs one launch less.
+// gradient exchange, Adam (libtorch operation order) and the refresh of the bf16 weight planes.
+//   k_wide_reduce (wide_update.cu): wide_reduce_small (coalesced column sums of the dW1 / head partial rows) +
+//     wide_reduce_finish2 (W2, two elements per thread) -- one wave of 128-thread blocks; the fixed-order dW2 mode
+//     (B2_WIDE_DETERMINISTIC=1) takes its W2 blocks from wide_reduce_body<false>.
+//   tail of the dW2 GEMM kernel (wide_gemm.cu, opt-in B2_WIDE_FUSE_REDUCE=1): wide_reduce_body<true> over virtual
+//     blocks behind a grid barrier, one launch less (measured slower, kept measurable).
+// Both end in wide_reduce_finish: chunk accumulation, exchange, Adam, planes.
 #pragma once
 #include "tc_ptx.cuh"
 #include "wide.h"
