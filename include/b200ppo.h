@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define B2_ABI_VERSION 1
+#define B2_ABI_VERSION 2   /* 2: b2_config.gae_lambda takes the first 8 bytes of the former reserved[6] (same size) */
 
 typedef enum {
   B2_OK = 0,
@@ -79,7 +79,9 @@ typedef struct {
   uint64_t env_offset;    /* global id of local env 0: same global seed => same trajectories for any sharding */
   int device;             /* CUDA ordinal */
   int env_flags;          /* B2_ENV_* (0 = the shipped environment) */
-  int reserved[6];
+  double gae_lambda;      /* lambda-returns R_k = r_k + gamma ((1 - lambda) V(s_{k+1}) + lambda R_{k+1}) between flagged records;
+                             1 (and 0 = unset) = the reference's plain discounted returns (src/ppo_nn.cpp:231) */
+  int reserved[4];
 } b2_config;
 
 /* One trajectory batch in host memory: what MemoryNN holds (include/ppo_nn.h:20-29).
@@ -131,7 +133,9 @@ int b2_get_params(b2_handle h, float* p, int64_t n);
 int b2_set_adam_state(b2_handle h, const float* m, const float* v, int64_t n, int64_t step);
 int b2_get_adam_state(b2_handle h, float* m, float* v, int64_t n, int64_t* step);
 int b2_get_grads(b2_handle h, float* g, int64_t n);          /* gradient of the last optimizer step (after all-reduce) */
-int b2_save_checkpoint(b2_handle h, const char* path);       /* params + Adam m, v, step */
+/* params + Adam m, v, step + the Philox counters (rollout step, act / reset calls) + env state, so that a resumed run
+ * CONTINUES the noise stream and the episodes of the run that saved (env block restored when n_envs matches) */
+int b2_save_checkpoint(b2_handle h, const char* path);
 int b2_load_checkpoint(b2_handle h, const char* path);
 
 /* ---- action query: replaces getAction -> PPO::select_action -> ActorCritic::act

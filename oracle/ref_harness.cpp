@@ -282,6 +282,13 @@ void env_kat(const std::string& dir) {
   for (int i = 0; i < 300; i++) { s = s * 6364136223846793005ull + 1442695040888963407ull;
     f.push_back(((double)(s >> 11) / 9007199254740992.0) * 30.0 - 15.0); }
   run("kat_c", f);
+  // forces the reference does not clip (src/main.cpp:57-60; `bounded` unused :17): square waves strong enough that
+  // |thetadot| crosses 16 rad/s repeatedly, the range where the CUDA engine leaves its carried-rotation stage for the
+  // reference-shaped substep (csrc/cartpole.cuh kOmegaFast)
+  std::vector<double> fa, fb;
+  for (int i = 0; i < 100; i++) { fa.push_back(((i / 4) % 2 == 0) ? 150.0 : -150.0); fb.push_back(((i / 10) % 2 == 0) ? 40.0 : -40.0); }
+  run("kat_fast_a", fa);
+  run("kat_fast_b", fb);
 }
 
 int cmd_golden(const std::string& dir) {

@@ -32,7 +32,7 @@ class Config(C.Structure):
                 ("k_epochs", C.c_int), ("hidden1", C.c_int), ("hidden2", C.c_int),
                 ("n_envs", C.c_int64), ("horizon", C.c_int), ("n_minibatches", C.c_int),
                 ("precision", C.c_int), ("seed", C.c_uint64), ("env_offset", C.c_uint64),
-                ("device", C.c_int), ("env_flags", C.c_int), ("reserved", C.c_int * 6)]
+                ("device", C.c_int), ("env_flags", C.c_int), ("gae_lambda", C.c_double), ("reserved", C.c_int * 4)]
 
 
 class Batch(C.Structure):

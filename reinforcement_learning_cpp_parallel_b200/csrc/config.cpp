@@ -45,6 +45,7 @@ extern "C" int b2_config_default(b2_config* c) {
   c->seed = 0x5EED;
   c->env_offset = 0;
   c->device = 0;
+  c->gae_lambda = 1.0;  // plain discounted returns (src/ppo_nn.cpp:231)
   return B2_OK;
 }
 

@@ -32,7 +32,7 @@ struct NcclApi {
   int (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
   const char* (*GetErrorString)(int) = nullptr;
 };
-enum { NCCL_UINT8 = 1 };
+enum { NCCL_UINT8 = 1, NCCL_INT64 = 4 };
 static NcclApi g_nccl;
 
 namespace b2 {
@@ -110,6 +110,11 @@ struct b2_engine {
   int64_t stage_u8_n = 0;
   int* status = nullptr;
   int* status_host = nullptr;  // pinned
+  // scratch of the segment-per-warp returns path (returns.cu): segment-end record indices + their count
+  int64_t* seg_ends = nullptr;
+  int64_t seg_cap = 0;
+  unsigned long long* seg_count = nullptr;
+  int64_t* denom_dev = nullptr;   // [2] global sample counts of a regular / the last minibatch (all-reduced over ranks)
   uint64_t act_calls = 0;
   int64_t launches = 0;
   float* flush_buf = nullptr;
@@ -145,6 +150,7 @@ void make_hyper(b2_engine* E) {
   const float v1 = (float)pow(2 * M_PI * M_E, 1);                // :56 (Q8: (2 pi e)^k, not its log)
   h.loss3 = (float)(-0.01 * (double)(0.5f * (logf(var) + v1)));  // :64, :289
   h.gamma = (float)c.gamma;
+  h.gae_lambda = c.gae_lambda > 0 ? (float)c.gae_lambda : 1.0f;   // 0 = unset = the reference's plain returns
   h.clip_lo = (float)(1 - c.eps_clip);
   h.clip_hi = (float)(1 + c.eps_clip);
   h.lr = c.lr; h.beta1 = c.beta1; h.beta2 = c.beta2; h.eps = 1e-8;  // libtorch AdamOptions default eps
@@ -192,6 +198,11 @@ int ensure_stage(b2_engine* E, int64_t floats, int64_t bytes_u8) {
 int check_status(b2_engine* E, const char* where) {
   CK(cudaMemcpyAsync(E->status_host, E->status, sizeof(int), cudaMemcpyDeviceToHost, E->stream));
   CK(cudaStreamSynchronize(E->stream));
+  if (*E->status_host & 4) {   // rollout.cu: a hand-off wait of the persistent rollout kernel expired
+    cudaMemsetAsync(E->status, 0, sizeof(int), E->stream);
+    return set_error(B2_ERR_STATE, "%s: the rollout kernel's hand-off wait expired (its warps were not all resident: is another "
+                                   "stream or process holding SMs?); the trajectory of this rollout is incomplete", where);
+  }
   if (*E->status_host & 1) {
     cudaMemsetAsync(E->status, 0, sizeof(int), E->stream);
     return set_error(B2_ERR_NONFINITE, "%s: non-finite action on device (cf. src/main.cpp:50-55)", where);
@@ -202,11 +213,27 @@ int check_status(b2_engine* E, const char* where) {
 // K2 on whatever E->tr holds: bootstrap values at the flagged records, then the reverse scan.
 int run_returns(b2_engine* E) {
   int nl = 0;
+  const int64_t B = E->tr.n_envs * E->tr.horizon;
   if (E->wide) {
     int rc = wide_bootstrap(E->wide, E->params, E->tr, E->stream, &E->launches);
     if (rc) return rc;
+    if (E->hp.gae_lambda < 1.0f) {   // lambda-returns need V at every record, not only at the flagged ones
+      cudaError_t ce = launch_wide_forward(E->dims, E->params + E->dims.SIZE, E->tr.obs, E->tr.cap, 1, nullptr, B, 0, E->tr.vcur, E->stream);
+      if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "values: %s", cudaGetErrorString(ce));
+      E->launches += 1;
+    }
   }
-  cudaError_t ce = launch_returns(E->params, E->tr, E->hp, E->stream, &nl, E->wide != nullptr);
+  if (returns_needs_segment_list(E->tr)) {
+    if (!E->seg_count) CK(cudaMalloc(&E->seg_count, sizeof *E->seg_count));
+    if (B > E->seg_cap) {
+      cudaFree(E->seg_ends);
+      E->seg_ends = nullptr;
+      E->seg_cap = 0;
+      CK(cudaMalloc(&E->seg_ends, sizeof(int64_t) * (size_t)B));
+      E->seg_cap = B;
+    }
+  }
+  cudaError_t ce = launch_returns(E->params, E->tr, E->hp, E->stream, &nl, E->wide != nullptr, E->seg_ends, E->seg_count);
   if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "returns: %s", cudaGetErrorString(ce));
   E->launches += nl;
   return B2_OK;
@@ -243,6 +270,18 @@ int run_update(b2_engine* E, b2_update_stats* stats) {
     CK(cudaMalloc(&E->partials, sizeof(float) * (size_t)rows_needed * E->pstride));
     E->partial_rows = rows_needed;
   }
+  // The means are over the GLOBAL (mini)batch (src/ppo_nn.cpp:302: one mean over the merged memory).  Ranks may hold
+  // different numbers of samples (sharding.shard_envs hands the remainder to the low ranks), so the denominators are
+  // all-reduced: [0] a regular minibatch, [1] the last one (which takes the remainder of B / M).
+  int64_t denom_g[2] = {per, B - (int64_t)(M - 1) * per};
+  if (E->world > 1) {
+    if (!E->denom_dev) CK(cudaMalloc(&E->denom_dev, 2 * sizeof(int64_t)));
+    CK(cudaMemcpyAsync(E->denom_dev, denom_g, sizeof denom_g, cudaMemcpyHostToDevice, E->stream));
+    int ne = g_nccl.AllReduce(E->denom_dev, E->denom_dev, 2, NCCL_INT64, NCCL_SUM, E->comm, E->stream);
+    if (ne != 0) return set_error(B2_ERR_COMM, "ncclAllReduce(sample counts): %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(ne) : "?");
+    CK(cudaMemcpyAsync(denom_g, E->denom_dev, sizeof denom_g, cudaMemcpyDeviceToHost, E->stream));
+    CK(cudaStreamSynchronize(E->stream));
+  }
   UpdateArgs a{};
   a.params = E->params; a.adam_m = E->adam_m; a.adam_v = E->adam_v; a.grads = E->grads;
   a.partials = E->partials; a.adam_step = E->adam_step; a.loss_log = E->loss_log;
@@ -252,7 +291,7 @@ int run_update(b2_engine* E, b2_update_stats* stats) {
     for (int m = 0; m < M; m++, slot++) { // M == 1 is the reference (full batch, Q9)
       a.first = (int64_t)m * per;
       a.count = (m == M - 1) ? (B - a.first) : per;
-      a.denom = a.count * E->world;       // every rank holds an equal shard of the global minibatch
+      a.denom = denom_g[m == M - 1];      // samples of this minibatch over ALL ranks
       a.grid = update_grid_for(a.count, E->sm_count);
       a.step_slot = slot;
       // several GPUs: the reduce + Adam kernel exchanges every gradient element with its peers over NVLink peer memory
@@ -300,7 +339,15 @@ int run_update(b2_engine* E, b2_update_stats* stats) {
     int st = 0;
     CK(cudaMemcpyAsync(&st, E->status, sizeof(int), cudaMemcpyDeviceToHost, E->stream));
     CK(cudaStreamSynchronize(E->stream));
-    if (st & 2) return set_error(B2_ERR_COMM, "update: a peer never published its gradient (peer-memory exchange timed out)");
+    if (st & 2) {
+      // reported once: clear the bit so that the next update starts clean (the kernels of this one stopped pushing and
+      // applying as soon as it was raised, engine.h px_alive)
+      st &= ~2;
+      CK(cudaMemcpyAsync(E->status, &st, sizeof(int), cudaMemcpyHostToDevice, E->stream));
+      CK(cudaStreamSynchronize(E->stream));
+      return set_error(B2_ERR_COMM, "update: a peer never published its gradient (peer-memory exchange timed out); the update was "
+                                    "abandoned part-way, reload the parameters (b2_load_checkpoint / b2_set_params) before continuing");
+    }
   }
   if (!finite) return set_error(B2_ERR_NONFINITE, "update: non-finite loss");
   return B2_OK;
@@ -467,6 +514,8 @@ int b2_device_count(void) {
   return n;
 }
 
+static int create_body(b2_engine* E, const b2_config* cfg, bool is_default_net);
+
 int b2_create(const b2_config* cfg, b2_handle* out) {
   if (!cfg || !out) return set_error(B2_ERR_INVALID, "b2_create: null argument");
   *out = nullptr;
@@ -481,12 +530,21 @@ int b2_create(const b2_config* cfg, b2_handle* out) {
   if (cfg->env_flags && cfg->precision != B2_PREC_F64) return set_error(B2_ERR_INVALID, "env variants (env_flags 0x%x) run the double-precision physics only", cfg->env_flags);
   if (cfg->k_epochs < 1 || cfg->n_minibatches < 1) return set_error(B2_ERR_INVALID, "k_epochs and n_minibatches must be >= 1");
   if (!(cfg->action_std > 0)) return set_error(B2_ERR_INVALID, "action_std must be > 0");
+  if (!(cfg->gae_lambda >= 0.0 && cfg->gae_lambda <= 1.0)) return set_error(B2_ERR_INVALID, "gae_lambda must be in (0, 1] (0 = unset = 1, the reference's returns)");
   int ndev = b2_device_count();
   if (ndev <= 0) return set_error(B2_ERR_NO_DEVICE, "no CUDA device: this engine has no CPU path");
   if (cfg->device < 0 || cfg->device >= ndev) return set_error(B2_ERR_INVALID, "device %d out of range (%d visible)", cfg->device, ndev);
   CK(cudaSetDevice(cfg->device));
   b2_engine* E = new (std::nothrow) b2_engine();
   if (!E) return set_error(B2_ERR_INVALID, "out of host memory");
+  // any failure past this point releases the engine and everything it allocated so far (b2_destroy keeps the message)
+  const int rc = create_body(E, cfg, is_default_net);
+  if (rc) { b2_destroy(E); return rc; }
+  *out = E;
+  return B2_OK;
+}
+
+static int create_body(b2_engine* E, const b2_config* cfg, bool is_default_net) {
   E->cfg = *cfg;
   E->dims = NetDims::make(OBS, cfg->hidden1, cfg->hidden2);
   E->P = E->dims.P;
@@ -527,23 +585,20 @@ int b2_create(const b2_config* cfg, b2_handle* out) {
   CK(cudaMemset(E->state, 0, sizeof(double) * 4 * NE));   // CartPole::reset: u = 0 (cart_pole.h:86)
   if (cfg->env_flags & B2_ENV_RANDOM_INIT) {
     cudaError_t ce = launch_env_init(E->state, NE, cfg->env_flags, cfg->seed, cfg->env_offset, 0, E->stream);
-    if (ce != cudaSuccess) { b2_destroy(E); return set_error(B2_ERR_CUDA, "env init: %s", cudaGetErrorString(ce)); }
+    if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "env init: %s", cudaGetErrorString(ce));
     E->launches += 1;
   }
   CK(cudaMemset(E->ep_step, 0, sizeof(int32_t) * NE));
   CK(cudaMemset(E->ep_count, 0, sizeof(int32_t) * NE));
   CK(cudaMemset(E->ep_ret, 0, sizeof(float) * NE));
   int rc = ensure_traj(E, NE * cfg->horizon);
-  if (rc) { b2_destroy(E); return rc; }
+  if (rc) return rc;
   if (!is_default_net) {
     const int64_t B0 = NE * cfg->horizon;
     rc = wide_create(&E->wide, cfg->hidden1, cfg->hidden2, (B0 + cfg->n_minibatches - 1) / cfg->n_minibatches + cfg->n_minibatches, E->sm_count);
-    if (rc) { b2_destroy(E); return rc; }
+    if (rc) return rc;
   }
-  *out = E;
-  rc = b2_init_params(E, cfg->seed);
-  if (rc) { b2_destroy(E); *out = nullptr; return rc; }
-  return B2_OK;
+  return b2_init_params(E, cfg->seed);
 }
 
 int b2_destroy(b2_handle E) {
@@ -556,7 +611,7 @@ int b2_destroy(b2_handle E) {
   void* ptrs[] = {E->params, E->adam_m, E->adam_v, E->grads, E->partials, E->adam_step, E->loss_log, E->state,
                   E->ep_step, E->ep_count, E->ep_ret, E->ep_log, t.obs, t.action, t.logp, t.mu, t.reward, t.ret,
                   t.vboot, t.vcur, t.flags, t.state_trace, E->forced, E->stage, E->stage_u8, E->status, E->flush_buf,
-                  E->progress, E->env_term};
+                  E->progress, E->env_term, E->seg_ends, E->seg_count, E->denom_dev};
   for (void* p : ptrs) cudaFree(p);
   for (int r = 0; r < B2_MAX_PEERS; r++)
     if (r != E->rank && E->peer_base[r]) cudaIpcCloseMemHandle(E->peer_base[r]);
@@ -645,7 +700,11 @@ int b2_get_grads(b2_handle E, float* g, int64_t n) {
   return get_vec(E, g, E->grads);
 }
 
-// checkpoint: "B2CK" | version | P | step | params | m | v   (the reference has none)
+// checkpoint: "B2CK" | version | P | step | [v2: global_step, act_calls, reset_calls, n_envs, then env state u[n][4],
+// ep_step[n], ep_ret[n]] | params | m | v   (the reference has none).  Version 2 also carries the
+// Philox counters and the environment state, so that save -> load -> rollout continues the noise stream and the
+// episodes of the run that saved, instead of replaying its first iterations; version-1 files still load (weights and
+// Adam state only).  The env block is restored only into an engine with the same n_envs.
 int b2_save_checkpoint(b2_handle E, const char* path) {
   NEED(E);
   if (!path) return set_error(B2_ERR_INVALID, "null path");
@@ -656,8 +715,17 @@ int b2_save_checkpoint(b2_handle E, const char* path) {
   if ((rc = b2_get_adam_state(E, m.data(), v.data(), E->P_ext, &step))) return rc;
   FILE* f = fopen(path, "wb");
   if (!f) return set_error(B2_ERR_IO, "cannot open %s for writing", path);
-  int32_t hdr[2] = {1, E->P_ext};
+  int32_t hdr[2] = {2, E->P_ext};
+  const int64_t NE = E->cfg.n_envs;
+  std::vector<double> u((size_t)4 * NE);
+  std::vector<int32_t> es((size_t)NE);
+  std::vector<float> er((size_t)NE);
+  if ((rc = b2_env_get_state(E, u.data(), es.data(), NE))) { fclose(f); return rc; }
+  if (cudaMemcpy(er.data(), E->ep_ret, sizeof(float) * NE, cudaMemcpyDeviceToHost) != cudaSuccess) { fclose(f); return set_error(B2_ERR_CUDA, "checkpoint: ep_ret D2H"); }
+  const uint64_t ctr[4] = {E->global_step, E->act_calls, E->reset_calls, (uint64_t)NE};
   bool ok = fwrite("B2CK", 1, 4, f) == 4 && fwrite(hdr, sizeof hdr, 1, f) == 1 && fwrite(&step, sizeof step, 1, f) == 1 &&
+            fwrite(ctr, sizeof ctr, 1, f) == 1 && fwrite(u.data(), sizeof(double), u.size(), f) == u.size() &&
+            fwrite(es.data(), sizeof(int32_t), es.size(), f) == es.size() && fwrite(er.data(), sizeof(float), er.size(), f) == er.size() &&
             fwrite(p.data(), sizeof(float), E->P_ext, f) == (size_t)E->P_ext && fwrite(m.data(), sizeof(float), E->P_ext, f) == (size_t)E->P_ext &&
             fwrite(v.data(), sizeof(float), E->P_ext, f) == (size_t)E->P_ext;
   ok = (fclose(f) == 0) && ok;
@@ -673,14 +741,34 @@ int b2_load_checkpoint(b2_handle E, const char* path) {
   int64_t step = 0;
   std::vector<float> p(E->P_ext), m(E->P_ext), v(E->P_ext);
   bool ok = fread(magic, 1, 4, f) == 4 && memcmp(magic, "B2CK", 4) == 0 && fread(hdr, sizeof hdr, 1, f) == 1 &&
-            hdr[0] == 1 && hdr[1] == E->P_ext && fread(&step, sizeof step, 1, f) == 1 &&
-            fread(p.data(), sizeof(float), E->P_ext, f) == (size_t)E->P_ext && fread(m.data(), sizeof(float), E->P_ext, f) == (size_t)E->P_ext &&
+            (hdr[0] == 1 || hdr[0] == 2) && hdr[1] == E->P_ext && fread(&step, sizeof step, 1, f) == 1;
+  uint64_t ctr[4] = {0, 0, 0, 0};
+  std::vector<double> u;
+  std::vector<int32_t> es;
+  std::vector<float> er;
+  if (ok && hdr[0] == 2) {
+    ok = fread(ctr, sizeof ctr, 1, f) == 1 && ctr[3] >= 1 && ctr[3] <= (1ull << 40);
+    if (ok) {
+      u.resize((size_t)4 * ctr[3]); es.resize((size_t)ctr[3]); er.resize((size_t)ctr[3]);
+      ok = fread(u.data(), sizeof(double), u.size(), f) == u.size() && fread(es.data(), sizeof(int32_t), es.size(), f) == es.size() &&
+           fread(er.data(), sizeof(float), er.size(), f) == er.size();
+    }
+  }
+  ok = ok && fread(p.data(), sizeof(float), E->P_ext, f) == (size_t)E->P_ext && fread(m.data(), sizeof(float), E->P_ext, f) == (size_t)E->P_ext &&
             fread(v.data(), sizeof(float), E->P_ext, f) == (size_t)E->P_ext;
   fclose(f);
   if (!ok) return set_error(B2_ERR_IO, "%s is not a matching b200ppo checkpoint", path);
   int rc = b2_set_params(E, p.data(), E->P_ext);
   if (rc) return rc;
-  return b2_set_adam_state(E, m.data(), v.data(), E->P_ext, step);
+  if ((rc = b2_set_adam_state(E, m.data(), v.data(), E->P_ext, step))) return rc;
+  if (hdr[0] == 2) {
+    E->global_step = ctr[0]; E->act_calls = ctr[1]; E->reset_calls = ctr[2];
+    if ((int64_t)ctr[3] == E->cfg.n_envs) {
+      if ((rc = b2_env_set_state(E, u.data(), es.data(), E->cfg.n_envs))) return rc;
+      CK(cudaMemcpy(E->ep_ret, er.data(), sizeof(float) * er.size(), cudaMemcpyHostToDevice));
+    }
+  }
+  return B2_OK;
 }
 
 int b2_act(b2_handle E, const float* obs, int64_t n, const float* eps, float* action, float* logp, float* mu) {

@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
 #include <string>
 #include <vector>
 
@@ -12,6 +13,17 @@
 namespace b2 {
 
 int set_error(int code, const char* fmt, ...);
+
+// Function attributes (cudaFuncSetAttribute) and occupancy answers are PER DEVICE: a process may hold engines on several
+// GPUs (b2_config.device), so "already set" is remembered per call site AND per device ordinal, and safely across host
+// threads.  Usage:  static b2::PerDeviceOnce once;  if (once.need()) { ...set attributes...; once.done(); }
+struct PerDeviceOnce {
+  std::atomic<uint64_t> mask{0};
+  static int dev() { int d = 0; if (cudaGetDevice(&d) != cudaSuccess) d = 0; return d & 63; }
+  bool need() const { return !((mask.load(std::memory_order_acquire) >> dev()) & 1ull); }
+  void done() { mask.fetch_or(1ull << dev(), std::memory_order_release); }
+};
+
 
 // Device-resident trajectory buffer, SoA, flat index k = t * n_envs + e (time-major).
 //   obs[c * cap + k]  c < 6          24 B/record
@@ -37,6 +49,7 @@ struct Traj {
 struct HyperDev {       // passed by value to kernels
   float sigma, inv_var, half_log_norm, loss3;
   float gamma, clip_lo, clip_hi;
+  float gae_lambda;     // 1 = the reference's plain discounted returns (src/ppo_nn.cpp:231)
   double sigma_d;
   double lr, beta1, beta2, eps;
 };
@@ -67,8 +80,9 @@ struct RolloutArgs {
   int* progress;        // [ceil(n_envs/32)] steps of this rollout already published per env group (hand-off word)
 };
 
-// Gradient exchange over NVLink peer memory, fused into the reduce + Adam kernel (multi-GPU, one process per GPU; opt-in
-// alternative to reduce -> ncclAllReduce -> Adam, see DESIGN.md s5 for the measurements).  Flag-in-data protocol (what
+// Gradient exchange over NVLink peer memory, fused into the reduce + Adam kernel (multi-GPU, one process per GPU; the
+// DEFAULT whenever every rank can map every peer, B2_COMM_P2P=0 selects reduce -> ncclAllReduce -> Adam instead; see
+// DESIGN.md s5 for the measurements).  Flag-in-data protocol (what
 // NCCL calls LL): every rank owns, in memory its peers have mapped (cudaIpc),
 //     slots[2][world][pstride] of {value, epoch} pairs (8 bytes, written and read as ONE 8-byte access).
 // Step e (parity e & 1), every thread that finishes a gradient element i:
@@ -77,7 +91,11 @@ struct RolloutArgs {
 //   3. adds the values in RANK ORDER (identical sum on every rank: weights stay bit-identical without a broadcast) and
 //      applies Adam to element i.
 // A thread waits only for the SAME thread of its peers, which pushes before it waits, so there is no circular wait as
-// long as blocks are dispatched in index order; every wait is bounded (status bit 1 instead of a hung GPU).  Two parities
+// long as blocks are dispatched in index order; every wait is bounded (status bit 1 instead of a hung GPU): a thread whose
+// wait expires raises the bit and does NOT apply Adam to its element, and every later step of the update finds the bit
+// raised on entry (px_alive) and neither pushes nor applies, so its peers run into their own bounded waits and stop too;
+// the host then reports B2_ERR_COMM (the parameters of the handle are unspecified from then on: reload a checkpoint)
+// and clears the bit.  Two parities
 // are enough: a rank pushes step e+2 only after its step e+1 kernel ended, i.e. after every peer pushed e+1, i.e. after
 // every peer's step-e kernel -- the last reader of that parity -- ended.
 constexpr int B2_MAX_PEERS = 8;
@@ -119,7 +137,9 @@ __device__ __forceinline__ void px_push(const PeerXchg& x, int i, float v) {
     asm volatile("st.relaxed.sys.global.v2.b32 [%0], {%1, %2};" ::"l"(x.slots[r] + mine), "r"(__float_as_uint(v)), "r"(x.epoch)
                  : "memory");
 }
-__device__ __forceinline__ float px_pull(const PeerXchg& x, int i) {
+// false once any wait of this update has expired (on this rank): the rest of the update is abandoned
+__device__ __forceinline__ bool px_alive(const PeerXchg& x) { return !(*(volatile const int*)x.status & 2); }
+__device__ __forceinline__ float px_pull(const PeerXchg& x, int i, bool* ok) {
   const uint2* base = x.slots[x.rank] + x.par_off + i;
   // every rank's slot is read at once (one L2 round trip when the peers are ahead, not `world` of them); a slot whose
   // tag is not this step's yet is re-read until it is
@@ -136,7 +156,7 @@ __device__ __forceinline__ float px_pull(const PeerXchg& x, int i) {
   for (int r = 0; r < B2_MAX_PEERS; r++) {
     if (r < x.world) {
       while (tag[r] != x.epoch) {
-        if (++spins > (1ll << 26)) { atomicOr(x.status, 2); break; }   // ~2 s: surface a lost peer instead of hanging the GPU
+        if (++spins > (1ll << 26)) { atomicOr(x.status, 2); *ok = false; break; }   // ~2 s: surface a lost peer instead of hanging the GPU
         asm volatile("ld.relaxed.sys.global.v2.b32 {%0, %1}, [%2];" : "=r"(val[r]), "=r"(tag[r]) : "l"(base + (int64_t)r * x.pstride) : "memory");
       }
       s = r == 0 ? __uint_as_float(val[r]) : __fadd_rn(s, __uint_as_float(val[r]));
@@ -145,9 +165,11 @@ __device__ __forceinline__ float px_pull(const PeerXchg& x, int i) {
   x.out[i] = s;
   return s;
 }
-__device__ __forceinline__ float px_allreduce_elem(const PeerXchg& x, int i, float v) {
+__device__ __forceinline__ float px_allreduce_elem(const PeerXchg& x, int i, float v, bool* ok) {
+  *ok = px_alive(x);
+  if (!*ok) return v;
   px_push(x, i, v);
-  return px_pull(x, i);
+  return px_pull(x, i, ok);
 }
 #endif
 
@@ -160,8 +182,10 @@ cudaError_t launch_act(const float* params, const float* obs_aos, const float* e
 cudaError_t launch_value(const float* params, const float* obs_aos, int64_t n, float* v, cudaStream_t st);
 cudaError_t launch_aos_to_soa(const float* obs_aos, float* obs_soa, int64_t cap, int64_t n, cudaStream_t st);
 cudaError_t launch_soa_to_aos(const float* obs_soa, float* obs_aos, int64_t cap, int64_t n, cudaStream_t st);
+// seg_ends / seg_count: scratch of the segment-per-warp path (needed iff returns_needs_segment_list(tr): few envs)
+bool returns_needs_segment_list(const Traj& tr);
 cudaError_t launch_returns(const float* params, const Traj& tr, const HyperDev& hp, cudaStream_t st, int* n_launches,
-                           bool skip_bootstrap = false);
+                           bool skip_bootstrap, int64_t* seg_ends, unsigned long long* seg_count);
 int update_grid_for(int64_t count, int sm_count);
 int update_partial_stride();
 cudaError_t launch_ppo_grad(const UpdateArgs& a, cudaStream_t st);

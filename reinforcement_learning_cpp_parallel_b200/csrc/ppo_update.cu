@@ -447,8 +447,9 @@ __global__ void __launch_bounds__(128) k_reduce(const UpdateArgs a, int apply_ad
   float g = 0.f;
   for (int c = 0; c < a.grid; c++) g += a.partials[(int64_t)c * PSTRIDE + p];
   a.grads[slot] = g;
-  if (peers) g = px_allreduce_elem(a.px, slot, g);
-  if (!(apply_adam || peers)) return;
+  bool ok = true;
+  if (peers) g = px_allreduce_elem(a.px, slot, g, &ok);
+  if (!ok || !(apply_adam || peers)) return;
   if (p < N::P) adam_apply(a, p, g, *a.adam_step);
   else {
     const int q = p - N::P;
@@ -477,11 +478,11 @@ int update_grid_for(int64_t count, int sm_count) {
 }
 
 cudaError_t launch_ppo_grad(const UpdateArgs& a, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  static b2::PerDeviceOnce once;   // function attributes are per device
+  if (once.need()) {
     cudaError_t e = cudaFuncSetAttribute(k_ppo_grad, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if (e != cudaSuccess) return e;
-    attr_set = true;
+    once.done();
   }
   k_ppo_grad<<<a.grid, NT, SMEM_BYTES, st>>>(a);
   return cudaGetLastError();

@@ -21,7 +21,7 @@
 // with equal speeds nobody waits.  Hand-off goes through the state arrays in global memory plus a
 // per-group progress word (release/acquire).  All warps are co-resident by construction, and a waiting
 // warp only ever depends on work that a lower-numbered warp does before anything else, so the spin
-// cannot deadlock.
+// cannot deadlock (and the wait is bounded all the same, see rollout_segment).
 //
 // Roofline: FP64 (B2_PREC_F64) or FP32 FMA issue, not HBM -- 41 B are written per env-step against
 // ~12k-24k arithmetic instructions.
@@ -56,9 +56,19 @@ __device__ __forceinline__ void rollout_segment(const RolloutArgs& a, const floa
   const int64_t NE = a.n_envs;
   const int64_t e = g * 32 + lane;
   if (t0 > 0) {  // hand-off: wait until the warp that owns the earlier steps has published the state
-    if (lane == 0)
-      while (ld_acquire(a.progress + g) < t0) __nanosleep(200);
-    __syncwarp();
+    // The wait is BOUNDED (~3 s): the no-deadlock argument above needs every warp of the grid to be resident, which another
+    // stream or process holding SMs can break.  On expiry status bit 2 is raised (b2_rollout reports B2_ERR_STATE) and
+    // the segment is skipped -- an error, never a hung GPU.
+    int ok = 1;
+    if (lane == 0) {
+      int spins = 0;
+      while (ld_acquire(a.progress + g) < t0) {
+        if (++spins > (1 << 24)) { atomicOr(a.status, 4); ok = 0; break; }
+        __nanosleep(200);
+      }
+    }
+    ok = __shfl_sync(0xffffffffu, ok, 0);
+    if (!ok) return;
   }
   if (e >= NE) return;  // ragged last group (no warp-level sync below this line, except under full_group)
   const bool full_group = g * 32 + 32 <= NE;
@@ -202,7 +212,9 @@ static cudaError_t launch_t(const RolloutArgs& a, int sm_count, cudaStream_t st)
   using N = NetDefault;
   auto kern = k_rollout<Real, N, TRACE, VAR>;
   const int smem = mlp_smem_bytes<N>(ROLLOUT_BLOCK);
-  static int per_sm = 0;  // per instantiation
+  static b2::PerDeviceOnce once;           // per instantiation; attributes and occupancy are per device
+  static std::atomic<int> per_sm_dev[64];
+  int per_sm = once.need() ? 0 : per_sm_dev[b2::PerDeviceOnce::dev()].load();
   if (per_sm == 0) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
@@ -215,6 +227,8 @@ static cudaError_t launch_t(const RolloutArgs& a, int sm_count, cudaStream_t st)
       if (v >= 1 && v < n) n = v;
     }
     per_sm = n;
+    per_sm_dev[b2::PerDeviceOnce::dev()].store(n);
+    once.done();
   }
   const int64_t G = (a.n_envs + 31) / 32;
   const int wpb = ROLLOUT_BLOCK / 32;

@@ -439,12 +439,12 @@ cudaError_t launch_gemm_x3(const CUtensorMap& tmA, const CUtensorMap& tmB, const
   if (a.fuse_m && !(a.mn_major && a.m_tiles == 2 && a.stages >= 2)) return cudaErrorInvalidValue;
   const int smem = a.stages * (a.mn_major ? ((a.fuse_m ? 8 : 4) + 2 * (a.N / 64)) * MNB_BYTES : stage_bytes(a.N)) + STG_BYTES + BAR_BYTES +
                    1024 + (a.mn_major ? DW1_SMEM : 0);
-  static bool attr_set = false;
-  if (!attr_set) {
+  static b2::PerDeviceOnce once;   // function attributes are per device
+  if (once.need()) {
     cudaError_t e;
     if ((e = cudaFuncSetAttribute(k_gemm_x3<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(k_gemm_x3<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)) != cudaSuccess) return e;
-    attr_set = true;
+    once.done();
   }
   const int n_items = a.G * (a.fuse_m ? 1 : a.m_tiles) * a.splits;
   int grid = n_items < sm_count ? n_items : sm_count;

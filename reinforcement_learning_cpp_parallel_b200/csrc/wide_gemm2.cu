@@ -211,12 +211,12 @@ bool gemm2_supported(int N, int K, bool bmn) {
 
 cudaError_t launch_gemm2(bool bmn, const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const Gemm2Args& a,
                          int sm_count, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  static b2::PerDeviceOnce once;   // function attributes are per device
+  if (once.need()) {
     cudaError_t e;
     if ((e = cudaFuncSetAttribute(k_gemm2_ws<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(k_gemm2_ws<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)) != cudaSuccess) return e;
-    attr_set = true;
+    once.done();
   }
   const int tiles = (a.M + 2 * BM - 1) / (2 * BM);
   int ppg = (sm_count / 2) / a.G;                         // pairs per group

@@ -165,8 +165,9 @@ __device__ __forceinline__ void wide_reduce_finish(const ReduceArgs& r, ReduceEl
   r.u.grads[e.slot] = e.s;
   if (!r.last_chunk) return;
   const bool peers = r.u.px.world > 1;   // several GPUs: exchange over NVLink peer memory right here (engine.h PeerXchg)
-  if (peers) e.s = px_allreduce_elem(r.u.px, e.slot, e.s);
-  if (!(r.apply_adam || peers)) return;
+  bool ok = true;
+  if (peers) e.s = px_allreduce_elem(r.u.px, e.slot, e.s, &ok);
+  if (!ok || !(r.apply_adam || peers)) return;
   if (e.p < r.d.P) wide_store_planes(r.d, r.w2p, r.bias2, e.p, wide_adam_apply(r.u, *r.coef, e.p, e.s));
   else wide_loss_log(r.u, e.p - r.d.P, e.s);
 }
@@ -184,13 +185,14 @@ __device__ __forceinline__ void wide_reduce_finish2(const ReduceArgs& r, int p0,
   r.u.grads[p1] = s1;
   if (!r.last_chunk) return;
   const bool peers = r.u.px.world > 1;
-  if (peers) {
+  bool ok = true;
+  if (peers && (ok = px_alive(r.u.px))) {
     px_push(r.u.px, p0, s0);
     px_push(r.u.px, p1, s1);
-    s0 = px_pull(r.u.px, p0);
-    s1 = px_pull(r.u.px, p1);
+    s0 = px_pull(r.u.px, p0, &ok);
+    s1 = px_pull(r.u.px, p1, &ok);
   }
-  if (!(r.apply_adam || peers)) return;
+  if (!ok || !(r.apply_adam || peers)) return;
   const AdamCoef c = *r.coef;
   float m0 = r.u.adam_m[p0], m1 = r.u.adam_m[p1], v0 = r.u.adam_v[p0], v1 = r.u.adam_v[p1];
   const float w0 = r.u.params[p0], w1 = r.u.params[p1];

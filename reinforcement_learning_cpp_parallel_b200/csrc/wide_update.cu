@@ -556,11 +556,11 @@ template <int NJ>
 static cudaError_t launch_head(const WideArgs& wa, int grid, cudaStream_t st) {
   constexpr int H2 = NJ * 32;
   const int smem = (4 * H2 + 8 * 2 * (2 * H2 + 4)) * 4;
-  static bool attr = false;
-  if (!attr) {
+  static b2::PerDeviceOnce once;   // function attributes are per device
+  if (once.need()) {
     cudaError_t e = cudaFuncSetAttribute(k_wide_head<NJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
-    attr = true;
+    once.done();
   }
   return launch_pdl(k_wide_head<NJ>, dim3(grid), dim3(256), (size_t)smem, st, wa);
 }

@@ -27,7 +27,7 @@ def test_header_symbols_all_exported(capi):
     for name in sorted(declared):
         assert hasattr(L, name), f"{name} declared in include/b200ppo.h but not exported"
     assert declared == set(capi.SYMBOLS), declared ^ set(capi.SYMBOLS)
-    assert L.b2_abi_version() == 1
+    assert L.b2_abi_version() == 2
 
 
 def test_struct_layouts_match_header(capi):

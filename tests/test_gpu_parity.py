@@ -123,6 +123,41 @@ def test_env_known_answers_fp64(pkg, kat):
     E.close()
 
 
+@pytest.mark.parametrize("kat", ["kat_fast_a", "kat_fast_b"])
+@pytest.mark.parametrize("entry", ["rollout", "env_step"])
+def test_env_exact_branch_known_answers(pkg, kat, entry):
+    """The reference never clips the force (src/main.cpp:57-60, `bounded` unused :17), so |thetadot| can exceed the
+    16 rad/s below which the carried-rotation stage of csrc/cartpole.cuh is valid; above it substeps run through
+    CartPoleDyn<double>::substep_exact.  These KATs (minted by the unmodified header, +-150 N / +-40 N square waves)
+    cross that threshold in both directions several times: GPU f64 against the reference states, every step."""
+    F = gold(f"{kat}_force.f64")
+    S = gold(f"{kat}_state.f64").reshape(-1, 4)
+    om = np.abs(S[:, 3])
+    assert om.max() > 16 and om.min() < 16                      # both branches run
+    assert ((om[1:] > 16) != (om[:-1] > 16)).sum() >= 2        # and the switch is crossed more than once
+    T = F.size
+    E = make_engine(pkg, n_envs=1, horizon=T, n_timestep=T + 1)
+    if entry == "rollout":
+        a = (F / 10.0).astype(np.float32)                       # 15.0 / 4.0: the scaling chain returns F exactly
+        assert all(oracle().orc_scale_action(float(x)) == f for x, f in zip(a, F))
+        E.set_state_trace(True)
+        E.rollout(T, forced_action=a.reshape(T, 1))
+        out = E.traj_download(T, state_trace=True)
+        got = out["state_trace"][:, 0]
+        np.testing.assert_array_equal(out["reward"][:, 0], gold(f"{kat}_reward.f64").astype(np.float32))
+        # record t holds the PRE-step observation: obs[t+1] is getobs() after step t
+        O = gold(f"{kat}_obs.f64").reshape(-1, 6).astype(np.float32)
+        np.testing.assert_allclose(out["obs"][1:, 0], O[:-1], rtol=1e-6, atol=1e-7)
+    else:
+        got = np.zeros((T, 4))
+        for k in range(T):
+            E.env_step(np.array([F[k]]))
+            got[k] = E.env_get_state()[0][0]
+    err = np.abs(got - S).max(axis=1) / np.maximum(np.abs(S).max(axis=1), 1e-3)
+    assert err.max() < 1e-9, (int(err.argmax()), err.max())
+    E.close()
+
+
 @pytest.mark.parametrize("case", ["c1"])
 def test_env_replay_fp32_drift_is_bounded(pkg, case):
     """The f32 throughput path is NOT parity-gated; this only guards against gross bugs and
@@ -265,3 +300,142 @@ def test_checkpoint_roundtrip(pkg, tmp_path):
     E.update(obs, act, lp, rw, fl); E2.update(obs, act, lp, rw, fl)
     np.testing.assert_array_equal(E.get_params(), E2.get_params())  # resume is bit-exact
     E.close(); E2.close()
+
+
+def test_checkpoint_resume_continues_the_run(pkg, tmp_path):
+    """save -> load -> rollout must CONTINUE the saved run (Philox step counter, env state, episode counters), not replay
+    its first iterations: two train iterations without interruption == one iteration, checkpoint, a fresh engine that
+    loads it, one more iteration -- trajectories and weights bit for bit."""
+    kw = dict(n_envs=96, horizon=64, k_epochs=2, seed=77)
+    A = make_engine(pkg, **kw)
+    A.set_params(gold("init_params.f32"))
+    A.train_iteration(64)
+    path = str(tmp_path / "run.b2")
+    A.save_checkpoint(path)
+    A.train_iteration(64)
+    ta = A.traj_download(64)
+    B = make_engine(pkg, **kw)
+    B.load_checkpoint(path)
+    B.train_iteration(64)
+    tb = B.traj_download(64)
+    for k in ("obs", "action", "logp", "reward", "flags"):
+        np.testing.assert_array_equal(ta[k], tb[k], err_msg=k)
+    np.testing.assert_array_equal(A.get_params(), B.get_params())
+    ua, ub = A.env_get_state(), B.env_get_state()
+    np.testing.assert_array_equal(ua[0], ub[0]); np.testing.assert_array_equal(ua[1], ub[1])
+    # a different env count takes the weights and the counters, not the env block
+    C2 = make_engine(pkg, n_envs=32, horizon=64, k_epochs=2, seed=77)
+    C2.load_checkpoint(path)
+    assert C2.get_adam_state()[2] == 2
+    A.close(); B.close(); C2.close()
+
+
+# ------------------------------------------------------------------- returns: segment-parallel scan, lambda
+def np_returns(r, fl, vboot, vall, gamma, lam=1.0):
+    """NumPy restatement of src/ppo_nn.cpp:220-233 for time-major [T][N] arrays, vectorised over envs, f32 arithmetic in
+    the reference's order (mul, then add); lam < 1 mixes in V(s_{t+1}) (include/b200ppo.h b2_config.gae_lambda)."""
+    T, N = r.shape
+    g, lam32 = np.float32(gamma), np.float32(lam)
+    R = np.empty((T, N), np.float32)
+    carry = np.zeros(N, np.float32)
+    vnext = np.zeros(N, np.float32)
+    for t in range(T - 1, -1, -1):
+        boot = (fl[t] & 6) != 0
+        term = ((fl[t] & 1) != 0) & ~boot
+        c = carry
+        if lam < 1.0:
+            c = (np.float32(1) - lam32) * vnext + lam32 * carry
+        c = np.where(boot, vboot[t], np.where(term, np.float32(0), c)).astype(np.float32)
+        carry = (r[t] + g * c).astype(np.float32)
+        R[t] = carry
+        if vall is not None:
+            vnext = vall[t]
+    return R
+
+
+def np_returns_flat(r, fl, vboot, gamma):
+    """The same recurrence on ONE column, vectorised over its segments (a segment ends at a flagged record or at the
+    last record): bit-identical to walking the column record by record, in seconds instead of minutes."""
+    B = r.size
+    g = np.float32(gamma)
+    ends = np.flatnonzero((fl != 0) | (np.arange(B) == B - 1))
+    starts = np.concatenate([[0], ends[:-1] + 1])
+    R = np.empty(B, np.float32)
+    f = fl[ends]
+    carry = np.where((f & 6) != 0, vboot[ends], np.float32(0)).astype(np.float32)   # TIMEUP/TRUNC: V; TERMINATE / tail: 0
+    for j in range(int((ends - starts).max()) + 1):
+        idx = ends - j
+        live = idx >= starts
+        carry = np.where(live, (r[np.maximum(idx, 0)] + g * carry).astype(np.float32), carry)
+        R[idx[live]] = carry[live]
+    return R
+
+
+def test_returns_flat_million_records(pkg):
+    """PPO::update(MemoryNN) hands the engine ONE column of B records (n_envs = 1).  Round 1 walked it with a single GPU
+    thread; now every segment between two flagged records gets a warp.  1,048,576 records, 100-step episodes, a TERMINATE
+    every 977 records: bit-identical to the sequential f32 recurrence; then a batch WITHOUT flags (one segment of 300k
+    records: the affine-map scan) inside 1e-5."""
+    import time
+    B, L = 1 << 20, 100
+    rng = np.random.default_rng(5)
+    th = 0.2 * rng.standard_normal(B)
+    obs = np.stack([rng.standard_normal(B), rng.standard_normal(B), rng.standard_normal(B), th, np.cos(th), np.sin(th)],
+                   1).astype(np.float32)
+    rw = (rng.random(B) < 0.8).astype(np.float32)
+    fl = np.zeros(B, np.uint8)
+    fl[L - 1::L] = 2
+    fl[500::977] |= 1
+    fl[fl == 3] = 2
+    E = make_engine(pkg)
+    E.set_params(gold("c1_k5_params.f32"))
+    R = E.returns(obs, rw, fl)            # warm-up + result
+    t0 = time.perf_counter()
+    R = E.returns(obs, rw, fl)
+    dt = time.perf_counter() - t0
+    V = E.value(obs)
+    ref = np_returns_flat(rw, fl, V, GAMMA)
+    small = np_returns(rw[:3000].reshape(3000, 1), fl[:3000].reshape(3000, 1), V[:3000].reshape(3000, 1), None, GAMMA)[:, 0]
+    np.testing.assert_array_equal(ref[:2900], small[:2900])   # the two NumPy restatements agree where both are complete
+    np.testing.assert_array_equal(R, ref)
+    print(f"b2_returns on {B} flat records incl. H2D/D2H: {dt * 1e3:.1f} ms")
+    assert dt < 0.25                      # round 1: one thread, ~0.5 us per record = 0.5 s of kernel alone
+    # no flags at all: one long segment; sequential for the first 2048 records from the end, affine-map scan after
+    n = 100000
+    R2 = E.returns(obs[:n], rw[:n], np.zeros(n, np.uint8))
+    ref2 = np_returns(rw[:n].reshape(n, 1), np.zeros((n, 1), np.uint8), V[:n].reshape(n, 1), None, GAMMA)[:, 0]
+    np.testing.assert_array_equal(R2[-2048:], ref2[-2048:])
+    np.testing.assert_allclose(R2, ref2, rtol=1e-5, atol=1e-5)
+    E.close()
+
+
+@pytest.mark.parametrize("shape", [(1, 4000), (3, 700), (2048, 128)])
+@pytest.mark.parametrize("lam", [0.95, 0.5])
+def test_returns_lambda(pkg, shape, lam):
+    """b2_config.gae_lambda < 1: R_k = r_k + gamma ((1 - lam) V(s_{k+1}) + lam R_{k+1}) between flagged records, on the
+    segment-per-warp path (few envs) and the per-env walk (many envs), against the NumPy restatement."""
+    N, T = shape
+    rng = np.random.default_rng(N)
+    B = N * T
+    th = 0.2 * rng.standard_normal(B)
+    obs = np.stack([rng.standard_normal(B), rng.standard_normal(B), rng.standard_normal(B), th, np.cos(th), np.sin(th)],
+                   1).astype(np.float32)
+    rw = (rng.random((T, N)) < 0.8).astype(np.float32)
+    fl = np.zeros((T, N), np.uint8)
+    fl[99::100] = 2
+    fl[rng.random((T, N)) < 0.004] = 1
+    if N == 3:
+        fl[T - 1] = 4
+    E = make_engine(pkg, gae_lambda=lam)
+    E.set_params(gold("c1_k5_params.f32"))
+    R = E.returns(obs, rw.reshape(-1), fl.reshape(-1), n_envs=N, horizon=T).reshape(T, N)
+    V = E.value(obs).reshape(T, N)
+    ref = np_returns(rw, fl, V, V, GAMMA, lam)
+    np.testing.assert_allclose(R, ref, rtol=2e-6, atol=2e-6)
+    # lambda = 1 on the same batch is the reference recurrence, bit for bit
+    E1 = make_engine(pkg)
+    E1.set_params(gold("c1_k5_params.f32"))
+    R1 = E1.returns(obs, rw.reshape(-1), fl.reshape(-1), n_envs=N, horizon=T).reshape(T, N)
+    np.testing.assert_array_equal(R1, np_returns(rw, fl, V, None, GAMMA))
+    assert np.abs(R1 - R).max() > 1e-3    # and lambda does change the answer
+    E.close(); E1.close()

@@ -176,6 +176,64 @@ def test_full_size_properties(pkg):
     E.close(); E2.close(); E3.close()
 
 
+def test_time_sliced_handoff_is_bit_exact(pkg):
+    """The persistent rollout kernel cuts (group, step) units along the TIME axis once there are >= 592 env groups
+    (csrc/rollout.cu: a group's steps are then shared by two warps through a release/acquire hand-off in global memory).
+    Small engines (one group per warp, no hand-off) over the same GLOBAL env ids must give the same trajectory bit for
+    bit -- sharding invariance already promises it -- at the head, the middle and the tail of the full-size grid."""
+    N, T = 65536, 128
+    params = gold("c1_k80_params.f32")
+    full = make_engine(pkg, n_envs=N, horizon=T, seed=0x5EED)
+    full.set_params(params)
+    full.rollout(T)
+    A = full.traj_download(T)
+    uA, esA = full.env_get_state()
+    cntA, retA = full.episode_stats(2)
+    full.close()
+    for off in (0, 20000, 65024):
+        sh = make_engine(pkg, n_envs=512, horizon=T, seed=0x5EED, env_offset=off)
+        sh.set_params(params)
+        sh.rollout(T)
+        Bq = sh.traj_download(T)
+        for k in ("obs", "action", "logp", "mu", "reward", "flags"):
+            np.testing.assert_array_equal(Bq[k], A[k][:, off: off + 512], err_msg=f"{k} @ env_offset {off}")
+        u, es = sh.env_get_state()
+        np.testing.assert_array_equal(u, uA[off: off + 512])
+        np.testing.assert_array_equal(es, esA[off: off + 512])
+        cnt, ret = sh.episode_stats(2)
+        np.testing.assert_array_equal(cnt, cntA[off: off + 512])
+        np.testing.assert_array_equal(ret, retA[off: off + 512])
+        sh.close()
+
+
+def test_time_sliced_handoff_forced_action_replay(pkg):
+    """32,768 envs (1,024 groups > 592 sub-partitions: time-sliced grid) replaying the oracle's actions on 256 sampled
+    envs, zeros elsewhere: fp64 states of the sampled envs against orc_rollout at 1e-9, rewards and flags exact."""
+    N, T = 32768, 100
+    params = gold("init_params.f32")
+    ids = (np.arange(256) * 127 + 5) % N
+    assert np.unique(ids).size == 256
+    ref = oracle_rollout(params, 256, T, seed=21)
+    forced = np.zeros((T, N), np.float32)
+    forced[:, ids] = ref["action"]
+    E = make_engine(pkg, n_envs=N, horizon=T, seed=21)
+    E.set_params(params)
+    E.set_state_trace(True)
+    E.rollout(T, forced_action=forced)
+    out = E.traj_download(T, fields=("reward", "flags", "obs"), state_trace=True)
+    got = out["state_trace"][:, ids]
+    scale = np.maximum(np.abs(ref["state_trace"]).max(axis=-1, keepdims=True), 1e-300)
+    err = (np.abs(got - ref["state_trace"]) / scale).max()
+    assert err < 1e-9, err
+    np.testing.assert_array_equal(out["reward"][:, ids], ref["reward"])
+    np.testing.assert_array_equal(out["flags"][:, ids], ref["flags"])
+    np.testing.assert_allclose(out["obs"][:, ids], ref["obs"], rtol=1e-6, atol=1e-7)
+    # the envs that were fed a = 0 all saw the same force: identical trajectories, whichever warp advanced them
+    rest = np.setdiff1d(np.arange(N), ids)
+    assert (out["state_trace"][:, rest] == out["state_trace"][:, rest[:1]]).all()
+    E.close()
+
+
 def test_training_learns_cartpole(pkg):
     """T10: reference default shape (2000 samples per update, K=80, 100-step episodes) reaches the reference's
     plateau (trailing mean episode reward >= 95 of 100, cf. results/carpole1node) within ~60 updates."""

@@ -16,7 +16,7 @@ def test_param_count():
     assert L.orc_n_params(C.byref(DEFAULT_DIMS)) == 5122 == gold("init_params.f32").size
 
 
-@pytest.mark.parametrize("kat", ["kat_a", "kat_b", "kat_c"])
+@pytest.mark.parametrize("kat", ["kat_a", "kat_b", "kat_c", "kat_fast_a", "kat_fast_b"])
 def test_env_known_answers(kat):
     """cart_pole.h advance/getobs/getReward: fp64 states must match the header to ~1 ulp/step."""
     L = oracle()
