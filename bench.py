@@ -11,6 +11,11 @@ the update leg -> `update.value`, sample-epochs/s].  Everything is timed on the 
 the engine's stream, max over ranks.  `e2e` repeats the rollout leg through the C ABI with HOST buffers:
 weights H2D from pinned memory in, the whole trajectory batch D2H into pinned memory out.
 
+Further legs inside the same JSON line: `update` (default-net PPO update on the rollout's batch), `update_wide`
+(BASELINE configs[4]), `configs1` (BASELINE configs[1]: 3 env nodes x 7 episodes, N = 1 only), `c4` (BASELINE configs[3]:
+1,048,576 envs over the N GPUs, strong scaling) and, at N > 1, `multi_gpu_check` (weights bit-identical across ranks,
+gradients vs one GPU on the concatenated batch, peer-memory exchange vs ncclAllReduce; a violation makes the run exit 1).
+
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--precision f64|f32]
 """
 import argparse
@@ -49,6 +54,11 @@ def parse():
     ap.add_argument("--no-wide", action="store_true", help="skip the configs[4] leg (2x256 MLP update sweep on tensor cores)")
     ap.add_argument("--no-wide-whole", action="store_true", help="skip the whole-4M-batch-on-one-GPU variant of the configs[4] leg")
     ap.add_argument("--wide-samples", type=int, default=524288, help="samples per GPU of the configs[4] leg (4M over 8 GPUs)")
+    ap.add_argument("--no-c4", action="store_true", help="skip the configs[3] leg (1,048,576 envs over the N GPUs)")
+    ap.add_argument("--c4-envs", type=int, default=1048576)
+    ap.add_argument("--no-configs1", action="store_true", help="skip the configs[1] leg (3 envs x 700 steps, K = 80; N = 1 only)")
+    ap.add_argument("--no-multi-check", action="store_true", help="skip the multi-GPU parity self-check (N > 1)")
+    ap.add_argument("--no-mpi-baseline", action="store_true", help="reference arm: skip the mpirun-shaped runs (b2_mpirun -n 2 / -n 4)")
     return ap.parse_args()
 
 
@@ -69,6 +79,46 @@ def run_reference(updates, K=80, threads=1, nenv=1, episodes=20):
     r = json.loads(out.stdout.strip().splitlines()[-1])
     r["wall_s"] = time.time() - t0
     return r
+
+
+def run_reference_mpi(nranks, episodes, threads=1, timeout=600):
+    """The reference's OWN launch shape (README.md:82-92: mpirun -n N ./cpp-rl-training config): its unmodified
+    src/main.cpp + src/ppo_nn.cpp + libtorch CPU (oracle/_ref/ref_main_mpi) as N OS processes -- rank 0 the learner, the
+    others one CartPole each -- over tools/mpi_shim (shared-memory rings standing in for the MPI this image lacks), so
+    every env step pays the message round trip of src/main.cpp:47-48,104-131,186,230-234.  Runs `episodes` episodes
+    (>= 3 update cycles), stdout discarded; env-steps/s = 100 x episode lines in proc*_log.txt / wall."""
+    import glob
+    import shutil
+    import tempfile
+    exe = os.path.join(ROOT, "oracle", "_ref", "ref_main_mpi")
+    launcher = os.path.join(ROOT, "tools", "bin", "b2_mpirun")
+    if not (os.path.exists(exe) and os.path.exists(launcher)):
+        return None
+    d = tempfile.mkdtemp(prefix="b2_refmpi_")
+    try:
+        with open(os.path.join(d, "config"), "w") as f:   # the reference's 6-line format (config:1-6), Nepisodes shortened
+            f.write(f"1 = control_vars\n6 = obs_vars\n{episodes} = Nepisodes\n100 = N_timestep\n1000000 = Max_timestep\n2000 = updateTimestep\n")
+        env = dict(os.environ, OMP_NUM_THREADS=str(threads), MKL_NUM_THREADS=str(threads))
+        t0 = time.time()
+        out = subprocess.run([launcher, "-n", str(nranks), "-q", exe, "./config"], cwd=d, env=env, capture_output=True,
+                             text=True, timeout=timeout)
+        wall = time.time() - t0
+        lines = 0
+        for fn in glob.glob(os.path.join(d, "proc*_log.txt")):
+            lines += sum(1 for _ in open(fn))
+        if lines == 0:
+            return None
+        nenv = nranks - 1
+        per_update = 100 * nenv * -(-2000 // (100 * nenv))      # whole episodes on every env (src/main.cpp:264-307)
+        return {"value": 100.0 * lines / wall, "unit": "env-steps/s", "ranks": nranks, "env_ranks": nenv,
+                "libtorch_threads": threads, "episodes": lines, "env_steps": 100 * lines,
+                "updates": (100 * lines) // per_update, "wall_s": wall, "rc": out.returncode,
+                "how": f"tools/bin/b2_mpirun -n {nranks} -q oracle/_ref/ref_main_mpi config (unmodified src/main.cpp + "
+                       f"src/ppo_nn.cpp, libtorch CPU, shared-memory MPI shim), rollout + PPO::update(K=80) in one wall clock"}
+    except Exception as e:   # noqa: BLE001 -- a baseline that cannot run is reported, not fatal
+        return {"unavailable": repr(e)[:200]}
+    finally:
+        shutil.rmtree(d, ignore_errors=True)
 
 
 def cpu_port_baseline(seconds=6.0):
@@ -105,6 +155,18 @@ def reference_arm(args, rank):
         sample = (f"{r['updates']} cycles of (1 env x 20 episodes x 100 steps rollout + PPO::update K=80), "
                   f"in-process replay of src/main.cpp's protocol without MPI latency, stdout discarded, "
                   f"{r['torch_threads']} libtorch thread")
+    # BASELINE configs[1] (results/carpole3node: 1 learner + 3 env nodes) in process, and both configs as the reference
+    # launches them (N OS processes exchanging a message per env step)
+    c2 = run_reference(max(2, ups // 2), nenv=3, episodes=7) if r is not None else None
+    configs1 = None
+    if c2:
+        configs1 = {"value": c2["env_steps"] / c2["rollout_s"], "unit": "env-steps/s",
+                    "update": {"value": c2["sample_epochs"] / c2["update_s"], "unit": "sample-epochs/s"},
+                    "combined_env_steps_per_s": c2["env_steps"] / (c2["rollout_s"] + c2["update_s"]),
+                    "sample": f"{c2['updates']} cycles of (3 envs x 7 episodes x 100 steps + PPO::update K=80 on 2100 records), in process"}
+    mpi = None
+    if not args.no_mpi_baseline:
+        mpi = {"n2": run_reference_mpi(2, 100), "n4": run_reference_mpi(4, 105)}
     line = {"impl": "reference", "metric": "cartpole_env_steps_per_sec_incl_policy_inference", "value": v,
             "unit": "env-steps/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * per_update / v, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -113,6 +175,7 @@ def reference_arm(args, rank):
                        "n_envs": 1, "horizon": 2000},
             "cpu_baseline": {"value": v, "unit": "env-steps/s", "cores": cores, "kind": kind, "sample": sample},
             "update": {"value": upd, "unit": "sample-epochs/s"},
+            "configs1": configs1, "cpu_baseline_mpi": mpi,
             "e2e": {"value": v, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
@@ -165,10 +228,211 @@ class ClockSampler:
 
 
 def _ncu_traffic(key):
+    """(bytes per launch, where it came from): dram__bytes_read.sum + dram__bytes_write.sum of the named kernel from the
+    `ncu --set full` capture of THIS round, written into profiles/NCU_TRAFFIC.json by profiles/ncu_traffic.py (the
+    script that reads the .ncu-rep); null when the file has no entry."""
     try:
-        return json.load(open(os.path.join(ROOT, "profiles", "NCU_TRAFFIC.json"))).get(key)
+        tj = json.load(open(os.path.join(ROOT, "profiles", "NCU_TRAFFIC.json")))
+        e = tj.get(key)
+        if isinstance(e, dict):
+            return e.get("bytes"), f"profiles/NCU_TRAFFIC.json <- {e.get('source')} ({tj.get('_captured')})"
+        return e, "profiles/NCU_TRAFFIC.json"
     except Exception:
-        return None
+        return None, None
+
+
+def _rel(a, b):
+    import numpy as np
+    a = np.asarray(a, np.float64)
+    b = np.asarray(b, np.float64)
+    return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300))
+
+
+def multi_gpu_check(pkg, capi, np, torch, dist, rank, local, world):
+    """Parity of the multi-GPU path, inside the bench line (N > 1), BEFORE anything is timed.  Same shapes as
+    tests/test_gpu_multi.py, which a 1-GPU test box skips.  The reference computes ONE batch mean over the merged memory
+    of all env ranks (src/main.cpp:290-303, src/ppo_nn.cpp:302); sharded, that is: identical trajectories for any sharding,
+    gradients equal to one GPU's on the concatenated batch, weights bit-identical on every rank.
+      default nets : 515 envs (NOT divisible by N: uneven shards, global-count denominators) x 100 steps, K = 3
+      wide nets    : 2 x 256, 2048 samples, K = 2, M = 2 (every minibatch sharded across the ranks)
+    Both through the fused NVLink peer-memory exchange (default) and through ncclAllReduce (B2_COMM_P2P=0)."""
+    from reinforcement_learning_cpp_parallel_b200 import sharding
+    NG, T, K = 515, 100, 3
+    res = {"world": world}
+
+    def gather_equal(vec):
+        t = torch.from_numpy(np.ascontiguousarray(vec)).cuda()
+        parts = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(parts, t)
+        return all(bool(torch.equal(parts[0].view(torch.int32), q.view(torch.int32))) for q in parts[1:])
+
+    def sharded(p2p):
+        old = os.environ.get("B2_COMM_P2P")
+        os.environ["B2_COMM_P2P"] = "1" if p2p else "0"       # read by b2_comm_init
+        try:
+            n_local, off = sharding.shard_envs(NG, rank, world)
+            E = pkg.Engine(capi.default_config(n_envs=n_local, horizon=T, seed=21, env_offset=off, k_epochs=K, device=local))
+            E.init_params(4)
+            E.comm_init(rank, world, sharding.broadcast_comm_id(dist, pkg.Engine.comm_unique_id))
+            mode = E.comm_mode()
+            E.rollout(T)
+            traj = E.traj_download(T, fields=("obs", "action", "reward", "flags"))
+            st = E.update_resident()
+            out = (E.get_grads(), E.get_params(), st.loss, mode, traj, off, n_local)
+            E.close()
+            return out
+        finally:
+            if old is None:
+                os.environ.pop("B2_COMM_P2P", None)
+            else:
+                os.environ["B2_COMM_P2P"] = old
+
+    g_p, w_p, loss_p, mode_p, traj, off, n_local = sharded(True)
+    g_n, w_n, loss_n, mode_n, _, _, _ = sharded(False)
+    res["comm_mode_default"] = mode_p
+    res["weights_bit_identical_across_ranks"] = bool(gather_equal(w_p) and gather_equal(w_n))
+    res["p2p_vs_nccl_relerr"] = max(_rel(w_p, w_n), _rel(g_p, g_n)) if mode_p == 2 else None
+    # one GPU holding every env (every rank computes it on its own GPU: no communication, same answer)
+    E = pkg.Engine(capi.default_config(n_envs=NG, horizon=T, seed=21, k_epochs=K, device=local))
+    E.init_params(4)
+    E.rollout(T)
+    full = E.traj_download(T, fields=("obs", "action", "reward", "flags"))
+    st1 = E.update_resident()
+    g1, w1 = E.get_grads(), E.get_params()
+    E.close()
+    traj_ok = all(np.array_equal(traj[k], full[k][:, off:off + n_local]) for k in traj)
+    res["trajectories_identical_to_single_gpu"] = bool(traj_ok)
+    res["grad_relerr_vs_single_gpu"] = max(_rel(g_p, g1), _rel(g_n, g1))
+    res["weights_relerr_vs_single_gpu"] = max(_rel(w_p, w1), _rel(w_n, w1))
+    res["loss_relerr_vs_single_gpu"] = abs(loss_p - st1.loss) / max(abs(st1.loss), 1e-30)
+    res["uneven_shards"] = [int(sharding.shard_envs(NG, r, world)[0]) for r in range(world)]
+
+    # ---- wide nets: each rank owns 1/N of every minibatch
+    WB, WK, WM = 2048, 2, 2
+    rng = np.random.default_rng(99)
+    th = 0.3 * rng.standard_normal(WB)
+    obs = np.stack([rng.standard_normal(WB), rng.standard_normal(WB), rng.standard_normal(WB), th, np.cos(th), np.sin(th)],
+                   1).astype(np.float32)
+    eps = rng.standard_normal(WB).astype(np.float32)
+    reward = (rng.random(WB) < 0.9).astype(np.float32)
+    E = pkg.Engine(capi.default_config(n_envs=WB // world, horizon=1, hidden1=256, hidden2=256, k_epochs=WK, n_minibatches=WM, device=local))
+    E.init_params(4)
+    E.comm_init(rank, world, sharding.broadcast_comm_id(dist, pkg.Engine.comm_unique_id))
+    act, lp, _ = E.act(obs, eps)
+    per = WB // WM
+    part = per // world
+    sel = np.concatenate([np.arange(m * per + rank * part, m * per + (rank + 1) * part) for m in range(WM)])
+    stw = E.update(obs[sel], act[sel], lp[sel], reward[sel], np.ones(sel.size, np.uint8))
+    gw, ww = E.get_grads(), E.get_params()
+    E.close()
+    E = pkg.Engine(capi.default_config(n_envs=WB, horizon=1, hidden1=256, hidden2=256, k_epochs=WK, n_minibatches=WM, device=local))
+    E.init_params(4)
+    a1, l1, _ = E.act(obs, eps)
+    st1w = E.update(obs, a1, l1, reward, np.ones(WB, np.uint8))
+    g1w, w1w = E.get_grads(), E.get_params()
+    E.close()
+    res["wide"] = {"weights_bit_identical_across_ranks": bool(gather_equal(ww)),
+                   "grad_relerr_vs_single_gpu": _rel(gw, g1w), "weights_relerr_vs_single_gpu": _rel(ww, w1w),
+                   "loss_relerr_vs_single_gpu": abs(stw.loss - st1w.loss) / max(abs(st1w.loss), 1e-30)}
+    ok = (res["weights_bit_identical_across_ranks"] and traj_ok and res["grad_relerr_vs_single_gpu"] < 1e-5
+          and res["weights_relerr_vs_single_gpu"] < 1e-6 and res["loss_relerr_vs_single_gpu"] < 1e-5
+          and (res["p2p_vs_nccl_relerr"] is None or res["p2p_vs_nccl_relerr"] < 1e-6)
+          and res["wide"]["weights_bit_identical_across_ranks"] and res["wide"]["grad_relerr_vs_single_gpu"] < 2e-5
+          and res["wide"]["weights_relerr_vs_single_gpu"] < 1e-6 and res["wide"]["loss_relerr_vs_single_gpu"] < 1e-4)
+    # every rank must agree on the verdict (a rank-local failure fails the run everywhere)
+    t = torch.tensor([1.0 if ok else 0.0], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    res["ok"] = bool(t.item() > 0.5)
+    return res
+
+
+def c4_leg(args, pkg, capi, np, rank, local, world, dist, barrier, max_over_ranks, peak64, peak32):
+    """BASELINE configs[3]: 1,048,576 envs sharded over the N GPUs (524,288 / 262,144 / 131,072 per GPU at N = 2 / 4 / 8;
+    all of them on one GPU at N = 1, the strong-scaling anchor) x 128 steps, f64 rollout + 4 full-batch epochs of the
+    default-net update with the gradient exchange of DESIGN.md s5.  STRONG scaling: the global batch is fixed."""
+    NG, T, K = args.c4_envs, args.horizon, args.epochs
+    if NG % world:
+        return {"skipped": f"{NG} envs do not divide over {world} GPUs"}
+    n_local = NG // world
+    E = pkg.Engine(capi.default_config(n_envs=n_local, horizon=T, precision=pkg.PREC_F64, seed=0x5EED,
+                                       env_offset=rank * n_local, k_epochs=K, device=local))
+    E.init_params(0)
+    if world > 1:
+        uid = [pkg.Engine.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        E.comm_init(rank, world, uid[0])
+    E.rollout(T); E.update_resident()          # warm-up (the 1M-env buffers are touched once)
+    barrier(E)
+    reps = max(2, min(args.steps, 3))
+    l0 = E.kernel_launches()
+    rms, ums = [], []
+    for _ in range(reps):
+        E.timer_start(); E.rollout(T); rms.append(E.timer_stop_ms())
+        E.timer_start(); st = E.update_resident(); ums.append(E.timer_stop_ms())
+    barrier(E)
+    launches = E.kernel_launches() - l0
+    rt, ut = max_over_ranks(sum(rms)), max_over_ranks(sum(ums))
+    value = NG * T * reps / (rt * 1e-3)
+    upd = NG * T * K * reps / (ut * 1e-3)
+    mode = E.comm_mode()
+    E.close()
+    mine_r, mine_u = sum(rms) / reps, sum(ums) / reps
+    ach = FLOP_PHYS * n_local * T / (mine_r * 1e-3) / 1e12
+    uach = FLOP_UPDATE * n_local * T * K / (mine_u * 1e-3) / 1e12
+    out = {"value": value, "unit": "env-steps/s", "ms_per_rollout": rt / reps, "scaling": "strong",
+           "config": {"workload": "BASELINE configs[3]: batched CartPole, 1,048,576 envs sharded over the GPUs x 128-step horizon, "
+                                  "default MLP, gradient exchange per optimizer step", "n_envs_global": NG,
+                      "n_envs_per_gpu": n_local, "horizon": T, "precision": "f64", "epochs": K},
+           "roofline": {"kernel": "k_rollout<double>", "bound": "fp64-fma", "achieved": ach, "peak": peak64, "unit": "TFLOP/s",
+                        "frac": ach / peak64 if peak64 else None},
+           "update": {"value": upd, "unit": "sample-epochs/s", "ms_per_update": ut / reps,
+                      "roofline": {"kernel": "k_ppo_grad", "bound": "fp32-fma", "achieved": uach, "peak": peak32,
+                                   "unit": "TFLOP/s", "frac": uach / peak32 if peak32 else None}},
+           "gpu_launches": int(launches), "comm_mode": mode, "last_loss": st.loss}
+    # strong-scaling efficiency against the N = 1 run of the same leg ON THIS BOX (the driver runs N = 1, 2, 4, 8 back to
+    # back): the N = 1 run leaves its numbers in a scratch file, later runs read it
+    anchor = os.path.join(os.environ.get("TMPDIR", "/tmp"), f"b2_c4_anchor_{NG}x{T}x{K}.json")
+    if rank == 0:
+        try:
+            if world == 1:
+                json.dump({"value": value, "update": upd, "when": time.time()}, open(anchor, "w"))
+            elif os.path.exists(anchor):
+                a = json.load(open(anchor))
+                if time.time() - a["when"] < 6 * 3600:
+                    out["strong_scaling_efficiency_vs_n1"] = {"rollout": value / (world * a["value"]),
+                                                              "update": upd / (world * a["update"]),
+                                                              "n1_value": a["value"], "n1_update": a["update"],
+                                                              "n1_age_s": time.time() - a["when"], "source": anchor}
+        except Exception:
+            pass
+    return out
+
+
+def configs1_leg(args, pkg, capi, np, local):
+    """BASELINE configs[1]: the results/carpole3node shape (1 learner + 3 env nodes) on ONE GPU: 3 envs x 7 episodes x
+    100 steps per update (the reference's trigger rounds 2000 up to whole episodes on every env: 2,100 records,
+    src/main.cpp:264-307), K = 80 full-batch epochs.  Latency-bound on a GPU (3 lanes busy); reported beside the
+    reference arm's `configs1` / `cpu_baseline_mpi.n4`, not as a throughput claim."""
+    N, T, K = 3, 700, 80
+    E = pkg.Engine(capi.default_config(n_envs=N, horizon=T, k_epochs=K, seed=0x5EED, device=local))
+    E.init_params(0)
+    E.train_iteration(T)
+    reps = 5
+    rms, ums = [], []
+    l0 = E.kernel_launches()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        E.timer_start(); E.rollout(T); rms.append(E.timer_stop_ms())
+        E.timer_start(); E.update_resident(); ums.append(E.timer_stop_ms())
+    wall = time.perf_counter() - t0
+    launches = E.kernel_launches() - l0
+    E.close()
+    return {"value": N * T * reps / (sum(rms) * 1e-3), "unit": "env-steps/s",
+            "update": {"value": N * T * K * reps / (sum(ums) * 1e-3), "unit": "sample-epochs/s"},
+            "combined_env_steps_per_s": N * T * reps / wall, "ms_per_rollout": sum(rms) / reps, "ms_per_update": sum(ums) / reps,
+            "gpu_launches": int(launches),
+            "config": {"workload": "BASELINE configs[1]: 1 learner + 3 env nodes (results/carpole3node) on one GPU",
+                       "n_envs": N, "horizon": T, "epochs": K, "records_per_update": N * T}}
 
 
 def wide_leg(args, pkg, capi, np, rank, local, world, dist, barrier, max_over_ranks, bf16_peak, bf16_src):
@@ -264,7 +528,7 @@ def wide_leg(args, pkg, capi, np, rank, local, world, dist, barrier, max_over_ra
                          "unit": "TFLOP/s", "frac": ach / (bf16_peak / 3.0) if bf16_peak else None,
                          "peak_source": bf16_src + " / 3 (every fp32 product is three bf16 MMAs)",
                          "issued_bf16_tflops": 3 * ach, "flop_per_sample_epoch": FLOP_UPDATE_WIDE,
-                         "traffic": _ncu_traffic("k_gemm2_ws_fwd_2x16384x256x256"),
+                         "traffic": _ncu_traffic("wide_dominant_kernel")[0], "traffic_source": _ncu_traffic("wide_dominant_kernel")[1],
                          "comm_mode": comm_mode},
             "whole_batch_one_gpu": whole, "last_loss": st.loss}
 
@@ -315,6 +579,11 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     prec = pkg.PREC_F64 if args.precision == "f64" else pkg.PREC_F32
     N, T = args.envs, args.horizon
+
+    # ---------------- multi-GPU parity self-check (N > 1), before anything is timed ----------------
+    mcheck = None
+    if world > 1 and not args.no_multi_check:
+        mcheck = multi_gpu_check(pkg, capi, np, torch, dist, rank, local, world)
 
     def engine(k_epochs):
         return pkg.Engine(capi.default_config(n_envs=N, horizon=T, precision=prec, seed=0x5EED, env_offset=rank * N,
@@ -418,10 +687,30 @@ def main():
     if not args.no_wide:
         update_wide = wide_leg(args, pkg, capi, np, rank, local, world, dist, barrier, max_over_ranks, bf16_peak, bf16_src)
 
+    # ---------------- roofline denominators: measured FMA-issue peak AND the arithmetic one; frac uses the larger ----------
+    sm_mhz = (clocks or {}).get("sm_mhz") or (clocks or {}).get("sm_max_mhz") or peaks.get("sm_max_mhz") or 1965.0
+    n_sm = torch.cuda.get_device_properties(local).multi_processor_count
+    arith32 = n_sm * 128 * 2 * sm_mhz * 1e6 / 1e12     # 128 FP32 lanes per SM x 2 flop per FMA
+    arith64 = n_sm * 64 * 2 * sm_mhz * 1e6 / 1e12      # 64 FP64 lanes per SM
+    peak32_meas, peak64_meas = peak32, peak64
+    peak32, peak64 = max(peak32_meas, arith32), max(peak64_meas, arith64)
+    if dist:   # every rank needs rank 0's denominators for its own legs below
+        t = torch.tensor([peak32, peak64], dtype=torch.float64, device="cuda")
+        dist.broadcast(t, src=0)
+        peak32, peak64 = float(t[0]), float(t[1])
+    E.close()
+
+    c4 = None
+    if not args.no_c4 and args.precision == "f64":
+        c4 = c4_leg(args, pkg, capi, np, rank, local, world, dist, barrier, max_over_ranks, peak64, peak32)
+
     if rank != 0:
         if dist:
             dist.destroy_process_group()
+        if mcheck is not None and not mcheck["ok"]:
+            raise SystemExit(1)
         return
+    configs1 = configs1_leg(args, pkg, capi, np, local) if (world == 1 and not args.no_configs1) else None
 
     # ---------------- roofline of the dominant kernel (k_rollout) ----------------
     ms_launch = sum(roll_ms) / len(roll_ms)           # one k_rollout launch per rollout leg (rank 0's own)
@@ -434,15 +723,13 @@ def main():
         achieved = (FLOP_PHYS + FLOP_ACTOR) * steps_launch / (ms_launch * 1e-3) / 1e12
     # dram__bytes_read.sum + dram__bytes_write.sum of one k_rollout launch at this exact shape, from the committed
     # `ncu --set full` capture (profiles/NCU_TRAFFIC.json; algorithmic bytes are 41 B x N x T = 344 MB)
-    traffic = None
-    try:
-        tj = json.load(open(os.path.join(ROOT, "profiles", "NCU_TRAFFIC.json")))
-        traffic = tj.get(f"k_rollout_{args.precision}_{N}x{T}")
-    except Exception:
-        pass
+    traffic, traffic_src = _ncu_traffic(f"k_rollout_{args.precision}_{N}x{T}")
     roofline = {"kernel": "k_rollout", "bound": bound, "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                "frac": achieved / peak if peak else None, "traffic": traffic,
-                "peak_source": "b2_measure_fma_peak (live FMA-issue microbenchmark, this GPU, this run)",
+                "frac": achieved / peak if peak else None, "traffic": traffic, "traffic_source": traffic_src,
+                "peak_measured": peak64_meas if args.precision == "f64" else peak32_meas,
+                "peak_arithmetic": arith64 if args.precision == "f64" else arith32,
+                "peak_source": "max(b2_measure_fma_peak: live FMA-issue microbenchmark on this GPU in this run, arithmetic: "
+                               f"SMs x lanes x 2 x {sm_mhz:.0f} MHz sampled under load)",
                 "flop_per_env_step": FLOP_PHYS if args.precision == "f64" else FLOP_PHYS + FLOP_ACTOR,
                 "hbm": {"achieved_gbs": BYTES_STEP * steps_launch / (ms_launch * 1e-3) / 1e9, "peak_gbs": hbm_peak,
                         "peak_source": hbm_src}}
@@ -454,6 +741,7 @@ def main():
                   "minibatches": 1, "samples": N * T,
                   "roofline": {"kernel": "k_ppo_grad", "bound": "fp32-fma", "achieved": ua, "peak": peak32,
                                "unit": "TFLOP/s", "frac": ua / peak32 if peak32 else None,
+                               "peak_measured": peak32_meas, "peak_arithmetic": arith32,
                                "hbm_achieved_gbs": BYTES_UPDATE * N * T * args.epochs / (ums * 1e-3) / 1e9},
                   "last_loss": st.loss}
 
@@ -478,11 +766,16 @@ def main():
                        "l2": "inputs larger than L2 (344 MB trajectory buffer rewritten per step)",
                        "parallelism": f"env-sharded x{world}, NCCL grad all-reduce"},
             "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "update": update,
-            "update_wide": update_wide, "cpu_baseline": cpu_baseline, "fma_peaks_tflops": {"fp32": peak32, "fp64": peak64},
+            "update_wide": update_wide, "c4": c4, "configs1": configs1, "multi_gpu_check": mcheck,
+            "cpu_baseline": cpu_baseline,
+            "fma_peaks_tflops": {"fp32_measured": peak32_meas, "fp64_measured": peak64_meas, "fp32_arithmetic": arith32,
+                                 "fp64_arithmetic": arith64, "sm_mhz": sm_mhz},
             "wall_s_timed_region": t_wall}
     print(json.dumps(line), flush=True)
     if dist:
         dist.destroy_process_group()
+    if mcheck is not None and not mcheck["ok"]:
+        raise SystemExit(1)
 
 
 if __name__ == "__main__":
