@@ -201,6 +201,10 @@ int b2_flush_l2(b2_handle h);                                  /* overwrite a >L
 int b2_measure_fma_peak(b2_handle h, int fp64, double* tflops); /* CUDA-core FMA issue peak of this GPU (roofline denominator) */
 int b2_host_alloc(void** p, size_t bytes);                     /* pinned host memory for the host-buffer entry points */
 int b2_host_free(void* p);
+/* debug: with B2_GUARD=1 in the environment every device buffer of the library is allocated between two 4-KiB guard
+ * zones and poisoned with 0xFF; this checks every guard zone of every live allocation of the process.  Returns the
+ * number of corrupted zones (0 = clean; b2_last_error names the first), -1 when guard mode is off. */
+int b2_debug_guard_check(void);
 /* diagnostic for the tensor-core path of wide nets: C[M][N] = A[M][K] . B[N][K]^T (host fp32 in/out) through the
  * bf16x3 tcgen05 GEMM that the 2x256 update uses; N % 32 == 0, N <= 256; splits > 1 exercises the split-K partials.
  * mn_major = 1: operands are given contraction-major, A[K][M] and B[K][N] (the layout of dW2 = D2^T H1), M, N % 64 == 0;

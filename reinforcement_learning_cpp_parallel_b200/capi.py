@@ -56,6 +56,7 @@ _H = C.c_void_p
 _P = C.POINTER
 SYMBOLS = {
     "b2_abi_version": (C.c_int, []),
+    "b2_debug_guard_check": (C.c_int, []),
     "b2_last_error": (C.c_char_p, []),
     "b2_device_count": (C.c_int, []),
     "b2_config_default": (C.c_int, [_P(Config)]),

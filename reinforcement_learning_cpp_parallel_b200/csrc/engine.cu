@@ -13,6 +13,8 @@
 #include <string.h>
 
 #include <algorithm>
+#include <map>
+#include <mutex>
 #include <fstream>
 #include <new>
 #include <sstream>
@@ -44,6 +46,42 @@ int set_error(int code, const char* fmt, ...) {
   vsnprintf(g_err, sizeof g_err, fmt, ap);
   va_end(ap);
   return code;
+}
+
+// ---- debug allocator (engine.h) ----
+namespace {
+constexpr size_t GUARD_BYTES = 4096;
+struct GuardBook {
+  std::mutex mu;
+  std::map<void*, size_t> live;   // payload pointer -> payload bytes
+};
+GuardBook& guard_book() { static GuardBook b; return b; }
+bool guard_on() {
+  static const bool on = [] { const char* e = getenv("B2_GUARD"); return e && e[0] == '1'; }();
+  return on;
+}
+}  // namespace
+
+cudaError_t dmalloc_bytes(void** p, size_t bytes) {
+  if (!guard_on()) return cudaMalloc(p, bytes);
+  char* base = nullptr;
+  const size_t padded = ((bytes + 255) / 256) * 256;
+  cudaError_t e = cudaMalloc(&base, padded + 2 * GUARD_BYTES);
+  if (e != cudaSuccess) return e;
+  if ((e = cudaMemset(base, 0xA5, padded + 2 * GUARD_BYTES)) != cudaSuccess) return e;
+  if ((e = cudaMemset(base + GUARD_BYTES, 0xFF, bytes)) != cudaSuccess) return e;   // poison: NaN / -1
+  *p = base + GUARD_BYTES;
+  std::lock_guard<std::mutex> lk(guard_book().mu);
+  guard_book().live[*p] = bytes;
+  return cudaSuccess;
+}
+cudaError_t dfree(void* p) {
+  if (!p || !guard_on()) return cudaFree(p);
+  {
+    std::lock_guard<std::mutex> lk(guard_book().mu);
+    guard_book().live.erase(p);
+  }
+  return cudaFree(static_cast<char*>(p) - GUARD_BYTES);
 }
 
 static bool load_nccl() {
@@ -160,36 +198,36 @@ int ensure_traj(b2_engine* E, int64_t cap) {
   Traj& t = E->tr;
   if (cap <= t.cap && (!E->trace || t.state_trace)) return B2_OK;
   if (cap > t.cap) {
-    cudaFree(t.obs); cudaFree(t.action); cudaFree(t.logp); cudaFree(t.mu); cudaFree(t.reward);
-    cudaFree(t.ret); cudaFree(t.vboot); cudaFree(t.vcur); cudaFree(t.flags); cudaFree(t.state_trace);
+    dfree(t.obs); dfree(t.action); dfree(t.logp); dfree(t.mu); dfree(t.reward);
+    dfree(t.ret); dfree(t.vboot); dfree(t.vcur); dfree(t.flags); dfree(t.state_trace);
     t = Traj();
     t.cap = cap;
-    CK(cudaMalloc(&t.obs, sizeof(float) * OBS * cap));
-    CK(cudaMalloc(&t.action, sizeof(float) * cap));
-    CK(cudaMalloc(&t.logp, sizeof(float) * cap));
-    CK(cudaMalloc(&t.mu, sizeof(float) * cap));
-    CK(cudaMalloc(&t.reward, sizeof(float) * cap));
-    CK(cudaMalloc(&t.ret, sizeof(float) * cap));
-    CK(cudaMalloc(&t.vboot, sizeof(float) * cap));
-    CK(cudaMalloc(&t.vcur, sizeof(float) * cap));
-    CK(cudaMalloc(&t.flags, cap));
+    CK(dmalloc(&t.obs, sizeof(float) * OBS * cap));
+    CK(dmalloc(&t.action, sizeof(float) * cap));
+    CK(dmalloc(&t.logp, sizeof(float) * cap));
+    CK(dmalloc(&t.mu, sizeof(float) * cap));
+    CK(dmalloc(&t.reward, sizeof(float) * cap));
+    CK(dmalloc(&t.ret, sizeof(float) * cap));
+    CK(dmalloc(&t.vboot, sizeof(float) * cap));
+    CK(dmalloc(&t.vcur, sizeof(float) * cap));
+    CK(dmalloc(&t.flags, cap));
     E->have_traj = false;
   }
-  if (E->trace && !t.state_trace) CK(cudaMalloc(&t.state_trace, sizeof(double) * 4 * t.cap));
+  if (E->trace && !t.state_trace) CK(dmalloc(&t.state_trace, sizeof(double) * 4 * t.cap));
   return B2_OK;
 }
 
 int ensure_stage(b2_engine* E, int64_t floats, int64_t bytes_u8) {
   if (floats > E->stage_floats) {
-    cudaFree(E->stage);
+    dfree(E->stage);
     E->stage = nullptr;
-    CK(cudaMalloc(&E->stage, sizeof(float) * floats));
+    CK(dmalloc(&E->stage, sizeof(float) * floats));
     E->stage_floats = floats;
   }
   if (bytes_u8 > E->stage_u8_n) {
-    cudaFree(E->stage_u8);
+    dfree(E->stage_u8);
     E->stage_u8 = nullptr;
-    CK(cudaMalloc(&E->stage_u8, bytes_u8));
+    CK(dmalloc(&E->stage_u8, bytes_u8));
     E->stage_u8_n = bytes_u8;
   }
   return B2_OK;
@@ -224,12 +262,12 @@ int run_returns(b2_engine* E) {
     }
   }
   if (returns_needs_segment_list(E->tr)) {
-    if (!E->seg_count) CK(cudaMalloc(&E->seg_count, sizeof *E->seg_count));
+    if (!E->seg_count) CK(dmalloc(&E->seg_count, sizeof *E->seg_count));
     if (B > E->seg_cap) {
-      cudaFree(E->seg_ends);
+      dfree(E->seg_ends);
       E->seg_ends = nullptr;
       E->seg_cap = 0;
-      CK(cudaMalloc(&E->seg_ends, sizeof(int64_t) * (size_t)B));
+      CK(dmalloc(&E->seg_ends, sizeof(int64_t) * (size_t)B));
       E->seg_cap = B;
     }
   }
@@ -256,18 +294,18 @@ int run_update(b2_engine* E, b2_update_stats* stats) {
   int rc0 = run_returns(E);  // once, at entry (:207-236)
   if (rc0) return rc0;
   if (steps > E->loss_log_cap) {
-    cudaFree(E->loss_log);
+    dfree(E->loss_log);
     E->loss_log = nullptr;
-    CK(cudaMalloc(&E->loss_log, sizeof(double) * 4 * steps));
+    CK(dmalloc(&E->loss_log, sizeof(double) * 4 * steps));
     E->loss_log_cap = steps;
   }
   CK(cudaMemsetAsync(E->loss_log, 0, sizeof(double) * 4 * steps, E->stream));
   const int64_t per = B / M;
   int rows_needed = E->wide ? 0 : update_grid_for(per + (B % M), E->sm_count);
   if (rows_needed > E->partial_rows) {
-    cudaFree(E->partials);
+    dfree(E->partials);
     E->partials = nullptr;
-    CK(cudaMalloc(&E->partials, sizeof(float) * (size_t)rows_needed * E->pstride));
+    CK(dmalloc(&E->partials, sizeof(float) * (size_t)rows_needed * E->pstride));
     E->partial_rows = rows_needed;
   }
   // The means are over the GLOBAL (mini)batch (src/ppo_nn.cpp:302: one mean over the merged memory).  Ranks may hold
@@ -275,7 +313,7 @@ int run_update(b2_engine* E, b2_update_stats* stats) {
   // all-reduced: [0] a regular minibatch, [1] the last one (which takes the remainder of B / M).
   int64_t denom_g[2] = {per, B - (int64_t)(M - 1) * per};
   if (E->world > 1) {
-    if (!E->denom_dev) CK(cudaMalloc(&E->denom_dev, 2 * sizeof(int64_t)));
+    if (!E->denom_dev) CK(dmalloc(&E->denom_dev, 2 * sizeof(int64_t)));
     CK(cudaMemcpyAsync(E->denom_dev, denom_g, sizeof denom_g, cudaMemcpyHostToDevice, E->stream));
     int ne = g_nccl.AllReduce(E->denom_dev, E->denom_dev, 2, NCCL_INT64, NCCL_SUM, E->comm, E->stream);
     if (ne != 0) return set_error(B2_ERR_COMM, "ncclAllReduce(sample counts): %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(ne) : "?");
@@ -363,7 +401,7 @@ int setup_peer_exchange(b2_engine* E) {
   const char* env = getenv("B2_COMM_P2P");
   const bool want = !(env && env[0] == '0') && E->world <= B2_MAX_PEERS && g_nccl.AllGather;
   const size_t buf_bytes = xchg_slot_bytes(E);
-  CK(cudaMalloc(&E->xchg, buf_bytes + 256));
+  CK(cudaMalloc(&E->xchg, buf_bytes + 256));   // plain: cudaIpcGetMemHandle wants the allocation base
   CK(cudaMemset(E->xchg, 0, buf_bytes + 256));
   struct Rec { cudaIpcMemHandle_t h; int ok; int pad[3]; };
   static_assert(sizeof(Rec) == 80, "record size");
@@ -371,11 +409,11 @@ int setup_peer_exchange(b2_engine* E) {
   mine.ok = want && cudaIpcGetMemHandle(&mine.h, E->xchg) == cudaSuccess;
   cudaGetLastError();
   Rec* d_recs = nullptr;
-  CK(cudaMalloc(&d_recs, sizeof(Rec) * E->world));
+  CK(dmalloc(&d_recs, sizeof(Rec) * E->world));
   CK(cudaMemcpyAsync(d_recs + E->rank, &mine, sizeof(Rec), cudaMemcpyHostToDevice, E->stream));
   std::vector<Rec> recs((size_t)E->world);
   int ne = g_nccl.AllGather ? g_nccl.AllGather(d_recs + E->rank, d_recs, sizeof(Rec), NCCL_UINT8, E->comm, E->stream) : 1;
-  if (ne != 0) { cudaFree(d_recs); return B2_OK; }          // no exchange possible: NCCL all-reduce path
+  if (ne != 0) { dfree(d_recs); return B2_OK; }          // no exchange possible: NCCL all-reduce path
   CK(cudaMemcpyAsync(recs.data(), d_recs, sizeof(Rec) * E->world, cudaMemcpyDeviceToHost, E->stream));
   CK(cudaStreamSynchronize(E->stream));
   bool ok = true;
@@ -399,7 +437,7 @@ int setup_peer_exchange(b2_engine* E) {
     CK(cudaMemcpyAsync(&sum, d_ok, sizeof(float), cudaMemcpyDeviceToHost, E->stream));
     CK(cudaStreamSynchronize(E->stream));
   }
-  cudaFree(d_recs);
+  dfree(d_recs);
   E->p2p = ne == 0 && (int)(sum + 0.5f) == E->world;
   if (!E->p2p)
     for (int r = 0; r < E->world; r++)
@@ -559,12 +597,12 @@ static int create_body(b2_engine* E, const b2_config* cfg, bool is_default_net) 
   CK(cudaEventCreate(&E->ev0));
   CK(cudaEventCreate(&E->ev1));
   const int64_t NE = cfg->n_envs;
-  CK(cudaMalloc(&E->params, sizeof(float) * E->P));
-  CK(cudaMalloc(&E->adam_m, sizeof(float) * E->P));
-  CK(cudaMalloc(&E->adam_v, sizeof(float) * E->P));
-  CK(cudaMalloc(&E->grads, sizeof(float) * E->pstride));
-  CK(cudaMalloc(&E->adam_step, sizeof(int64_t)));
-  CK(cudaMalloc(&E->status, sizeof(int)));
+  CK(dmalloc(&E->params, sizeof(float) * E->P));
+  CK(dmalloc(&E->adam_m, sizeof(float) * E->P));
+  CK(dmalloc(&E->adam_v, sizeof(float) * E->P));
+  CK(dmalloc(&E->grads, sizeof(float) * E->pstride));
+  CK(dmalloc(&E->adam_step, sizeof(int64_t)));
+  CK(dmalloc(&E->status, sizeof(int)));
   CK(cudaMallocHost(&E->status_host, sizeof(int)));
   CK(cudaMemset(E->params, 0, sizeof(float) * E->P));
   CK(cudaMemset(E->adam_m, 0, sizeof(float) * E->P));
@@ -574,14 +612,14 @@ static int create_body(b2_engine* E, const b2_config* cfg, bool is_default_net) 
   CK(cudaMemset(E->status, 0, sizeof(int)));
   // episodes one env can finish inside one rollout: TIMEUP every n_timestep steps; with early termination every step
   E->max_eps = (cfg->env_flags & B2_ENV_EARLY_TERM) ? cfg->horizon + 1 : cfg->horizon / cfg->n_timestep + 2;
-  CK(cudaMalloc(&E->env_term, (size_t)cfg->n_envs));
+  CK(dmalloc(&E->env_term, (size_t)cfg->n_envs));
   CK(cudaMemset(E->env_term, 0, (size_t)cfg->n_envs));
-  CK(cudaMalloc(&E->state, sizeof(double) * 4 * NE));
-  CK(cudaMalloc(&E->ep_step, sizeof(int32_t) * NE));
-  CK(cudaMalloc(&E->ep_count, sizeof(int32_t) * NE));
-  CK(cudaMalloc(&E->ep_ret, sizeof(float) * NE));
-  CK(cudaMalloc(&E->ep_log, sizeof(float) * NE * E->max_eps));
-  CK(cudaMalloc(&E->progress, sizeof(int) * ((NE + 31) / 32)));
+  CK(dmalloc(&E->state, sizeof(double) * 4 * NE));
+  CK(dmalloc(&E->ep_step, sizeof(int32_t) * NE));
+  CK(dmalloc(&E->ep_count, sizeof(int32_t) * NE));
+  CK(dmalloc(&E->ep_ret, sizeof(float) * NE));
+  CK(dmalloc(&E->ep_log, sizeof(float) * NE * E->max_eps));
+  CK(dmalloc(&E->progress, sizeof(int) * ((NE + 31) / 32)));
   CK(cudaMemset(E->state, 0, sizeof(double) * 4 * NE));   // CartPole::reset: u = 0 (cart_pole.h:86)
   if (cfg->env_flags & B2_ENV_RANDOM_INIT) {
     cudaError_t ce = launch_env_init(E->state, NE, cfg->env_flags, cfg->seed, cfg->env_offset, 0, E->stream);
@@ -612,7 +650,7 @@ int b2_destroy(b2_handle E) {
                   E->ep_step, E->ep_count, E->ep_ret, E->ep_log, t.obs, t.action, t.logp, t.mu, t.reward, t.ret,
                   t.vboot, t.vcur, t.flags, t.state_trace, E->forced, E->stage, E->stage_u8, E->status, E->flush_buf,
                   E->progress, E->env_term, E->seg_ends, E->seg_count, E->denom_dev};
-  for (void* p : ptrs) cudaFree(p);
+  for (void* p : ptrs) dfree(p);
   for (int r = 0; r < B2_MAX_PEERS; r++)
     if (r != E->rank && E->peer_base[r]) cudaIpcCloseMemHandle(E->peer_base[r]);
   cudaFree(E->xchg);
@@ -984,9 +1022,9 @@ static int rollout_prepare(b2_engine* E, int T, const float* forced_action) {
   if (rc) return rc;
   if (forced_action) {
     if (NE * T > E->forced_cap) {
-      cudaFree(E->forced);
+      dfree(E->forced);
       E->forced = nullptr;
-      CK(cudaMalloc(&E->forced, sizeof(float) * NE * T));
+      CK(dmalloc(&E->forced, sizeof(float) * NE * T));
       E->forced_cap = NE * T;
     }
     CK(cudaMemcpyAsync(E->forced, forced_action, sizeof(float) * NE * T, cudaMemcpyHostToDevice, E->stream));
@@ -1215,7 +1253,7 @@ int b2_flush_l2(b2_handle E) {
   NEED(E);
   if (!E->flush_buf) {
     E->flush_n = (int64_t)160 << 18;  // 160 MiB of floats: larger than the 126 MB L2
-    CK(cudaMalloc(&E->flush_buf, sizeof(float) * E->flush_n));
+    CK(dmalloc(&E->flush_buf, sizeof(float) * E->flush_n));
   }
   cudaError_t ce = launch_flush(E->flush_buf, E->flush_n, E->stream);
   if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "flush: %s", cudaGetErrorString(ce));
@@ -1241,9 +1279,9 @@ int b2_selftest_gemm(b2_handle E, int M, int N, int K, const float* A, const flo
   if (!A || !B || !C || M < 1 || N < 1 || K < 1) return set_error(B2_ERR_INVALID, "selftest_gemm: bad argument");
   CK(cudaSetDevice(E->cfg.device));
   float *dA = nullptr, *dB = nullptr, *dC = nullptr;
-  CK(cudaMalloc(&dA, sizeof(float) * (size_t)M * K));
-  CK(cudaMalloc(&dB, sizeof(float) * (size_t)N * K));
-  CK(cudaMalloc(&dC, sizeof(float) * (size_t)M * N));
+  CK(dmalloc(&dA, sizeof(float) * (size_t)M * K));
+  CK(dmalloc(&dB, sizeof(float) * (size_t)N * K));
+  CK(dmalloc(&dC, sizeof(float) * (size_t)M * N));
   CK(cudaMemcpyAsync(dA, A, sizeof(float) * (size_t)M * K, cudaMemcpyHostToDevice, E->stream));
   CK(cudaMemcpyAsync(dB, B, sizeof(float) * (size_t)N * K, cudaMemcpyHostToDevice, E->stream));
   int rc = wide_selftest_gemm(M, N, K, dA, dB, dC, splits, mn_major, E->sm_count, E->stream);
@@ -1252,8 +1290,35 @@ int b2_selftest_gemm(b2_handle E, int M, int N, int K, const float* A, const flo
     cudaError_t ce = cudaMemcpy(C, dC, sizeof(float) * (size_t)M * N, cudaMemcpyDeviceToHost);
     if (ce != cudaSuccess) rc = set_error(B2_ERR_CUDA, "selftest_gemm D2H: %s", cudaGetErrorString(ce));
   }
-  cudaFree(dA); cudaFree(dB); cudaFree(dC);
+  dfree(dA); dfree(dB); dfree(dC);
   return rc;
+}
+
+// every guard zone of every live device allocation of this process (B2_GUARD=1): number of corrupted zones, 0 = clean,
+// -1 = guard mode is off.  The message names the first offender.
+int b2_debug_guard_check(void) {
+  if (!guard_on()) return -1;
+  std::lock_guard<std::mutex> lk(guard_book().mu);
+  cudaDeviceSynchronize();
+  std::vector<unsigned char> buf(GUARD_BYTES);
+  int bad = 0;
+  for (auto& kv : guard_book().live) {
+    char* p = static_cast<char*>(kv.first);
+    const size_t bytes = kv.second;
+    for (int side = 0; side < 2; side++) {
+      const char* zone = side == 0 ? p - GUARD_BYTES : p + bytes;
+      const size_t n = GUARD_BYTES;   // after the payload: the alignment padding, then the guard zone (all 0xA5)
+      if (cudaMemcpy(buf.data(), zone, n, cudaMemcpyDeviceToHost) != cudaSuccess) { cudaGetLastError(); continue; }
+      for (size_t i = 0; i < n; i++)
+        if (buf[i] != 0xA5) {
+          if (!bad) set_error(B2_ERR_STATE, "guard zone %s a %zu-byte device allocation was overwritten (first bad byte at offset %zu)",
+                              side == 0 ? "BEFORE" : "AFTER", bytes, i);
+          bad++;
+          break;
+        }
+    }
+  }
+  return bad;
 }
 
 int b2_host_free(void* p) {

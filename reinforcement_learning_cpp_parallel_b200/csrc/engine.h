@@ -25,6 +25,16 @@ struct PerDeviceOnce {
 };
 
 
+// Debug allocator behind every device buffer of the engine.  With B2_GUARD=1 in the environment (read once) an
+// allocation gets a 4-KiB guard zone on either side filled with 0xA5 and its payload filled with 0xFF (a NaN for every
+// float, -1 for every integer: reading memory nobody wrote shows up in the results); b2_debug_guard_check() verifies
+// every guard zone of every live allocation.  This is the memcheck / initcheck stand-in where compute-sanitizer cannot
+// be run (tests/test_gpu_guard.py).  Without B2_GUARD it is plain cudaMalloc / cudaFree.
+cudaError_t dmalloc_bytes(void** p, size_t bytes);
+cudaError_t dfree(void* p);
+template <class T>
+inline cudaError_t dmalloc(T** p, size_t bytes) { return dmalloc_bytes(reinterpret_cast<void**>(p), bytes); }
+
 // Device-resident trajectory buffer, SoA, flat index k = t * n_envs + e (time-major).
 //   obs[c * cap + k]  c < 6          24 B/record
 //   action, logp, mu, reward, ret    f32 each

@@ -479,10 +479,10 @@ int64_t wide_chunk_cap(const WideNet* w) { return w ? w->cap : 0; }
 
 void wide_destroy(WideNet* w) {
   if (!w) return;
-  cudaFree(w->w2p); cudaFree(w->h1p); cudaFree(w->d2p);
-  cudaFree(w->bias2); cudaFree(w->h2); cudaFree(w->d1); cudaFree(w->coef);
-  cudaFree(w->part_head); cudaFree(w->part_dw1); cudaFree(w->part_dw2); cudaFree(w->bar_counter);
-  cudaFree(w->boot_idx); cudaFree(w->boot_count);
+  dfree(w->w2p); dfree(w->h1p); dfree(w->d2p);
+  dfree(w->bias2); dfree(w->h2); dfree(w->d1); dfree(w->coef);
+  dfree(w->part_head); dfree(w->part_dw1); dfree(w->part_dw2); dfree(w->bar_counter);
+  dfree(w->boot_idx); dfree(w->boot_count);
   delete w;
 }
 
@@ -507,13 +507,13 @@ int wide_create(WideNet** out, int H1, int H2, int64_t max_chunk, int sm_count) 
       return set_error(B2_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(_e));                                \
     }                                                                                                        \
   } while (0)
-  WCK(cudaMalloc(&w->w2p, bf * 4 * H2 * H1));
-  WCK(cudaMalloc(&w->h1p, bf * 4 * cap * H1));
-  WCK(cudaMalloc(&w->d2p, bf * 4 * cap * H2));
-  WCK(cudaMalloc(&w->bias2, sizeof(float) * 2 * H2));
-  WCK(cudaMalloc(&w->coef, sizeof(AdamCoef)));
-  WCK(cudaMalloc(&w->h2, sizeof(float) * 2 * cap * H2));
-  WCK(cudaMalloc(&w->d1, sizeof(float) * 2 * cap * H1));
+  WCK(dmalloc(&w->w2p, bf * 4 * H2 * H1));
+  WCK(dmalloc(&w->h1p, bf * 4 * cap * H1));
+  WCK(dmalloc(&w->d2p, bf * 4 * cap * H2));
+  WCK(dmalloc(&w->bias2, sizeof(float) * 2 * H2));
+  WCK(dmalloc(&w->coef, sizeof(AdamCoef)));
+  WCK(dmalloc(&w->h2, sizeof(float) * 2 * cap * H2));
+  WCK(dmalloc(&w->d1, sizeof(float) * 2 * cap * H1));
   // stale bits must never be NaN where a zero-weighted product could meet them
   WCK(cudaMemset(w->h1p, 0, bf * 4 * cap * H1));
   WCK(cudaMemset(w->d2p, 0, bf * 4 * cap * H2));
@@ -521,15 +521,15 @@ int wide_create(WideNet** out, int H1, int H2, int64_t max_chunk, int sm_count) 
   w->head_row = 2 * H2 + 4;
   w->dw1_blocks = sm_count;
   w->splits_max = sm_count;
-  WCK(cudaMalloc(&w->part_head, sizeof(float) * (size_t)w->head_blocks * 2 * w->head_row));
-  WCK(cudaMalloc(&w->part_dw1, sizeof(float) * (size_t)w->dw1_blocks * 2 * H1 * 8));
-  WCK(cudaMalloc(&w->part_dw2, sizeof(float) * (size_t)2 * w->splits_max * H2 * H1));
+  WCK(dmalloc(&w->part_head, sizeof(float) * (size_t)w->head_blocks * 2 * w->head_row));
+  WCK(dmalloc(&w->part_dw1, sizeof(float) * (size_t)w->dw1_blocks * 2 * H1 * 8));
+  WCK(dmalloc(&w->part_dw2, sizeof(float) * (size_t)2 * w->splits_max * H2 * H1));
   WCK(cudaMemset(w->part_dw2, 0, sizeof(float) * (size_t)2 * w->splits_max * H2 * H1));
   { const char* e = getenv("B2_WIDE_DETERMINISTIC"); w->dw2_add = !(e && e[0] == '1'); }
   w->fuse_reduce = w->dw2_add && getenv("B2_WIDE_FUSE_REDUCE") != nullptr;
-  WCK(cudaMalloc(&w->bar_counter, sizeof(int)));
+  WCK(dmalloc(&w->bar_counter, sizeof(int)));
   WCK(cudaMemset(w->bar_counter, 0, sizeof(int)));
-  WCK(cudaMalloc(&w->boot_count, sizeof(int)));
+  WCK(dmalloc(&w->boot_count, sizeof(int)));
 #undef WCK
   int rc = 0;
   const uint64_t ucap = (uint64_t)cap;
@@ -735,9 +735,9 @@ cudaError_t launch_wide_act_finish(const float* mu, const float* eps, int64_t n,
 int wide_bootstrap(WideNet* w, const float* params, const Traj& tr, cudaStream_t st, int64_t* launches) {
   const int64_t B = tr.n_envs * tr.horizon;
   if (B > w->boot_cap) {
-    cudaFree(w->boot_idx);
+    dfree(w->boot_idx);
     w->boot_idx = nullptr;
-    B2_CUDA_CHECK(cudaMalloc(&w->boot_idx, sizeof(int32_t) * B));
+    B2_CUDA_CHECK(dmalloc(&w->boot_idx, sizeof(int32_t) * B));
     w->boot_cap = B;
   }
   B2_CUDA_CHECK(cudaMemsetAsync(w->boot_count, 0, sizeof(int), st));
