@@ -147,6 +147,10 @@ int b2_value(b2_handle h, const float* obs, int64_t n, float* value);
 /* ---- update on a trajectory batch: replaces PPO::update(MemoryNN) (src/ppo_nn.cpp:205-307) */
 int b2_update(b2_handle h, const b2_batch* batch, b2_update_stats* stats);
 int b2_returns(b2_handle h, const b2_batch* batch, float* returns); /* the returns part only (:207-236) */
+/* which evaluate/backward kernel the last update ran: 0 = FP32 FMA (k_ppo_grad; reference-sized batches), 1 = bf16x3
+ * tensor cores (k_ppo_grad_tc; global minibatch >= 32,768 rows; B2_UPDATE_TC=0/1 in the environment forces either),
+ * 2 = wide nets (tcgen05 GEMMs) */
+int b2_last_update_path(b2_handle h);
 /* loss terms of every optimizer step of the last update (n = optimizer_steps; arrays may be NULL) */
 int b2_last_update_losses(b2_handle h, double* loss1, double* loss2, double* loss3, double* loss, int n);
 

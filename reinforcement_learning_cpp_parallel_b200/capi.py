@@ -57,6 +57,7 @@ _P = C.POINTER
 SYMBOLS = {
     "b2_abi_version": (C.c_int, []),
     "b2_debug_guard_check": (C.c_int, []),
+    "b2_last_update_path": (C.c_int, [_H]),
     "b2_last_error": (C.c_char_p, []),
     "b2_device_count": (C.c_int, []),
     "b2_config_default": (C.c_int, [_P(Config)]),
@@ -257,6 +258,10 @@ class Engine:
         R = np.empty(keep[3].size, np.float32)
         _ck(self.L.b2_returns(self.h, C.byref(b), _vp(R)))
         return R
+
+    def last_update_path(self):
+        """0 FP32 FMA kernel, 1 bf16x3 tensor-core kernel, 2 wide nets."""
+        return int(self.L.b2_last_update_path(self.h))
 
     def last_update_losses(self, n):
         out = [np.empty(n, np.float64) for _ in range(4)]

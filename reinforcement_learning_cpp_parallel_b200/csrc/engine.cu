@@ -152,6 +152,7 @@ struct b2_engine {
   int64_t* seg_ends = nullptr;
   int64_t seg_cap = 0;
   unsigned long long* seg_count = nullptr;
+  int last_update_path = 0;       // 0 FP32 FMA kernel, 1 bf16x3 tensor-core kernel, 2 wide nets (tcgen05)
   int64_t* denom_dev = nullptr;   // [2] global sample counts of a regular / the last minibatch (all-reduced over ranks)
   uint64_t act_calls = 0;
   int64_t launches = 0;
@@ -277,6 +278,13 @@ int run_returns(b2_engine* E) {
   return B2_OK;
 }
 
+// B2_UPDATE_TC=0 / 1 forces the FP32 / the tensor-core kernel (A/B measurements, parity tests of either on any shape)
+bool use_tensor_update(int64_t global_count) {
+  const char* e = getenv("B2_UPDATE_TC");   // read per update: tests flip it between engines of one process
+  if (e && (e[0] == '0' || e[0] == '1')) return e[0] == '1';
+  return global_count >= 32768;
+}
+
 int setup_peer_exchange(b2_engine* E);
 void next_peer_step(b2_engine* E, UpdateArgs& a);
 inline size_t xchg_slot_bytes(const b2_engine* E) {
@@ -301,7 +309,7 @@ int run_update(b2_engine* E, b2_update_stats* stats) {
   }
   CK(cudaMemsetAsync(E->loss_log, 0, sizeof(double) * 4 * steps, E->stream));
   const int64_t per = B / M;
-  int rows_needed = E->wide ? 0 : update_grid_for(per + (B % M), E->sm_count);
+  int rows_needed = E->wide ? 0 : std::max(update_grid_for(per + (B % M), E->sm_count), update_grid_for_tc(per + (B % M), E->sm_count));
   if (rows_needed > E->partial_rows) {
     dfree(E->partials);
     E->partials = nullptr;
@@ -330,7 +338,11 @@ int run_update(b2_engine* E, b2_update_stats* stats) {
       a.first = (int64_t)m * per;
       a.count = (m == M - 1) ? (B - a.first) : per;
       a.denom = denom_g[m == M - 1];      // samples of this minibatch over ALL ranks
-      a.grid = update_grid_for(a.count, E->sm_count);
+      // default nets: the FP32 FMA kernel for reference-sized batches, the bf16x3 tensor-core kernel once the GLOBAL
+      // minibatch is a real GEMM (>= 32,768 rows; decided on the global count so that every sharding takes the same path)
+      const bool tc = !E->wide && use_tensor_update(a.denom);
+      E->last_update_path = E->wide ? 2 : (tc ? 1 : 0);
+      a.grid = tc ? update_grid_for_tc(a.count, E->sm_count) : update_grid_for(a.count, E->sm_count);
       a.step_slot = slot;
       // several GPUs: the reduce + Adam kernel exchanges every gradient element with its peers over NVLink peer memory
       // (engine.h PeerXchg); reduce -> ncclAllReduce -> Adam only if the peer mapping was refused or switched off
@@ -346,7 +358,7 @@ int run_update(b2_engine* E, b2_update_stats* stats) {
         }
         continue;
       }
-      if ((ce = launch_ppo_grad(a, E->stream)) != cudaSuccess) return set_error(B2_ERR_CUDA, "ppo_grad: %s", cudaGetErrorString(ce));
+      if ((ce = tc ? launch_ppo_grad_tc(a, E->stream) : launch_ppo_grad(a, E->stream)) != cudaSuccess) return set_error(B2_ERR_CUDA, "ppo_grad: %s", cudaGetErrorString(ce));
       if (E->world == 1 || E->p2p) {   // one kernel: reduce (+ peer-memory exchange) + Adam
         if ((ce = launch_reduce(a, true, E->stream)) != cudaSuccess) return set_error(B2_ERR_CUDA, "reduce: %s", cudaGetErrorString(ce));
         E->launches += 2;
@@ -881,6 +893,8 @@ int b2_returns(b2_handle E, const b2_batch* batch, float* returns) {
   CK(cudaStreamSynchronize(E->stream));
   return B2_OK;
 }
+
+int b2_last_update_path(b2_handle E) { return E ? E->last_update_path : -1; }
 
 int b2_last_update_losses(b2_handle E, double* l1, double* l2, double* l3, double* lt, int n) {
   NEED(E);

@@ -197,6 +197,8 @@ bool returns_needs_segment_list(const Traj& tr);
 cudaError_t launch_returns(const float* params, const Traj& tr, const HyperDev& hp, cudaStream_t st, int* n_launches,
                            bool skip_bootstrap, int64_t* seg_ends, unsigned long long* seg_count);
 int update_grid_for(int64_t count, int sm_count);
+int update_grid_for_tc(int64_t count, int sm_count);                  // ppo_update_tc.cu: the bf16x3 tensor-core kernel
+cudaError_t launch_ppo_grad_tc(const UpdateArgs& a, cudaStream_t st);
 int update_partial_stride();
 cudaError_t launch_ppo_grad(const UpdateArgs& a, cudaStream_t st);
 cudaError_t launch_reduce(const UpdateArgs& a, bool apply_adam, cudaStream_t st);
