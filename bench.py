@@ -375,6 +375,7 @@ def c4_leg(args, pkg, capi, np, rank, local, world, dist, barrier, max_over_rank
     value = NG * T * reps / (rt * 1e-3)
     upd = NG * T * K * reps / (ut * 1e-3)
     mode = E.comm_mode()
+    upath = E.last_update_path()
     E.close()
     mine_r, mine_u = sum(rms) / reps, sum(ums) / reps
     ach = FLOP_PHYS * n_local * T / (mine_r * 1e-3) / 1e12
@@ -386,8 +387,10 @@ def c4_leg(args, pkg, capi, np, rank, local, world, dist, barrier, max_over_rank
            "roofline": {"kernel": "k_rollout<double>", "bound": "fp64-fma", "achieved": ach, "peak": peak64, "unit": "TFLOP/s",
                         "frac": ach / peak64 if peak64 else None},
            "update": {"value": upd, "unit": "sample-epochs/s", "ms_per_update": ut / reps,
-                      "roofline": {"kernel": "k_ppo_grad", "bound": "fp32-fma", "achieved": uach, "peak": peak32,
-                                   "unit": "TFLOP/s", "frac": uach / peak32 if peak32 else None}},
+                      "kernel_path": {0: "k_ppo_grad (fp32-fma)", 1: "k_ppo_grad_tc (bf16x3 mma.sync)"}.get(upath),
+                      "roofline": {"achieved": uach, "unit": "TFLOP/s", "fp32_fma_peak": peak32,
+                                   "frac_of_fp32_fma_peak": uach / peak32 if peak32 else None,
+                                   "note": "see update.roofline of the main line for the tensor denominators"}},
            "gpu_launches": int(launches), "comm_mode": mode, "last_loss": st.loss}
     # strong-scaling efficiency against the N = 1 run of the same leg ON THIS BOX (the driver runs N = 1, 2, 4, 8 back to
     # back): the N = 1 run leaves its numbers in a scratch file, later runs read it
@@ -654,6 +657,7 @@ def main():
     barrier()
     t_wall = time.time() - t_wall0
     launches = E.kernel_launches() - l0
+    upd_path = E.last_update_path() if upd_ms else None
     clocks = cs.stop() if rank == 0 else None
     roll_total = max_over_ranks(sum(roll_ms))
     upd_total = max_over_ranks(sum(upd_ms)) if upd_ms else 0.0
@@ -737,13 +741,26 @@ def main():
     if upd_ms:
         ums = sum(upd_ms) / len(upd_ms)
         ua = FLOP_UPDATE * N * T * args.epochs / (ums * 1e-3) / 1e12
+        if upd_path == 1:
+            # k_ppo_grad_tc: warp-level bf16x3 MMAs (legacy mma.sync path, HMMA).  Three denominators, all stated: the
+            # measured tcgen05 bf16 peak / 3 (what a tcgen05 formulation could reach; the binding one for "tensor"), the
+            # legacy-HMMA rate this kernel actually issues at (1,024 MAC/clk/SM measured by ncu: profiles/r2/) / 3, and the
+            # FP32-FMA peak that bounded the kernel it replaces (a fraction > 1 means: past the old formulation's roofline)
+            hmma = n_sm * 1024 * 2 * sm_mhz * 1e6 / 1e12
+            uroof = {"kernel": "k_ppo_grad_tc", "bound": "tensor", "achieved": ua, "peak": bf16_peak / 3.0, "unit": "TFLOP/s",
+                     "frac": ua / (bf16_peak / 3.0) if bf16_peak else None,
+                     "peak_source": bf16_src + " / 3 (bf16x3: every fp32 product is three bf16 MMAs)",
+                     "legacy_hmma_peak_div3": hmma / 3.0, "frac_of_legacy_hmma_div3": ua / (hmma / 3.0),
+                     "fp32_fma_peak": peak32, "frac_of_fp32_fma_peak": ua / peak32 if peak32 else None,
+                     "hbm_achieved_gbs": 76 * N * T * args.epochs / (ums * 1e-3) / 1e9}
+        else:
+            uroof = {"kernel": "k_ppo_grad", "bound": "fp32-fma", "achieved": ua, "peak": peak32,
+                     "unit": "TFLOP/s", "frac": ua / peak32 if peak32 else None,
+                     "peak_measured": peak32_meas, "peak_arithmetic": arith32,
+                     "hbm_achieved_gbs": BYTES_UPDATE * N * T * args.epochs / (ums * 1e-3) / 1e9}
         update = {"value": upd_value, "unit": "sample-epochs/s", "ms_per_update": ums, "epochs": args.epochs,
-                  "minibatches": 1, "samples": N * T,
-                  "roofline": {"kernel": "k_ppo_grad", "bound": "fp32-fma", "achieved": ua, "peak": peak32,
-                               "unit": "TFLOP/s", "frac": ua / peak32 if peak32 else None,
-                               "peak_measured": peak32_meas, "peak_arithmetic": arith32,
-                               "hbm_achieved_gbs": BYTES_UPDATE * N * T * args.epochs / (ums * 1e-3) / 1e9},
-                  "last_loss": st.loss}
+                  "minibatches": 1, "samples": N * T, "kernel_path": {0: "fp32-fma", 1: "bf16x3 tensor cores (mma.sync)"}.get(upd_path),
+                  "roofline": uroof, "last_loss": st.loss}
 
     cpu_baseline = None
     if not args.no_cpu_baseline and world == 1:

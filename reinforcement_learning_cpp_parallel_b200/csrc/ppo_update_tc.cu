@@ -176,8 +176,7 @@ __global__ void __launch_bounds__(NT, 1) k_ppo_grad_tc(const UpdateArgs a) {
       for (int h = 0; h < 2; h++) {
         const int64_t s = base + g + 8 * h;
         const bool valid = s < a.count;
-        const int64_t p = a.first + (valid ? s : 0);
-        const int64_t k = a.idx ? (int64_t)a.idx[p] : p;
+        const int64_t k = a.first + (valid ? s : 0);       // minibatches are contiguous ranges (no gather: launch_ppo_grad_tc refuses a.idx)
         if (tig < 3) {
           t.x[2 * h] = valid ? __ldg(a.tr.obs + (int64_t)(2 * tig) * cap + k) : 0.f;
           t.x[2 * h + 1] = valid ? __ldg(a.tr.obs + (int64_t)(2 * tig + 1) * cap + k) : 0.f;
@@ -263,8 +262,7 @@ __global__ void __launch_bounds__(NT, 1) k_ppo_grad_tc(const UpdateArgs a) {
           if (valid) dz = e * inv_denom;
           if (own) {
             loss2_sum = fmaf(e, e, loss2_sum);             // :288  0.5 * MSE
-            const int64_t p = a.first + s;
-            a.tr.vcur[a.idx ? (int64_t)a.idx[p] : p] = V;
+            a.tr.vcur[a.first + s] = V;
           }
         } else if (valid) {
           const float mu = act_tanh(y);                    // ppo_nn.h:102
@@ -447,6 +445,7 @@ int update_grid_for_tc(int64_t count, int sm_count) {
 }
 
 cudaError_t launch_ppo_grad_tc(const UpdateArgs& a, cudaStream_t st) {
+  if (a.idx) return cudaErrorInvalidValue;   // gather indices are a k_ppo_grad feature; the engine's minibatches are ranges
   k_ppo_grad_tc<<<a.grid, NT, SMEM_BYTES, st>>>(a);
   return cudaGetLastError();
 }
