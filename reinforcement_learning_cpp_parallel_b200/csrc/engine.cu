@@ -288,7 +288,8 @@ bool use_tensor_update(int64_t global_count) {
 int setup_peer_exchange(b2_engine* E);
 void next_peer_step(b2_engine* E, UpdateArgs& a);
 inline size_t xchg_slot_bytes(const b2_engine* E) {
-  return ((sizeof(uint2) * 2 * (size_t)E->world * (size_t)E->pstride + 255) / 256) * 256;
+  // slots[2][world][pstride] + sums[2][pstride] (engine.h PeerXchg)
+  return ((sizeof(uint2) * 2 * ((size_t)E->world + 1) * (size_t)E->pstride + 255) / 256) * 256;
 }
 
 // K2 + K optimizer steps on whatever E->tr currently holds.
@@ -464,6 +465,10 @@ void next_peer_step(b2_engine* E, UpdateArgs& a) {
   x.world = E->world; x.rank = E->rank; x.pstride = E->pstride;
   x.epoch = (unsigned)++E->px_epoch;
   x.par_off = (int64_t)(x.epoch & 1u) * E->world * E->pstride;
+  // more than two ranks: reduce-scatter + all-gather shape (B2_COMM_SCATTER=0 / 1 forces either, A/B measurements)
+  const char* sc = getenv("B2_COMM_SCATTER");
+  x.scatter = (sc && (sc[0] == '0' || sc[0] == '1')) ? (sc[0] == '1') : (E->world > 2);
+  x.sum_off = (int64_t)2 * E->world * E->pstride + (int64_t)(x.epoch & 1u) * E->pstride;
   for (int r = 0; r < E->world; r++) x.slots[r] = reinterpret_cast<uint2*>(E->peer_base[r]);
   x.out = E->grads;
   x.status = E->status;

@@ -108,6 +108,38 @@ def test_peer_memory_exchange_equals_nccl_allreduce(monkeypatch):
     assert out["1"][7] == out["0"][7] == K
 
 
+def test_scatter_shaped_exchange_equals_nccl_allreduce(monkeypatch):
+    """More than two ranks exchange gradients reduce-scatter + all-gather shaped (engine.h PeerXchg `scatter`: every
+    element has an owner rank that sums the contributions in rank order and publishes the sum).  Forced on at world = 2
+    (B2_COMM_SCATTER=1), where its rank-order sum must equal ncclAllReduce's bit for bit; default and wide nets."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    for target in (_rank, _wide_rank):
+        out = {}
+        for mode in ("scatter", "nccl"):
+            monkeypatch.setenv("B2_COMM_P2P", "1" if mode == "scatter" else "0")
+            monkeypatch.setenv("B2_COMM_SCATTER", "1")
+            monkeypatch.setenv("B2_WIDE_DETERMINISTIC", "1")   # fixed-order dW2 split-K sum: runs comparable bit for bit
+            ctx = mp.get_context("spawn")
+            q = ctx.Queue()
+            port = _free_port()
+            procs = [ctx.Process(target=target, args=(r, 2, port, q)) for r in range(2)]
+            for p in procs:
+                p.start()
+            res = sorted([q.get(timeout=300) for _ in procs], key=lambda r: r[0])
+            for p in procs:
+                p.join(60)
+            out[mode] = res
+        gi, wi = (4, 5) if target is _rank else (1, 2)
+        for mode in out:
+            np.testing.assert_array_equal(out[mode][0][wi], out[mode][1][wi])      # weights identical across ranks
+            np.testing.assert_array_equal(out[mode][0][gi], out[mode][1][gi])      # and the summed gradient
+        np.testing.assert_array_equal(out["scatter"][0][gi], out["nccl"][0][gi])
+        np.testing.assert_array_equal(out["scatter"][0][wi], out["nccl"][0][wi])
+
+
 # ---- wide nets (BASELINE configs[4]): each rank holds half of every minibatch, gradients all-reduced over NCCL ----
 WB, WK, WM = 2048, 2, 2
 
