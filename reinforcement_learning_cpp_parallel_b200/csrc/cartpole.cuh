@@ -5,8 +5,9 @@
 // One env step is 50 substeps x 6 stages = 300 evaluations of Diff, each needing sin/cos of the pole
 // angle and one true division.  Calling libdevice sincos()/"/" 300 times costs ~150 instructions per
 // stage, two thirds of them integer fix-up code (round-1 ncu, profiles/r1a_*: FP64 pipe 42 % busy, ALU
-// 18 %, instruction fetch the top stall).  The double path therefore restates the two expensive pieces
-// so that a stage is 32 straight-line DFMA/DMUL/DADD and almost nothing else:
+// 18 %, instruction fetch the top stall).  The double path therefore restates the expensive pieces
+// so that a stage is 27 straight-line DFMA/DMUL/DADD (32 in round 1) and almost nothing else -- the kernel is bound by
+// FP64 instruction ISSUE (a DFMA holds the port for two cycles), so every instruction removed is time:
 //   * sin/cos are carried along with the state and ROTATED by the stage's angle increment d
 //     (|d| ~ 1e-5..1e-3; |d| < 1.8e-3 is enforced): sin d and cos d - 1 from two-term Taylor series
 //     (truncation below double rounding in that range), then the angle-addition formulas as two FMAs
@@ -17,6 +18,17 @@
 //     relative between stages, typically 1e-6), followed by one residual correction of the quotient:
 //     error ~ e^4, i.e. < 1e-12 in the worst case and ~1e-24 typically.
 //   * the RK accumulator is kept as W = w / dt and b_i dt is folded into one constant.
+// Round 2 (same algebra, fewer instructions; every change re-checked against the 1e-9 replay gates):
+//   * (sin, cos) ride along SCALED by g: the rotation is linear, so g s and g c rotate like s and c, and g folds
+//     into the constants of fac2, F1 / M and the numerator (one DMUL per stage gone);
+//   * the rotation by d is three shears, (s, c) -> s += c tau, c -= s sigma, s += c tau with tau = tan(d / 2),
+//     sigma = sin d from their two-term series: an EXACT rotation in three FMAs instead of four;
+//   * the carried 1 / fac2 takes one third-order step, r (1 + e + e^2) with e = 1 - fac2 r: |e| < 1.3e-4 while
+//     |d| < 1.8e-3 (fac2 moves by 0.07 d relative per stage), so the quotient is good to e^3 < 2.2e-12 in the worst
+//     case and ~1e-18 typically, and the residual correction (two instructions) is gone;
+//   * x and xdot never feed back into Diff (include/cart_pole.h:161-168 reads theta and thetadot only), so they are not
+//     carried through the low-storage recurrence: unrolling it gives u_final = u_0 + dt sum_j beta_j f_j, and for the
+//     pair (x, xdot) that is one FMA each per stage with precomputed weights (rk_derived()) instead of two each.
 // Measured against the unmodified header: <= 1e-12 relative per env step (tests/test_gpu_parity.py).
 #pragma once
 #include "../../include/b200ppo.h"
@@ -46,19 +58,58 @@ struct CartPoleDyn;
 // Every double constant of the hot loop lives in one __constant__ table so that it reaches the DFMA as
 // a c[bank][offset] operand (ptxas otherwise rebuilds each literal with two UMOVs per use: 312 of the
 // 965 instructions of a substep in the first version).
+// The low-storage recurrence w_i = a_i w_{i-1} + dt f_i, u_i = u_{i-1} + b_i w_i unrolled (include/cart_pole.h:39-43):
+//   u_k = u_0 + dt sum_{j<=k} B[k][j] f_j,   B[k][j] = sum_{i=j..k} b_i prod_{m=j+1..i} a_m,   beta_j = B[5][j].
+// For xdot, f_j = xddot_j.  For x, f_j is xdot BEFORE stage j, i.e. xdot_0 + dt sum_{m<j} B[j-1][m] xddot_m, hence
+//   x_6 = x_0 + dt (sum beta) xdot_0 + dt^2 sum_m gamma_m xddot_m,   gamma_m = sum_{j>m} beta_j B[j-1][m].
+struct RKDerived { double beta[6], gamma[6], cbeta; };
+constexpr RKDerived rk_derived() {
+  constexpr double a[6] = B2_RK_A;
+  constexpr double b[6] = B2_RK_B;
+  double B[6][6] = {};
+  for (int j = 0; j < 6; j++)
+    for (int k = j; k < 6; k++) {
+      double s = 0;
+      for (int i = j; i <= k; i++) {
+        double p = 1;
+        for (int m = j + 1; m <= i; m++) p *= a[m];
+        s += b[i] * p;
+      }
+      B[k][j] = s;
+    }
+  RKDerived r{};
+  for (int j = 0; j < 6; j++) { r.beta[j] = B[5][j]; r.cbeta += B[5][j]; }
+  for (int m = 0; m < 6; m++) {
+    double s = 0;
+    for (int j = m + 1; j < 6; j++) s += B[5][j] * B[j - 1][m];
+    r.gamma[m] = s;
+  }
+  return r;
+}
+constexpr RKDerived kRK = rk_derived();
+
 struct CPTable {
   double a[6], bdt[6];          // RK46-NL a_i and b_i * dt  (the accumulator is kept as W = w / dt)
-  double A0, A1, k1, g;         // fac2 = A0 - A1 c^2 ; k1 = mp l / M ; gravity
-  double s3;                    // sin d = d + s3 d^3                  |error| <= d^5 / 120
-  double c2, c4;                // cos d - 1 = d^2 (c2 + c4 d^2)       |error| <= d^6 / 720
+  double cv[6], cx[6];          // xdot += cv_j (xddot_j / g), x += cx_j (xddot_j / g):  g dt beta_j,  g dt^2 gamma_j
+  double dtcb;                  // dt * sum beta:  x += dtcb * xdot_0 at the start of a substep
+  double A0, A1g, k2;           // fac2 = A0 - A1g (g c)^2, A1g = A1 / g^2 ;  k2 = mp l / (M g^2)
+  double t1, t3;                // tan(d / 2) = d (t1 + t3 d^2)        |error| <= d^5 / 240
+  double s3;                    // sin d = d (1 + s3 d^2)              |error| <= d^5 / 120
 };
+#define B2_G 9.81
 __device__ __constant__ CPTable kCP = {
     B2_RK_A,
     {0.032918605146 * 4e-4, 0.823256998200 * 4e-4, 0.381530948900 * 4e-4, 0.200092213184 * 4e-4,
      1.718581042715 * 4e-4, 0.270000000000 * 4e-4},
-    CPC::A0, CPC::A1, CPC::mpl* CPC::inv_tot, CPC::g,
-    -1.0 / 6,
-    -0.5, 1.0 / 24};
+    {B2_G * 4e-4 * kRK.beta[0], B2_G * 4e-4 * kRK.beta[1], B2_G * 4e-4 * kRK.beta[2], B2_G * 4e-4 * kRK.beta[3],
+     B2_G * 4e-4 * kRK.beta[4], B2_G * 4e-4 * kRK.beta[5]},
+    {B2_G * 4e-4 * 4e-4 * kRK.gamma[0], B2_G * 4e-4 * 4e-4 * kRK.gamma[1], B2_G * 4e-4 * 4e-4 * kRK.gamma[2],
+     B2_G * 4e-4 * 4e-4 * kRK.gamma[3], B2_G * 4e-4 * 4e-4 * kRK.gamma[4], B2_G * 4e-4 * 4e-4 * kRK.gamma[5]},
+    4e-4 * kRK.cbeta,
+    CPC::A0, CPC::A1 / (B2_G * B2_G), CPC::mpl* CPC::inv_tot / (B2_G * B2_G),
+    0.5, 1.0 / 24,
+    -1.0 / 6};
+static_assert(CPC::g == B2_G && CPC::dt == 4e-4, "kCP is built from the same constants");
 
 // Stage increments of the angle are |d| = |W2 b_i dt| <= 0.27 |thetadot| dt for this scheme (W2 is a
 // convex-like blend of the stage velocities).  Below 16 rad/s that is |d| < 1.8e-3, where the two
@@ -95,51 +146,55 @@ struct CartPoleDyn<double> {
     return make_double4(u[0], u[1], u[2], u[3]);
   }
 
-  // state: u = (x, xdot, theta, thetadot).  (s, c, rinv) = (sin theta, cos theta, 1/fac2) ride along.
+  // state: u = (x, xdot, theta, thetadot).  (gs, gc, rinv) = (g sin theta, g cos theta, 1 / fac2) ride along.
   static __device__ __forceinline__ void advance(double (&u)[4], double F) {
-    double s, c;
-    sincos(u[2], &s, &c);                                  // anchor (full precision), once per env step
-    double rinv = 1.0 / fma(-kCP.A1, c * c, kCP.A0);
-    const double Fm = F * CPC::inv_tot;                    // F / M
+    double gs, gc;
+    sincos(u[2], &gs, &gc);                                // anchor (full precision), once per env step
+    gs *= CPC::g; gc *= CPC::g;
+    double rinv = 1.0 / fma(-kCP.A1g, gc * gc, kCP.A0);
+    const double Fmg = F * (CPC::inv_tot / CPC::g);        // F / (M g)
 #pragma unroll 1
     for (int sub = 0; sub < CPC::nsteps; sub++) {
       if (__builtin_expect(fabs(u[3]) > kOmegaFast, 0)) {  // |d| could leave the polynomial range: exact substep
         const double4 r = substep_exact(make_double4(u[0], u[1], u[2], u[3]), F);
         u[0] = r.x; u[1] = r.y; u[2] = r.z; u[3] = r.w;
-        sincos(u[2], &s, &c);
-        rinv = 1.0 / fma(-kCP.A1, c * c, kCP.A0);
+        sincos(u[2], &gs, &gc);
+        gs *= CPC::g; gc *= CPC::g;
+        rinv = 1.0 / fma(-kCP.A1g, gc * gc, kCP.A0);
         continue;
       }
-      double W0, W1, W2, W3;                               // w / dt of the reference (:41)
+      u[0] = fma(kCP.dtcb, u[1], u[0]);                    // x += dt (sum beta) xdot_0; the xddot terms follow per stage
+      double W2, W3;                                       // w / dt of the reference (:41), theta and thetadot only
 #pragma unroll
       for (int i = 0; i < 6; i++) {
-        // ---- Diff (:161-168), with F1m = F1 / M ----
-        const double fac2 = fma(-kCP.A1, c * c, kCP.A0);                   // :162
+        // ---- Diff (:161-168) in units of g: F1mg = F1 / (M g), num = g s - (F1 / M) c ----
+        const double fac2 = fma(-kCP.A1g, gc * gc, kCP.A0);                // :162
         const double om = u[3];
-        const double F1m = fma(kCP.k1 * (om * om), s, Fm);                 // :163 / M
-        const double num = fma(-F1m, c, kCP.g * s);                        // :164 numerator
-        const double e = fma(-fac2, rinv, 1.0);                            // one Newton step on the carried 1/fac2
-        rinv = fma(rinv, e, rinv);
-        double dd4 = num * rinv;
-        dd4 = fma(fma(-dd4, fac2, num), rinv, dd4);                        // residual correction: num / fac2
-        const double dd2 = fma(-kCP.k1 * dd4, c, F1m);                     // :165
-        // ---- low-storage RK update (:41-42) on W = w / dt; w starts at 0 and a[0] = 0 ----
+        const double F1mg = fma(kCP.k2 * (om * om), gs, Fmg);              // :163 / (M g)
+        const double num = fma(-F1mg, gc, gs);                             // :164 numerator
+        const double e = fma(-fac2, rinv, 1.0);                            // third-order step on the carried 1 / fac2
+        rinv = fma(rinv, fma(e, e, e), rinv);
+        const double dd4 = num * rinv;                                     // thetaddot (:164)
+        const double dd2g = fma(-kCP.k2 * dd4, gc, F1mg);                  // xddot / g (:165)
+        // ---- x, xdot: outside the recurrence (nothing reads them back), weights of the unrolled scheme ----
+        u[1] = fma(kCP.cv[i], dd2g, u[1]);
+        if (i < 5) u[0] = fma(kCP.cx[i], dd2g, u[0]);                      // (gamma_5 = 0)
+        // ---- theta, thetadot: low-storage RK update (:41-42) on W = w / dt; w starts at 0 and a[0] = 0 ----
         if (i == 0) {
-          W0 = u[1]; W1 = dd2; W2 = om; W3 = dd4;
+          W2 = om; W3 = dd4;
         } else {
-          W0 = fma(W0, kCP.a[i], u[1]); W1 = fma(W1, kCP.a[i], dd2);
-          W2 = fma(W2, kCP.a[i], om);   W3 = fma(W3, kCP.a[i], dd4);
+          W2 = fma(W2, kCP.a[i], om); W3 = fma(W3, kCP.a[i], dd4);
         }
         const double d = W2 * kCP.bdt[i];                                  // the angle increment of this stage
-        u[0] = fma(W0, kCP.bdt[i], u[0]); u[1] = fma(W1, kCP.bdt[i], u[1]);
-        u[2] = u[2] + d;                  u[3] = fma(W3, kCP.bdt[i], u[3]);
-        // ---- rotate (sin, cos) by d ----
+        u[2] = u[2] + d;
+        u[3] = fma(W3, kCP.bdt[i], u[3]);
+        // ---- rotate (g sin, g cos) by d: three shears, tau = tan(d / 2), sigma = sin d ----
         const double d2 = d * d;
-        const double sd = fma(d * d2, kCP.s3, d);                          // sin d
-        const double cm1 = d2 * fma(d2, kCP.c4, kCP.c2);                   // cos d - 1
-        const double s_new = fma(s, cm1, fma(c, sd, s));                   // s cos d + c sin d
-        const double c_new = fma(c, cm1, fma(-s, sd, c));                  // c cos d - s sin d
-        s = s_new; c = c_new;
+        const double tau = d * fma(d2, kCP.t3, kCP.t1);
+        const double sig = d * fma(d2, kCP.s3, 1.0);
+        gs = fma(gc, tau, gs);
+        gc = fma(-gs, sig, gc);
+        gs = fma(gc, tau, gs);
       }
     }
   }
