@@ -684,8 +684,8 @@ def main():
         dt = max_over_ranks(time.perf_counter() - t0)
         d2h = sum(a.nbytes for a in out.values())
         e2e = {"value": steps_all / dt, "unit": "env-steps/s", "h2d_bytes_per_step": int(hp.nbytes),
-               "d2h_bytes_per_step": int(d2h), "host_numa_binding": numa, "api": "b2_set_params + b2_rollout_host (pinned host buffers: the rollout kernel stores every field straight into "
-                      "host memory over PCIe while it simulates; B2_ROLLOUT_HOST_DIRECT=0 selects the chunked copy-engine pipeline)"}
+               "d2h_bytes_per_step": int(d2h), "host_numa_binding": numa, "api": "b2_set_params + b2_rollout_host (pinned host buffers; chunked launches with the copy engine moving chunk i "
+                      "while chunk i+1 is simulated; B2_ROLLOUT_HOST_DIRECT=1 selects direct host stores from the kernel)"}
 
     update_wide = None
     if not args.no_wide:

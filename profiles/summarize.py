@@ -46,6 +46,11 @@ def main(path):
         for k in KEYS:
             if k in d:
                 print(f"{k:95s} {d[k]:>16s} {u.get(k, '')}")
+        for k in hdr:   # every tensor-pipe counter ncu exposes (HMMA for mma.sync, the tcgen05 / UTCMMA ones for UMMA)
+            want = ("pipe_tensor" in k or "mem_tensor" in k or "utchmma_src_bf16_dst_fp32_sparsity_off" in k
+                    or "hmma_src_bf16_dst_fp32_sparsity_off" in k)
+            if want and (".avg" in k or ".sum" in k) and ".min" not in k and ".max" not in k and k not in KEYS and d.get(k) not in (None, "", "0"):
+                print(f"{k:95s} {d[k]:>16s} {u.get(k, '')}")
         print()
 
 

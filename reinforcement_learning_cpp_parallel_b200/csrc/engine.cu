@@ -1081,13 +1081,15 @@ int b2_rollout_host(b2_handle E, int T, int n_chunks, const b2_batch_out* out) {
   if (n_chunks > B2_MAX_CHUNKS) n_chunks = B2_MAX_CHUNKS;
   const int64_t NE = E->cfg.n_envs;
   Traj& t = E->tr;
-  // Pinned destinations (b2_host_alloc / cudaHostAlloc) and 6-wide observations: ONE launch whose stores go to the device
-  // trajectory AND straight into the host buffers (posted PCIe writes, the observations transposed in the warp so that
-  // every store is a whole 128-B line).  Measured at the reference shape (tools/e2e_probe.py): 7.1-7.2 ms -- SM-issued
-  // writes sustain ~44 GB/s and 37 B per record need 49 GB/s to hide completely behind the 6.3 ms of simulation; the
-  // chunked copy-engine pipeline below takes 7.3-7.4 ms; splitting the fields between the two (small fields direct,
-  // observations by DMA) 9.3 ms: SM writes and DMA contend for the link.  B2_ROLLOUT_HOST_DIRECT=0 forces the pipeline,
-  // which pageable buffers and 4-wide observations always take.
+  // Two ways to get the trajectory into host buffers.  (a) DIRECT (B2_ROLLOUT_HOST_DIRECT=1, pinned destinations, 6-wide
+  // observations): ONE launch whose stores go to the device trajectory AND straight into the host buffers (posted PCIe
+  // writes, the observations transposed in the warp so that every store is a whole 128-B line).  SM-issued writes
+  // sustain ~44 GB/s, so 37 B per record cost 7.05 ms at the reference shape whatever the kernel does.  (b) The chunked
+  // copy-engine PIPELINE below (default): the DMA engine moves 57 GB/s (5.4 ms for the same bytes) behind the simulation.
+  // Round 1 (6.3 ms of simulation): direct 7.1-7.2 ms, pipeline 7.3-7.4 ms -> direct was the default.  Round 2 (5.6 ms of
+  // simulation, the 27-instruction stage): direct 7.45 ms = 1.13e9 env-steps/s, pipeline 6.7 ms = 1.25e9 -> the pipeline
+  // is (profiles/r2/r2d_e2e_ab.txt).  Splitting the fields between the two (small fields direct, observations by DMA)
+  // was 9.3 ms: SM writes and DMA contend for the link.
   {
     auto pinned = [](const void* p) {
       if (!p) return true;
@@ -1096,7 +1098,7 @@ int b2_rollout_host(b2_handle E, int T, int n_chunks, const b2_batch_out* out) {
       return at.type == cudaMemoryTypeHost;
     };
     const char* env = getenv("B2_ROLLOUT_HOST_DIRECT");
-    const bool direct_ok = !(env && env[0] == '0') && E->S_ext == OBS && pinned(out->obs) && pinned(out->action) &&
+    const bool direct_ok = (env && env[0] == '1') && E->S_ext == OBS && pinned(out->obs) && pinned(out->action) &&
                            pinned(out->logp) && pinned(out->mu) && pinned(out->reward) && pinned(out->flags);
     if (direct_ok) {
       if ((rc = rollout_window(E, T, 0, T, false, out->obs, out))) return rc;
@@ -1115,12 +1117,15 @@ int b2_rollout_host(b2_handle E, int T, int n_chunks, const b2_batch_out* out) {
   // (all simulation) + (the LAST chunk's copy).  Hence equal chunks of T / n_chunks steps (long launches keep the
   // persistent kernel's launch quantisation small) and a halving tail (.., cap/2, cap/4, .., 2, 2 steps) so that only
   // ~2 steps' worth of bytes is still in flight when the simulation ends.
+  // The copy engine is nearly as busy as the SMs (5.4 vs 5.6 ms at the reference shape), so the FIRST chunk matters as
+  // much: nothing can leave before it is simulated.  Doubling head (2, 2, 4, .. steps), equal chunks, halving tail.
   int bounds[B2_MAX_CHUNKS + 1];
   int nb = 0;
   {
     const int cap = (T + n_chunks - 1) / n_chunks;
     int t = 0;
     bounds[0] = 0;
+    for (int len = 2; len < cap && T - t > 2 * cap && nb < 6; len *= 2) { t += len; bounds[++nb] = t; if (nb == 1) { t += len; bounds[++nb] = t; } }
     while (T - t > cap && nb < B2_MAX_CHUNKS - 8) { t += cap; bounds[++nb] = t; }
     int r = T - t;                                   // the last <= cap steps (more only if out of events): halving tail
     while (r > 2 && nb < B2_MAX_CHUNKS - 1) { const int len = r / 2; t += len; r -= len; bounds[++nb] = t; }

@@ -252,13 +252,18 @@ def test_training_learns_cartpole(pkg):
     E.close()
 
 
-@pytest.mark.parametrize("pinned", [True, False])
-def test_rollout_host_pipelined_equals_resident_rollout(pkg, pinned):
-    """b2_rollout_host delivers exactly what b2_rollout + b2_traj_download deliver and carries env state on: with pinned
-    buffers the kernel stores straight into host memory (one launch; 200 envs = 6 full warps + a ragged one, so both
-    observation store paths run); with pageable buffers the chunked launches + copy-engine pipeline, for chunk counts
-    that do and do not divide the horizon."""
+@pytest.mark.parametrize("pinned,direct", [(True, False), (True, True), (False, False)])
+def test_rollout_host_pipelined_equals_resident_rollout(pkg, monkeypatch, pinned, direct):
+    """b2_rollout_host delivers exactly what b2_rollout + b2_traj_download deliver and carries env state on.  Default:
+    chunked launches + the copy-engine pipeline (doubling head, equal chunks, halving tail), for chunk counts that do and
+    do not divide the horizon, pinned or pageable buffers.  B2_ROLLOUT_HOST_DIRECT=1 with pinned buffers: the kernel
+    stores straight into host memory (one launch; 200 envs = 6 full warps + a ragged one, so both observation store
+    paths run)."""
     from reinforcement_learning_cpp_parallel_b200 import capi
+    if direct:
+        monkeypatch.setenv("B2_ROLLOUT_HOST_DIRECT", "1")
+    else:
+        monkeypatch.delenv("B2_ROLLOUT_HOST_DIRECT", raising=False)
     alloc = capi.pinned_empty if pinned else (lambda shape, dt: np.empty(shape, dt))
     N, T = 200, 37
     ref = make_engine(pkg, n_envs=N, horizon=T, seed=5)
@@ -267,7 +272,7 @@ def test_rollout_host_pipelined_equals_resident_rollout(pkg, pinned):
     a = ref.traj_download(T)
     ref.rollout(T)
     a2 = ref.traj_download(T)
-    for chunks in (1, 4, 37):
+    for chunks in (1, 2, 4, 37):
         E = make_engine(pkg, n_envs=N, horizon=T, seed=5)
         E.init_params(3)
         out = {"obs": alloc((T, N, 6), np.float32), "action": alloc((T, N), np.float32), "logp": alloc((T, N), np.float32),
