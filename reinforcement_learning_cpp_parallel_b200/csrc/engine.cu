@@ -1022,9 +1022,14 @@ static int rollout_window(b2_engine* E, int T, int t_begin, int t_end, bool forc
   a.n_envs = E->cfg.n_envs; a.T = T; a.t_begin = t_begin; a.t_end = t_end; a.n_timestep = E->cfg.n_timestep;
   a.seed = E->cfg.seed; a.env_offset = E->cfg.env_offset; a.step0 = E->global_step;
   a.hp = E->hp; a.status = E->status; a.progress = E->progress; a.env_flags = E->cfg.env_flags;
-  cudaError_t ce = launch_rollout(a, E->cfg.precision, E->trace, E->sm_count, E->stream, E->cfg.hidden1, E->cfg.hidden2);
+  cudaError_t ce;
+  if (E->wide) {   // wide actors: one env step = observe + actor forward + step (rollout_wide.cu)
+    ce = launch_rollout_wide(a, E->dims, E->cfg.precision, E->trace, E->stream, &E->launches);
+  } else {
+    ce = launch_rollout(a, E->cfg.precision, E->trace, E->sm_count, E->stream, E->cfg.hidden1, E->cfg.hidden2);
+    E->launches += 1;
+  }
   if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "rollout: %s", cudaGetErrorString(ce));
-  E->launches += 1;
   if (E->S_ext != OBS) {   // getobs(4): the stored cos/sin planes must be exact zeros (see S_ext above)
     const int64_t k0 = (int64_t)t_begin * E->cfg.n_envs, n = (int64_t)(t_end - t_begin) * E->cfg.n_envs;
     for (int c = E->S_ext; c < OBS; c++) CK(cudaMemsetAsync(E->tr.obs + (size_t)c * E->tr.cap + k0, 0, sizeof(float) * n, E->stream));
@@ -1033,7 +1038,6 @@ static int rollout_window(b2_engine* E, int T, int t_begin, int t_end, bool forc
 }
 
 static int rollout_prepare(b2_engine* E, int T, const float* forced_action) {
-  if (E->wide) return set_error(B2_ERR_INVALID, "the fused rollout kernel is built for the reference's 64x32 nets only; wide nets (%dx%d) support act/value/returns/update", E->cfg.hidden1, E->cfg.hidden2);
   CK(cudaSetDevice(E->cfg.device));
   if (T < 1 || T > E->cfg.horizon) return set_error(B2_ERR_INVALID, "rollout: T=%d outside [1, horizon=%d]", T, E->cfg.horizon);
   const int64_t NE = E->cfg.n_envs;
@@ -1098,7 +1102,7 @@ int b2_rollout_host(b2_handle E, int T, int n_chunks, const b2_batch_out* out) {
       return at.type == cudaMemoryTypeHost;
     };
     const char* env = getenv("B2_ROLLOUT_HOST_DIRECT");
-    const bool direct_ok = (env && env[0] == '1') && E->S_ext == OBS && pinned(out->obs) && pinned(out->action) &&
+    const bool direct_ok = (env && env[0] == '1') && !E->wide && E->S_ext == OBS && pinned(out->obs) && pinned(out->action) &&
                            pinned(out->logp) && pinned(out->mu) && pinned(out->reward) && pinned(out->flags);
     if (direct_ok) {
       if ((rc = rollout_window(E, T, 0, T, false, out->obs, out))) return rc;
@@ -1135,7 +1139,7 @@ int b2_rollout_host(b2_handle E, int T, int n_chunks, const b2_batch_out* out) {
     const int t0 = bounds[c], t1 = bounds[c + 1];
     // 6-wide observations leave the kernel record-major as well (RolloutArgs::obs_aos): no transpose between the
     // simulation and the copy.  4-wide ones (S_ext = 4) keep the transpose: their stored cos/sin planes are zeroed first.
-    const bool direct = out->obs && E->S_ext == OBS;
+    const bool direct = out->obs && E->S_ext == OBS && !E->wide;
     if ((rc = rollout_window(E, T, t0, t1, false, direct ? E->stage : nullptr))) return rc;
     const int64_t k0 = (int64_t)t0 * NE, n = (int64_t)(t1 - t0) * NE;
     if (out->obs && !direct) {

@@ -150,6 +150,10 @@ cudaError_t launch_wide_forward(const NetDims& d, const float* net_params, const
                                 int64_t obs_stride_k, const int32_t* rows, int64_t n, int final_tanh, float* y,
                                 cudaStream_t st);
 
+// device-resident rollout for wide actors, one env step = observe + actor forward + step (rollout_wide.cu)
+cudaError_t launch_rollout_wide(const RolloutArgs& a, const NetDims& d, int precision, bool trace, cudaStream_t st,
+                                int64_t* launches);
+
 cudaError_t launch_wide_act_finish(const float* mu, const float* eps, int64_t n, uint64_t seed, uint64_t call, float* action,
                                    float* logp, const HyperDev& hp, int* status, cudaStream_t st);
 

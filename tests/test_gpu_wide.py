@@ -189,11 +189,64 @@ def test_wide_update_opt_in_modes_match_oracle(env, monkeypatch):
         assert np.array_equal(runs[0], runs[1])
 
 
-def test_wide_rollout_is_refused_loudly():
+@pytest.mark.parametrize("H1,H2", WIDE)
+def test_wide_rollout_matches_oracle(H1, H2):
+    """A wide policy collects its own data on the device (csrc/rollout_wide.cu: observe + actor forward + step per env
+    step).  Same env semantics and Philox streams as the fused kernel: replaying the oracle's actions reproduces its fp64
+    states to 1e-9, rewards / flags exactly and mu / log-prob to the forward-pass gate; free-running, the noise stream is
+    the oracle's draw for draw; TIMEUP / TRUNC / reset / episode bookkeeping as k_rollout."""
+    import reinforcement_learning_cpp_parallel_b200 as pkg
     from reinforcement_learning_cpp_parallel_b200 import capi
-    with wide_engine(256, 256) as E:
-        with pytest.raises(capi.B2Error):
-            E.rollout(1)
+    dims = H.Dims(6, H1, H2, 1)
+    rng = np.random.default_rng(H1)
+    P = H.oracle().orc_n_params(C.byref(dims))
+    params = (rng.standard_normal(P) / np.sqrt(H1)).astype(np.float32)
+    N, T = 67, 128
+    ref = H.oracle_rollout(params, N, T, seed=31, env0=9, dims=dims)
+    E = pkg.Engine(capi.default_config(n_envs=N, horizon=T, hidden1=H1, hidden2=H2, seed=31, env_offset=9, k_epochs=1))
+    E.set_params(params)
+    E.set_state_trace(True)
+    E.rollout(T, forced_action=ref["action"])
+    out = E.traj_download(T, state_trace=True)
+    scale = np.maximum(np.abs(ref["state_trace"]).max(axis=-1, keepdims=True), 1e-300)
+    assert (np.abs(out["state_trace"] - ref["state_trace"]) / scale).max() < 1e-9
+    np.testing.assert_array_equal(out["reward"], ref["reward"])
+    np.testing.assert_array_equal(out["flags"], ref["flags"])
+    assert (out["flags"][99] == 2).all() and (out["flags"][127] == 4).all()
+    np.testing.assert_allclose(out["obs"], ref["obs"], rtol=1e-6, atol=1e-7)
+    np.testing.assert_allclose(out["mu"], ref["mu"], rtol=2e-6, atol=2e-6)
+    np.testing.assert_allclose(out["logp"], ref["logp"], rtol=1e-5, atol=1e-5)
+    cnt, ret = E.episode_stats(2)
+    assert (cnt == 1).all()
+    np.testing.assert_array_equal(ret[:, 0], ref["reward"][:100].sum(axis=0))
+    # free-running: eps recovered from (a - mu) / sigma is the oracle's Philox draw (counter continues at step T)
+    E.rollout(8)
+    fr = E.traj_download(8, fields=("action", "mu"))
+    eps = (fr["action"].astype(np.float64) - fr["mu"]) / H.SIGMA
+    want = np.array([[H.oracle().orc_gauss(31, 9 + e, T + t) for e in range(N)] for t in range(8)])
+    np.testing.assert_allclose(eps, want, rtol=0, atol=3e-6)
+    # and the wide learner trains on what the wide actor collected
+    st = E.update_resident()
+    assert np.isfinite(st.loss) and st.samples == N * 8
+    E.close()
+
+
+def test_wide_rollout_host_buffers():
+    """b2_rollout_host on a wide engine takes the chunked copy-engine pipeline and equals rollout + download."""
+    import reinforcement_learning_cpp_parallel_b200 as pkg
+    from reinforcement_learning_cpp_parallel_b200 import capi
+    N, T = 40, 12
+    mk = lambda: pkg.Engine(capi.default_config(n_envs=N, horizon=T, hidden1=128, hidden2=64, seed=4))
+    A, B = mk(), mk()
+    A.rollout(T)
+    a = A.traj_download(T)
+    out = {"obs": capi.pinned_empty((T, N, 6), np.float32), "action": capi.pinned_empty((T, N), np.float32),
+           "logp": capi.pinned_empty((T, N), np.float32), "mu": capi.pinned_empty((T, N), np.float32),
+           "reward": capi.pinned_empty((T, N), np.float32), "flags": capi.pinned_empty((T, N), np.uint8)}
+    B.rollout_host(T, out, n_chunks=3)
+    for k in out:
+        np.testing.assert_array_equal(out[k], a[k], err_msg=k)
+    A.close(); B.close()
 
 
 @pytest.mark.parametrize("M,N,K,splits", [(128, 256, 256, 1), (256, 256, 1000, 3), (64, 128, 96, 1), (192, 64, 4096, 5)])
