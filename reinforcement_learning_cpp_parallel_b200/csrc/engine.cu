@@ -70,6 +70,9 @@ cudaError_t dmalloc_bytes(void** p, size_t bytes) {
   if (e != cudaSuccess) return e;
   if ((e = cudaMemset(base, 0xA5, padded + 2 * GUARD_BYTES)) != cudaSuccess) return e;
   if ((e = cudaMemset(base + GUARD_BYTES, 0xFF, bytes)) != cudaSuccess) return e;   // poison: NaN / -1
+  // cudaMemset on device memory returns before it has run, and the engine's streams are non-blocking: without this the
+  // poison can land AFTER the first real write on E->stream (seen as a spurious "non-finite loss" in one run out of three)
+  if ((e = cudaDeviceSynchronize()) != cudaSuccess) return e;
   *p = base + GUARD_BYTES;
   std::lock_guard<std::mutex> lk(guard_book().mu);
   guard_book().live[*p] = bytes;
