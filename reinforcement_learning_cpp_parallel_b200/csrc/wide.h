@@ -110,6 +110,32 @@ struct GemmArgs {
   int bar_target;                   // value it reaches when every CTA of THIS launch has arrived
 };
 
+constexpr float HEADW_B2_SCALE = 2.8853900817779268f;   // 2 log2(e): tanh x = 1 - 2 / (2^(x * this) + 1)
+// k_wide_fh (wide_fused.cu): layer-2 forward GEMM + loss head in one kernel, both nets (critic first)
+struct FhArgs {
+  NetDims d;
+  int N, K, stages;            // N = H2, K = H1
+  int count, m_pad;            // valid samples of this chunk, padded to 128
+  int64_t cap, first;          // chunk capacity (row count of the planes), position of sample 0
+  const int32_t* idx;
+  Traj tr;
+  const float* params;
+  const float* headw;          // [g][2][H2]: b2 * HEADW_B2_SCALE, W3 (16-B aligned copies kept current by the Adam step)
+  float* vtmp;                 // [4][cap]: V of the critic pass, one copy per column-quarter warp
+  float inv_denom;
+  HyperDev hp;
+  float* part_head;            // [grid][2][head_row]
+  int head_row;
+  long long* dbg;              // optional clock64 timeline of the head warps, [grid][16] (B2_FH_DBG=1, diagnostic runs)
+};
+int fh_stages(int N, int K);
+bool fh_supported(int N, int K);
+// tmA: h1p operand map (128-row boxes), tmB: K-major W2 in (H2/2)-row boxes, tmD: bf16 plane store map of d2p (32 x 32 boxes)
+cudaError_t launch_wide_fh(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmD, const FhArgs& a, int sm_count,
+                           int* grid_out, cudaStream_t st);
+// bf16 planes [planes][rows][N] written in boxes of 16 columns x 32 rows x 2 planes with the 32-B swizzle (the head's staging tiles)
+int make_plane_store_map(CUtensorMap* out, const void* base, uint64_t N, uint64_t rows, uint64_t planes);
+
 // the CTA-pair, weights-resident GEMM of wide_gemm2.cu (layer-2 forward and dX): C[g][M][N] = A[g][M][K] . B[g]
 struct Gemm2Args {
   int G, M, N, K;      // K, N <= 256, multiples of 64 (N % 128 == 0 when B is contraction-major)

@@ -26,7 +26,7 @@ __device__ __forceinline__ AdamCoef adam_coef(const HyperDev& hp, int64_t step) 
   return c;
 }
 
-// a parameter changed: keep the bf16 planes (both majors) of W2 and the bias copy in step with it
+// a parameter changed: keep the bf16 planes of W2 and the aligned copy of (b2, W3) the fused head reads in step with it
 __device__ __forceinline__ void wide_store_planes(const NetDims& d, __nv_bfloat16* w2p, float* bias2,
                                                   int p, float val) {
   const int g = p / d.SIZE, o = p % d.SIZE;
@@ -37,8 +37,8 @@ __device__ __forceinline__ void wide_store_planes(const NetDims& d, __nv_bfloat1
     const int64_t ps = (int64_t)d.H2 * d.H1;
     w2p[(g * 2 + 0) * ps + e] = hi;
     w2p[(g * 2 + 1) * ps + e] = mid;
-  } else if (o >= d.ob2 && o < d.oW3) {
-    bias2[g * d.H2 + (o - d.ob2)] = val;
+  } else if (o >= d.ob2 && o < d.ob3) {                   // b2 | W3 are adjacent in the parameter vector, and in headw[g][2][H2]
+    bias2[g * 2 * d.H2 + (o - d.ob2)] = o < d.oW3 ? val * HEADW_B2_SCALE : val;   // b2 pre-scaled for the head's ex2 (wide_fused.cu)
   }
 }
 

@@ -4,7 +4,7 @@
 // (src/ppo_nn.cpp:126-194), the loss (:263-290), autograd backward (:301-302) and Adam::step (:303).
 //
 // Memory plan for a chunk of CAP samples (CAP % 128 == 0), g = net (0 actor, 1 critic), pl = bf16 plane (hi, mid):
-//   w2p  [g*2+pl][H2][H1]   bias2 [g][H2]                            (kept current by the Adam step)
+//   w2p  [g*2+pl][H2][H1]   bias2 [g][2][H2] = (b2 * 2 log2 e, W3)   (kept current by the Adam step)
 //   h1p  [g*2+pl][CAP][H1]                                           (layer-1 activations, sample-major)
 //   h2   [g][CAP][H2] f32                                            (layer-2 activations)
 //   d2p  [g*2+pl][CAP][H2]                                           (dL/dz2, sample-major)
@@ -15,6 +15,7 @@
 // (dW2) needs no masking.
 #include <algorithm>
 #include <new>
+#include <vector>
 
 #include "tc_ptx.cuh"
 #include "wide.h"
@@ -64,8 +65,8 @@ __global__ void __launch_bounds__(256) k_wide_prep(const WideArgs a) {
     a.w2p[(g * 2 + 0) * ps + r] = hi;
     a.w2p[(g * 2 + 1) * ps + r] = mid;
   }
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 2 * H2; i += gridDim.x * blockDim.x)
-    a.bias2[i] = a.params[(i / H2) * a.d.SIZE + a.d.ob2 + (i % H2)];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 4 * H2; i += gridDim.x * blockDim.x)   // headw[g][2][H2]: b2, W3
+    a.bias2[i] = a.params[(i / (2 * H2)) * a.d.SIZE + a.d.ob2 + (i % (2 * H2))] * ((i % (2 * H2)) < H2 ? HEADW_B2_SCALE : 1.0f);
 }
 
 // layer 1: H1 = tanh(W1 x + b1) -> (hi, mid) bf16 planes, sample-major.  grid (blocks, 2 nets); a block owns an equal
@@ -452,6 +453,11 @@ struct WideNet {
   int64_t cap = 0;                 // samples per chunk, multiple of 128
   __nv_bfloat16 *w2p = nullptr, *h1p = nullptr, *d2p = nullptr;
   float *bias2 = nullptr, *h2 = nullptr, *d1 = nullptr;
+  float* vtmp = nullptr;           // [4][cap] V of the critic pass of the fused forward + head kernel
+  bool fused_fh = false;           // k_wide_fh instead of the forward GEMM + k_wide_head (B2_WIDE_FUSED=0: the two kernels)
+  int fh_grid = 0;                 // CTAs of the last k_wide_fh launch (= partial rows the reduce sums)
+  long long* fh_dbg = nullptr;     // B2_FH_DBG=1: clock64 timeline of the head warps, printed once (diagnostic)
+  CUtensorMap tm_d2_st;            // d2p planes as a store target (32 x 32 boxes, 64-B swizzle)
   AdamCoef* coef = nullptr;
   float *part_head = nullptr, *part_dw1 = nullptr, *part_dw2 = nullptr;
   int head_blocks = 0, head_row = 0, dw1_blocks = 0, splits_max = 0;
@@ -480,7 +486,7 @@ int64_t wide_chunk_cap(const WideNet* w) { return w ? w->cap : 0; }
 void wide_destroy(WideNet* w) {
   if (!w) return;
   dfree(w->w2p); dfree(w->h1p); dfree(w->d2p);
-  dfree(w->bias2); dfree(w->h2); dfree(w->d1); dfree(w->coef);
+  dfree(w->bias2); dfree(w->h2); dfree(w->d1); dfree(w->coef); dfree(w->vtmp); dfree(w->fh_dbg);
   dfree(w->part_head); dfree(w->part_dw1); dfree(w->part_dw2); dfree(w->bar_counter);
   dfree(w->boot_idx); dfree(w->boot_count);
   delete w;
@@ -510,7 +516,9 @@ int wide_create(WideNet** out, int H1, int H2, int64_t max_chunk, int sm_count) 
   WCK(dmalloc(&w->w2p, bf * 4 * H2 * H1));
   WCK(dmalloc(&w->h1p, bf * 4 * cap * H1));
   WCK(dmalloc(&w->d2p, bf * 4 * cap * H2));
-  WCK(dmalloc(&w->bias2, sizeof(float) * 2 * H2));
+  WCK(dmalloc(&w->bias2, sizeof(float) * 4 * H2));
+  WCK(dmalloc(&w->vtmp, sizeof(float) * 4 * cap));
+  if (getenv("B2_FH_DBG")) { WCK(dmalloc(&w->fh_dbg, sizeof(long long) * 16 * 160)); WCK(cudaMemset(w->fh_dbg, 0, sizeof(long long) * 16 * 160)); }
   WCK(dmalloc(&w->coef, sizeof(AdamCoef)));
   WCK(dmalloc(&w->h2, sizeof(float) * 2 * cap * H2));
   WCK(dmalloc(&w->d1, sizeof(float) * 2 * cap * H1));
@@ -544,6 +552,8 @@ int wide_create(WideNet** out, int H1, int H2, int64_t max_chunk, int sm_count) 
   w->pair_fwd = gemm2_supported(H2, H1, false);
   w->pair_bwd = gemm2_supported(H1, H2, true);
   if (!rc && w->pair_fwd) rc = make_operand_map(&w->tm_w2_half, w->w2p, H1, H2, 4, H1, (uint64_t)H2 * H1, (uint32_t)(H2 / 2));
+  { const char* e = getenv("B2_WIDE_FUSED"); w->fused_fh = w->pair_fwd && fh_supported(H2, H1) && !(e && e[0] == '0'); }
+  if (!rc && w->fused_fh) rc = make_plane_store_map(&w->tm_d2_st, w->d2p, H2, ucap, 4);
   if (!rc) rc = make_output_map(&w->tm_out_h2, w->h2, H2, ucap, 2);
   if (!rc) rc = make_output_map(&w->tm_out_d1, w->d1, H1, ucap, 2);
   if (!rc) rc = make_output_map(&w->tm_out_dw2, w->part_dw2, H1, H2, (uint64_t)2 * w->splits_max);
@@ -606,6 +616,34 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     GemmArgs g{};
     g.G = 2; g.M = wa.count; g.N = H2; g.K = H1; g.m_tiles = m_tiles; g.splits = 1; g.kb_per_split = H1 / 64;
     g.stages = gemm_x3_stages(H2);
+    int head_rows = w->head_blocks;                       // partial rows of the head the reduce kernel sums
+    if (w->fused_fh) {                                    // forward GEMM + head in one kernel (wide_fused.cu)
+      FhArgs f{};
+      f.d = d; f.N = H2; f.K = H1; f.stages = fh_stages(H2, H1); f.count = wa.count; f.m_pad = wa.m_pad; f.cap = w->cap;
+      f.first = wa.first; f.idx = a.idx; f.tr = a.tr; f.params = a.params; f.headw = w->bias2; f.vtmp = w->vtmp;
+      f.inv_denom = wa.inv_denom; f.hp = a.hp; f.part_head = w->part_head; f.head_row = w->head_row;
+      f.dbg = w->fh_dbg;
+      if (!(skip & 6))
+      if ((ce = launch_wide_fh(w->tm_h1, w->tm_w2_half, w->tm_d2_st, f, w->sm_count, &w->fh_grid, st)) != cudaSuccess)
+        return set_error(B2_ERR_CUDA, "wide fwd+head: %s", cudaGetErrorString(ce));
+      (*launches)++;
+      head_rows = w->fh_grid;
+      static int dbg_calls = 0;
+      if (w->fh_dbg && ++dbg_calls == 50) {               // one warm launch in the middle of an update
+        cudaStreamSynchronize(st);
+        std::vector<long long> h(16 * 160);
+        cudaMemcpy(h.data(), w->fh_dbg, sizeof(long long) * h.size(), cudaMemcpyDeviceToHost);
+        for (int c : {0, 1, 64, 127}) {
+          if (c >= w->fh_grid) continue;
+          const long long* r = &h[(size_t)c * 16];
+          fprintf(stderr, "fh cta %3d:", c);
+          for (int it = 0; it < 2; it++)
+            fprintf(stderr, "  tile %d wait %6lld acc_ready %6lld pass1_done %6lld pass2_done %6lld |", it, r[it * 4] - r[12], r[it * 4 + 1] - r[12],
+                    r[it * 4 + 2] - r[12], r[it * 4 + 3] - r[12]);
+          fprintf(stderr, "  head_done %6lld (cycles after entry)\n", r[13] - r[12]);
+        }
+      }
+    } else {
     if (skip & 2) ce = cudaSuccess;
     else if (w->pair_fwd) {   // CTA pairs with the weight halves resident (wide_gemm2.cu)
       const Gemm2Args g2{2, wa.count, H2, H1, gemm2_stages(H2, H1)};
@@ -631,6 +669,7 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
       }
       if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "wide head: %s", cudaGetErrorString(ce));
       (*launches)++;
+    }
     }
     // D1 = (D2 W2) .* (1 - H1^2)
     g = GemmArgs{};
@@ -669,7 +708,7 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     // reduce (+ Adam on the last chunk): in the tail of the dW2 kernel behind a grid barrier, or as a launch of its own
     ReduceArgs r{};
     r.d = d; r.u = a; r.part_head = w->part_head; r.part_dw1 = w->part_dw1; r.part_dw2 = w->part_dw2;
-    r.head_blocks = w->head_blocks; r.head_row = w->head_row; r.dw1_blocks = dw2_grid; r.splits = splits;
+    r.head_blocks = head_rows; r.head_row = w->head_row; r.dw1_blocks = dw2_grid; r.splits = splits;
     r.dw2_added = w->dw2_add ? 1 : 0;
     r.pstride = wide_pstride(H1, H2);
     r.w2p = w->w2p; r.bias2 = w->bias2; r.coef = w->coef;
