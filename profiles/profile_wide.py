@@ -27,8 +27,12 @@ flags = np.zeros((T, N), np.uint8)
 flags[99] = 2
 flags[T - 1] = 4
 t0 = time.perf_counter()
-st = E.update(obs, act, lp, reward, flags.reshape(-1), n_envs=N, horizon=T)
-print("first update (incl. upload) %.1f ms, loss %.5f" % (1e3 * (time.perf_counter() - t0), st.loss))
+try:
+    st = E.update(obs, act, lp, reward, flags.reshape(-1), n_envs=N, horizon=T)
+    print("first update (incl. upload) %.1f ms, loss %.5f" % (1e3 * (time.perf_counter() - t0), st.loss))
+except capi.B2Error as e:           # B2_WIDE_SKIP diagnostic runs compute garbage
+    print("  (", e, ")")
+    st = None
 for _ in range(reps):
     l0 = E.kernel_launches()
     E.timer_start()
@@ -39,4 +43,4 @@ for _ in range(reps):
     ms = E.timer_stop_ms()
     se = B * K / (ms * 1e-3)
     print("update_resident %.2f ms  %.3e sample-epochs/s  %.1f TFLOP/s algorithmic (x3 issued)  loss %.5f  launches %d"
-          % (ms, se, se * 801792 / 1e12, st.loss, E.kernel_launches() - l0))
+          % (ms, se, se * 801792 / 1e12, st.loss if st else float("nan"), E.kernel_launches() - l0))
