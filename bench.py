@@ -16,7 +16,7 @@ Further legs inside the same JSON line: `update` (default-net PPO update on the 
 1,048,576 envs over the N GPUs, strong scaling) and, at N > 1, `multi_gpu_check` (weights bit-identical across ranks,
 gradients vs one GPU on the concatenated batch, peer-memory exchange vs ncclAllReduce; a violation makes the run exit 1).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--precision f64|f32]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--precision f64|f32|mixed]
 """
 import argparse
 import json
@@ -43,7 +43,8 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--precision", default="f64", choices=["f64", "f32"])
+    ap.add_argument("--precision", default="f64", choices=["f64", "f32", "mixed"],
+                    help="f64: the parity-gated headline; mixed: double state + RK accumulators, f32 Diff (teacher-forced gate 1e-5); f32: drift reported only")
     ap.add_argument("--envs", type=int, default=65536)
     ap.add_argument("--horizon", type=int, default=128)
     ap.add_argument("--epochs", type=int, default=4, help="full-batch PPO epochs per timed update leg")
@@ -580,7 +581,7 @@ def main():
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    prec = pkg.PREC_F64 if args.precision == "f64" else pkg.PREC_F32
+    prec = {"f64": pkg.PREC_F64, "f32": pkg.PREC_F32, "mixed": pkg.PREC_MIXED}[args.precision]
     N, T = args.envs, args.horizon
 
     # ---------------- multi-GPU parity self-check (N > 1), before anything is timed ----------------

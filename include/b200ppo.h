@@ -42,6 +42,8 @@ typedef enum {
 /* physics arithmetic of the rollout kernel */
 #define B2_PREC_F64 0 /* double state + double Diff: the parity-gated path (reference is double) */
 #define B2_PREC_F32 1 /* float everything: throughput path, drift vs reference is reported, not gated */
+#define B2_PREC_MIXED 2 /* double state + RK accumulators, Diff in float: teacher-forced step within 1e-5 of the
+                         reference's double states (gated), free-running drift reported; ~1.5x the F64 rollout rate */
 
 /* environment variants the reference header documents but ships disabled (opt-in; 0 = the shipped cart-pole):
  *   B2_ENV_SWINGUP      the `#if SWINGUP` branches: Diff include/cart_pole.h:154-159, getReward :136-139,

@@ -7,7 +7,7 @@ thin ctypes view used by tests/ and bench.py; it contains no compute and no fall
 shared library is missing, importing :mod:`capi` raises.
 """
 from .capi import (B2Error, Batch, Config, ENV_EARLY_TERM, ENV_RANDOM_INIT, ENV_SWINGUP, Engine, FLAG_TERMINAL,
-                   FLAG_TIMEUP, FLAG_TRUNC, PREC_F32, PREC_F64, UpdateStats, lib, lib_path)
+                   FLAG_TIMEUP, FLAG_TRUNC, PREC_F32, PREC_F64, PREC_MIXED, UpdateStats, lib, lib_path)
 
 __all__ = ["B2Error", "Batch", "Config", "ENV_EARLY_TERM", "ENV_RANDOM_INIT", "ENV_SWINGUP", "Engine", "FLAG_TERMINAL", "FLAG_TIMEUP", "FLAG_TRUNC",
-           "PREC_F32", "PREC_F64", "UpdateStats", "lib", "lib_path"]
+           "PREC_F32", "PREC_F64", "PREC_MIXED", "UpdateStats", "lib", "lib_path"]

@@ -12,7 +12,7 @@ def lib_path():
 
 
 FLAG_TERMINAL, FLAG_TIMEUP, FLAG_TRUNC = 1, 2, 4
-PREC_F64, PREC_F32 = 0, 1
+PREC_F64, PREC_F32, PREC_MIXED = 0, 1, 2
 ENV_SWINGUP, ENV_RANDOM_INIT, ENV_EARLY_TERM = 1, 2, 4
 COMM_ID_BYTES = 128
 

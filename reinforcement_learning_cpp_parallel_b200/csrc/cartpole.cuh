@@ -256,6 +256,63 @@ struct CartPoleDyn<float> {
   }
 };
 
+// ------------------------------------------------------------------------------------------- mixed
+// B2_PREC_MIXED: the STATE and the RK accumulators stay double, Diff -- sin, cos, the
+// divide and the dozen multiply-adds around them, include/cart_pole.h:161-168 -- runs in f32 on the FP32 / MUFU pipes.
+// A stage is then 6 DFMA (the low-storage recurrence for theta / thetadot, the unrolled weights for x / xdot, as in the
+// double path) + 4 conversions on the FP64 pipe instead of 27 instructions: the kernel is bound by FP64 ISSUE, so this
+// is the one variant faster than the double path whose error is BOUNDED rather than accumulated in the state: every
+// stage's rounding enters through f (relative 2^-24 .. 2^-21 of the accelerations), never through u itself.
+// Gate (tests/test_gpu_parity.py): teacher-forced single step <= 1e-5 of ||u||_inf against the reference's double
+// states (survey probe: 8e-6 worst); the free-running drift over an episode is reported, like the f32 path's.
+struct MixedPrec {};
+template <typename P> struct StateOf { using type = P; };
+template <> struct StateOf<MixedPrec> { using type = double; };
+
+struct CPTableMixed { double cvm[6], cxm[6]; };   // xdot += cvm_j xddot_j, x += cxm_j xddot_j:  dt beta_j,  dt^2 gamma_j
+__device__ __constant__ CPTableMixed kCPM = {
+    {4e-4 * kRK.beta[0], 4e-4 * kRK.beta[1], 4e-4 * kRK.beta[2], 4e-4 * kRK.beta[3], 4e-4 * kRK.beta[4], 4e-4 * kRK.beta[5]},
+    {4e-4 * 4e-4 * kRK.gamma[0], 4e-4 * 4e-4 * kRK.gamma[1], 4e-4 * 4e-4 * kRK.gamma[2], 4e-4 * 4e-4 * kRK.gamma[3],
+     4e-4 * 4e-4 * kRK.gamma[4], 4e-4 * 4e-4 * kRK.gamma[5]}};
+
+template <>
+struct CartPoleDyn<MixedPrec> {
+  static __device__ __forceinline__ void advance(double (&u)[4], double F) {
+    constexpr float A0 = (float)CPC::A0, A1 = (float)CPC::A1, mpl = (float)CPC::mpl, inv_tot = (float)CPC::inv_tot,
+                    g = (float)CPC::g;
+    const float Ff = (float)F;                             // exact: the force is an f32 widened (scale_action)
+#pragma unroll 1
+    for (int sub = 0; sub < CPC::nsteps; sub++) {
+      u[0] = fma(kCP.dtcb, u[1], u[0]);                    // x += dt (sum beta) xdot_0; the xddot terms follow per stage
+      double W2, W3;
+#pragma unroll
+      for (int i = 0; i < 6; i++) {
+        const double omd = u[3];
+        const float th = (float)u[2], om = (float)omd;
+        float s, c;
+        sincosf(th, &s, &c);                               // (the MUFU pair __sincosf costs 1.3e-5 teacher-forced: outside the gate)
+        const float fac2 = fmaf(-A1, c * c, A0);           // :162
+        const float F1 = fmaf(mpl * (om * om), s, Ff);     // :163
+        const float num = fmaf(g, s, -(F1 * c) * inv_tot); // :164
+        const float dd4 = __fdividef(num, fac2);
+        const float dd2 = fmaf(-mpl * dd4, c, F1) * inv_tot;   // :165
+        const double dd2d = (double)dd2, dd4d = (double)dd4;
+        u[1] = fma(kCPM.cvm[i], dd2d, u[1]);
+        if (i < 5) u[0] = fma(kCPM.cxm[i], dd2d, u[0]);    // (gamma_5 = 0)
+        if (i == 0) {
+          W2 = omd; W3 = dd4d;
+        } else {
+          W2 = fma(W2, kCP.a[i], omd); W3 = fma(W3, kCP.a[i], dd4d);
+        }
+        u[2] = fma(W2, kCP.bdt[i], u[2]);
+        u[3] = fma(W3, kCP.bdt[i], u[3]);
+      }
+    }
+  }
+  static __device__ __forceinline__ float reward(const double (&u)[4]) { return CartPoleDyn<double>::reward(u); }
+  static __device__ __forceinline__ void observe(const double (&u)[4], float (&o)[6]) { CartPoleDyn<double>::observe(u, o); }
+};
+
 // ---------------------------------------------------------------------------------------- variants
 // The branches the reference header documents but ships disabled (b200ppo.h B2_ENV_*): SWINGUP dynamics / reward /
 // is_over, early termination inside advance(), random initial state.  Opt-in and never on the benchmark path, so the

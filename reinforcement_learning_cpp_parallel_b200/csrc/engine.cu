@@ -583,7 +583,7 @@ int b2_create(const b2_config* cfg, b2_handle* out) {
   if (!is_default_net && (cfg->hidden1 < 64 || cfg->hidden2 < 64 || cfg->hidden1 > 256 || cfg->hidden2 > 256 || cfg->hidden1 % 64 || cfg->hidden2 % 64))
     return set_error(B2_ERR_INVALID, "hidden widths %dx%d not built: 64x32 (reference) or both in {64,128,192,256}", cfg->hidden1, cfg->hidden2);
   if (cfg->n_envs < 1 || cfg->horizon < 1 || cfg->n_timestep < 1) return set_error(B2_ERR_INVALID, "n_envs, horizon, n_timestep must be >= 1");
-  if (cfg->precision != B2_PREC_F64 && cfg->precision != B2_PREC_F32) return set_error(B2_ERR_INVALID, "unknown precision %d", cfg->precision);
+  if (cfg->precision != B2_PREC_F64 && cfg->precision != B2_PREC_F32 && cfg->precision != B2_PREC_MIXED) return set_error(B2_ERR_INVALID, "unknown precision %d", cfg->precision);
   if (cfg->env_flags & ~(B2_ENV_SWINGUP | B2_ENV_RANDOM_INIT | B2_ENV_EARLY_TERM)) return set_error(B2_ERR_INVALID, "unknown env_flags 0x%x", cfg->env_flags);
   if (cfg->env_flags && cfg->precision != B2_PREC_F64) return set_error(B2_ERR_INVALID, "env variants (env_flags 0x%x) run the double-precision physics only", cfg->env_flags);
   if (cfg->k_epochs < 1 || cfg->n_minibatches < 1) return set_error(B2_ERR_INVALID, "k_epochs and n_minibatches must be >= 1");

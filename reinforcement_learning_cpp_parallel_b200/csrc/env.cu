@@ -13,10 +13,11 @@ __global__ void __launch_bounds__(128) k_env_step(double* __restrict__ state, in
                                                   const double* __restrict__ force, int64_t n) {
   const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= n) return;
-  Real u[4];
+  using S = typename StateOf<Real>::type;   // double for B2_PREC_MIXED
+  S u[4];
 #pragma unroll
-  for (int j = 0; j < 4; j++) u[j] = (Real)state[j * n + e];
-  CartPoleDyn<Real>::advance(u, (Real)force[e]);   // F = action[0]; step++ (:108-109)
+  for (int j = 0; j < 4; j++) u[j] = (S)state[j * n + e];
+  CartPoleDyn<Real>::advance(u, (S)force[e]);   // F = action[0]; step++ (:108-109)
 #pragma unroll
   for (int j = 0; j < 4; j++) state[j * n + e] = (double)u[j];
   ep_step[e] += 1;
@@ -72,6 +73,7 @@ cudaError_t launch_env_step(double* state, int32_t* ep_step, const double* force
   cudaError_t e = cudaMemsetAsync(terminated, 0, (size_t)n, st);        // the shipped advance() returns 0 (:117)
   if (e != cudaSuccess) return e;
   if (precision == B2_PREC_F64) k_env_step<double><<<grid, 128, 0, st>>>(state, ep_step, force, n);
+  else if (precision == B2_PREC_MIXED) k_env_step<MixedPrec><<<grid, 128, 0, st>>>(state, ep_step, force, n);
   else k_env_step<float><<<grid, 128, 0, st>>>(state, ep_step, force, n);
   return cudaGetLastError();
 }

@@ -73,9 +73,10 @@ __device__ __forceinline__ void rollout_segment(const RolloutArgs& a, const floa
   if (e >= NE) return;  // ragged last group (no warp-level sync below this line, except under full_group)
   const bool full_group = g * 32 + 32 <= NE;
 
-  Real u[4];
+  using S = typename StateOf<Real>::type;   // double for B2_PREC_MIXED
+  S u[4];
 #pragma unroll
-  for (int j = 0; j < 4; j++) u[j] = (Real)__ldcg(a.state + j * NE + e);
+  for (int j = 0; j < 4; j++) u[j] = (S)__ldcg(a.state + j * NE + e);
   int es = __ldcg(a.ep_step + e);
   float er = __ldcg(a.ep_ret + e);
   int ecount = (a.t_begin + t0 == 0) ? 0 : __ldcg(a.ep_count + e);
@@ -102,12 +103,12 @@ __device__ __forceinline__ void rollout_segment(const RolloutArgs& a, const floa
     if constexpr (VAR) {
       const CartPoleVar::Adv adv = CartPoleVar::advance(make_double4((double)u[0], (double)u[1], (double)u[2], (double)u[3]),
                                                         scale_action(act), a.env_flags, es + 1);
-      u[0] = (Real)adv.u.x; u[1] = (Real)adv.u.y; u[2] = (Real)adv.u.z; u[3] = (Real)adv.u.w;
+      u[0] = (S)adv.u.x; u[1] = (S)adv.u.y; u[2] = (S)adv.u.z; u[3] = (S)adv.u.w;
       terminal = adv.term != 0;                                          // src/main.cpp:81-85
       const double ud[4] = {adv.u.x, adv.u.y, adv.u.z, adv.u.w};
       r = CartPoleVar::reward(a.env_flags, ud);
     } else {
-      Dyn::advance(u, (Real)scale_action(act));                          // src/main.cpp:57-71
+      Dyn::advance(u, (S)scale_action(act));                          // src/main.cpp:57-71
       r = Dyn::reward(u);                                                // :73
     }
     es += 1;
@@ -159,9 +160,9 @@ __device__ __forceinline__ void rollout_segment(const RolloutArgs& a, const floa
       if constexpr (VAR) {
         double u0[4];
         CartPoleVar::init_state(a.env_flags, a.seed, a.env_offset + (uint64_t)e, a.step0 + (uint64_t)t + 1, u0);
-        u[0] = (Real)u0[0]; u[1] = (Real)u0[1]; u[2] = (Real)u0[2]; u[3] = (Real)u0[3];
+        u[0] = (S)u0[0]; u[1] = (S)u0[1]; u[2] = (S)u0[2]; u[3] = (S)u0[3];
       } else {
-        u[0] = u[1] = u[2] = u[3] = (Real)0;                             // cart_pole.h:86
+        u[0] = u[1] = u[2] = u[3] = (S)0;                             // cart_pole.h:86
       }
       es = 0;
       er = 0.0f;
@@ -254,6 +255,8 @@ cudaError_t launch_rollout(const RolloutArgs& a, int precision, bool trace, int 
   }
   if (precision == B2_PREC_F64)
     return trace ? launch_t<double, true>(a, sm_count, st) : launch_t<double, false>(a, sm_count, st);
+  if (precision == B2_PREC_MIXED)
+    return trace ? launch_t<MixedPrec, true>(a, sm_count, st) : launch_t<MixedPrec, false>(a, sm_count, st);
   return trace ? launch_t<float, true>(a, sm_count, st) : launch_t<float, false>(a, sm_count, st);
 }
 

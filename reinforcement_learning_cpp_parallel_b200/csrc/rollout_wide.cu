@@ -21,9 +21,10 @@ __global__ void __launch_bounds__(128) k_rw_observe(const RolloutArgs a, int t) 
   const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= a.n_envs) return;
   const int64_t NE = a.n_envs, k = (int64_t)t * NE + e;
-  Real u[4];
+  using S = typename StateOf<Real>::type;   // double for B2_PREC_MIXED
+  S u[4];
 #pragma unroll
-  for (int j = 0; j < 4; j++) u[j] = (Real)a.state[j * NE + e];
+  for (int j = 0; j < 4; j++) u[j] = (S)a.state[j * NE + e];
   float o[6];
   CartPoleDyn<Real>::observe(u, o);
 #pragma unroll
@@ -36,9 +37,10 @@ __global__ void __launch_bounds__(128) k_rw_step(const RolloutArgs a, int t, int
   const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= a.n_envs) return;
   const int64_t NE = a.n_envs, k = (int64_t)t * NE + e;
-  Real u[4];
+  using S = typename StateOf<Real>::type;   // double for B2_PREC_MIXED
+  S u[4];
 #pragma unroll
-  for (int j = 0; j < 4; j++) u[j] = (Real)a.state[j * NE + e];
+  for (int j = 0; j < 4; j++) u[j] = (S)a.state[j * NE + e];
   int es = a.ep_step[e];
   float er = a.ep_ret[e];
   int ecount = (t == 0) ? 0 : a.ep_count[e];
@@ -57,12 +59,12 @@ __global__ void __launch_bounds__(128) k_rw_step(const RolloutArgs a, int t, int
   if constexpr (VAR) {
     const CartPoleVar::Adv adv = CartPoleVar::advance(make_double4((double)u[0], (double)u[1], (double)u[2], (double)u[3]),
                                                       scale_action(act), a.env_flags, es + 1);
-    u[0] = (Real)adv.u.x; u[1] = (Real)adv.u.y; u[2] = (Real)adv.u.z; u[3] = (Real)adv.u.w;
+    u[0] = (S)adv.u.x; u[1] = (S)adv.u.y; u[2] = (S)adv.u.z; u[3] = (S)adv.u.w;
     terminal = adv.term != 0;                                             // src/main.cpp:81-85
     const double ud[4] = {adv.u.x, adv.u.y, adv.u.z, adv.u.w};
     r = CartPoleVar::reward(a.env_flags, ud);
   } else {
-    Dyn::advance(u, (Real)scale_action(act));                             // src/main.cpp:57-71
+    Dyn::advance(u, (S)scale_action(act));                             // src/main.cpp:57-71
     r = Dyn::reward(u);                                                   // :73
   }
   es += 1;
@@ -81,9 +83,9 @@ __global__ void __launch_bounds__(128) k_rw_step(const RolloutArgs a, int t, int
     if constexpr (VAR) {
       double u0[4];
       CartPoleVar::init_state(a.env_flags, a.seed, a.env_offset + (uint64_t)e, a.step0 + (uint64_t)t + 1, u0);
-      u[0] = (Real)u0[0]; u[1] = (Real)u0[1]; u[2] = (Real)u0[2]; u[3] = (Real)u0[3];
+      u[0] = (S)u0[0]; u[1] = (S)u0[1]; u[2] = (S)u0[2]; u[3] = (S)u0[3];
     } else {
-      u[0] = u[1] = u[2] = u[3] = (Real)0;                                // cart_pole.h:86
+      u[0] = u[1] = u[2] = u[3] = (S)0;                                // cart_pole.h:86
     }
     es = 0;
     er = 0.0f;
@@ -105,13 +107,14 @@ cudaError_t launch_rollout_wide(const RolloutArgs& a, const NetDims& d, int prec
   const unsigned grid = (unsigned)((a.n_envs + 127) / 128);
   cudaError_t e;
   for (int t = a.t_begin; t < a.t_end; t++) {
-    if (precision == B2_PREC_F64) k_rw_observe<double><<<grid, 128, 0, st>>>(a, t);
+    if (precision != B2_PREC_F32) k_rw_observe<double><<<grid, 128, 0, st>>>(a, t);   // (mixed: double state, same observe)
     else k_rw_observe<float><<<grid, 128, 0, st>>>(a, t);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     const int64_t k0 = (int64_t)t * a.n_envs;
     if ((e = launch_wide_forward(d, a.params, a.tr.obs + k0, a.tr.cap, 1, nullptr, a.n_envs, 1, a.tr.mu + k0, st)) != cudaSuccess) return e;
     if (a.env_flags) k_rw_step<double, true><<<grid, 128, 0, st>>>(a, t, trace ? 1 : 0);
     else if (precision == B2_PREC_F64) k_rw_step<double, false><<<grid, 128, 0, st>>>(a, t, trace ? 1 : 0);
+    else if (precision == B2_PREC_MIXED) k_rw_step<MixedPrec, false><<<grid, 128, 0, st>>>(a, t, trace ? 1 : 0);
     else k_rw_step<float, false><<<grid, 128, 0, st>>>(a, t, trace ? 1 : 0);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     *launches += 3;

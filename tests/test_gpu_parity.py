@@ -177,6 +177,43 @@ def test_env_replay_fp32_drift_is_bounded(pkg, case):
     E.close()
 
 
+@pytest.mark.parametrize("case", ["c1", "c2"])
+def test_env_mixed_precision_teacher_forced(pkg, case):
+    """B2_PREC_MIXED (double state + RK accumulators, f32 Diff; SURVEY s7.3.1 / T2 "mixed: 1e-5 teacher-forced"): every
+    step starts from the REFERENCE's double state (b2_env_set_state), takes the recorded force and must land within 1e-5
+    of ||u||_inf of the reference's next state.  The free-running drift over whole episodes is printed, not gated
+    (survey probe, BASELINE.md s2: median 1.7e-5, p99 1.6e-4 after 100 steps)."""
+    nenv, T, tn = _case_tn(case)
+    st = tn(gold(f"{case}_state.f64"), 4)                      # [T][nenv][4]: the state AFTER step t
+    act = tn(gold(f"{case}_action.f32"))                        # [T][nenv]
+    prev = np.concatenate([np.zeros((1, nenv, 4)), st[:-1]], axis=0)
+    prev[np.arange(T) % 100 == 0] = 0.0                         # episodes restart from the zero state (cart_pole.h:86)
+    force = ((act.astype(np.float32) + np.float32(1.0)).astype(np.float64) * 10.0 - 10.0).astype(np.float32).astype(np.float64)
+    n = T * nenv
+    E = make_engine(pkg, n_envs=n, horizon=1, precision=pkg.PREC_MIXED)
+    E.env_set_state(np.ascontiguousarray(prev.reshape(n, 4)), np.zeros(n, np.int32))
+    E.env_step(np.ascontiguousarray(force.reshape(n)))
+    u, _ = E.env_get_state()
+    ref = st.reshape(n, 4)
+    scale = np.maximum(np.abs(ref).max(axis=-1, keepdims=True), 1e-3)
+    err = np.abs(u - ref) / scale
+    print("mixed precision, teacher-forced single step: max %.3e, median %.3e" % (err.max(), np.median(err.max(axis=-1))))
+    assert err.max() < 1e-5, err.max()
+    E.close()
+    # free-running replay of the recorded actions: rewards / flags must still match, the drift is reported
+    E = make_engine(pkg, n_envs=nenv, horizon=T, precision=pkg.PREC_MIXED)
+    E.set_params(gold("init_params.f32"))
+    E.set_state_trace(True)
+    E.rollout(T, forced_action=act)
+    out = E.traj_download(T, state_trace=True)
+    scale = np.maximum(np.abs(st).max(axis=-1, keepdims=True), 1e-3)
+    d = (np.abs(out["state_trace"] - st) / scale).max(axis=(1, 2)).reshape(-1, 100)
+    print("mixed precision drift: first-step max %.3e, end-of-episode median %.3e max %.3e" % (d[:, 0].max(), np.median(d[:, -1]), d[:, -1].max()))
+    assert d[:, 0].max() < 1e-5 and np.median(d[:, -1]) < 1e-3
+    assert (out["reward"] == tn(gold(f"{case}_reward.f32"))).mean() > 0.999
+    E.close()
+
+
 # ------------------------------------------------------------------------------------------- T4
 @pytest.mark.parametrize("case,flagcase", [("c1", "c1"), ("c2", "c2"), ("c1", "c1_term")])
 def test_returns(pkg, case, flagcase):

@@ -75,7 +75,7 @@ Options parse(int argc, char** argv) {
     };
     if (a == "--envs") o.envs = atol(next());
     else if (a == "--iters") o.iters = atol(next());
-    else if (a == "--precision") o.precision = std::string(next()) == "f32" ? B2_PREC_F32 : B2_PREC_F64;
+    else if (a == "--precision") { const std::string v = next(); o.precision = v == "f32" ? B2_PREC_F32 : (v == "mixed" ? B2_PREC_MIXED : B2_PREC_F64); }
     else if (a == "--seed") o.seed = strtoull(next(), nullptr, 0);
     else if (a == "--log-dir") o.log_dir = next();
     else if (a == "--log-envs") o.log_envs = atol(next());
