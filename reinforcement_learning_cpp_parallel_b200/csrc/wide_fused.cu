@@ -49,37 +49,6 @@ constexpr int SMEM_LIMIT = 227 * 1024;
 
 __device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 
-__device__ __forceinline__ uint32_t pack2_bf16(float lo, float hi) {   // lower 16 bits = lo (the lower column)
-  uint32_t d;
-  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
-  return d;
-}
-// (x0, x1) -> packed hi pair and packed mid pair, x = hi + mid + O(2^-17 |x|)   (== tc::split_bf16 per element)
-__device__ __forceinline__ void split2(float x0, float x1, uint32_t& hi, uint32_t& mid) {
-  hi = pack2_bf16(x0, x1);
-  mid = pack2_bf16(x0 - __uint_as_float(hi << 16), x1 - __uint_as_float(hi & 0xffff0000u));
-}
-
-// tanh of four values with ONE reciprocal: tanh x = 1 - 2 / (e + 1), e = 2^(2 x log2 e), and 1 / a_i out of 1 / (a0 a1 a2 a3).
-// The head is MUFU-bound with two MUFU per element (ex2 + rcp, 16 lanes per clock per SM against 128 for FMA): this
-// is 1.25.  x is clamped at 10 (tanh 10 = 1 - 4e-9 rounds to 1.0f), so the product of four a_i <= 2^116 stays finite.
-// Absolute error ~3e-7 like act_tanh (both cancel in 1 - 2 r near 0), far inside the bf16x3 products' 2^-16.
-// The arguments come PRE-SCALED, t = 2 log2(e) x (one FFMA from the accumulator: z K + b2 K, the bias stored scaled).
-constexpr float TANH_K = 2.8853900817779268f;
-__device__ __forceinline__ void tanh4(float t0, float t1, float t2, float t3, float& h0, float& h1, float& h2, float& h3) {
-  float e0, e1, e2, e3, r;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(fminf(t0, 10.0f * TANH_K)));
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(fminf(t1, 10.0f * TANH_K)));
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e2) : "f"(fminf(t2, 10.0f * TANH_K)));
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e3) : "f"(fminf(t3, 10.0f * TANH_K)));
-  const float a0 = e0 + 1.0f, a1 = e1 + 1.0f, a2 = e2 + 1.0f, a3 = e3 + 1.0f;
-  const float p01 = a0 * a1, p23 = a2 * a3;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(p01 * p23));
-  const float r01 = r * p23, r23 = r * p01;
-  h0 = fmaf(-2.0f, r01 * a1, 1.0f); h1 = fmaf(-2.0f, r01 * a0, 1.0f);
-  h2 = fmaf(-2.0f, r23 * a3, 1.0f); h3 = fmaf(-2.0f, r23 * a2, 1.0f);
-}
-
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FH_THREADS, 1)
 k_wide_fh(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
           const __grid_constant__ CUtensorMap tmD, const FhArgs a) {

@@ -107,6 +107,12 @@ __global__ void __launch_bounds__(256, L1_CTAS) k_wide_l1(const WideArgs a) {
 #pragma unroll
   for (int v = 0; v < 6; v++) *reinterpret_cast<float4*>(&w[4 * v]) = *reinterpret_cast<const float4*>(ws + kg * 28 + 4 * v);
   *reinterpret_cast<float4*>(b) = *reinterpret_cast<const float4*>(ws + kg * 28 + 24);
+  // pre-scaled by 2 log2 e: tanh z = 1 - 2 / (2^(z K) + 1), and the four features of a thread share ONE reciprocal (tanh4):
+  // the kernel is MUFU-bound (XU pipe the busiest unit, profiles/r1l_prof_wide_side.txt), 1.25 instead of 2 per element
+#pragma unroll
+  for (int v = 0; v < 24; v++) w[v] *= TANH_K;
+#pragma unroll
+  for (int v = 0; v < 4; v++) b[v] *= TANH_K;
   for (int r0 = lo; r0 < hi; r0 += L1_TILE) {
     if (r0 != lo) {
       __syncthreads();                          // the previous tile's readers are done
@@ -116,20 +122,22 @@ __global__ void __launch_bounds__(256, L1_CTAS) k_wide_l1(const WideArgs a) {
     const int n = min(L1_TILE, hi - r0);
     for (int r = sl; worker && r < n; r += sstep) {
       const bool valid = r0 + r < a.count;
-      __align__(8) __nv_bfloat16 th[4], tm[4];
-      float x[S];
+      float x[S], z[4];
 #pragma unroll
       for (int c = 0; c < S; c++) x[c] = xs[r][c];
 #pragma unroll
       for (int u = 0; u < 4; u++) {
-        float z = b[u];
+        z[u] = b[u];
 #pragma unroll
-        for (int c = 0; c < S; c++) z = fmaf(w[u * S + c], x[c], z);
-        tc::split_bf16(valid ? act_tanh(z) : 0.0f, th[u], tm[u]);
+        for (int c = 0; c < S; c++) z[u] = fmaf(w[u * S + c], x[c], z[u]);
       }
+      tanh4(z[0], z[1], z[2], z[3], z[0], z[1], z[2], z[3]);
+      uint2 th, tm;
+      split2(valid ? z[0] : 0.f, valid ? z[1] : 0.f, th.x, tm.x);
+      split2(valid ? z[2] : 0.f, valid ? z[3] : 0.f, th.y, tm.y);
       const int64_t o = (int64_t)(r0 + r) * H1 + kg * 4;
-      *reinterpret_cast<uint2*>(a.h1p + (g * 2 + 0) * plane + o) = *reinterpret_cast<const uint2*>(th);
-      *reinterpret_cast<uint2*>(a.h1p + (g * 2 + 1) * plane + o) = *reinterpret_cast<const uint2*>(tm);
+      *reinterpret_cast<uint2*>(a.h1p + (g * 2 + 0) * plane + o) = th;
+      *reinterpret_cast<uint2*>(a.h1p + (g * 2 + 1) * plane + o) = tm;
     }
   }
 }
