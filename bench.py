@@ -439,6 +439,25 @@ def configs1_leg(args, pkg, capi, np, local):
                        "n_envs": N, "horizon": T, "epochs": K, "records_per_update": N * T}}
 
 
+def _nvlink_kib(local):
+    """NVML's NVLink data counters of GPU `local` (payload KiB sent / received over all links since the driver loaded), or
+    None where NVML or the counters are unavailable.  Sampled around the timed wide updates at world > 1: the measured
+    bytes per optimizer step of the peer-memory gradient exchange (DESIGN.md s5 states them as arithmetic)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local)
+        vals = pynvml.nvmlDeviceGetFieldValues(h, [pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX, pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX])
+        out = []
+        for v in vals:
+            if v.nvmlReturn != 0:
+                return None
+            out.append(int(v.value.ullVal))
+        return tuple(out)
+    except Exception:
+        return None
+
+
 def wide_leg(args, pkg, capi, np, rank, local, world, dist, barrier, max_over_ranks, bf16_peak, bf16_src):
     """BASELINE configs[4]: PPO update sweep, 2x256 MLPs, 4M-sample batch over 8 GPUs = 524,288 samples per GPU,
     32 minibatches x 10 epochs; weak scaling (every rank owns its own 524,288 samples, gradients all-reduced)."""
@@ -473,12 +492,22 @@ def wide_leg(args, pkg, capi, np, rank, local, world, dist, barrier, max_over_ra
     barrier(E)
     ms = []
     l_before = E.kernel_launches()
+    nv0 = _nvlink_kib(local) if world > 1 else None
     for _ in range(args.steps):
         E.timer_start()
         st = E.update_resident()                 # returns scan + K x M optimizer steps on the resident batch
         ms.append(E.timer_stop_ms())
     launches = E.kernel_launches() - l_before
     barrier(E)
+    nv1 = _nvlink_kib(local) if world > 1 else None
+    nvlink = None
+    if nv0 and nv1:
+        osteps = args.steps * K * M
+        nvlink = {"tx_bytes_per_optimizer_step": 1024.0 * (nv1[0] - nv0[0]) / osteps,
+                  "rx_bytes_per_optimizer_step": 1024.0 * (nv1[1] - nv0[1]) / osteps, "optimizer_steps": osteps,
+                  "source": "NVML NVLINK_THROUGHPUT_DATA_TX / _RX of this rank's GPU, sampled around the timed updates (rank 0)",
+                  "arithmetic": {"scatter_shape": 2 * (world - 1) / world * 8 * 135682, "all_to_all": (world - 1) * 8 * 135682,
+                                 "note": "payload bytes per rank and step of the {value, step} pairs, P = 135,682 parameters + 3 sums"}}
     tot = max_over_ranks(sum(ms))
     value = B * K * args.steps * world / (tot * 1e-3)
     # e2e: the ppo_nn.h-shaped call, PPO::update(MemoryNN) on HOST buffers (pinned): H2D of the batch inside the timed region
@@ -527,13 +556,14 @@ def wide_leg(args, pkg, capi, np, rank, local, world, dist, barrier, max_over_ra
             "gpu_launches": int(launches),
             "e2e": {"value": B * K * args.steps * world / dt, "unit": "sample-epochs/s", "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": 4 * 8 * K * M, "api": "b2_update on pinned host buffers (PPO::update(MemoryNN))"},
-            "roofline": {"kernel": "whole optimizer step: k_gemm2_ws x2 + k_gemm_x3<MN> on tcgen05, 3 FP32 side kernels",
+            "roofline": {"kernel": "whole optimizer step: k_wide_fh (forward GEMM + loss head), k_gemm2_ws<dX>, k_gemm_x3<MN> (dW2 + dw1) on tcgen05; "
+                                   "k_wide_l1 and k_wide_reduce (+Adam) on FP32; traffic = the longest kernel of the chain (k_wide_fh)",
                          "bound": "tensor", "achieved": ach, "peak": bf16_peak / 3.0,
                          "unit": "TFLOP/s", "frac": ach / (bf16_peak / 3.0) if bf16_peak else None,
                          "peak_source": bf16_src + " / 3 (every fp32 product is three bf16 MMAs)",
                          "issued_bf16_tflops": 3 * ach, "flop_per_sample_epoch": FLOP_UPDATE_WIDE,
                          "traffic": _ncu_traffic("wide_dominant_kernel")[0], "traffic_source": _ncu_traffic("wide_dominant_kernel")[1],
-                         "comm_mode": comm_mode},
+                         "comm_mode": comm_mode, "nvlink": nvlink},
             "whole_batch_one_gpu": whole, "last_loss": st.loss}
 
 
@@ -687,6 +717,24 @@ def main():
         e2e = {"value": steps_all / dt, "unit": "env-steps/s", "h2d_bytes_per_step": int(hp.nbytes),
                "d2h_bytes_per_step": int(d2h), "host_numa_binding": numa, "api": "b2_set_params + b2_rollout_host (pinned host buffers; chunked launches with the copy engine moving chunk i "
                       "while chunk i+1 is simulated; B2_ROLLOUT_HOST_DIRECT=1 selects direct host stores from the kernel)"}
+        # the same through the opt-in compact record (25 instead of 37 B per env-step: obs4 + reward bit in the flag byte)
+        if True:
+            del out
+            outc = {"obs4": capi.pinned_empty((T, N, 4), np.float32), "action": capi.pinned_empty((T, N), np.float32),
+                    "logp": capi.pinned_empty((T, N), np.float32), "rflags": capi.pinned_empty((T, N), np.uint8)}
+            for _ in range(2):
+                E.set_params(hp); E.rollout_host_compact(T, outc, n_chunks=args.chunks)
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                E.set_params(hp)
+                E.rollout_host_compact(T, outc, n_chunks=args.chunks)
+            barrier()
+            dtc = max_over_ranks(time.perf_counter() - t0)
+            e2e["compact_record"] = {"value": steps_all / dtc, "unit": "env-steps/s",
+                                     "d2h_bytes_per_step": int(sum(a.nbytes for a in outc.values())),
+                                     "api": "b2_set_params + b2_rollout_host_compact (opt-in; the headline e2e above is MemoryNN's 37-B layout)"}
+            del outc
 
     update_wide = None
     if not args.no_wide:

@@ -38,6 +38,7 @@ typedef enum {
 #define B2_FLAG_TERMINAL 1u /* TERMINATE: return restarts from 0      (src/ppo_nn.cpp:229-230) */
 #define B2_FLAG_TIMEUP 2u   /* TIMEUP: bootstrap with V(pre-step obs) (src/ppo_nn.cpp:226-228) */
 #define B2_FLAG_TRUNC 4u    /* engine extension: rollout horizon cut an episode; bootstraps like TIMEUP */
+#define B2_FLAG_REWARD 8u   /* b2_batch_compact::rflags only: the record's reward is 1 (getReward is 0 / 1, cart_pole.h:142) */
 
 /* physics arithmetic of the rollout kernel */
 #define B2_PREC_F64 0 /* double state + double Diff: the parity-gated path (reference is double) */
@@ -104,6 +105,16 @@ typedef struct {
 typedef struct {
   float* obs; float* action; float* logp; float* mu; float* reward; uint8_t* flags; float* returns;
 } b2_batch_out;
+
+/* Compact host record of b2_rollout_host_compact: 25 B per env-step instead of the 37 B of MemoryNN's layout.  The
+ * observation leaves as getobs(4) = (x, xdot, thetadot, theta) (cos / sin are functions of theta, cart_pole.h:128-129)
+ * and the 0 / 1 reward rides in the flag byte.  Any field may be NULL. */
+typedef struct {
+  float* obs4;      /* [T][N][4] */
+  float* action;    /* [T][N] */
+  float* logp;      /* [T][N] */
+  uint8_t* rflags;  /* [T][N] B2_FLAG_* | B2_FLAG_REWARD */
+} b2_batch_compact;
 
 typedef struct {
   double loss1, loss2, loss3, loss; /* means over the LAST optimizer step's samples (src/ppo_nn.cpp:292-297) */
@@ -177,6 +188,10 @@ int b2_env_terminated(b2_handle h, uint8_t* terminated, int64_t n);
  * being simulated.  Fields of `out` may be NULL (skipped); `returns` is ignored (no returns exist yet).  Pinned
  * buffers (b2_host_alloc) are needed for the overlap; pageable ones work but serialise. */
 int b2_rollout_host(b2_handle h, int T, int n_chunks, const b2_batch_out* out);
+/* The same pipeline with the compact record (opt-in; the 37-B layout above stays what MemoryNN holds).  The transfer is
+ * PCIe-bound: 25 B per env-step leave in less time than the simulation takes, 37 B do not.  Default
+ * 6-64-32-1 nets and the shipped environment only. */
+int b2_rollout_host_compact(b2_handle h, int T, int n_chunks, const b2_batch_compact* out);
 int b2_update_resident(b2_handle h, b2_update_stats* stats);   /* returns + K epochs on the resident trajectory */
 int b2_train_iteration(b2_handle h, int T, b2_update_stats* stats); /* rollout + update_resident */
 int b2_traj_download(b2_handle h, b2_batch_out* out, double* state_trace /* [T][N][4] or NULL, only if tracing on */);

@@ -12,6 +12,7 @@ def lib_path():
 
 
 FLAG_TERMINAL, FLAG_TIMEUP, FLAG_TRUNC = 1, 2, 4
+FLAG_REWARD = 8   # b2_batch_compact.rflags only
 PREC_F64, PREC_F32, PREC_MIXED = 0, 1, 2
 ENV_SWINGUP, ENV_RANDOM_INIT, ENV_EARLY_TERM = 1, 2, 4
 COMM_ID_BYTES = 128
@@ -43,6 +44,10 @@ class Batch(C.Structure):
 
 class BatchOut(C.Structure):
     _fields_ = [(k, C.c_void_p) for k in ("obs", "action", "logp", "mu", "reward", "flags", "returns")]
+
+
+class BatchCompact(C.Structure):
+    _fields_ = [(k, C.c_void_p) for k in ("obs4", "action", "logp", "rflags")]
 
 
 class UpdateStats(C.Structure):
@@ -84,6 +89,7 @@ SYMBOLS = {
     "b2_env_get_state": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_int64]),
     "b2_rollout": (C.c_int, [_H, C.c_int, C.c_void_p]),
     "b2_rollout_host": (C.c_int, [_H, C.c_int, C.c_int, _P(BatchOut)]),
+    "b2_rollout_host_compact": (C.c_int, [_H, C.c_int, C.c_int, _P(BatchCompact)]),
     "b2_env_step": (C.c_int, [_H, C.c_void_p, C.c_int64]),
     "b2_env_observe": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_int64]),
     "b2_env_terminated": (C.c_int, [_H, C.c_void_p, C.c_int64]),
@@ -318,6 +324,12 @@ class Engine:
         bo = BatchOut(*[out[k].ctypes.data if k in out else None
                         for k in ("obs", "action", "logp", "mu", "reward", "flags")], None)
         _ck(self.L.b2_rollout_host(self.h, T, n_chunks, C.byref(bo)))
+        return out
+
+    def rollout_host_compact(self, T, out, n_chunks=8):
+        """b2_rollout_host_compact: the 25-B record (obs4 [T][N][4], action, logp, rflags = flags | FLAG_REWARD)."""
+        bc = BatchCompact(*[out[k].ctypes.data if k in out else None for k in ("obs4", "action", "logp", "rflags")])
+        _ck(self.L.b2_rollout_host_compact(self.h, T, n_chunks, C.byref(bc)))
         return out
 
     def update_resident(self):

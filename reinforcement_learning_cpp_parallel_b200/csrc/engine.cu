@@ -1014,13 +1014,14 @@ int b2_set_state_trace(b2_handle E, int enable) {
 
 // one k_rollout launch covering steps [t_begin, t_end) of a T-step rollout that started at E->global_step
 static int rollout_window(b2_engine* E, int T, int t_begin, int t_end, bool forced, float* obs_aos = nullptr,
-                          const b2_batch_out* host = nullptr) {
+                          const b2_batch_out* host = nullptr, float* obs4_aos = nullptr, uint8_t* rflags = nullptr) {
   RolloutArgs a{};
   a.params = E->params; a.state = E->state; a.ep_step = E->ep_step; a.ep_ret = E->ep_ret;
   a.ep_count = E->ep_count; a.ep_log = E->ep_log; a.max_eps = E->max_eps;
   a.tr = E->tr;
   a.forced_action = forced ? E->forced : nullptr;
   a.obs_aos = obs_aos;
+  a.obs4_aos = obs4_aos; a.rflags = rflags;
   if (host) { a.h_action = host->action; a.h_logp = host->logp; a.h_mu = host->mu; a.h_reward = host->reward; a.h_flags = host->flags; }
   a.n_envs = E->cfg.n_envs; a.T = T; a.t_begin = t_begin; a.t_end = t_end; a.n_timestep = E->cfg.n_timestep;
   a.seed = E->cfg.seed; a.env_offset = E->cfg.env_offset; a.step0 = E->global_step;
@@ -1072,6 +1073,22 @@ int b2_rollout(b2_handle E, int T, const float* forced_action) {
   if ((rc = rollout_window(E, T, 0, T, forced_action != nullptr))) return rc;
   rollout_finish(E, T);
   return B2_OK;
+}
+
+// chunk boundaries of the host pipeline (see b2_rollout_host): doubling head (2, 2, 4, .. steps), equal chunks, halving tail
+// (copy_bound = false: the copies take less time than the simulation -- the compact record -- so no doubling head: short
+// windows cost the persistent kernel its balance, 2 steps x 2,048 groups over 1,776 warps quantise to 3 units for 2.3)
+static int host_chunk_schedule(int T, int n_chunks, int* bounds, bool copy_bound = true) {
+  int nb = 0;
+  const int cap = (T + n_chunks - 1) / n_chunks;
+  int t = 0;
+  bounds[0] = 0;
+  for (int len = 2; copy_bound && len < cap && T - t > 2 * cap && nb < 6; len *= 2) { t += len; bounds[++nb] = t; if (nb == 1) { t += len; bounds[++nb] = t; } }
+  while (T - t > cap && nb < B2_MAX_CHUNKS - 8) { t += cap; bounds[++nb] = t; }
+  int r = T - t;                                   // the last <= cap steps (more only if out of events): halving tail
+  while (r > 2 && nb < B2_MAX_CHUNKS - 1) { const int len = r / 2; t += len; r -= len; bounds[++nb] = t; }
+  bounds[++nb] = T;
+  return nb;
 }
 
 // Rollout with the trajectory delivered into HOST buffers.  The horizon is cut into n_chunks launches; while
@@ -1127,17 +1144,7 @@ int b2_rollout_host(b2_handle E, int T, int n_chunks, const b2_batch_out* out) {
   // The copy engine is nearly as busy as the SMs (5.4 vs 5.6 ms at the reference shape), so the FIRST chunk matters as
   // much: nothing can leave before it is simulated.  Doubling head (2, 2, 4, .. steps), equal chunks, halving tail.
   int bounds[B2_MAX_CHUNKS + 1];
-  int nb = 0;
-  {
-    const int cap = (T + n_chunks - 1) / n_chunks;
-    int t = 0;
-    bounds[0] = 0;
-    for (int len = 2; len < cap && T - t > 2 * cap && nb < 6; len *= 2) { t += len; bounds[++nb] = t; if (nb == 1) { t += len; bounds[++nb] = t; } }
-    while (T - t > cap && nb < B2_MAX_CHUNKS - 8) { t += cap; bounds[++nb] = t; }
-    int r = T - t;                                   // the last <= cap steps (more only if out of events): halving tail
-    while (r > 2 && nb < B2_MAX_CHUNKS - 1) { const int len = r / 2; t += len; r -= len; bounds[++nb] = t; }
-    bounds[++nb] = T;
-  }
+  const int nb = host_chunk_schedule(T, n_chunks, bounds);
   for (int c = 0; c < nb; c++) {
     const int t0 = bounds[c], t1 = bounds[c + 1];
     // 6-wide observations leave the kernel record-major as well (RolloutArgs::obs_aos): no transpose between the
@@ -1164,6 +1171,47 @@ int b2_rollout_host(b2_handle E, int T, int n_chunks, const b2_batch_out* out) {
   }
   rollout_finish(E, T);
   // the main stream must not overwrite the buffer (next rollout) before the copies have drained
+  CK(cudaEventRecord(E->copy_done, E->copy_stream));
+  CK(cudaStreamWaitEvent(E->stream, E->copy_done, 0));
+  CK(cudaStreamSynchronize(E->copy_stream));
+  return check_status(E, "rollout");
+}
+
+// The chunked copy-engine pipeline of b2_rollout_host with the compact record (b200ppo.h b2_batch_compact): the kernel
+// also leaves (x, xdot, thetadot, theta) as one 16-B record per env-step and flags | reward bit in device staging,
+// and 25 instead of 37 B per env-step cross PCIe -- less time than the simulation takes, so the run is compute-bound.
+int b2_rollout_host_compact(b2_handle E, int T, int n_chunks, const b2_batch_compact* out) {
+  NEED(E);
+  if (!out) return set_error(B2_ERR_INVALID, "rollout_host_compact: null out");
+  if (E->wide || E->cfg.env_flags || E->S_ext != OBS)
+    return set_error(B2_ERR_INVALID, "rollout_host_compact: default nets, the shipped environment and obs_vars = 6 only");
+  int rc = rollout_prepare(E, T, nullptr);
+  if (rc) return rc;
+  if (n_chunks < 1) n_chunks = 1;
+  if (n_chunks > T) n_chunks = T;
+  if (n_chunks > B2_MAX_CHUNKS) n_chunks = B2_MAX_CHUNKS;
+  const int64_t NE = E->cfg.n_envs;
+  Traj& t = E->tr;
+  if ((rc = ensure_stage(E, NE * T * 4, NE * T))) return rc;
+  if (!E->copy_stream) {
+    CK(cudaStreamCreateWithFlags(&E->copy_stream, cudaStreamNonBlocking));
+    for (auto& ev : E->chunk_ev) CK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&E->copy_done, cudaEventDisableTiming));
+  }
+  int bounds[B2_MAX_CHUNKS + 1];
+  const int nb = host_chunk_schedule(T, n_chunks, bounds, false);
+  for (int c = 0; c < nb; c++) {
+    const int t0 = bounds[c], t1 = bounds[c + 1];
+    if ((rc = rollout_window(E, T, t0, t1, false, nullptr, nullptr, E->stage, E->stage_u8))) return rc;
+    const int64_t k0 = (int64_t)t0 * NE, n = (int64_t)(t1 - t0) * NE;
+    CK(cudaEventRecord(E->chunk_ev[c], E->stream));
+    CK(cudaStreamWaitEvent(E->copy_stream, E->chunk_ev[c], 0));
+    if (out->obs4) CK(cudaMemcpyAsync(out->obs4 + k0 * 4, E->stage + k0 * 4, sizeof(float) * 4 * n, cudaMemcpyDeviceToHost, E->copy_stream));
+    if (out->action) CK(cudaMemcpyAsync(out->action + k0, t.action + k0, sizeof(float) * n, cudaMemcpyDeviceToHost, E->copy_stream));
+    if (out->logp) CK(cudaMemcpyAsync(out->logp + k0, t.logp + k0, sizeof(float) * n, cudaMemcpyDeviceToHost, E->copy_stream));
+    if (out->rflags) CK(cudaMemcpyAsync(out->rflags + k0, E->stage_u8 + k0, (size_t)n, cudaMemcpyDeviceToHost, E->copy_stream));
+  }
+  rollout_finish(E, T);
   CK(cudaEventRecord(E->copy_done, E->copy_stream));
   CK(cudaStreamWaitEvent(E->stream, E->copy_done, 0));
   CK(cudaStreamSynchronize(E->copy_stream));

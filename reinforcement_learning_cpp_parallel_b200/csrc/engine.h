@@ -78,6 +78,8 @@ struct RolloutArgs {
   // PCIe writes, 37 B per record ~ 49 GB/s at the reference shape), so the trajectory is on the host when the kernel ends
   float *h_action, *h_logp, *h_mu, *h_reward;   // each null or [T][N] in pinned host memory
   uint8_t* h_flags;
+  float* obs4_aos;             // null, or [T][N][4] device staging of (x, xdot, thetadot, theta): b2_rollout_host_compact
+  uint8_t* rflags;             // null, or [T][N] device staging of flags | B2_FLAG_REWARD
   float* obs_aos;              // null, or [T][N][6] (device staging or pinned host): the observations ALSO as records (what MemoryNN holds) for b2_rollout_host,
                                // so that no transpose kernel sits between the simulation and the D2H copy
   int64_t n_envs;

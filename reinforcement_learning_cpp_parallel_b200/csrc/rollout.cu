@@ -140,6 +140,10 @@ __device__ __forceinline__ void rollout_segment(const RolloutArgs& a, const floa
         __stcs(rec, make_float2(o[0], o[1])); __stcs(rec + 1, make_float2(o[2], o[3])); __stcs(rec + 2, make_float2(o[4], o[5]));
       }
     }
+    if (a.obs4_aos) {                                                    // compact host record: one 16-B store per record
+      __stcs(reinterpret_cast<float4*>(a.obs4_aos) + k, make_float4(o[0], o[1], o[2], o[3]));
+      a.rflags[k] = (uint8_t)(fl | (r != 0.0f ? B2_FLAG_REWARD : 0u));
+    }
     __stcs(a.tr.action + k, act);
     __stcs(a.tr.logp + k, lp);
     __stcs(a.tr.mu + k, mu);

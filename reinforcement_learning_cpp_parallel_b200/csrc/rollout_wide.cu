@@ -103,7 +103,7 @@ __global__ void __launch_bounds__(128) k_rw_step(const RolloutArgs a, int t, int
 cudaError_t launch_rollout_wide(const RolloutArgs& a, const NetDims& d, int precision, bool trace, cudaStream_t st,
                                 int64_t* launches) {
   if (a.env_flags && precision != B2_PREC_F64) return cudaErrorInvalidValue;
-  if (a.obs_aos || a.h_action || a.h_logp || a.h_mu || a.h_reward || a.h_flags) return cudaErrorInvalidValue;   // k_rollout only
+  if (a.obs_aos || a.obs4_aos || a.h_action || a.h_logp || a.h_mu || a.h_reward || a.h_flags) return cudaErrorInvalidValue;   // k_rollout only
   const unsigned grid = (unsigned)((a.n_envs + 127) / 128);
   cudaError_t e;
   for (int t = a.t_begin; t < a.t_end; t++) {

@@ -305,3 +305,29 @@ def test_rollout_host_four_wide_observations(pkg):
     for k in out:
         np.testing.assert_array_equal(out[k], a[k], err_msg=k)
     E.close()
+
+
+def test_rollout_host_compact_record(pkg):
+    """b2_rollout_host_compact (25 B per env-step): obs4 = the first four observation components, the reward rides in
+    the flag byte; everything bit-identical to the resident rollout of a twin engine (same seed), ragged env count."""
+    from reinforcement_learning_cpp_parallel_b200 import capi
+    N, T = 1000 + 7, 40
+    A = make_engine(pkg, n_envs=N, horizon=T, seed=11)
+    B = make_engine(pkg, n_envs=N, horizon=T, seed=11)
+    p = gold("init_params.f32")
+    A.set_params(p); B.set_params(p)
+    A.rollout(T)
+    ref = A.traj_download(T)
+    out = {"obs4": capi.pinned_empty((T, N, 4), np.float32), "action": capi.pinned_empty((T, N), np.float32),
+           "logp": capi.pinned_empty((T, N), np.float32), "rflags": capi.pinned_empty((T, N), np.uint8)}
+    for k in out:
+        out[k][...] = 0x55 if out[k].dtype == np.uint8 else np.nan
+    B.rollout_host_compact(T, out, n_chunks=5)
+    assert np.array_equal(out["obs4"], ref["obs"][..., :4])
+    assert np.array_equal(out["action"], ref["action"]) and np.array_equal(out["logp"], ref["logp"])
+    assert np.array_equal(out["rflags"] & 7, ref["flags"])
+    assert np.array_equal((out["rflags"] >> 3) & 1, (ref["reward"] != 0).astype(np.uint8))
+    # the device-resident trajectory is the same one: an update on it matches the twin's
+    sa, sb = A.update_resident(), B.update_resident()
+    assert sa.loss == sb.loss and np.array_equal(A.get_params(), B.get_params())
+    A.close(); B.close()
