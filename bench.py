@@ -447,15 +447,17 @@ def _nvlink_kib(local):
         import pynvml
         pynvml.nvmlInit()
         h = pynvml.nvmlDeviceGetHandleByIndex(local)
-        vals = pynvml.nvmlDeviceGetFieldValues(h, [pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX, pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX])
+        ALL = 0xFFFFFFFF      # scopeId: the sum over the GPU's links
+        vals = pynvml.nvmlDeviceGetFieldValues(h, [(pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX, ALL),
+                                                   (pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX, ALL)])
         out = []
         for v in vals:
             if v.nvmlReturn != 0:
-                return None
+                return "nvmlReturn %d" % v.nvmlReturn
             out.append(int(v.value.ullVal))
         return tuple(out)
-    except Exception:
-        return None
+    except Exception as e:
+        return "%s: %s" % (type(e).__name__, e)
 
 
 def wide_leg(args, pkg, capi, np, rank, local, world, dist, barrier, max_over_ranks, bf16_peak, bf16_src):
@@ -489,10 +491,10 @@ def wide_leg(args, pkg, capi, np, rank, local, world, dist, barrier, max_over_ra
     st = E.update(obs, act, lp, reward, fl, n_envs=N, horizon=T)       # upload + warm-up 1
     for _ in range(2):
         E.set_params(w0); E.update_resident()
+    nv0 = _nvlink_kib(local) if world > 1 else None   # (before the barrier: NVML start-up differs by tens of ms between ranks)
     barrier(E)
     ms = []
     l_before = E.kernel_launches()
-    nv0 = _nvlink_kib(local) if world > 1 else None
     for _ in range(args.steps):
         E.timer_start()
         st = E.update_resident()                 # returns scan + K x M optimizer steps on the resident batch
@@ -501,7 +503,9 @@ def wide_leg(args, pkg, capi, np, rank, local, world, dist, barrier, max_over_ra
     barrier(E)
     nv1 = _nvlink_kib(local) if world > 1 else None
     nvlink = None
-    if nv0 and nv1:
+    if isinstance(nv0, str) or isinstance(nv1, str):
+        nvlink = {"unavailable": str(nv0 if isinstance(nv0, str) else nv1)}
+    elif nv0 and nv1:
         osteps = args.steps * K * M
         nvlink = {"tx_bytes_per_optimizer_step": 1024.0 * (nv1[0] - nv0[0]) / osteps,
                   "rx_bytes_per_optimizer_step": 1024.0 * (nv1[1] - nv0[1]) / osteps, "optimizer_steps": osteps,
