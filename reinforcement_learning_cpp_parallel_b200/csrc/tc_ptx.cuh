@@ -252,7 +252,8 @@ __device__ __forceinline__ uint32_t pack2_bf16(float lo, float hi) {   // lower 
 // (x0, x1) -> packed hi pair and packed mid pair, x = hi + mid + O(2^-17 |x|)   (== tc::split_bf16 per element)
 __device__ __forceinline__ void split2(float x0, float x1, uint32_t& hi, uint32_t& mid) {
   hi = pack2_bf16(x0, x1);
-  mid = pack2_bf16(x0 - __uint_as_float(hi << 16), x1 - __uint_as_float(hi & 0xffff0000u));
+  const float2 d = __fadd2_rn(make_float2(x0, x1), make_float2(-__uint_as_float(hi << 16), -__uint_as_float(hi & 0xffff0000u)));
+  mid = pack2_bf16(d.x, d.y);
 }
 
 // tanh of four values with ONE reciprocal: tanh x = 1 - 2 / (e + 1), e = 2^(2 x log2 e), and 1 / a_i out of 1 / (a0 a1 a2 a3).
@@ -262,17 +263,22 @@ __device__ __forceinline__ void split2(float x0, float x1, uint32_t& hi, uint32_
 // The arguments come PRE-SCALED, t = 2 log2(e) x (one FFMA from the accumulator: z K + b2 K, the bias stored scaled).
 constexpr float TANH_K = 2.8853900817779268f;
 __device__ __forceinline__ void tanh4(float t0, float t1, float t2, float t3, float& h0, float& h1, float& h2, float& h3) {
+  // packed FP32 (FADD2 / FMUL2 / FFMA2, sm_100): the pairwise products cost one issue slot per two -- these kernels are
+  // bound by instruction issue, not by the FMA pipe
   float e0, e1, e2, e3, r;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(fminf(t0, 10.0f * TANH_K)));
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(fminf(t1, 10.0f * TANH_K)));
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e2) : "f"(fminf(t2, 10.0f * TANH_K)));
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e3) : "f"(fminf(t3, 10.0f * TANH_K)));
-  const float a0 = e0 + 1.0f, a1 = e1 + 1.0f, a2 = e2 + 1.0f, a3 = e3 + 1.0f;
-  const float p01 = a0 * a1, p23 = a2 * a3;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(p01 * p23));
-  const float r01 = r * p23, r23 = r * p01;
-  h0 = fmaf(-2.0f, r01 * a1, 1.0f); h1 = fmaf(-2.0f, r01 * a0, 1.0f);
-  h2 = fmaf(-2.0f, r23 * a3, 1.0f); h3 = fmaf(-2.0f, r23 * a2, 1.0f);
+  const float2 one = make_float2(1.0f, 1.0f);
+  const float2 a02 = __fadd2_rn(make_float2(e0, e2), one), a13 = __fadd2_rn(make_float2(e1, e3), one);   // (a0, a2), (a1, a3)
+  const float2 p = __fmul2_rn(a02, a13);                                  // (a0 a1, a2 a3)
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(p.x * p.y));
+  const float2 rr = __fmul2_rn(make_float2(r, r), make_float2(p.y, p.x)); // (1 / (a0 a1), 1 / (a2 a3))
+  const float2 i02 = __fmul2_rn(rr, a13), i13 = __fmul2_rn(rr, a02);      // (1 / a0, 1 / a2), (1 / a1, 1 / a3)
+  const float2 m2 = make_float2(-2.0f, -2.0f);
+  const float2 h02 = __ffma2_rn(m2, i02, one), h13 = __ffma2_rn(m2, i13, one);
+  h0 = h02.x; h2 = h02.y; h1 = h13.x; h3 = h13.y;
 }
 
 }  // namespace b2

@@ -193,7 +193,7 @@ k_wide_fh(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         if (a.dbg && threadIdx.x == 64) a.dbg[blockIdx.x * 16 + it * 4 + 1] = clock64();
         const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * 256u;
         // ---- pass 1 over the row: activation, dot with W3, h back into TMEM
-        float ya = 0.f, yb = 0.f;
+        float2 yab = make_float2(0.f, 0.f);              // two chains of the row's dot product, one FFMA2 per pair
 #pragma unroll
         for (int ci = 0; ci < 4; ci++) {
           const int c = c_begin + ci * 16;
@@ -212,9 +212,12 @@ k_wide_fh(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
               float h0, h1, h2, h3;
               // (rows of the padding need no masking: their inputs are finite -- zero-filled or stale plane rows -- and their
               //  dz is exactly 0, so they add nothing to any sum and their D2 rows are written as zeros)
-              tanh4(fmaf(v[4 * i], TANH_K, bb[i].x), fmaf(v[4 * i + 1], TANH_K, bb[i].y), fmaf(v[4 * i + 2], TANH_K, bb[i].z),
-                    fmaf(v[4 * i + 3], TANH_K, bb[i].w), h0, h1, h2, h3);
-              ya = fmaf(ww[i].x, h0, ya); yb = fmaf(ww[i].y, h1, yb); ya = fmaf(ww[i].z, h2, ya); yb = fmaf(ww[i].w, h3, yb);
+              const float2 kk = make_float2(TANH_K, TANH_K);
+              const float2 t01 = __ffma2_rn(make_float2(v[4 * i], v[4 * i + 1]), kk, make_float2(bb[i].x, bb[i].y));
+              const float2 t23 = __ffma2_rn(make_float2(v[4 * i + 2], v[4 * i + 3]), kk, make_float2(bb[i].z, bb[i].w));
+              tanh4(t01.x, t01.y, t23.x, t23.y, h0, h1, h2, h3);
+              yab = __ffma2_rn(make_float2(ww[i].x, ww[i].y), make_float2(h0, h1), yab);
+              yab = __ffma2_rn(make_float2(ww[i].z, ww[i].w), make_float2(h2, h3), yab);
               v[4 * i] = h0; v[4 * i + 1] = h1; v[4 * i + 2] = h2; v[4 * i + 3] = h3;
             }
             tc::tmem_st16(t0 + (uint32_t)c, v);
@@ -223,7 +226,7 @@ k_wide_fh(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         // the four warps of this row quarter add their partial dot products through the staging buffers
         if (lane == 0) tc::bulk_wait_read<0>();           // (the last store of the previous tile has read this buffer)
         __syncwarp();
-        reinterpret_cast<float*>(sb)[lane] = ya + yb;
+        reinterpret_cast<float*>(sb)[lane] = yab.x + yab.y;
         tc::tmem_st_wait();
         bar_sync(1 + q, 128);
         float ytot = b3;
@@ -291,25 +294,26 @@ k_wide_fh(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
             for (int i = 0; i < 4; i++)
               *reinterpret_cast<float4*>(sb + lane * 64 + ((i ^ ((lane >> 1) & 3)) << 4)) = make_float4(h[4 * i], h[4 * i + 1], h[4 * i + 2], h[4 * i + 3]);
             __syncwarp();
-            float s1 = 0.f, s2 = 0.f;
+            float2 s12 = make_float2(0.f, 0.f);           // (sum dz h, sum dz (1 - h^2)): one FFMA2 per row step
 #pragma unroll
             for (int rr = 0; rr < 16; rr++) {             // this lane's row of the step: 2 rr + rh
               const float hv = *reinterpret_cast<const float*>(colb[rr & 3] + rr * 128);
               const float dr = __shfl_sync(0xffffffffu, dz, 2 * rr + rh);
-              s1 = fmaf(dr, hv, s1);
-              s2 = fmaf(dr, fmaf(-hv, hv, 1.0f), s2);
+              s12 = __ffma2_rn(make_float2(dr, dr), make_float2(hv, fmaf(-hv, hv, 1.0f)), s12);
             }
+            float s1 = s12.x, s2 = s12.y;
             s1 += __shfl_xor_sync(0xffffffffu, s1, 16);   // even rows + odd rows (the same sum in both halves of the warp)
             s2 += __shfl_xor_sync(0xffffffffu, s2, 16);
             gW3acc[ci] += s1;
             gb2acc[ci] += s2;
             // D2 in place of h, then the (hi | mid) bf16 tiles: 32 rows of 32 B per plane, 16-B chunk j of row r at j ^ ((r >> 2) & 1)
 #pragma unroll
-            for (int i = 0; i < 4; i++) {
-              h[4 * i] = dz * ww[i].x * (1.0f - h[4 * i] * h[4 * i]);
-              h[4 * i + 1] = dz * ww[i].y * (1.0f - h[4 * i + 1] * h[4 * i + 1]);
-              h[4 * i + 2] = dz * ww[i].z * (1.0f - h[4 * i + 2] * h[4 * i + 2]);
-              h[4 * i + 3] = dz * ww[i].w * (1.0f - h[4 * i + 3] * h[4 * i + 3]);
+            for (int i = 0; i < 4; i++) {                 // dz w3 (1 - h^2), two columns per instruction
+              const float2 dz2 = make_float2(dz, dz), one = make_float2(1.0f, 1.0f);
+              const float2 h01 = make_float2(h[4 * i], h[4 * i + 1]), h23 = make_float2(h[4 * i + 2], h[4 * i + 3]);
+              const float2 d01 = __fmul2_rn(__fmul2_rn(dz2, make_float2(ww[i].x, ww[i].y)), __ffma2_rn(make_float2(-h01.x, -h01.y), h01, one));
+              const float2 d23 = __fmul2_rn(__fmul2_rn(dz2, make_float2(ww[i].z, ww[i].w)), __ffma2_rn(make_float2(-h23.x, -h23.y), h23, one));
+              h[4 * i] = d01.x; h[4 * i + 1] = d01.y; h[4 * i + 2] = d23.x; h[4 * i + 3] = d23.y;
             }
             __syncwarp();                                 // every lane has read its column of the h tile
 #pragma unroll
