@@ -127,12 +127,17 @@ struct FhArgs {
   float* part_head;            // [grid][2][head_row]
   int head_row;
   long long* dbg;              // optional clock64 timeline of the head warps, [grid][16] (B2_FH_DBG=1, diagnostic runs)
+  int dx;                      // 1: the dX GEMM Z1 = D2 W2 of both nets runs in this kernel too (passes 2, 3)
 };
 int fh_stages(int N, int K);
 bool fh_supported(int N, int K);
 // tmA: h1p operand map (128-row boxes), tmB: K-major W2 in (H2/2)-row boxes, tmD: bf16 plane store map of d2p (32 x 32 boxes)
-cudaError_t launch_wide_fh(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmD, const FhArgs& a, int sm_count,
-                           int* grid_out, cudaStream_t st);
+// a.dx: tmA2 = d2p operand map (128-row boxes), tmB2 = W2 as [K = j][N = k] in 64 x 64 boxes, tmC = d1 (fp32) store map with
+// 16-column boxes (make_output_map16); ignored otherwise
+cudaError_t launch_wide_fh(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmD, const CUtensorMap& tmA2,
+                           const CUtensorMap& tmB2, const CUtensorMap& tmC, const FhArgs& a, int sm_count, int* grid_out, cudaStream_t st);
+// fp32 output map with boxes of 16 columns x 32 rows and the 64-B swizzle (the head warps' 2-KB staging tiles)
+int make_output_map16(CUtensorMap* out, const void* base, uint64_t N, uint64_t rows, uint64_t planes);
 // bf16 planes [planes][rows][N] written in boxes of 16 columns x 32 rows x 2 planes with the 32-B swizzle (the head's staging tiles)
 int make_plane_store_map(CUtensorMap* out, const void* base, uint64_t N, uint64_t rows, uint64_t planes);
 

@@ -51,7 +51,8 @@ __device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FH_THREADS, 1)
 k_wide_fh(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-          const __grid_constant__ CUtensorMap tmD, const FhArgs a) {
+          const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmA2,
+          const __grid_constant__ CUtensorMap tmB2, const __grid_constant__ CUtensorMap tmC, const FhArgs a) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = tc::smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
@@ -68,8 +69,17 @@ k_wide_fh(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
   uint64_t* tfull = empty + 4;
   uint64_t* tempty = tfull + 2;
   uint64_t* bfull = tempty + 2;                           // [4] one per K block of the resident weights (K <= 256)
-  uint64_t* wfree = bfull + 4;                            // [4] critic block kb no longer read: the actor's may land
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wfree + 4);
+  uint64_t* wfree = bfull + 4;                            // [4] weight block kb of the pass that ends is no longer read
+  uint64_t* d2done = wfree + 4;                           // [2] (a.dx) every D2 tile of net g written by THIS CTA's head warps has landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(d2done + 2);
+  // Passes.  0, 1: forward GEMM + head of the critic / the actor.  2, 3 (a.dx): the dX GEMM Z1 = D2 W2 of the critic / the
+  // actor on the SAME pair -- its A operand is the D2 tile this CTA's head warps have just stored, its weights (W2 as
+  // stored, read as an MN-major operand, this CTA's half of the COLUMNS) land over the forward weights, its MMAs run while
+  // the tensor pipe would otherwise idle under the actor's head, and its raw epilogue is done by the head warps.
+  // One launch, one prologue and one weight fetch less than k_wide_fh + k_gemm2_ws<true>, and no drain between them.
+  const int npass = a.dx ? 4 : 2;
+  const int N2 = a.K, NH2 = N2 / 2, KB2 = a.N / BK;       // dX: N = H1 output columns, K = H2
+  const int B2_KBLOCK = NH2 * 128;                        // (KB2 * 2 * B2_KBLOCK == B_BYTES: the same H1 H2 2 bytes)
 
   const int n_pairs = gridDim.x / 2, pair = blockIdx.x / 2;
   const int tiles = (a.m_pad + 2 * BM - 1) / (2 * BM);
@@ -78,6 +88,8 @@ k_wide_fh(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     tc::tma_prefetch_desc(&tmA);
     tc::tma_prefetch_desc(&tmB);
     tc::tma_prefetch_desc(&tmD);
+    if (a.dx) { tc::tma_prefetch_desc(&tmA2); tc::tma_prefetch_desc(&tmB2); tc::tma_prefetch_desc(&tmC); }
+    for (int b = 0; b < 2; b++) tc::mbar_init(&d2done[b], HEAD_WARPS);
     for (int s = 0; s < stages; s++) { tc::mbar_init(&full[s], 1); tc::mbar_init(&empty[s], 1); }
     for (int b = 0; b < 2; b++) { tc::mbar_init(&tfull[b], 1); tc::mbar_init(&tempty[b], 2 * HEAD_WARPS * 32); }
     for (int kb = 0; kb < 4; kb++) { tc::mbar_init(&bfull[kb], 1); tc::mbar_init(&wfree[kb], 1); }
@@ -95,23 +107,50 @@ k_wide_fh(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
   if (warp == 0) {
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
-      for (int pass = 0; pass < 2; pass++) {
-        const int g = 1 - pass;                           // critic first
+      uint32_t wfree_seen[4] = {0, 0, 0, 0};              // completions of wfree[kb] consumed so far (parity = count & 1)
+      for (int pass = 0; pass < npass; pass++) {
+        const bool isdx = pass >= 2;
+        const int g = (pass & 1) ? 0 : 1;                 // critic first
+        const int KBp = isdx ? KB2 : KB;
+        const int KBprev = pass == 0 ? 0 : (pass <= 2 ? KB : KB2);   // K blocks of the pass whose weights are being replaced
+        bool d2_ready = !isdx;                            // (the weights do not depend on D2: they are fetched first)
+        if (pass >= 2)                                    // different block layout: every block of the old weights must be free
+          for (int kb = 0; kb < KBprev; kb++) { tc::mbar_wait(&wfree[kb], wfree_seen[kb] & 1u); wfree_seen[kb]++; }
         bool first_tile = true;
         for (int t = pair; t < tiles; t += n_pairs, first_tile = false) {
           const int row0 = t * 2 * BM + (int)rank * BM;
-          for (int kb = 0; kb < KB; kb++) {
-            if (first_tile) {                             // this net's resident weight half, one barrier per K block
-              if (pass == 1) tc::mbar_wait(&wfree[kb], 0);
-              if (rank == 0) tc::mbar_arrive_expect_tx(&bfull[kb], (uint32_t)(4 * B_KBLOCK));   // 2 planes x 2 CTAs
-              for (int pl = 0; pl < 2; pl++)
+          // this pass's resident weight half, one barrier per K block.  Forward passes: block kb in front of the first tile's
+          // A stage kb (the first MMA waits for a quarter of the weights).  dX passes: all blocks at once, BEFORE the wait for
+          // the D2 tiles -- the weights do not depend on them.
+          auto load_weights = [&](int kb) {
+            if (rank == 0) tc::mbar_arrive_expect_tx(&bfull[kb], (uint32_t)(4 * (isdx ? B2_KBLOCK : B_KBLOCK)));   // 2 planes x 2 CTAs
+            for (int pl = 0; pl < 2; pl++) {
+              if (isdx) {
+                uint8_t* dst = sB + (size_t)(kb * 2 + pl) * B2_KBLOCK;
+                for (int fb = 0; fb < NH2 / 64; fb++)
+                  tc::tma_load_3d_2sm(dst + fb * (BK * 128), &tmB2, &bfull[kb], (int)rank * NH2 + fb * 64, kb * BK, g * 2 + pl);
+              } else {
                 tc::tma_load_3d_2sm(sB + (size_t)(kb * 2 + pl) * B_KBLOCK, &tmB, &bfull[kb], kb * BK, (int)rank * NH, g * 2 + pl);
+              }
+            }
+          };
+          if (first_tile && isdx)
+            for (int kb = 0; kb < KBp; kb++) load_weights(kb);
+          for (int kb = 0; kb < KBp; kb++) {
+            if (first_tile && !isdx) {
+              if (pass == 1) { tc::mbar_wait(&wfree[kb], wfree_seen[kb] & 1u); wfree_seen[kb]++; }   // same layout: block by block
+              load_weights(kb);
+            }
+            if (!d2_ready) {                              // the D2 tiles of net g are complete in global memory
+              tc::mbar_wait(&d2done[g], 0);
+              tc::fence_proxy_async();
+              d2_ready = true;
             }
             tc::mbar_wait(&empty[stage], phase ^ 1);
             if (rank == 0) tc::mbar_arrive_expect_tx(&full[stage], (uint32_t)(2 * A_STAGE));
             uint8_t* s = sA + (size_t)stage * A_STAGE;
-            tc::tma_load_3d_2sm(s, &tmA, &full[stage], kb * BK, row0, g * 2 + 0);
-            tc::tma_load_3d_2sm(s + A_PLANE, &tmA, &full[stage], kb * BK, row0, g * 2 + 1);
+            tc::tma_load_3d_2sm(s, isdx ? &tmA2 : &tmA, &full[stage], kb * BK, row0, g * 2 + 0);
+            tc::tma_load_3d_2sm(s + A_PLANE, isdx ? &tmA2 : &tmA, &full[stage], kb * BK, row0, g * 2 + 1);
             if (++stage == stages) { stage = 0; phase ^= 1; }
           }
         }
@@ -119,37 +158,48 @@ k_wide_fh(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     }
   } else if (warp == 1) {
     if (lane == 0 && rank == 0) {
-      const uint32_t idesc = tc::idesc_bf16_f32(2 * BM, N);
       int stage = 0; uint32_t phase = 0;
       int it = 0;
-      for (int pass = 0; pass < 2; pass++) {
+      uint32_t bfull_seen[4] = {0, 0, 0, 0};
+      for (int pass = 0; pass < npass; pass++) {
+        const bool isdx = pass >= 2;
+        const int KBp = isdx ? KB2 : KB;
+        const uint32_t idesc = isdx ? (tc::idesc_bf16_f32(2 * BM, N2) | (1u << 16)) : tc::idesc_bf16_f32(2 * BM, N);
         bool first_tile = true;
         for (int t = pair; t < tiles; t += n_pairs, it++, first_tile = false) {
-          const bool last_critic = pass == 0 && t + n_pairs >= tiles;
+          const bool last_of_pass = pass + 1 < npass && t + n_pairs >= tiles;   // the next pass replaces the weights
           const int buf = it & 1;
           const uint32_t bphase = (uint32_t)(it >> 1) & 1u;
           tc::mbar_wait(&tempty[buf], bphase ^ 1);         // both CTAs' head warps are done with this accumulator
           tc::tc_fence_after();
           const uint32_t d_tmem = tmem_base + (uint32_t)buf * 256u;
           uint32_t acc = 0;
-          for (int kb = 0; kb < KB; kb++) {
-            if (first_tile) tc::mbar_wait(&bfull[kb], (uint32_t)pass);
+          for (int kb = 0; kb < KBp; kb++) {
+            if (first_tile) { tc::mbar_wait(&bfull[kb], bfull_seen[kb] & 1u); bfull_seen[kb]++; }
             tc::mbar_wait(&full[stage], phase);
             tc::tc_fence_after();
             const uint32_t sa = tc::smem_u32(sA + (size_t)stage * A_STAGE);
-            const uint32_t sb = tc::smem_u32(sB + (size_t)(kb * 2) * B_KBLOCK);
             const uint64_t dAh = tc::smem_desc_sw128(sa), dAm = tc::smem_desc_sw128(sa + A_PLANE);
-            const uint64_t dBh = tc::smem_desc_sw128(sb), dBm = tc::smem_desc_sw128(sb + B_KBLOCK);
+            uint64_t dBh, dBm, bstep;
+            if (isdx) {                                   // W2 as stored, [K = j][N = k]: MN-major operand, 64-column boxes BK * 128 B apart
+              const uint32_t sb = tc::smem_u32(sB + (size_t)(kb * 2) * B2_KBLOCK);
+              dBh = tc::smem_desc_mn_sw128(sb, BK * 128); dBm = tc::smem_desc_mn_sw128(sb + B2_KBLOCK, BK * 128);
+              bstep = 2048 >> 4;
+            } else {
+              const uint32_t sb = tc::smem_u32(sB + (size_t)(kb * 2) * B_KBLOCK);
+              dBh = tc::smem_desc_sw128(sb); dBm = tc::smem_desc_sw128(sb + B_KBLOCK);
+              bstep = 32 >> 4;
+            }
 #pragma unroll
             for (int k = 0; k < BK / 16; k++) {
-              const uint64_t off = (uint64_t)((k * 32) >> 4);
-              tc::umma_bf16_2sm(d_tmem, dAm + off, dBh + off, idesc, acc);   // small terms first
-              tc::umma_bf16_2sm(d_tmem, dAh + off, dBm + off, idesc, 1u);
-              tc::umma_bf16_2sm(d_tmem, dAh + off, dBh + off, idesc, 1u);
+              const uint64_t off = (uint64_t)((k * 32) >> 4), offb = (uint64_t)k * bstep;
+              tc::umma_bf16_2sm(d_tmem, dAm + off, dBh + offb, idesc, acc);   // small terms first
+              tc::umma_bf16_2sm(d_tmem, dAh + off, dBm + offb, idesc, 1u);
+              tc::umma_bf16_2sm(d_tmem, dAh + off, dBh + offb, idesc, 1u);
               acc = 1u;
             }
             tc::umma_commit_2sm(&empty[stage], 3);
-            if (last_critic) tc::umma_commit_2sm(&wfree[kb], 3);   // both CTAs may overwrite this weight block
+            if (last_of_pass) tc::umma_commit_2sm(&wfree[kb], 3);   // both CTAs may overwrite this weight block
             if (++stage == stages) { stage = 0; phase ^= 1; }
           }
           tc::umma_commit_2sm(&tfull[buf], 3);
@@ -340,7 +390,11 @@ k_wide_fh(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         if (a.dbg && threadIdx.x == 64) a.dbg[blockIdx.x * 16 + it * 4 + 3] = clock64();
       }
       // ---- end of this net's pass: fold the four row quarters in order, write this CTA's partial row
-      if (lane == 0) tc::bulk_wait_read<0>();             // staging is about to be reused as plain memory ...
+      if (a.dx) {                                         // the dX pass of this net reads the D2 tiles back: they must have LANDED
+        if (lane == 0) { tc::bulk_wait_all(); tc::fence_proxy_async(); tc::mbar_arrive(&d2done[g]); }
+      } else if (lane == 0) {
+        tc::bulk_wait_read<0>();                          // staging is about to be reused as plain memory ...
+      }
       __syncwarp();
       bar_sync(5, HEAD_WARPS * 32);                       // ... by every head warp, across each other's buffers
 #pragma unroll
@@ -382,7 +436,46 @@ k_wide_fh(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
       }
       bar_sync(5, HEAD_WARPS * 32);                       // fold is staging again
     }
-    if (lane == 0) tc::bulk_wait_all();                   // every D2 tile has landed before the CTA retires
+    // ---- passes 2, 3 (a.dx): raw epilogue of the dX GEMM, Z1 tiles -> d1 (fp32), 16 columns at a time through the same staging
+    // buffers: TMEM -> registers -> 64-B-swizzled 32 x 16 tile -> TMA store
+    if (a.dx) {
+      const int c2_begin = cq * (N2 / 4), c2_end = c2_begin + N2 / 4;
+      for (int pass = 2; pass < 4; pass++) {
+        const int g = (pass & 1) ? 0 : 1;
+        for (int t = pair; t < tiles; t += n_pairs, it++) {
+          const int buf = it & 1;
+          const uint32_t bphase = (uint32_t)(it >> 1) & 1u;
+          tc::mbar_wait(&tfull[buf], bphase);
+          tc::tc_fence_after();
+          const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * 256u;
+          const int row0 = t * 2 * BM + (int)rank * BM + q * 32;
+#pragma unroll
+          for (int ci = 0; ci < 4; ci++) {
+            const int c = c2_begin + ci * 16;
+            if (c < c2_end) {
+              float v[16];
+              tc::tmem_ld16(t0 + (uint32_t)c, v);
+              tc::tmem_ld_wait();
+              if (lane == 0) tc::bulk_wait_read<0>();
+              __syncwarp();
+#pragma unroll
+              for (int i = 0; i < 4; i++)
+                *reinterpret_cast<float4*>(sb + lane * 64 + ((i ^ ((lane >> 1) & 3)) << 4)) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+              tc::fence_proxy_async();
+              __syncwarp();
+              if (lane == 0) {
+                tc::tma_store_3d(&tmC, sb, c, row0, g);
+                tc::bulk_commit();
+              }
+            }
+          }
+          tc::tc_fence_before();
+          tc::mbar_arrive_leader_cta(&tempty[buf]);
+        }
+      }
+    }
+    if (lane == 0) tc::bulk_wait_read<0>();               // every store has READ its staging tile; the writes complete with the grid
+                                                          // (the next kernel's griddepcontrol.wait waits for this grid's memory flush)
   }
 
   if (a.dbg && threadIdx.x == 64) a.dbg[blockIdx.x * 16 + 13] = clock64();   // head done
@@ -407,8 +500,8 @@ bool fh_supported(int N, int K) {
   return fh_stages(N, K) >= 2;
 }
 
-cudaError_t launch_wide_fh(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmD, const FhArgs& a, int sm_count,
-                           int* grid_out, cudaStream_t st) {
+cudaError_t launch_wide_fh(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmD, const CUtensorMap& tmA2,
+                           const CUtensorMap& tmB2, const CUtensorMap& tmC, const FhArgs& a, int sm_count, int* grid_out, cudaStream_t st) {
   static b2::PerDeviceOnce once;   // function attributes are per device
   if (once.need()) {
     cudaError_t e;
@@ -422,7 +515,7 @@ cudaError_t launch_wide_fh(const CUtensorMap& tmA, const CUtensorMap& tmB, const
   const int smem = (a.K / BK) * 2 * (a.N / 2) * 128 + a.stages * A_STAGE + STG_BYTES + YBUF_BYTES + BAR_BYTES + 1024;
   const int smem_req = smem > 120 * 1024 ? smem : 120 * 1024;   // one CTA per SM (512 TMEM columns)
   *grid_out = 2 * pairs;
-  return launch_pdl(k_wide_fh, dim3(2 * pairs), dim3(FH_THREADS), (size_t)smem_req, st, tmA, tmB, tmD, a);
+  return launch_pdl(k_wide_fh, dim3(2 * pairs), dim3(FH_THREADS), (size_t)smem_req, st, tmA, tmB, tmD, tmA2, tmB2, tmC, a);
 }
 
 }  // namespace b2

@@ -434,6 +434,26 @@ int make_output_map(CUtensorMap* out, const void* base, uint64_t N, uint64_t row
   return B2_OK;
 }
 
+int make_output_map16(CUtensorMap* out, const void* base, uint64_t N, uint64_t rows, uint64_t planes) {
+  if (!g_encode) {
+    CUtensorMap tmp;
+    static __nv_bfloat16* dummy = nullptr;
+    if (!dummy) cudaMalloc(&dummy, 64 * 64 * 2);
+    int rc = make_operand_map(&tmp, dummy, 64, 64, 1, 64, 64 * 64, 32);   // resolves the driver entry point
+    if (rc) return rc;
+  }
+  cuuint64_t dims[3] = {N, rows, planes};
+  cuuint64_t strides[2] = {N * 4, rows * N * 4};
+  cuuint32_t box[3] = {16, 32, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_error(B2_ERR_CUDA, "cuTensorMapEncodeTiled(output16) failed (%d): N=%llu rows=%llu planes=%llu", (int)r,
+                                          (unsigned long long)N, (unsigned long long)rows, (unsigned long long)planes);
+  return B2_OK;
+}
+
 int make_plane_store_map(CUtensorMap* out, const void* base, uint64_t N, uint64_t rows, uint64_t planes) {
   if (!g_encode) {
     CUtensorMap tmp;

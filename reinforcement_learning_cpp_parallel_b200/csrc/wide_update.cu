@@ -465,7 +465,9 @@ struct WideNet {
   bool fused_fh = false;           // k_wide_fh instead of the forward GEMM + k_wide_head (B2_WIDE_FUSED=0: the two kernels)
   int fh_grid = 0;                 // CTAs of the last k_wide_fh launch (= partial rows the reduce sums)
   long long* fh_dbg = nullptr;     // B2_FH_DBG=1: clock64 timeline of the head warps, printed once (diagnostic)
-  CUtensorMap tm_d2_st;            // d2p planes as a store target (32 x 32 boxes, 64-B swizzle)
+  CUtensorMap tm_d2_st;            // d2p planes as a store target (16 x 32 x 2-plane boxes, 32-B swizzle)
+  CUtensorMap tm_out_d1_16;        // d1 (fp32) as a store target with 16-column boxes (k_wide_fh's dX passes)
+  bool fused_dx = false;           // the dX GEMM inside k_wide_fh (B2_WIDE_FUSE_DX=0: its own launch, k_gemm2_ws<true>)
   AdamCoef* coef = nullptr;
   float *part_head = nullptr, *part_dw1 = nullptr, *part_dw2 = nullptr;
   int head_blocks = 0, head_row = 0, dw1_blocks = 0, splits_max = 0;
@@ -562,6 +564,8 @@ int wide_create(WideNet** out, int H1, int H2, int64_t max_chunk, int sm_count) 
   if (!rc && w->pair_fwd) rc = make_operand_map(&w->tm_w2_half, w->w2p, H1, H2, 4, H1, (uint64_t)H2 * H1, (uint32_t)(H2 / 2));
   { const char* e = getenv("B2_WIDE_FUSED"); w->fused_fh = w->pair_fwd && fh_supported(H2, H1) && !(e && e[0] == '0'); }
   if (!rc && w->fused_fh) rc = make_plane_store_map(&w->tm_d2_st, w->d2p, H2, ucap, 4);
+  { const char* e = getenv("B2_WIDE_FUSE_DX"); w->fused_dx = w->fused_fh && w->pair_bwd && !(e && e[0] == '0'); }
+  if (!rc && w->fused_dx) rc = make_output_map16(&w->tm_out_d1_16, w->d1, H1, ucap, 2);
   if (!rc) rc = make_output_map(&w->tm_out_h2, w->h2, H2, ucap, 2);
   if (!rc) rc = make_output_map(&w->tm_out_d1, w->d1, H1, ucap, 2);
   if (!rc) rc = make_output_map(&w->tm_out_dw2, w->part_dw2, H1, H2, (uint64_t)2 * w->splits_max);
@@ -631,8 +635,9 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
       f.first = wa.first; f.idx = a.idx; f.tr = a.tr; f.params = a.params; f.headw = w->bias2; f.vtmp = w->vtmp;
       f.inv_denom = wa.inv_denom; f.hp = a.hp; f.part_head = w->part_head; f.head_row = w->head_row;
       f.dbg = w->fh_dbg;
+      f.dx = (w->fused_dx && !(skip & 8)) ? 1 : 0;
       if (!(skip & 6))
-      if ((ce = launch_wide_fh(w->tm_h1, w->tm_w2_half, w->tm_d2_st, f, w->sm_count, &w->fh_grid, st)) != cudaSuccess)
+      if ((ce = launch_wide_fh(w->tm_h1, w->tm_w2_half, w->tm_d2_st, w->tm_d2, w->tm_w2t, w->tm_out_d1_16, f, w->sm_count, &w->fh_grid, st)) != cudaSuccess)
         return set_error(B2_ERR_CUDA, "wide fwd+head: %s", cudaGetErrorString(ce));
       (*launches)++;
       head_rows = w->fh_grid;
@@ -683,7 +688,8 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     g = GemmArgs{};
     g.G = 2; g.M = wa.count; g.N = H1; g.K = H2; g.m_tiles = m_tiles; g.splits = 1; g.kb_per_split = H2 / 64;
     g.stages = gemm_x3_stages(H1); g.b_mn = 1;   // B = W2 as stored ([j][k]), read as an MN-major operand
-    if (skip & 8) ce = cudaSuccess;
+    const bool dx_in_fh = w->fused_fh && w->fused_dx && !(skip & 6);     // passes 2, 3 of k_wide_fh
+    if ((skip & 8) || dx_in_fh) ce = cudaSuccess;
     else if (w->pair_bwd) {
       const Gemm2Args g2{2, wa.count, H1, H2, gemm2_stages(H1, H2)};
       ce = launch_gemm2(true, w->tm_d2, w->tm_w2t, w->tm_out_d1, g2, w->sm_count, st);
@@ -691,7 +697,7 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
       ce = launch_gemm_x3(w->tm_d2, w->tm_w2t, w->tm_out_d1, g, w->sm_count, st);
     }
     if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "wide gemm bwd: %s", cudaGetErrorString(ce));
-    (*launches)++;
+    if (!dx_in_fh) (*launches)++;
     // dW2 partials = D2^T H1 over sample splits
     const int kb_total = wa.m_pad / MN_BOX_ROWS;
     const int jt = (H2 + 127) / 128;

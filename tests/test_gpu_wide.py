@@ -163,8 +163,8 @@ def test_wide_update_chunked_and_minibatched():
 
 
 @pytest.mark.parametrize("env", [{"B2_WIDE_DETERMINISTIC": "1"}, {"B2_WIDE_FUSE_REDUCE": "1"}, {"B2_WIDE_FUSE_M": "1"},
-                                 {"B2_WIDE_FUSED": "0"}, {"B2_WIDE_FUSED": "0", "B2_WIDE_DETERMINISTIC": "1"}],
-                         ids=["deterministic", "fused_reduce_tail", "fuse_m", "unfused_forward_head", "unfused_deterministic"])
+                                 {"B2_WIDE_FUSED": "0"}, {"B2_WIDE_FUSED": "0", "B2_WIDE_DETERMINISTIC": "1"}, {"B2_WIDE_FUSE_DX": "0"}],
+                         ids=["deterministic", "fused_reduce_tail", "fuse_m", "unfused_forward_head", "unfused_deterministic", "dx_own_launch"])
 def test_wide_update_opt_in_modes_match_oracle(env, monkeypatch):
     """the opt-in variants of the step (read from the environment when the engine is created / the step is launched) are
     held to the same oracle gates as the default; the fixed-order mode must also be bit-identical run to run"""
