@@ -153,6 +153,12 @@ bool gemm2_supported(int N, int K, bool bmn);
 cudaError_t launch_gemm2(bool bmn, const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const Gemm2Args& a,
                          int sm_count, cudaStream_t st);
 
+// the sample contraction on CTA pairs (wide_gemm_mn2.cu): M = 256 output rows per pair, split-K items g * splits + split
+int gemm_mn2_stages(int N);
+bool gemm_mn2_supported(int M, int N);
+cudaError_t launch_gemm_mn2(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const GemmArgs& a, int sm_count,
+                            int* grid_out, cudaStream_t st);
+
 cudaError_t launch_gemm_x3(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const GemmArgs& a,
                            int sm_count, cudaStream_t st);
 // fp32 output tensor [planes][rows][N] the epilogue TMA-stores 32 x 32 tiles into (plane = group, or group*splits + split)

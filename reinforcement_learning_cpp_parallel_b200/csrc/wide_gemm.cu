@@ -28,6 +28,7 @@
 #include "wide.h"
 #include "mlp.cuh"
 #include "wide_reduce.cuh"
+#include "wide_dw1.cuh"
 
 namespace b2 {
 
@@ -49,96 +50,6 @@ __host__ __device__ constexpr int stage_bytes(int N) { return 2 * A_PLANE_BYTES 
 // swizzle atom column: 8 sample rows per 1024-B group (SBO), 64-feature blocks MNB_BYTES apart (LBO).
 constexpr int BKS = 32;                       // samples per K block in MN mode
 constexpr int MNB_BYTES = BKS * 128;          // one 64-feature x 32-sample block
-
-constexpr int DW1_THREADS = 512;              // extra warps 10..25 of the MN-major kernel (fused k_wide_dw1 work)
-constexpr int DW1_SMEM = (2 * 64 * 8 + 256 * 8) * 4;   // two 64-sample observation tiles + the fold buffer
-
-// The dW1 / db1 partials of this CTA's slice of samples (see Dw1Args).  512 threads = 2 sample halves x 256 features;
-// a thread carries its feature of BOTH nets, so the observation tile is staged once and the Z1 loads of the two nets are
-// in flight together.  Loads are coalesced across k and batched: 8 samples x 2 nets in flight (16 x 2 spills at this
-// kernel's 72-register cap and is 2 ms per update slower), then 4 / 2 / 1 for the remainder -- an L2 round trip is
-// ~2,000 cycles beside the GEMM's operand stream, and these warps are nothing but
-// a chain of them (clock64 stamps: with a one-sample-at-a-time tail and the nets one after the other they ran 49k cycles
-// against the GEMM's 40k, 5 us per step on the critical path).  H1 is recomputed from x exactly as k_wide_l1 computes
-// it; per net and feature the adds keep the sample order; the two halves are folded through shared memory in a fixed order.
-__device__ __forceinline__ void dw1_worker(const Dw1Args& w, float* sm, int t) {
-  const int spb = (w.count + (int)gridDim.x - 1) / (int)gridDim.x;
-  const int sb = min((int)blockIdx.x * spb, w.count), se = min(sb + spb, w.count);
-  const int half = t >> 8, k = t & 255;
-  const int hlen = (se - sb + 1) / 2;
-  const int hb = sb + half * hlen, he = min(hb + hlen, se);
-  float* xs = sm + half * 64 * 8;
-  float* fold = sm + 2 * 64 * 8;
-  const bool live = k < w.H1;
-  float acc[2][OBS + 1], w1[2][OBS], b1[2];
-#pragma unroll
-  for (int g = 0; g < 2; g++) {
-#pragma unroll
-    for (int c = 0; c <= OBS; c++) acc[g][c] = 0.f;
-#pragma unroll
-    for (int c = 0; c < OBS; c++) w1[g][c] = live ? w.params[g * w.SIZE + w.oW1 + k * OBS + c] : 0.f;
-    b1[g] = live ? w.params[g * w.SIZE + w.ob1 + k] : 0.f;
-  }
-  for (int off = 0; off < hlen; off += 64) {           // uniform trip count for both halves
-    const int t0 = hb + off;
-    const int nt = max(min(64, he - t0), 0);
-    asm volatile("bar.sync 1, %0;" ::"n"(DW1_THREADS) : "memory");
-    for (int i = k; i < nt * OBS; i += 256) {
-      const int s = i / OBS, c = i % OBS;
-      const int64_t p = w.first + t0 + s;
-      xs[s * 8 + c] = w.obs[c * w.obs_cap + (w.idx ? (int64_t)w.idx[p] : p)];
-    }
-    asm volatile("bar.sync 1, %0;" ::"n"(DW1_THREADS) : "memory");
-    if (live && nt > 0) {
-      const float* dp0 = w.z1 + (int64_t)t0 * w.H1 + k;
-      const float* dp1 = dp0 + w.cap * w.H1;
-      auto batch = [&](auto bc, int s) {
-        constexpr int B = decltype(bc)::value;
-        float dv[2][B];
-#pragma unroll
-        for (int u = 0; u < B; u++) {
-          dv[0][u] = dp0[(int64_t)(s + u) * w.H1];
-          dv[1][u] = dp1[(int64_t)(s + u) * w.H1];
-        }
-#pragma unroll
-        for (int u = 0; u < B; u++) {
-          const float* x = xs + (s + u) * 8;
-#pragma unroll
-          for (int g = 0; g < 2; g++) {
-            float z = b1[g];
-#pragma unroll
-            for (int c = 0; c < OBS; c++) z = fmaf(w1[g][c], x[c], z);
-            const float h = act_tanh(z);
-            const float d = dv[g][u] * (1.0f - h * h);
-#pragma unroll
-            for (int c = 0; c < OBS; c++) acc[g][c] = fmaf(d, x[c], acc[g][c]);
-            acc[g][OBS] += d;
-          }
-        }
-      };
-      int s = 0;
-      for (; s + 8 <= nt; s += 8) batch(std::integral_constant<int, 8>{}, s);
-      if (s + 4 <= nt) { batch(std::integral_constant<int, 4>{}, s); s += 4; }
-      if (s + 2 <= nt) { batch(std::integral_constant<int, 2>{}, s); s += 2; }
-      if (s < nt) batch(std::integral_constant<int, 1>{}, s);
-    }
-  }
-#pragma unroll
-  for (int g = 0; g < 2; g++) {
-    asm volatile("bar.sync 1, %0;" ::"n"(DW1_THREADS) : "memory");
-    if (half == 1) {
-#pragma unroll
-      for (int c = 0; c <= OBS; c++) fold[k * 8 + c] = acc[g][c];
-    }
-    asm volatile("bar.sync 1, %0;" ::"n"(DW1_THREADS) : "memory");
-    if (half == 0 && live) {
-      float* out = w.part + ((int64_t)blockIdx.x * 2 + g) * w.H1 * 8 + k * 8;
-#pragma unroll
-      for (int c = 0; c <= OBS; c++) out[c] = acc[g][c] + fold[k * 8 + c];
-      out[OBS + 1] = 0.f;
-    }
-  }
-}
 
 template <bool MN>
 __global__ void __launch_bounds__(MN ? GEMM_THREADS + DW1_THREADS : GEMM_THREADS, 1)

@@ -466,6 +466,7 @@ struct WideNet {
   int fh_grid = 0;                 // CTAs of the last k_wide_fh launch (= partial rows the reduce sums)
   long long* fh_dbg = nullptr;     // B2_FH_DBG=1: clock64 timeline of the head warps, printed once (diagnostic)
   CUtensorMap tm_d2_st;            // d2p planes as a store target (16 x 32 x 2-plane boxes, 32-B swizzle)
+  CUtensorMap tm_out_dw2_16;       // the dW2 planes with 16-column boxes (k_gemm_mn2's epilogue)
   CUtensorMap tm_out_d1_16;        // d1 (fp32) as a store target with 16-column boxes (k_wide_fh's dX passes)
   bool fused_dx = false;           // the dX GEMM inside k_wide_fh (B2_WIDE_FUSE_DX=0: its own launch, k_gemm2_ws<true>)
   AdamCoef* coef = nullptr;
@@ -569,6 +570,7 @@ int wide_create(WideNet** out, int H1, int H2, int64_t max_chunk, int sm_count) 
   if (!rc) rc = make_output_map(&w->tm_out_h2, w->h2, H2, ucap, 2);
   if (!rc) rc = make_output_map(&w->tm_out_d1, w->d1, H1, ucap, 2);
   if (!rc) rc = make_output_map(&w->tm_out_dw2, w->part_dw2, H1, H2, (uint64_t)2 * w->splits_max);
+  if (!rc) rc = make_output_map16(&w->tm_out_dw2_16, w->part_dw2, H1, H2, (uint64_t)2 * w->splits_max);
   if (rc) { wide_destroy(w); return rc; }
   *out = w;
   return B2_OK;
@@ -718,7 +720,12 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     g.dw1.obs = a.tr.obs; g.dw1.obs_cap = a.tr.cap; g.dw1.idx = a.idx; g.dw1.first = wa.first;
     g.dw1.count = wa.count; g.dw1.H1 = H1; g.dw1.SIZE = d.SIZE; g.dw1.oW1 = d.oW1; g.dw1.ob1 = d.ob1;
     g.dw1.z1 = w->d1; g.dw1.cap = w->cap; g.dw1.part = w->part_dw1;
-    const int dw2_grid = std::min(2 * (fuse_m ? 1 : jt) * splits, w->sm_count);
+    int dw2_grid = std::min(2 * (fuse_m ? 1 : jt) * splits, w->sm_count);
+    // H2 = 256: CTA pairs (tcgen05 cta_group::2) own all 256 rows of dW2, every operand byte is fetched once, and the dW1
+    // warps take Z1 through a cp.async ring (wide_gemm_mn2.cu, wide_dw1.cuh); B2_WIDE_DW2_PAIR=0: k_gemm_x3<MN>
+    static const bool pair_env = [] { const char* e = getenv("B2_WIDE_DW2_PAIR"); return !(e && e[0] == '0'); }();
+    const bool dw2_pair = pair_env && !fuse_m && !w->fuse_reduce && gemm_mn2_supported(H2, H1);
+    if (dw2_pair) { g.stages = gemm_mn2_stages(H1); dw2_grid = 2 * std::min(w->sm_count / 2, 2 * splits); }
     // reduce (+ Adam on the last chunk): in the tail of the dW2 kernel behind a grid barrier, or as a launch of its own
     ReduceArgs r{};
     r.d = d; r.u = a; r.part_head = w->part_head; r.part_dw1 = w->part_dw1; r.part_dw2 = w->part_dw2;
@@ -739,7 +746,8 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
       g.bar_target = w->bar_count;
     }
     if (!(skip & 16))
-    if ((ce = launch_gemm_x3(w->tm_d2_mn, w->tm_h1_mn, w->tm_out_dw2, g, w->sm_count, st)) != cudaSuccess)
+    if ((ce = dw2_pair ? launch_gemm_mn2(w->tm_d2_mn, w->tm_h1_mn, w->tm_out_dw2_16, g, w->sm_count, &dw2_grid, st)
+                       : launch_gemm_x3(w->tm_d2_mn, w->tm_h1_mn, w->tm_out_dw2, g, w->sm_count, st)) != cudaSuccess)
       return set_error(B2_ERR_CUDA, "wide gemm dW2: %s", cudaGetErrorString(ce));
     (*launches)++;
     if (fused_tail) continue;
