@@ -352,7 +352,8 @@ int run_update(b2_engine* E, b2_update_stats* stats) {
       // (engine.h PeerXchg); reduce -> ncclAllReduce -> Adam only if the peer mapping was refused or switched off
       if (E->world > 1 && E->p2p) next_peer_step(E, a);
       if (E->wide) {
-        int rc = wide_step(E->wide, a, E->world == 1 || E->p2p, E->stream, &E->launches);
+        // (single GPU: the reduce + Adam of a step rides in the layer-1 kernel of the next one; the last step flushes itself)
+        int rc = wide_step(E->wide, a, E->world == 1 || E->p2p, slot + 1 < steps, E->stream, &E->launches);
         if (rc) return rc;
         if (E->world > 1 && !E->p2p) {
           int ne = g_nccl.AllReduce(E->grads, E->grads, (size_t)E->pstride, NCCL_FLOAT32, NCCL_SUM, E->comm, E->stream);

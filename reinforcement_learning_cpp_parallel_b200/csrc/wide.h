@@ -68,6 +68,8 @@ struct Dw1Args {
   const float* z1;          // [2][cap][H1]
   int64_t cap;
   float* part;              // [grid][2][H1 * 8]
+  float* sum;               // k_gemm_mn2 only, non-null: ONE row [2][H1 * 8] every CTA adds its partial into (bulk reduce-add)
+                            // instead of writing part[cta] -- the merged layer-1 + Adam kernel reads it (wide_update.cu k_wide_l1r)
 };
 
 // Adam coefficients of the current optimizer step (computed once per step by k_wide_l1)
@@ -125,6 +127,7 @@ struct FhArgs {
   float inv_denom;
   HyperDev hp;
   float* part_head;            // [grid][2][head_row]
+  float* head_sum;             // non-null: ONE row [2][head_row] every CTA adds its partial into (red.add) instead of part_head[cta]
   int head_row;
   long long* dbg;              // optional clock64 timeline of the head warps, [grid][16] (B2_FH_DBG=1, diagnostic runs)
   int dx;                      // 1: the dX GEMM Z1 = D2 W2 of both nets runs in this kernel too (passes 2, 3)
@@ -178,7 +181,11 @@ void wide_destroy(WideNet* w);
 int64_t wide_chunk_cap(const WideNet* w);
 // gradient of one minibatch [first, first+count) (mapped through idx if set) into a.grads (P grads + 3 loss sums in
 // the tail, same convention as k_reduce); apply_adam fuses the Adam step (single GPU).  *launches += kernels launched.
-int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st, int64_t* launches);
+// more_follow: another step of the same update comes next -- the reduce + Adam of this step may then ride in the layer-1
+// kernel of the next one (k_wide_l1r); wide_flush() applies whatever is still pending (call it before the parameters,
+// gradients or the loss log are read; a no-op when nothing is pending).
+int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, bool more_follow, cudaStream_t st, int64_t* launches);
+int wide_flush(WideNet* w, cudaStream_t st, int64_t* launches);
 cudaError_t launch_wide_adam(WideNet* w, const UpdateArgs& a, cudaStream_t st);
 int wide_bootstrap(WideNet* w, const float* params, const Traj& tr, cudaStream_t st, int64_t* launches);
 int wide_pstride(int H1, int H2);

@@ -203,6 +203,9 @@ __device__ __forceinline__ void dw1_worker_async(const Dw1Args& w, float* sm, in
       if (producer && gidx + DW1_NGR < total_groups) issue(gidx + DW1_NGR);
     }
   }
+  // this CTA's row [2][H1][8]: to part[cta], or (w.sum) assembled in the drained ring and ADDED into the one row of the step
+  // with a single bulk reduce (fp32 adds in the L2: 16 KB per CTA instead of a partial row the reduce kernel sums later)
+  float* rowbuf = sm + DW1_SMEM / 4;
 #pragma unroll
   for (int g = 0; g < 2; g++) {
     asm volatile("bar.sync 1, %0;" ::"n"(DW1_THREADS) : "memory");
@@ -212,10 +215,19 @@ __device__ __forceinline__ void dw1_worker_async(const Dw1Args& w, float* sm, in
     }
     asm volatile("bar.sync 1, %0;" ::"n"(DW1_THREADS) : "memory");
     if (half == 0 && live) {
-      float* out = w.part + ((int64_t)blockIdx.x * 2 + g) * H1 * 8 + k * 8;
+      float* out = w.sum ? rowbuf + (g * H1 + k) * 8 : w.part + ((int64_t)blockIdx.x * 2 + g) * H1 * 8 + k * 8;
 #pragma unroll
       for (int c = 0; c <= OBS; c++) out[c] = acc[g][c] + fold[k * 8 + c];
       out[OBS + 1] = 0.f;
+    }
+  }
+  if (w.sum) {
+    tc::fence_proxy_async();
+    asm volatile("bar.sync 1, %0;" ::"n"(DW1_THREADS) : "memory");
+    if (t == 0) {
+      tc::bulk_reduce_add_f32(w.sum, rowbuf, (uint32_t)(2 * H1 * 8 * 4));
+      tc::bulk_commit();
+      tc::bulk_wait_read<0>();                         // the CTA's shared memory outlives the read (k_gemm_mn2 ends in a cluster barrier)
     }
   }
 }

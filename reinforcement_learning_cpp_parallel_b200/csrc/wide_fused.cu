@@ -411,7 +411,11 @@ k_wide_fh(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
       }
       if (cq == 0 && lane == 0) { float* sc = fold + HEAD_WARPS * 128 + ((warp - 2) & 3) * 4; sc[0] = gb3; sc[1] = lsum; sc[2] = csum; }
       bar_sync(5, HEAD_WARPS * 32);
-      float* out = a.part_head + ((size_t)blockIdx.x * 2 + g) * a.head_row;
+      // the CTA's partial row, or (a.head_sum) its share of the ONE row the merged layer-1 + Adam kernel consumes: red.add in
+      // the L2, issued with most of the kernel still ahead (the critic's in the middle, the actor's before the dX passes)
+      float* out = a.head_sum ? a.head_sum + (size_t)g * a.head_row : a.part_head + ((size_t)blockIdx.x * 2 + g) * a.head_row;
+      const bool addrow = a.head_sum != nullptr;
+      auto put = [&](int i, float v) { if (addrow) atomicAdd(out + i, v); else out[i] = v; };
       if (((warp - 2) & 3) == 0) {                        // one warp per column quarter: lanes = (quantity, column)
 #pragma unroll
         for (int ci = 0; ci < 4; ci++) {
@@ -420,18 +424,19 @@ k_wide_fh(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
             float sv = 0.f;
 #pragma unroll
             for (int qq = 0; qq < 4; qq++) sv += fold[(cq * 4 + qq) * 128 + rh * 64 + ci * 16 + cj];
-            if (rh == 0) out[N + c + cj] = __ldg(w3p + c + cj) * sv;   // [H2, 2 H2) db2 = w3_j sum_s dz_s (1 - h_sj^2)
-            else out[c + cj] = sv;                                     // [0, H2) dW3
+            if (rh == 0) put(N + c + cj, __ldg(w3p + c + cj) * sv);   // [H2, 2 H2) db2 = w3_j sum_s dz_s (1 - h_sj^2)
+            else put(c + cj, sv);                                     // [0, H2) dW3
           }
         }
         if (cq == 0 && lane == 0) {
           float t3 = 0.f, tl = 0.f, tcn = 0.f;
 #pragma unroll
           for (int qq = 0; qq < 4; qq++) { const float* sc = fold + HEAD_WARPS * 128 + qq * 4; t3 += sc[0]; tl += sc[1]; tcn += sc[2]; }
-          out[2 * N] = t3;
-          out[2 * N + 1] = tl;                             // g == 0: loss1 sum, g == 1: sum e^2
-          out[2 * N + 2] = g == 0 ? tcn : 0.f;
-          out[2 * N + 3] = 0.f;
+          put(2 * N, t3);
+          put(2 * N + 1, tl);                              // g == 0: loss1 sum, g == 1: sum e^2
+          if (g == 0) put(2 * N + 2, tcn);
+          else if (!addrow) out[2 * N + 2] = 0.f;
+          if (!addrow) out[2 * N + 3] = 0.f;
         }
       }
       bar_sync(5, HEAD_WARPS * 32);                       // fold is staging again

@@ -142,6 +142,192 @@ __global__ void __launch_bounds__(256, L1_CTAS) k_wide_l1(const WideArgs a) {
   }
 }
 
+// ---- layer 1 of step s AND the reduce + Adam of step s-1 in one kernel (the default single-GPU sequence) ----------------
+// Between the dW2 GEMM of one step and the forward GEMM of the next the tensor pipe used to wait for two launches in a row:
+// k_wide_reduce (a chain of L2 round trips, 5.6 us) and k_wide_l1 (7.6 us) -- and only W1 / b1 of the reduce's output is
+// what layer 1 needs.  Here the producers of a step leave SUMS instead of partial rows (k_gemm_mn2's dW1 warps and
+// k_wide_fh's head add theirs into one row each in the L2, as the dW2 GEMM's split-K tiles always did), and this kernel
+//   * applies Adam to W1 / b1 itself: a CTA owns 32 features of one net for a slice of the rows (grid = row slices x
+//     feature slices x nets), so it needs 224 parameters -- one per thread, straight into the shared-memory weight table
+//     the layer-1 loop reads.  Every row slice repeats that arithmetic (37 x at 2x256 on 148 SMs: 9 M of the kernel's
+//     ~170 M instructions) instead of waiting for another CTA's result; row slice 0 writes it back.  The state is double
+//     buffered (w1_rd -> w1_wr): CTAs of one launch must all read the OLD moments while slice 0 stores the new ones;
+//   * spreads the rest of the reduce (W2, b2, W3, b3, the loss sums: one element per thread, grid-stride) over all CTAs
+//     in front of the layer-1 loop: sum -> Adam -> parameter, bf16 planes, headw, exactly wide_reduce_finish;
+//   * then runs layer 1 as k_wide_l1 does (same arithmetic per element; a warp stores 4 rows x 64 contiguous bytes).
+// pending == 0 (first step of an update): layer 1 only, W1 from the canonical vector (seed), which also primes w1_wr.
+// rows == 0 (wide_flush after the last step): the reduce + Adam only.
+struct L1rArgs {
+  WideArgs a;
+  ReduceArgs r;            // of the PENDING step (grads, Adam state, loss log slot, coefficients, planes)
+  int pending, seed;
+  const float* dw1_sum;    // [2][H1 * 8] dW1aug sums of the pending step
+  float* dw1_zero;         // the other buffer: zeroed here, the next dW2 kernel adds into it
+  float* head_sum;         // [2][head_row] sums of the pending step's head; consumed and zeroed element by element
+  const float* w1_rd;      // [2 nets][3: w, m, v][H1][S + 1] (column S = the bias)
+  float* w1_wr;
+  float *cparams, *cm, *cv, *cgrads;   // the canonical vectors (row slice 0 keeps W1 / b1 current there too)
+};
+constexpr int L1R_FS = 32;        // features per CTA
+constexpr int L1R_THREADS = 288;  // 8 layer-1 warps + the reduce warp
+constexpr int L1R_RB = 4;         // elements a lane of the reduce warp keeps in flight
+constexpr int L1R_TILE = 448;     // observation rows per shared-memory tile: a CTA's whole row slice at 16,384-sample minibatches
+                                  // (443 rows on 148 SMs), fetched BEFORE the dependency wait -- with k_wide_l1's 64-row tiles
+                                  // the slice took seven exposed gathers
+
+// element e of the pending step's reduce (everything but W1 / b1) -> where its sum waits, its parameter, its gradient slot
+__device__ __forceinline__ void l1r_locate(const L1rArgs& q, int e, float*& src, int& p, int& slot) {
+  const NetDims& d = q.a.d;
+  const int w2n = d.H2 * d.H1, hn = 2 * d.H2 + 1;
+  if (e < 2 * w2n) {                                  // W2: the L2 has added the split-K tiles of the dW2 GEMM
+    src = q.r.part_dw2 + e;
+    p = slot = (e / w2n) * d.SIZE + d.oW2 + (e % w2n);
+  } else if (e < 2 * w2n + 2 * hn) {                  // head row of net g2: [0,H2) dW3, [H2,2H2) db2, 2H2 db3
+    const int h = e - 2 * w2n, g2 = h / hn, col = h % hn;
+    src = q.head_sum + g2 * q.r.head_row + col;
+    p = slot = g2 * d.SIZE + (col < d.H2 ? d.oW3 + col : (col < 2 * d.H2 ? d.ob2 + (col - d.H2) : d.ob3));
+  } else {                                            // 0 loss1 sum (actor), 1 sum e^2 (critic), 2 clipped count (actor)
+    const int l = e - 2 * w2n - 2 * hn;
+    src = q.head_sum + (l == 1 ? 1 : 0) * q.r.head_row + 2 * d.H2 + (l == 2 ? 2 : 1);
+    p = d.P + l; slot = q.r.pstride - 4 + l;
+  }
+}
+
+__global__ void __launch_bounds__(L1R_THREADS, L1_CTAS) k_wide_l1r(const L1rArgs q) {
+  __shared__ float xs[L1R_TILE][S + 2];
+  __shared__ __align__(16) float ws[(L1R_FS / 4) * 28];   // per feature group of 4: 24 weights + 4 biases, pre-scaled by TANH_K
+  const WideArgs& a = q.a;
+  const NetDims& d = a.d;
+  const int H1 = d.H1, g = blockIdx.z, k0 = blockIdx.y * L1R_FS, tid = threadIdx.x;
+  const int n_cta = (int)(gridDim.x * gridDim.y * gridDim.z);
+  const int cta = (int)((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x);
+  pdl_launch_dependents();
+
+  if (tid >= 256) {
+    // ---- the reduce warp: the pending step's W2, b2, W3, b3 and loss sums, 256 elements per CTA and round, beside the
+    // layer-1 warps (its chain of L2 round trips hides under their loop).  Adam state first -- it is older than the kernel
+    // in front -- then the dependency wait, then the sums.
+    if (!q.pending) return;
+    const int lane = tid - 256;
+    const int w2n = d.H2 * H1, n_red = 2 * w2n + 2 * (2 * d.H2 + 1) + 3;
+    const AdamCoef cf = *q.r.coef;
+    bool waited = false;
+    for (int e0 = cta * 256; e0 < n_red; e0 += n_cta * 256) {
+#pragma unroll 1
+      for (int b0 = 0; b0 < 256; b0 += 32 * L1R_RB) {
+        float* src[L1R_RB];
+        int p[L1R_RB], slot[L1R_RB];
+        float m[L1R_RB], v[L1R_RB], w[L1R_RB], sv[L1R_RB];
+        bool live[L1R_RB];
+#pragma unroll
+        for (int u = 0; u < L1R_RB; u++) {
+          const int e = e0 + b0 + 32 * u + lane;
+          live[u] = e < n_red;
+          src[u] = nullptr; p[u] = 0; slot[u] = 0; m[u] = v[u] = w[u] = 0.f;
+          if (live[u]) {
+            l1r_locate(q, e, src[u], p[u], slot[u]);
+            if (p[u] < d.P) { m[u] = q.cm[p[u]]; v[u] = q.cv[p[u]]; w[u] = q.cparams[p[u]]; }
+          }
+        }
+        if (!waited) { pdl_wait(); waited = true; }
+#pragma unroll
+        for (int u = 0; u < L1R_RB; u++) sv[u] = live[u] ? *src[u] : 0.f;
+#pragma unroll
+        for (int u = 0; u < L1R_RB; u++) {
+          if (!live[u]) continue;
+          *src[u] = 0.f;                                  // the next step adds into zeros
+          q.cgrads[slot[u]] = sv[u];
+          if (p[u] < d.P) {
+            const float nw = wide_adam_math(cf, sv[u], m[u], v[u], w[u]);
+            q.cm[p[u]] = m[u]; q.cv[p[u]] = v[u]; q.cparams[p[u]] = nw;
+            wide_store_planes(d, q.r.w2p, q.r.bias2, p[u], nw);
+          } else {
+            wide_loss_log(q.r.u, p[u] - d.P, sv[u]);
+          }
+        }
+      }
+    }
+    if (!waited) pdl_wait();
+    return;
+  }
+
+  const int lo = (int)((int64_t)blockIdx.x * a.m_pad / gridDim.x), hi = (int)((int64_t)(blockIdx.x + 1) * a.m_pad / gridDim.x);
+  auto load_tile = [&](int r0) {
+    const int n = min(L1R_TILE, hi - r0);
+    for (int i = tid; i < n * S; i += 256) {
+      const int r = i / S, c = i % S;
+      xs[r][c] = (r0 + r < a.count) ? a.tr.obs[c * a.tr.cap + sample_pos(a, r0 + r)] : 0.0f;
+    }
+  };
+  if (hi > lo) load_tile(lo);   // the observations are constant during an update
+  // ---- this thread's W1 / b1 parameter: feature k0 + tid / 7, column tid % 7.  Its state is older than the kernel in front
+  // (the previous k_wide_l1r launch or the canonical vector): fetched before the dependency wait
+  const bool w1t = tid < L1R_FS * (S + 1);
+  const int kl = tid / (S + 1), wc = tid % (S + 1);
+  const int pcan = g * d.SIZE + (wc < S ? d.oW1 + (k0 + kl) * S + wc : d.ob1 + k0 + kl);
+  const int64_t wblk = (int64_t)H1 * (S + 1), wi = (int64_t)(k0 + kl) * (S + 1) + wc;
+  float pw = 0.f, pm = 0.f, pv = 0.f;
+  if (w1t) {
+    if (q.seed) { pw = q.cparams[pcan]; pm = q.cm[pcan]; pv = q.cv[pcan]; }
+    else { pw = q.w1_rd[(g * 3 + 0) * wblk + wi]; pm = q.w1_rd[(g * 3 + 1) * wblk + wi]; pv = q.w1_rd[(g * 3 + 2) * wblk + wi]; }
+  }
+  AdamCoef cf{};
+  if (q.pending) cf = *q.r.coef;   // of the pending step: written by the launch that ran ITS layer 1
+  pdl_wait();                      // the sums come from the kernels of the pending step
+  if (cta == 0 && tid == 0 && a.bump_step) {   // one optimizer step
+    const int64_t step = *a.bump_step + 1;
+    *a.bump_step = step;
+    *a.coef_out = adam_coef(a.hp, step);
+  }
+  if (w1t) {
+    const bool writer = blockIdx.x == 0;
+    if (q.pending) {
+      const int si = (g * H1 + k0 + kl) * 8 + wc;
+      const float gs = q.dw1_sum[si];
+      pw = wide_adam_math(cf, gs, pm, pv, pw);
+      if (writer) { q.cgrads[pcan] = gs; q.cparams[pcan] = pw; q.cm[pcan] = pm; q.cv[pcan] = pv; q.dw1_zero[si] = 0.f; }
+    }
+    if (writer) { q.w1_wr[(g * 3 + 0) * wblk + wi] = pw; q.w1_wr[(g * 3 + 1) * wblk + wi] = pm; q.w1_wr[(g * 3 + 2) * wblk + wi] = pv; }
+    ws[(kl >> 2) * 28 + (wc < S ? (kl & 3) * S + wc : 24 + (kl & 3))] = pw * TANH_K;
+  }
+  if (hi <= lo) return;
+  asm volatile("bar.sync 1, 256;" ::: "memory");
+  // ---- layer 1 of this step: 8 feature groups of 4 x 32 sample lanes
+  const int64_t plane = a.cap * H1;
+  const int kg = tid & 7, sl = tid >> 3;
+  float w[24], b[4];
+#pragma unroll
+  for (int v = 0; v < 6; v++) *reinterpret_cast<float4*>(&w[4 * v]) = *reinterpret_cast<const float4*>(ws + kg * 28 + 4 * v);
+  *reinterpret_cast<float4*>(b) = *reinterpret_cast<const float4*>(ws + kg * 28 + 24);
+  for (int r0 = lo; r0 < hi; r0 += L1R_TILE) {
+    if (r0 != lo) {
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      load_tile(r0);
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+    }
+    const int n = min(L1R_TILE, hi - r0);
+    for (int r = sl; r < n; r += 32) {
+      const bool valid = r0 + r < a.count;
+      float x[S], z[4];
+#pragma unroll
+      for (int c = 0; c < S; c++) x[c] = xs[r][c];
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        z[u] = b[u];
+#pragma unroll
+        for (int c = 0; c < S; c++) z[u] = fmaf(w[u * S + c], x[c], z[u]);
+      }
+      tanh4(z[0], z[1], z[2], z[3], z[0], z[1], z[2], z[3]);
+      uint2 th, tm;
+      split2(valid ? z[0] : 0.f, valid ? z[1] : 0.f, th.x, tm.x);
+      split2(valid ? z[2] : 0.f, valid ? z[3] : 0.f, th.y, tm.y);
+      const int64_t o = (int64_t)(r0 + r) * H1 + k0 + kg * 4;
+      *reinterpret_cast<uint2*>(a.h1p + (g * 2 + 0) * plane + o) = th;
+      *reinterpret_cast<uint2*>(a.h1p + (g * 2 + 1) * plane + o) = tm;
+    }
+  }
+}
+
 // layer 2 activation + layer 3 + loss head + D2 for both nets.  The GEMM left Z2 = H1 W2^T; here H2 = tanh(Z2 + b2).
 // One warp per sample; lane l owns the NJ consecutive features j = l*NJ .. l*NJ+NJ-1, so the Z2 row is read and the D2
 // planes are written as contiguous vectors.  The critic is finished first (its V feeds the actor's advantage, :274), so
@@ -485,6 +671,15 @@ struct WideNet {
   int32_t* boot_idx = nullptr;
   int64_t boot_cap = 0;
   int* boot_count = nullptr;
+  // the merged sequence (k_wide_l1r: reduce + Adam of step s-1 inside the layer-1 kernel of step s; B2_WIDE_MERGE=0: off)
+  bool merge_env = true;
+  float* dw1_sum = nullptr;        // [2 phases][2][H1 * 8]
+  float* head_sum = nullptr;       // [2][head_row]
+  float* w1s = nullptr;            // [2 phases][2 nets][3][H1][S + 1]
+  int phase = 0;                   // flips with every k_wide_l1r launch
+  bool pending = false;            // a step's sums wait for the next k_wide_l1r launch (or wide_flush)
+  bool seeded = false;             // w1s[phase ^ 1] holds the current W1 state
+  ReduceArgs pend_r{};             // of the pending step
 };
 
 int wide_pstride(int H1, int H2) {
@@ -500,6 +695,7 @@ void wide_destroy(WideNet* w) {
   dfree(w->bias2); dfree(w->h2); dfree(w->d1); dfree(w->coef); dfree(w->vtmp); dfree(w->fh_dbg);
   dfree(w->part_head); dfree(w->part_dw1); dfree(w->part_dw2); dfree(w->bar_counter);
   dfree(w->boot_idx); dfree(w->boot_count);
+  dfree(w->dw1_sum); dfree(w->head_sum); dfree(w->w1s);
   delete w;
 }
 
@@ -530,7 +726,7 @@ int wide_create(WideNet** out, int H1, int H2, int64_t max_chunk, int sm_count) 
   WCK(dmalloc(&w->bias2, sizeof(float) * 4 * H2));
   WCK(dmalloc(&w->vtmp, sizeof(float) * 4 * cap));
   if (getenv("B2_FH_DBG")) { WCK(dmalloc(&w->fh_dbg, sizeof(long long) * 16 * 160)); WCK(cudaMemset(w->fh_dbg, 0, sizeof(long long) * 16 * 160)); }
-  WCK(dmalloc(&w->coef, sizeof(AdamCoef)));
+  WCK(dmalloc(&w->coef, 2 * sizeof(AdamCoef)));   // [phase]: the merged sequence reads step s-1's while it writes step s's
   WCK(dmalloc(&w->h2, sizeof(float) * 2 * cap * H2));
   WCK(dmalloc(&w->d1, sizeof(float) * 2 * cap * H1));
   // stale bits must never be NaN where a zero-weighted product could meet them
@@ -549,6 +745,13 @@ int wide_create(WideNet** out, int H1, int H2, int64_t max_chunk, int sm_count) 
   WCK(dmalloc(&w->bar_counter, sizeof(int)));
   WCK(cudaMemset(w->bar_counter, 0, sizeof(int)));
   WCK(dmalloc(&w->boot_count, sizeof(int)));
+  { const char* e = getenv("B2_WIDE_MERGE"); w->merge_env = !(e && e[0] == '0'); }
+  WCK(dmalloc(&w->dw1_sum, sizeof(float) * 2 * 2 * H1 * 8));
+  WCK(dmalloc(&w->head_sum, sizeof(float) * 2 * w->head_row));
+  WCK(dmalloc(&w->w1s, sizeof(float) * 2 * 2 * 3 * H1 * (S + 1)));
+  WCK(cudaMemset(w->dw1_sum, 0, sizeof(float) * 2 * 2 * H1 * 8));
+  WCK(cudaMemset(w->head_sum, 0, sizeof(float) * 2 * w->head_row));
+  WCK(cudaMemset(w->w1s, 0, sizeof(float) * 2 * 2 * 3 * H1 * (S + 1)));
 #undef WCK
   int rc = 0;
   const uint64_t ucap = (uint64_t)cap;
@@ -589,7 +792,44 @@ static cudaError_t launch_head(const WideArgs& wa, int grid, cudaStream_t st) {
   return launch_pdl(k_wide_head<NJ>, dim3(grid), dim3(256), (size_t)smem, st, wa);
 }
 
-int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st, int64_t* launches) {
+// one k_wide_l1r launch: layer 1 of the chunk wa describes (m_pad == 0: none) + whatever step is pending
+static cudaError_t launch_l1r(WideNet* w, const WideArgs& wa, const UpdateArgs& u, int skip, cudaStream_t st) {
+  const NetDims& d = w->d;
+  const int H1 = d.H1, n_fs = H1 / L1R_FS;
+  L1rArgs q{};
+  q.a = wa;
+  q.a.coef_out = w->coef + w->phase;
+  q.pending = (w->pending && !(skip & 32)) ? 1 : 0;
+  q.seed = w->seeded ? 0 : 1;
+  q.r = w->pend_r;
+  q.dw1_sum = w->dw1_sum + (size_t)(w->phase ^ 1) * 2 * H1 * 8;
+  q.dw1_zero = w->dw1_sum + (size_t)w->phase * 2 * H1 * 8;
+  q.head_sum = w->head_sum;
+  q.w1_rd = w->w1s + (size_t)(w->phase ^ 1) * 2 * 3 * H1 * (S + 1);
+  q.w1_wr = w->w1s + (size_t)w->phase * 2 * 3 * H1 * (S + 1);
+  q.cparams = u.params; q.cm = u.adam_m; q.cv = u.adam_v; q.cgrads = u.grads;
+  const int full = std::max(1, w->sm_count * L1_CTAS / (2 * n_fs));
+  const int n_rs = wa.m_pad > 0 ? std::max(1, std::min(full, wa.m_pad / 16)) : full;
+  cudaError_t ce = launch_pdl(k_wide_l1r, dim3(n_rs, n_fs, 2), dim3(L1R_THREADS), 0, st, q);
+  if (ce != cudaSuccess) return ce;
+  w->pending = false;
+  w->seeded = true;
+  w->phase ^= 1;
+  return cudaSuccess;
+}
+
+int wide_flush(WideNet* w, cudaStream_t st, int64_t* launches) {
+  if (!w || !w->pending) return B2_OK;
+  WideArgs wa{};
+  wa.d = w->d; wa.params = w->pend_r.u.params; wa.tr = w->pend_r.u.tr; wa.cap = w->cap; wa.hp = w->pend_r.u.hp;
+  wa.h1p = w->h1p;
+  cudaError_t ce = launch_l1r(w, wa, w->pend_r.u, 0, st);
+  if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "wide flush: %s", cudaGetErrorString(ce));
+  (*launches)++;
+  return B2_OK;
+}
+
+int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, bool more_follow, cudaStream_t st, int64_t* launches) {
   const NetDims& d = w->d;
   const int H1 = d.H1, H2 = d.H2;
   WideArgs wa{};
@@ -605,14 +845,29 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
       return set_error(B2_ERR_CUDA, "wide %s: %s", what, cudaGetErrorString(ce));              \
     (*launches)++;                                                                             \
   } while (0)
+  static const bool pair_env0 = [] { const char* e = getenv("B2_WIDE_DW2_PAIR"); return !(e && e[0] == '0'); }();
+  const int64_t n_chunks = (a.count + w->cap - 1) / w->cap;
+  // the merged sequence: one GPU, Adam applied here, one chunk, sums in the L2 (not the fixed-order mode), the fused forward +
+  // head kernel and the CTA-pair dW2 kernel (the two producers that can leave sums)
+  const bool merge = w->merge_env && apply_adam && a.px.world <= 1 && n_chunks == 1 && w->dw2_add && !w->fuse_reduce && w->fused_fh &&
+                     pair_env0 && gemm_mn2_supported(H2, H1) && getenv("B2_WIDE_FUSE_M") == nullptr;
+  if (a.step_slot == 0 || !merge) {
+    if (w->pending && !merge) { int rc = wide_flush(w, st, launches); if (rc) return rc; }
+    w->pending = false;       // (a step left pending by an update that failed part-way is dropped with it)
+    w->seeded = false;        // the canonical vector is the truth at the start of an update
+  }
   if (a.step_slot == 0) {   // first optimizer step of this update: the weights may have been set from outside
+    if (merge) {
+      if ((ce = cudaMemsetAsync(w->dw1_sum, 0, sizeof(float) * 2 * 2 * H1 * 8, st)) != cudaSuccess ||
+          (ce = cudaMemsetAsync(w->head_sum, 0, sizeof(float) * 2 * w->head_row, st)) != cudaSuccess)
+        return set_error(B2_ERR_CUDA, "wide memset: %s", cudaGetErrorString(ce));
+    }
     k_wide_prep<<<128, 256, 0, st>>>(wa);
     LCK("prep");
   }
   // diagnostic only (profiles/wide_marginal.sh): B2_WIDE_SKIP = bit mask of step kernels to leave out (1 l1, 2 fwd GEMM,
   // 4 head, 8 dX GEMM, 16 dW2 GEMM + dw1, 32 reduce) -- results are garbage, the timing shows each kernel's marginal cost
   static const int skip = [] { const char* e = getenv("B2_WIDE_SKIP"); return e ? atoi(e) : 0; }();
-  const int64_t n_chunks = (a.count + w->cap - 1) / w->cap;
   for (int64_t c = 0; c < n_chunks; c++) {
     wa.first = a.first + c * w->cap;
     wa.count = (int)std::min<int64_t>(w->cap, a.count - c * w->cap);
@@ -620,10 +875,12 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     wa.bump_step = c == 0 ? a.adam_step : nullptr;
     wa.coef_out = w->coef;
     const int m_tiles = wa.m_pad / 128;
-    // layer 1
+    AdamCoef* step_coef = merge ? w->coef + w->phase : w->coef;   // where this step's Adam coefficients are written
+    const int sum_phase = w->phase;                               // (launch_l1r flips it)
+    // layer 1 (merged: + the reduce and Adam of the step before)
     const int l1_grid = std::max(1, std::min(w->sm_count * L1_CTAS / 2, wa.m_pad / 16));
     if (!(skip & 1))
-    if ((ce = launch_pdl(k_wide_l1, dim3(l1_grid, 2), dim3(256), 0, st, wa)) != cudaSuccess)
+    if ((ce = merge ? launch_l1r(w, wa, a, skip, st) : launch_pdl(k_wide_l1, dim3(l1_grid, 2), dim3(256), 0, st, wa)) != cudaSuccess)
       return set_error(B2_ERR_CUDA, "wide l1: %s", cudaGetErrorString(ce));
     (*launches)++;
     // H2 = tanh(H1 W2^T + b2)
@@ -637,6 +894,7 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
       f.first = wa.first; f.idx = a.idx; f.tr = a.tr; f.params = a.params; f.headw = w->bias2; f.vtmp = w->vtmp;
       f.inv_denom = wa.inv_denom; f.hp = a.hp; f.part_head = w->part_head; f.head_row = w->head_row;
       f.dbg = w->fh_dbg;
+      f.head_sum = merge ? w->head_sum : nullptr;
       f.dx = (w->fused_dx && !(skip & 8)) ? 1 : 0;
       if (!(skip & 6))
       if ((ce = launch_wide_fh(w->tm_h1, w->tm_w2_half, w->tm_d2_st, w->tm_d2, w->tm_w2t, w->tm_out_d1_16, f, w->sm_count, &w->fh_grid, st)) != cudaSuccess)
@@ -720,6 +978,7 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     g.dw1.obs = a.tr.obs; g.dw1.obs_cap = a.tr.cap; g.dw1.idx = a.idx; g.dw1.first = wa.first;
     g.dw1.count = wa.count; g.dw1.H1 = H1; g.dw1.SIZE = d.SIZE; g.dw1.oW1 = d.oW1; g.dw1.ob1 = d.ob1;
     g.dw1.z1 = w->d1; g.dw1.cap = w->cap; g.dw1.part = w->part_dw1;
+    g.dw1.sum = merge ? w->dw1_sum + (size_t)sum_phase * 2 * H1 * 8 : nullptr;
     int dw2_grid = std::min(2 * (fuse_m ? 1 : jt) * splits, w->sm_count);
     // H2 = 256: CTA pairs (tcgen05 cta_group::2) own all 256 rows of dW2, every operand byte is fetched once, and the dW1
     // warps take Z1 through a cp.async ring (wide_gemm_mn2.cu, wide_dw1.cuh); B2_WIDE_DW2_PAIR=0: k_gemm_x3<MN>
@@ -732,7 +991,7 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
     r.head_blocks = head_rows; r.head_row = w->head_row; r.dw1_blocks = dw2_grid; r.splits = splits;
     r.dw2_added = w->dw2_add ? 1 : 0;
     r.pstride = wide_pstride(H1, H2);
-    r.w2p = w->w2p; r.bias2 = w->bias2; r.coef = w->coef;
+    r.w2p = w->w2p; r.bias2 = w->bias2; r.coef = step_coef;
     r.first_chunk = c == 0; r.last_chunk = c == n_chunks - 1; r.apply_adam = apply_adam ? 1 : 0;
     const int small = 2 * (H1 * (S + 1) + 2 * H2 + 1) + 3;
     const bool fused_tail = w->fuse_reduce && !(skip & (16 | 32));
@@ -751,6 +1010,12 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, cudaStream_t st,
       return set_error(B2_ERR_CUDA, "wide gemm dW2: %s", cudaGetErrorString(ce));
     (*launches)++;
     if (fused_tail) continue;
+    if (merge) {              // this step's reduce + Adam: in the next step's layer-1 kernel, or in a launch without rows right now
+      w->pend_r = r;
+      w->pending = !(skip & 32);
+      if (!more_follow) { int rc = wide_flush(w, st, launches); if (rc) return rc; }
+      continue;
+    }
     const int w2_blocks = w->dw2_add ? (2 * H2 * H1 + 2 * RED_THREADS - 1) / (2 * RED_THREADS) : (2 * H2 * H1 + RED_THREADS - 1) / RED_THREADS;
     const int rgrid = w2_blocks + wide_reduce_dw1_blocks(d) + wide_reduce_head_blocks(d);
     if (!(skip & 32))

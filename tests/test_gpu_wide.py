@@ -162,9 +162,48 @@ def test_wide_update_chunked_and_minibatched():
         assert H.relerr(E.get_params(), p) < 1e-5
 
 
+@pytest.mark.parametrize("merge", ["1", "0"], ids=["merged_l1r", "reduce_own_launch"])
+def test_wide_minibatched_updates_carry_state(merge, monkeypatch):
+    """3 ragged minibatches x 2 epochs, TWO updates in a row on one engine (the second starts from the first one's weights and
+    Adam moments): the default sequence defers every step's reduce + Adam into the next step's layer-1 kernel (k_wide_l1r)
+    and flushes after the last one, so the state the next update, get_params and get_adam_state see must be complete;
+    B2_WIDE_MERGE=0 is the sequence with k_wide_reduce as its own launch"""
+    monkeypatch.setenv("B2_WIDE_MERGE", merge)
+    H1, H2, B, K, M = 256, 256, 1000, 2, 3
+    dims = H.Dims(6, H1, H2, 1)
+    params, obs, act, oldlp, reward, flags = synth_batch(dims, B, 99)
+    L = H.oracle()
+    p, m, v = params.copy(), np.zeros_like(params), np.zeros_like(params)
+    per, step = B // M, 0
+    with wide_engine(H1, H2, n=B, k_epochs=K, n_minibatches=M) as E:
+        E.set_params(params)
+        for upd in range(2):
+            R = np.zeros(B, np.float32)
+            L.orc_returns(C.byref(dims), p, obs, reward, flags, B, H.GAMMA, R)   # bootstraps use the current critic
+            for k in range(K):
+                for mb in range(M):
+                    lo = mb * per
+                    hi = B if mb == M - 1 else lo + per
+                    idx = np.arange(lo, hi, dtype=np.int64)
+                    g, out = np.zeros_like(params), H.Loss()
+                    L.orc_loss_grad(C.byref(dims), p, obs, act, oldlp, R, idx.ctypes.data_as(C.c_void_p), idx.size, H.SIGMA,
+                                    H.EPS_CLIP, C.byref(out), g)
+                    step += 1
+                    L.orc_adam(p, g, m, v, p.size, step, H.LR, H.B1, H.B2, 1e-8)
+            st = E.update(obs, act, oldlp, reward, flags)
+            assert st.optimizer_steps == K * M and st.adam_step == step
+            assert abs(st.loss - out.loss) < 1e-4 * abs(out.loss) + 1e-6
+            assert H.relerr(E.get_grads(), g) < 1e-4
+            em, ev, es = E.get_adam_state()
+            assert es == step
+            assert H.relerr(E.get_params(), p) < 1e-5 and H.relerr(em, m) < 1e-4 and H.relerr(ev, v) < 2e-4
+
+
 @pytest.mark.parametrize("env", [{"B2_WIDE_DETERMINISTIC": "1"}, {"B2_WIDE_FUSE_REDUCE": "1"}, {"B2_WIDE_FUSE_M": "1"},
-                                 {"B2_WIDE_FUSED": "0"}, {"B2_WIDE_FUSED": "0", "B2_WIDE_DETERMINISTIC": "1"}, {"B2_WIDE_FUSE_DX": "0"}],
-                         ids=["deterministic", "fused_reduce_tail", "fuse_m", "unfused_forward_head", "unfused_deterministic", "dx_own_launch"])
+                                 {"B2_WIDE_FUSED": "0"}, {"B2_WIDE_FUSED": "0", "B2_WIDE_DETERMINISTIC": "1"}, {"B2_WIDE_FUSE_DX": "0"},
+                                 {"B2_WIDE_MERGE": "0"}],
+                         ids=["deterministic", "fused_reduce_tail", "fuse_m", "unfused_forward_head", "unfused_deterministic", "dx_own_launch",
+                              "reduce_own_launch"])
 def test_wide_update_opt_in_modes_match_oracle(env, monkeypatch):
     """the opt-in variants of the step (read from the environment when the engine is created / the step is launched) are
     held to the same oracle gates as the default; the fixed-order mode must also be bit-identical run to run"""
