@@ -454,22 +454,30 @@ k_wide_fh(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
           tc::tc_fence_after();
           const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * 256u;
           const int row0 = t * 2 * BM + (int)rank * BM + q * 32;
+          // the LAST accumulator of the kernel: no load is outstanding and tfull says every MMA has read its operands, so the
+          // weight / A-stage memory is free -- each chunk gets a staging tile of its own there and none waits for the TMA to
+          // have read the chunk before it (this epilogue is the exposed tail of the kernel)
+          const bool wide = pass == 3 && t + n_pairs >= tiles && (size_t)B_BYTES + (size_t)stages * A_STAGE >= (size_t)HEAD_WARPS * 4 * STG_WARP;
+          if (wide && lane == 0) tc::bulk_wait_read<0>();
 #pragma unroll
           for (int ci = 0; ci < 4; ci++) {
             const int c = c2_begin + ci * 16;
             if (c < c2_end) {
+              uint8_t* stg = wide ? smem + (size_t)((warp - 2) * 4 + ci) * STG_WARP : sb;
               float v[16];
               tc::tmem_ld16(t0 + (uint32_t)c, v);
               tc::tmem_ld_wait();
-              if (lane == 0) tc::bulk_wait_read<0>();
-              __syncwarp();
+              if (!wide) {
+                if (lane == 0) tc::bulk_wait_read<0>();
+                __syncwarp();
+              }
 #pragma unroll
               for (int i = 0; i < 4; i++)
-                *reinterpret_cast<float4*>(sb + lane * 64 + ((i ^ ((lane >> 1) & 3)) << 4)) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                *reinterpret_cast<float4*>(stg + lane * 64 + ((i ^ ((lane >> 1) & 3)) << 4)) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
               tc::fence_proxy_async();
               __syncwarp();
               if (lane == 0) {
-                tc::tma_store_3d(&tmC, sb, c, row0, g);
+                tc::tma_store_3d(&tmC, stg, c, row0, g);
                 tc::bulk_commit();
               }
             }

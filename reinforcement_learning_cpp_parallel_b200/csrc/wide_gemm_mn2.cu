@@ -142,31 +142,41 @@ k_gemm_mn2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
     const int c_begin = half ? ((n_chunks + 1) / 2) * 32 : 0;
     const int c_end = half ? N : ((n_chunks + 1) / 2) * 32;
     uint8_t* sb = smem + (size_t)stages * SB + (warp - 2) * STG_BUF;
+    // The pair's LAST item leaves the operand stages idle (every load has landed and tfull says every MMA has read them): its
+    // epilogue then gives each 16-column chunk a staging tile of its own there, so no chunk waits for the TMA to have read the
+    // one before it -- the drain is the exposed tail of the kernel (one item per pair at 2x256 on 148 SMs)
+    const bool wide_fits = (size_t)stages * SB >= 8 * (size_t)(((n_chunks + 1) / 2) * 2) * STG_BUF;
+    uint8_t* sb_wide = smem + (size_t)(warp - 2) * (size_t)(((n_chunks + 1) / 2) * 2) * STG_BUF;
     int it = 0;
     for (int item = pair; item < n_items; item += n_pairs, it++) {
       const int sp = item % a.splits, g = item / a.splits;
       const int buf = it & 1;
       const uint32_t bphase = (uint32_t)(it >> 1) & 1u;
+      const bool wide = wide_fits && item + n_pairs >= n_items;
       tc::mbar_wait(&tfull[buf], bphase);
       tc::tc_fence_after();
       const int row0 = (int)rank * BM + q * 32;           // first output row (feature j of D2) of this warp
       const int plane = a.reduce_add ? g : g * a.splits + sp;
       const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * 256u;
+      if (wide && lane == 0) tc::bulk_wait_read<0>();     // (the small tile of an earlier item)
       for (int c = c_begin; c < c_end; c += 16) {       // tmC: 16-column boxes, 64-B swizzle (make_output_map16)
+        uint8_t* stg = wide ? sb_wide + (size_t)((c - c_begin) / 16) * STG_BUF : sb;
         float v[16];
         tc::tmem_ld16(t0 + (uint32_t)c, v);
         tc::tmem_ld_wait();
-        if (lane == 0) tc::bulk_wait_read<0>();
-        __syncwarp();
+        if (!wide) {
+          if (lane == 0) tc::bulk_wait_read<0>();
+          __syncwarp();
+        }
 #pragma unroll
         for (int i = 0; i < 4; i++)
-          *reinterpret_cast<float4*>(sb + lane * 64 + ((i ^ ((lane >> 1) & 3)) << 4)) =
+          *reinterpret_cast<float4*>(stg + lane * 64 + ((i ^ ((lane >> 1) & 3)) << 4)) =
               make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
         tc::fence_proxy_async();
         __syncwarp();
         if (lane == 0) {
-          if (a.reduce_add) tc::tma_reduce_add_3d(&tmC, sb, c, row0, plane);
-          else tc::tma_store_3d(&tmC, sb, c, row0, plane);
+          if (a.reduce_add) tc::tma_reduce_add_3d(&tmC, stg, c, row0, plane);
+          else tc::tma_store_3d(&tmC, stg, c, row0, plane);
           tc::bulk_commit();
         }
       }

@@ -111,7 +111,7 @@ def test_wide_gradient_matches_torch_golden(H1, H2):
         assert st.adam_step == 1
 
 
-@pytest.mark.parametrize("H1,H2,B,K", [(256, 256, 1000, 4), (128, 64, 333, 3), (192, 128, 2048, 2)])
+@pytest.mark.parametrize("H1,H2,B,K", [(256, 256, 1000, 4), (128, 64, 333, 3), (192, 128, 2048, 2), (128, 256, 777, 3), (64, 256, 130, 3)])
 def test_wide_update_matches_oracle(H1, H2, B, K):
     """K full-batch epochs incl. returns with TIMEUP bootstraps, ragged B: weights, Adam state, per-epoch losses"""
     dims = H.Dims(6, H1, H2, 1)
