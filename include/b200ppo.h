@@ -232,6 +232,27 @@ int b2_debug_guard_check(void);
  * mn_major = 2: A[M][K] as usual, B contraction-major B[K][N] (the layout of Z1 = D2 W2 with W2 as stored), N % 64 == 0 */
 int b2_selftest_gemm(b2_handle h, int M, int N, int K, const float* A, const float* B, float* C, int splits, int mn_major);
 
+/* ---- allocation-free entry point ----
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The discounted returns of b2_returns' segment-per-warp path (k_seg_ends + k_seg_returns, csrc/returns.cu: the
+ * recurrence of src/ppo_nn.cpp:207-236 at gae_lambda = 1) on DEVICE buffers of the caller, with the segment list -- the
+ * scratch b2_returns keeps in a cudaMalloc'ed buffer of the engine -- in a file-scope `static __device__` array of the
+ * library: 8 B per record + 256 B = 2 MiB + 256 B for B2_NOALLOC_MAX_RECORDS records, held by every GPU that loads the
+ * library until the process exits.  No engine handle; no cudaMalloc / cudaFree / allocating library call, on the first
+ * call or any later one (the first call on a device resolves the array's device address with cudaGetSymbolAddress).
+ *   reward, flags, vboot, returns: device pointers, [horizon][n_envs] (flat index t * n_envs + e, as the engine's
+ *   trajectory); vboot[k] = V(obs_k) is read only where flags[k] has B2_FLAG_TIMEUP or B2_FLAG_TRUNC (b2_value gives it).
+ *   stream: a cudaStream_t, NULL = the default stream.  The call only ENQUEUES (memset of the counter + two kernels) and
+ *   does not synchronize.
+ * n_envs * horizon > B2_NOALLOC_MAX_RECORDS is rejected with B2_ERR_INVALID (b2_last_error says so); so are NULL
+ * pointers and non-positive sizes.  Every call on a GPU shares the ONE array: the call clears what must start at zero
+ * (the segment counter), the rest of the array keeps the previous call's contents and is overwritten before it is read;
+ * calls that overlap on one GPU (two streams, two threads) race on it -- serialize them. */
+#define B2_NOALLOC_MAX_RECORDS 262144
+int b2_returns_noalloc(const float* reward, const uint8_t* flags, const float* vboot, int64_t n_envs, int64_t horizon,
+                       float gamma, float* returns, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -113,7 +113,9 @@ SYMBOLS = {
     "b2_host_alloc": (C.c_int, [_P(C.c_void_p), C.c_size_t]),
     "b2_host_free": (C.c_int, [C.c_void_p]),
     "b2_selftest_gemm": (C.c_int, [_H, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
+    "b2_returns_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_float, C.c_void_p, C.c_void_p]),
 }
+NOALLOC_MAX_RECORDS = 262144   # B2_NOALLOC_MAX_RECORDS
 
 _lib = None
 

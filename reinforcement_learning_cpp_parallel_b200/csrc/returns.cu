@@ -201,3 +201,78 @@ cudaError_t launch_returns(const float* params, const Traj& tr, const HyperDev& 
 }
 
 }  // namespace b2
+
+// ------------------------------------------------------------------------------------------------------------
+// b2_returns_noalloc (include/b200ppo.h): the segment-per-warp returns on caller-owned device buffers with the segment
+// list in a static device array -- for callers that cannot call cudaMalloc (graph capture, serving loops).  No
+// counterpart in the reference.  Nothing above this line is changed by it.
+// ------------------------------------------------------------------------------------------------------------
+#include <mutex>
+
+namespace b2 {
+namespace {
+// [0, 8): the segment counter; [256, 256 + 8 * B2_NOALLOC_MAX_RECORDS): the segment ends (k_seg_ends writes at most one
+// entry per record).  One copy per GPU that loads the library, for the life of the process.
+constexpr size_t NOALLOC_COUNT_BYTES = 256;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_COUNT_BYTES + sizeof(int64_t) * B2_NOALLOC_MAX_RECORDS];
+
+// In host code `g_noalloc_scratch` is only the symbol's host-side stand-in: the device address comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+std::mutex g_noalloc_mu;
+unsigned char* g_noalloc_dev[64] = {};
+
+int noalloc_scratch(unsigned char** out) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return set_error(B2_ERR_NO_DEVICE, "b2_returns_noalloc: cudaGetDevice: %s", cudaGetErrorString(e));
+  if (dev < 0 || dev >= 64) return set_error(B2_ERR_INVALID, "b2_returns_noalloc: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (!g_noalloc_dev[dev]) {
+    unsigned char* p = nullptr;
+    e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_noalloc_scratch);
+    if (e != cudaSuccess || !p)
+      return set_error(B2_ERR_CUDA, "b2_returns_noalloc: cudaGetSymbolAddress(scratch) on device %d: %s", dev, cudaGetErrorString(e));
+    g_noalloc_dev[dev] = p;
+  }
+  *out = g_noalloc_dev[dev];
+  return B2_OK;
+}
+}  // namespace
+}  // namespace b2
+
+extern "C" int b2_returns_noalloc(const float* reward, const uint8_t* flags, const float* vboot, int64_t n_envs, int64_t horizon,
+                                  float gamma, float* returns, void* stream) {
+  using namespace b2;
+  if (!reward || !flags || !vboot || !returns)
+    return set_error(B2_ERR_INVALID, "b2_returns_noalloc: reward, flags, vboot and returns must be device pointers (got a NULL)");
+  if (n_envs <= 0 || horizon <= 0)
+    return set_error(B2_ERR_INVALID, "b2_returns_noalloc: n_envs (%lld) and horizon (%lld) must be positive", (long long)n_envs,
+                     (long long)horizon);
+  if (n_envs > B2_NOALLOC_MAX_RECORDS || horizon > B2_NOALLOC_MAX_RECORDS || n_envs * horizon > B2_NOALLOC_MAX_RECORDS)
+    return set_error(B2_ERR_INVALID,
+                     "b2_returns_noalloc: %lld x %lld records exceed B2_NOALLOC_MAX_RECORDS = %d (the static scratch array); "
+                     "use b2_returns / b2_update_resident for larger batches",
+                     (long long)n_envs, (long long)horizon, (int)B2_NOALLOC_MAX_RECORDS);
+  unsigned char* scratch = nullptr;
+  if (int rc = noalloc_scratch(&scratch)) return rc;
+  unsigned long long* count = reinterpret_cast<unsigned long long*>(scratch);
+  int64_t* ends = reinterpret_cast<int64_t*>(scratch + NOALLOC_COUNT_BYTES);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  Traj tr{};
+  const int64_t B = n_envs * horizon;
+  tr.cap = B; tr.n_envs = n_envs; tr.horizon = horizon;
+  tr.reward = const_cast<float*>(reward); tr.flags = const_cast<uint8_t*>(flags); tr.vboot = const_cast<float*>(vboot);
+  tr.ret = returns;
+  cudaError_t e;
+  // the counter must start at zero; ends[] keeps the previous call's entries, and k_seg_returns reads only the first
+  // `count` of them, all written by THIS call's k_seg_ends
+  if ((e = cudaMemsetAsync(count, 0, sizeof *count, st)) != cudaSuccess)
+    return set_error(B2_ERR_CUDA, "b2_returns_noalloc: cudaMemsetAsync: %s", cudaGetErrorString(e));
+  int64_t g = (B + 127) / 128;
+  if (g > 148 * 16) g = 148 * 16;
+  k_seg_ends<<<(int)g, 128, 0, st>>>(tr, B, ends, count);
+  if ((e = cudaGetLastError()) != cudaSuccess) return set_error(B2_ERR_CUDA, "b2_returns_noalloc: k_seg_ends: %s", cudaGetErrorString(e));
+  k_seg_returns<false><<<148 * 8, 128, 0, st>>>(tr, gamma, 1.0f, ends, count);
+  if ((e = cudaGetLastError()) != cudaSuccess) return set_error(B2_ERR_CUDA, "b2_returns_noalloc: k_seg_returns: %s", cudaGetErrorString(e));
+  return B2_OK;
+}
