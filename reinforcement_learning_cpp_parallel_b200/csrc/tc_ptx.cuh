@@ -68,6 +68,20 @@ __device__ __forceinline__ void tma_reduce_add_3d(const void* tmap, const void* 
                ::"l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2)
                : "memory");
 }
+// diagnostic timeline: earliest / latest %globaltimer (ns) over the calling threads, slot by slot, for kernel k.  Compiled in
+// only by `make TIMELINE=1` (-DB2_TIMELINE) and switched on with B2_WIDE_TL=1: even never-taken stamps cost the wide step
+// 2 us of 72 (registers and code layout of kernels that sit at their register limits), so the product build has none.
+#ifdef B2_TIMELINE
+__device__ __forceinline__ void tl_stamp(long long* tl, int k, int slot) {
+  if (!tl) return;
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  atomicMin(reinterpret_cast<unsigned long long*>(tl) + (k * 8 + slot) * 2, t);
+  atomicMax(reinterpret_cast<unsigned long long*>(tl) + (k * 8 + slot) * 2 + 1, t);
+}
+#else
+__device__ __forceinline__ void tl_stamp(long long*, int, int) {}
+#endif
 // 1-D bulk reduce: global[0 .. bytes) += shared[0 .. bytes) as fp32 adds in the L2 (16-B aligned, bytes % 16 == 0)
 __device__ __forceinline__ void bulk_reduce_add_f32(float* gdst, const void* smem_src, uint32_t bytes) {
   asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;"

@@ -103,6 +103,7 @@ struct GemmArgs {
   int reduce_add;                // split-K: every split ADDS its tile into plane g (TMA reduce, fp32 adds in L2) instead of
                                  // storing to plane g * splits + split; the output must be zero before the launch
   long long* dbg;                // optional per-CTA timeline (clock64), diagnostic runs only
+  long long* tl;                 // optional whole-step timeline (tc::tl_stamp), diagnostic runs only
   Dw1Args dw1;                   // MN-major kernel only
   // MN-major kernel only: the reduce + Adam stage of the step runs in the tail of this kernel, behind a grid barrier
   // (every CTA is resident: grid <= SM count, one CTA per SM), instead of in a launch of its own.  red.part_dw2 == nullptr: off
@@ -131,6 +132,7 @@ struct FhArgs {
   int head_row;
   long long* dbg;              // optional clock64 timeline of the head warps, [grid][16] (B2_FH_DBG=1, diagnostic runs)
   int dx;                      // 1: the dX GEMM Z1 = D2 W2 of both nets runs in this kernel too (passes 2, 3)
+  long long* tl;               // optional whole-step timeline (tc::tl_stamp), diagnostic runs only
 };
 int fh_stages(int N, int K);
 bool fh_supported(int N, int K);

@@ -96,9 +96,11 @@ k_wide_fh(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     tc::fence_barrier_init();
   }
   if (a.dbg && threadIdx.x == 64) a.dbg[blockIdx.x * 16 + 12] = clock64();   // kernel entry (slots 0..11: up to 3 tiles x 4 stamps)
+  if (threadIdx.x == 64) tc::tl_stamp(a.tl, 1, 0);
   pdl_launch_dependents();
   if (warp == 1) tc::tmem_alloc_2sm(tmem_slot, 512);
   pdl_wait();                                             // h1p comes from k_wide_l1, the weights from the previous step's Adam
+  if (threadIdx.x == 64) tc::tl_stamp(a.tl, 1, 1);
   tc::tc_fence_before();
   tc::cluster_sync();
   tc::tc_fence_after();
@@ -241,6 +243,7 @@ k_wide_fh(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         tc::mbar_wait(&tfull[buf], bphase);
         tc::tc_fence_after();
         if (a.dbg && threadIdx.x == 64) a.dbg[blockIdx.x * 16 + it * 4 + 1] = clock64();
+        if (threadIdx.x == 64) tc::tl_stamp(a.tl, 1, 2 + pass);   // accumulator of pass 0 / 1 ready
         const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * 256u;
         // ---- pass 1 over the row: activation, dot with W3, h back into TMEM
         float2 yab = make_float2(0.f, 0.f);              // two chains of the row's dot product, one FFMA2 per pair
@@ -440,6 +443,7 @@ k_wide_fh(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         }
       }
       bar_sync(5, HEAD_WARPS * 32);                       // fold is staging again
+      if (threadIdx.x == 64) tc::tl_stamp(a.tl, 1, 4 + pass);   // head of pass 0 / 1 done
     }
     // ---- passes 2, 3 (a.dx): raw epilogue of the dX GEMM, Z1 tiles -> d1 (fp32), 16 columns at a time through the same staging
     // buffers: TMEM -> registers -> 64-B-swizzled 32 x 16 tile -> TMA store
@@ -452,6 +456,7 @@ k_wide_fh(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
           const uint32_t bphase = (uint32_t)(it >> 1) & 1u;
           tc::mbar_wait(&tfull[buf], bphase);
           tc::tc_fence_after();
+          if (threadIdx.x == 64 && pass == 3) tc::tl_stamp(a.tl, 1, 7);   // accumulator of the last dX pass ready
           const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * 256u;
           const int row0 = t * 2 * BM + (int)rank * BM + q * 32;
           // the LAST accumulator of the kernel: no load is outstanding and tfull says every MMA has read its operands, so the
@@ -492,6 +497,7 @@ k_wide_fh(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
   }
 
   if (a.dbg && threadIdx.x == 64) a.dbg[blockIdx.x * 16 + 13] = clock64();   // head done
+  if (threadIdx.x == 64) tc::tl_stamp(a.tl, 1, 6);
   tc::tc_fence_before();
   tc::cluster_sync();                                     // no CTA of the pair exits while the other may still signal it
   if (warp == 1) {

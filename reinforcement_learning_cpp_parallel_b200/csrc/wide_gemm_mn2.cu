@@ -65,9 +65,11 @@ k_gemm_mn2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
     for (int b = 0; b < 2; b++) { tc::mbar_init(&tfull[b], 1); tc::mbar_init(&tempty[b], 512); }
     tc::fence_barrier_init();
   }
+  if (threadIdx.x == 0) tc::tl_stamp(a.tl, 2, 0);
   pdl_launch_dependents();
   if (warp == 1) tc::tmem_alloc_2sm(tmem_slot, 512);
   pdl_wait();                                             // operands come from the previous kernels of the step
+  if (threadIdx.x == 0) tc::tl_stamp(a.tl, 2, 1);
   tc::tc_fence_before();
   tc::cluster_sync();
   tc::tc_fence_after();
@@ -113,6 +115,8 @@ k_gemm_mn2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
         for (int kb = kb0; kb < kb1; kb++) {
           tc::mbar_wait(&full[stage], phase);
           tc::tc_fence_after();
+          if (kb == kb0) tc::tl_stamp(a.tl, 2, 2);         // first operands have landed
+          if (kb == kb1 - 1) tc::tl_stamp(a.tl, 2, 3);     // last operands have landed
           const uint32_t s = tc::smem_u32(smem + (size_t)stage * SB);
           const uint64_t mAh = tc::smem_desc_mn_sw128(s, MNB_BYTES), mAm = tc::smem_desc_mn_sw128(s + A_PLANE, MNB_BYTES);
           const uint64_t mBh = tc::smem_desc_mn_sw128(s + 2 * A_PLANE, MNB_BYTES);
@@ -135,6 +139,7 @@ k_gemm_mn2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
   } else if (warp >= GEMM_THREADS / 32) {
     if (a.dw1.params)
       dw1_worker_async(a.dw1, reinterpret_cast<float*>(smem + (size_t)stages * SB + STG_BYTES + BAR_BYTES), threadIdx.x - GEMM_THREADS);
+    if (threadIdx.x == GEMM_THREADS) tc::tl_stamp(a.tl, 2, 6);   // dW1 warps done
   } else {
     const int q = warp & 3;
     const int half = (warp - 2) >> 2;
@@ -155,6 +160,7 @@ k_gemm_mn2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
       const bool wide = wide_fits && item + n_pairs >= n_items;
       tc::mbar_wait(&tfull[buf], bphase);
       tc::tc_fence_after();
+      if (threadIdx.x == 64) tc::tl_stamp(a.tl, 2, 4);    // accumulator ready
       const int row0 = (int)rank * BM + q * 32;           // first output row (feature j of D2) of this warp
       const int plane = a.reduce_add ? g : g * a.splits + sp;
       const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * 256u;
@@ -184,10 +190,12 @@ k_gemm_mn2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
       tc::mbar_arrive_leader_cta(&tempty[buf]);
     }
     if (lane == 0) tc::bulk_wait_all();
+    if (threadIdx.x == 64) tc::tl_stamp(a.tl, 2, 5);      // epilogue done
   }
 
   tc::tc_fence_before();
   tc::cluster_sync();                                     // no CTA of the pair exits while the other may still signal it
+  if (threadIdx.x == 0) tc::tl_stamp(a.tl, 2, 7);
   if (warp == 1) {
     tc::tc_fence_after();
     tc::tmem_dealloc_2sm(tmem_base, 512);

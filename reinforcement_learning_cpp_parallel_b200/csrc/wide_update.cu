@@ -167,6 +167,8 @@ struct L1rArgs {
   const float* w1_rd;      // [2 nets][3: w, m, v][H1][S + 1] (column S = the bias)
   float* w1_wr;
   float *cparams, *cm, *cv, *cgrads;   // the canonical vectors (row slice 0 keeps W1 / b1 current there too)
+  long long* tl;           // optional whole-step timeline (tc::tl_stamp), diagnostic runs only
+  int tl_k;                // its kernel row: 0 = this step's launch, 3 = the launch of the step after the stamped one
 };
 constexpr int L1R_FS = 32;        // features per CTA
 constexpr int L1R_THREADS = 288;  // 8 layer-1 warps + the reduce warp
@@ -194,19 +196,26 @@ __device__ __forceinline__ void l1r_locate(const L1rArgs& q, int e, float*& src,
 }
 
 __global__ void __launch_bounds__(L1R_THREADS, L1_CTAS) k_wide_l1r(const L1rArgs q) {
-  __shared__ float xs[L1R_TILE][S + 2];
-  __shared__ __align__(16) float ws[(L1R_FS / 4) * 28];   // per feature group of 4: 24 weights + 4 biases, pre-scaled by TANH_K
+  __shared__ __align__(16) float xs[L1R_TILE][2 * S];     // every component twice: (x, x) pairs are the FFMA2 operands of the loop
+  __shared__ __align__(16) float ws[(L1R_FS / 4) * 28];   // per feature group of 4: 12 weight PAIRS (features 0|1, then 2|3, of
+                                                          // component c) + 4 biases, pre-scaled by TANH_K
   const WideArgs& a = q.a;
   const NetDims& d = a.d;
   const int H1 = d.H1, g = blockIdx.z, k0 = blockIdx.y * L1R_FS, tid = threadIdx.x;
   const int n_cta = (int)(gridDim.x * gridDim.y * gridDim.z);
   const int cta = (int)((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x);
+  if (tid == 0) tc::tl_stamp(q.tl, q.tl_k, 0);
   pdl_launch_dependents();
 
   if (tid >= 256) {
     // ---- the reduce warp: the pending step's W2, b2, W3, b3 and loss sums, 256 elements per CTA and round, beside the
     // layer-1 warps (its chain of L2 round trips hides under their loop).  Adam state first -- it is older than the kernel
     // in front -- then the dependency wait, then the sums.
+    if (cta == 0 && tid == 256 && a.bump_step) {   // one optimizer step: the counter and the coefficients of THIS step's Adam (two
+      const int64_t step = *a.bump_step + 1;       // fp64 pow() on one thread, off the layer-1 warps' path; the counter was last
+      *a.bump_step = step;                         // written by the launch before the kernels in front: no wait needed)
+      *a.coef_out = adam_coef(a.hp, step);
+    }
     if (!q.pending) return;
     const int lane = tid - 256;
     const int w2n = d.H2 * H1, n_red = 2 * w2n + 2 * (2 * d.H2 + 1) + 3;
@@ -248,15 +257,24 @@ __global__ void __launch_bounds__(L1R_THREADS, L1_CTAS) k_wide_l1r(const L1rArgs
       }
     }
     if (!waited) pdl_wait();
+    if (tid == 256) tc::tl_stamp(q.tl, q.tl_k, 4);        // reduce warp done
     return;
   }
 
   const int lo = (int)((int64_t)blockIdx.x * a.m_pad / gridDim.x), hi = (int)((int64_t)(blockIdx.x + 1) * a.m_pad / gridDim.x);
   auto load_tile = [&](int r0) {
     const int n = min(L1R_TILE, hi - r0);
-    for (int i = tid; i < n * S; i += 256) {
-      const int r = i / S, c = i % S;
-      xs[r][c] = (r0 + r < a.count) ? a.tr.obs[c * a.tr.cap + sample_pos(a, r0 + r)] : 0.0f;
+    static_assert(L1R_TILE <= 512, "two rows per thread and component");
+    float v[2 * S];                                     // every load of a thread in flight before the first store (one L2 round
+#pragma unroll                                          // trip instead of a dozen); a warp reads 32 consecutive rows of ONE component
+    for (int u = 0; u < 2 * S; u++) {
+      const int c = u >> 1, r = tid + 256 * (u & 1);
+      v[u] = (r < n && r0 + r < a.count) ? a.tr.obs[c * a.tr.cap + sample_pos(a, r0 + r)] : 0.0f;
+    }
+#pragma unroll
+    for (int u = 0; u < 2 * S; u++) {
+      const int c = u >> 1, r = tid + 256 * (u & 1);
+      if (r < n) *reinterpret_cast<float2*>(&xs[r][2 * c]) = make_float2(v[u], v[u]);
     }
   };
   if (hi > lo) load_tile(lo);   // the observations are constant during an update
@@ -274,11 +292,7 @@ __global__ void __launch_bounds__(L1R_THREADS, L1_CTAS) k_wide_l1r(const L1rArgs
   AdamCoef cf{};
   if (q.pending) cf = *q.r.coef;   // of the pending step: written by the launch that ran ITS layer 1
   pdl_wait();                      // the sums come from the kernels of the pending step
-  if (cta == 0 && tid == 0 && a.bump_step) {   // one optimizer step
-    const int64_t step = *a.bump_step + 1;
-    *a.bump_step = step;
-    *a.coef_out = adam_coef(a.hp, step);
-  }
+  if (tid == 0) tc::tl_stamp(q.tl, q.tl_k, 1);
   if (w1t) {
     const bool writer = blockIdx.x == 0;
     if (q.pending) {
@@ -288,10 +302,11 @@ __global__ void __launch_bounds__(L1R_THREADS, L1_CTAS) k_wide_l1r(const L1rArgs
       if (writer) { q.cgrads[pcan] = gs; q.cparams[pcan] = pw; q.cm[pcan] = pm; q.cv[pcan] = pv; q.dw1_zero[si] = 0.f; }
     }
     if (writer) { q.w1_wr[(g * 3 + 0) * wblk + wi] = pw; q.w1_wr[(g * 3 + 1) * wblk + wi] = pm; q.w1_wr[(g * 3 + 2) * wblk + wi] = pv; }
-    ws[(kl >> 2) * 28 + (wc < S ? (kl & 3) * S + wc : 24 + (kl & 3))] = pw * TANH_K;
+    ws[(kl >> 2) * 28 + (wc < S ? (((kl & 3) >> 1) * S + wc) * 2 + (kl & 1) : 24 + (kl & 3))] = pw * TANH_K;
   }
   if (hi <= lo) return;
   asm volatile("bar.sync 1, 256;" ::: "memory");
+  if (tid == 0) tc::tl_stamp(q.tl, q.tl_k, 2);            // W1 / b1 of this step in shared memory
   // ---- layer 1 of this step: 8 feature groups of 4 x 32 sample lanes
   const int64_t plane = a.cap * H1;
   const int kg = tid & 7, sl = tid >> 3;
@@ -306,26 +321,37 @@ __global__ void __launch_bounds__(L1R_THREADS, L1_CTAS) k_wide_l1r(const L1rArgs
       asm volatile("bar.sync 1, 256;" ::: "memory");
     }
     const int n = min(L1R_TILE, hi - r0);
-    for (int r = sl; r < n; r += 32) {
-      const bool valid = r0 + r < a.count;
-      float x[S], z[4];
+    const int nv = max(min(n, a.count - r0), 0);           // rows below hold samples, rows [nv, n) are the padding of the last tile
+    __nv_bfloat16* oh = a.h1p + (g * 2 + 0) * plane + (int64_t)(r0 + sl) * H1 + k0 + kg * 4;   // walks 32 rows at a time
+    __nv_bfloat16* om = oh + plane;
+    const float* xr = &xs[sl][0];
+    const int64_t ostep = (int64_t)32 * H1;
+    int r = sl;
+    for (; r < nv; r += 32, oh += ostep, om += ostep, xr += 32 * 2 * S) {
+      float z[4];
+      float4 xx[3];                                        // (x0, x0, x1, x1), (x2, x2, x3, x3), (x4, x4, x5, x5)
 #pragma unroll
-      for (int c = 0; c < S; c++) x[c] = xs[r][c];
+      for (int v = 0; v < 3; v++) xx[v] = *reinterpret_cast<const float4*>(xr + 4 * v);
+      float2 z01 = make_float2(b[0], b[1]), z23 = make_float2(b[2], b[3]);
 #pragma unroll
-      for (int u = 0; u < 4; u++) {
-        z[u] = b[u];
-#pragma unroll
-        for (int c = 0; c < S; c++) z[u] = fmaf(w[u * S + c], x[c], z[u]);
+      for (int c = 0; c < S; c++) {                        // two features per FFMA2, the same fma chain per feature as before
+        const float2 xc = (c & 1) ? make_float2(xx[c >> 1].z, xx[c >> 1].w) : make_float2(xx[c >> 1].x, xx[c >> 1].y);
+        z01 = __ffma2_rn(make_float2(w[2 * c], w[2 * c + 1]), xc, z01);
+        z23 = __ffma2_rn(make_float2(w[2 * (S + c)], w[2 * (S + c) + 1]), xc, z23);
       }
-      tanh4(z[0], z[1], z[2], z[3], z[0], z[1], z[2], z[3]);
+      tanh4(z01.x, z01.y, z23.x, z23.y, z[0], z[1], z[2], z[3]);
       uint2 th, tm;
-      split2(valid ? z[0] : 0.f, valid ? z[1] : 0.f, th.x, tm.x);
-      split2(valid ? z[2] : 0.f, valid ? z[3] : 0.f, th.y, tm.y);
-      const int64_t o = (int64_t)(r0 + r) * H1 + k0 + kg * 4;
-      *reinterpret_cast<uint2*>(a.h1p + (g * 2 + 0) * plane + o) = th;
-      *reinterpret_cast<uint2*>(a.h1p + (g * 2 + 1) * plane + o) = tm;
+      split2(z[0], z[1], th.x, tm.x);
+      split2(z[2], z[3], th.y, tm.y);
+      *reinterpret_cast<uint2*>(oh) = th;
+      *reinterpret_cast<uint2*>(om) = tm;
+    }
+    for (; r < n; r += 32, oh += ostep, om += ostep) {     // padding rows: zeros (the sample-contraction GEMM needs no masking)
+      *reinterpret_cast<uint2*>(oh) = make_uint2(0u, 0u);
+      *reinterpret_cast<uint2*>(om) = make_uint2(0u, 0u);
     }
   }
+  if (tid == 0) tc::tl_stamp(q.tl, q.tl_k, 3);            // layer-1 loop done
 }
 
 // layer 2 activation + layer 3 + loss head + D2 for both nets.  The GEMM left Z2 = H1 W2^T; here H2 = tanh(Z2 + b2).
@@ -680,6 +706,8 @@ struct WideNet {
   bool pending = false;            // a step's sums wait for the next k_wide_l1r launch (or wide_flush)
   bool seeded = false;             // w1s[phase ^ 1] holds the current W1 state
   ReduceArgs pend_r{};             // of the pending step
+  long long* tl = nullptr;         // B2_WIDE_TL=1: %globaltimer timeline of one step's kernels [4 kernels][8 slots][min, max]
+  int tl_state = 0, tl_calls = 0;  // 0 idle, 1 armed: this step's kernels stamp rows 0-2, 2: the next layer-1 launch stamps row 3
 };
 
 int wide_pstride(int H1, int H2) {
@@ -695,7 +723,7 @@ void wide_destroy(WideNet* w) {
   dfree(w->bias2); dfree(w->h2); dfree(w->d1); dfree(w->coef); dfree(w->vtmp); dfree(w->fh_dbg);
   dfree(w->part_head); dfree(w->part_dw1); dfree(w->part_dw2); dfree(w->bar_counter);
   dfree(w->boot_idx); dfree(w->boot_count);
-  dfree(w->dw1_sum); dfree(w->head_sum); dfree(w->w1s);
+  dfree(w->dw1_sum); dfree(w->head_sum); dfree(w->w1s); dfree(w->tl);
   delete w;
 }
 
@@ -752,6 +780,9 @@ int wide_create(WideNet** out, int H1, int H2, int64_t max_chunk, int sm_count) 
   WCK(cudaMemset(w->dw1_sum, 0, sizeof(float) * 2 * 2 * H1 * 8));
   WCK(cudaMemset(w->head_sum, 0, sizeof(float) * 2 * w->head_row));
   WCK(cudaMemset(w->w1s, 0, sizeof(float) * 2 * 2 * 3 * H1 * (S + 1)));
+#ifdef B2_TIMELINE
+  if (getenv("B2_WIDE_TL")) WCK(dmalloc(&w->tl, sizeof(long long) * 4 * 8 * 2));
+#endif
 #undef WCK
   int rc = 0;
   const uint64_t ucap = (uint64_t)cap;
@@ -808,6 +839,8 @@ static cudaError_t launch_l1r(WideNet* w, const WideArgs& wa, const UpdateArgs& 
   q.w1_rd = w->w1s + (size_t)(w->phase ^ 1) * 2 * 3 * H1 * (S + 1);
   q.w1_wr = w->w1s + (size_t)w->phase * 2 * 3 * H1 * (S + 1);
   q.cparams = u.params; q.cm = u.adam_m; q.cv = u.adam_v; q.cgrads = u.grads;
+  if (w->tl_state == 1) { q.tl = w->tl; q.tl_k = 0; }
+  else if (w->tl_state == 2) { q.tl = w->tl; q.tl_k = 3; w->tl_state = 3; }
   const int full = std::max(1, w->sm_count * L1_CTAS / (2 * n_fs));
   const int n_rs = wa.m_pad > 0 ? std::max(1, std::min(full, wa.m_pad / 16)) : full;
   cudaError_t ce = launch_pdl(k_wide_l1r, dim3(n_rs, n_fs, 2), dim3(L1R_THREADS), 0, st, q);
@@ -868,6 +901,17 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, bool more_follow
   // diagnostic only (profiles/wide_marginal.sh): B2_WIDE_SKIP = bit mask of step kernels to leave out (1 l1, 2 fwd GEMM,
   // 4 head, 8 dX GEMM, 16 dW2 GEMM + dw1, 32 reduce) -- results are garbage, the timing shows each kernel's marginal cost
   static const int skip = [] { const char* e = getenv("B2_WIDE_SKIP"); return e ? atoi(e) : 0; }();
+  // B2_WIDE_TL=1 (diagnostic): the 200th merged step of the process stamps its three kernels, the next step's layer-1 launch
+  // the fourth row; printed once, relative to the first stamp (profiles/r2/r2k_wide_timeline.txt)
+  if (w->tl && merge) {
+    if (w->tl_state == 0 && ++w->tl_calls == 200) {
+      std::vector<long long> init(4 * 8 * 2);
+      for (size_t i = 0; i < init.size(); i += 2) { init[i] = -1; init[i + 1] = 0; }   // (min as unsigned, max)
+      cudaStreamSynchronize(st);
+      cudaMemcpy(w->tl, init.data(), sizeof(long long) * init.size(), cudaMemcpyHostToDevice);
+      w->tl_state = 1;
+    }
+  }
   for (int64_t c = 0; c < n_chunks; c++) {
     wa.first = a.first + c * w->cap;
     wa.count = (int)std::min<int64_t>(w->cap, a.count - c * w->cap);
@@ -895,6 +939,7 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, bool more_follow
       f.inv_denom = wa.inv_denom; f.hp = a.hp; f.part_head = w->part_head; f.head_row = w->head_row;
       f.dbg = w->fh_dbg;
       f.head_sum = merge ? w->head_sum : nullptr;
+      f.tl = w->tl_state == 1 ? w->tl : nullptr;
       f.dx = (w->fused_dx && !(skip & 8)) ? 1 : 0;
       if (!(skip & 6))
       if ((ce = launch_wide_fh(w->tm_h1, w->tm_w2_half, w->tm_d2_st, w->tm_d2, w->tm_w2t, w->tm_out_d1_16, f, w->sm_count, &w->fh_grid, st)) != cudaSuccess)
@@ -979,6 +1024,7 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, bool more_follow
     g.dw1.count = wa.count; g.dw1.H1 = H1; g.dw1.SIZE = d.SIZE; g.dw1.oW1 = d.oW1; g.dw1.ob1 = d.ob1;
     g.dw1.z1 = w->d1; g.dw1.cap = w->cap; g.dw1.part = w->part_dw1;
     g.dw1.sum = merge ? w->dw1_sum + (size_t)sum_phase * 2 * H1 * 8 : nullptr;
+    g.tl = w->tl_state == 1 ? w->tl : nullptr;
     int dw2_grid = std::min(2 * (fuse_m ? 1 : jt) * splits, w->sm_count);
     // H2 = 256: CTA pairs (tcgen05 cta_group::2) own all 256 rows of dW2, every operand byte is fetched once, and the dW1
     // warps take Z1 through a cp.async ring (wide_gemm_mn2.cu, wide_dw1.cuh); B2_WIDE_DW2_PAIR=0: k_gemm_x3<MN>
@@ -1013,6 +1059,26 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, bool more_follow
     if (merge) {              // this step's reduce + Adam: in the next step's layer-1 kernel, or in a launch without rows right now
       w->pend_r = r;
       w->pending = !(skip & 32);
+      if (w->tl_state == 1) w->tl_state = 2;
+      else if (w->tl_state == 3) {
+        w->tl_state = 4;
+        cudaStreamSynchronize(st);
+        std::vector<unsigned long long> h(4 * 8 * 2);
+        cudaMemcpy(h.data(), w->tl, sizeof(long long) * h.size(), cudaMemcpyDeviceToHost);
+        const unsigned long long t0 = h[0];
+        static const char* kn[4] = {"l1r", "fh", "mn2", "l1r+1"};
+        static const char* sn[4][8] = {
+            {"entry", "dep_wait_done", "w1_ready", "l1_done", "reduce_done", "", "", ""},
+            {"entry", "dep_wait_done", "acc_critic", "acc_actor", "head_critic_done", "head_actor_done", "exit", "acc_last_dx"},
+            {"entry", "dep_wait_done", "ops_first", "ops_last", "acc_ready", "epilogue_done", "dw1_done", "exit"},
+            {"entry", "dep_wait_done", "w1_ready", "l1_done", "reduce_done", "", "", ""}};
+        for (int k = 0; k < 4; k++)
+          for (int sl = 0; sl < 8; sl++) {
+            const unsigned long long lo = h[(k * 8 + sl) * 2], hi = h[(k * 8 + sl) * 2 + 1];
+            if (!sn[k][sl][0] || hi == 0) continue;
+            fprintf(stderr, "tl %-6s %-18s first %8.2f us  last %8.2f us\n", kn[k], sn[k][sl], (double)(lo - t0) * 1e-3, (double)(hi - t0) * 1e-3);
+          }
+      }
       if (!more_follow) { int rc = wide_flush(w, st, launches); if (rc) return rc; }
       continue;
     }
