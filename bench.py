@@ -563,7 +563,7 @@ def wide_leg(args, pkg, capi, np, rank, local, world, dist, barrier, max_over_ra
             "e2e": {"value": B * K * args.steps * world / dt, "unit": "sample-epochs/s", "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": 4 * 8 * K * M, "api": "b2_update on pinned host buffers (PPO::update(MemoryNN))"},
             "roofline": {"kernel": "whole optimizer step: k_wide_fh (forward GEMM + loss head + dX GEMM), k_gemm_mn2 (dW2 on CTA pairs + dw1) on tcgen05; "
-                                   "k_wide_l1 and k_wide_reduce (+Adam) on FP32; traffic = the longest kernel of the chain (k_wide_fh)",
+                                   "k_wide_l1r (layer 1 + the reduce and Adam of the step before; N > 1: k_wide_l1 and k_wide_reduce) on FP32; traffic = the longest kernel of the chain (k_wide_fh)",
                          "bound": "tensor", "achieved": ach, "peak": bf16_peak / 3.0,
                          "unit": "TFLOP/s", "frac": ach / (bf16_peak / 3.0) if bf16_peak else None,
                          "peak_source": bf16_src + " / 3 (every fp32 product is three bf16 MMAs)",
