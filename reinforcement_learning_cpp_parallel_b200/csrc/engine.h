@@ -165,7 +165,9 @@ __device__ __forceinline__ void px_push(const PeerXchg& x, int i, float v) {
 }
 // false once any wait of this update has expired (on this rank): the rest of the update is abandoned
 __device__ __forceinline__ bool px_alive(const PeerXchg& x) { return !(*(volatile const int*)x.status & 2); }
-__device__ __forceinline__ float px_pull(const PeerXchg& x, int i, bool* ok) {
+// publish = false: a redundant reader of element i (k_wide_l1r: every row slice needs the summed W1 gradient, one slice
+// pushed it) -- it waits and sums like the owner but leaves the second hop's stores to the thread that pushed
+__device__ __forceinline__ float px_pull(const PeerXchg& x, int i, bool* ok, bool publish = true) {
   if (x.scatter && px_owner(x, i) != x.rank) {
     // not the owner: wait for the owner's sum of element i in this rank's sums[] (the second hop)
     const uint2* p = x.slots[x.rank] + x.sum_off + i;
@@ -202,7 +204,7 @@ __device__ __forceinline__ float px_pull(const PeerXchg& x, int i, bool* ok) {
       s = r == 0 ? __uint_as_float(val[r]) : __fadd_rn(s, __uint_as_float(val[r]));
     }
   }
-  if (x.scatter && *ok)       // the owner publishes the rank-order sum to every peer (its own copy is not read again)
+  if (x.scatter && *ok && publish)   // the owner publishes the rank-order sum to every peer (its own copy is not read again)
     for (int r = 0; r < x.world; r++)
       if (r != x.rank) px_store(x.slots[r] + x.sum_off + i, s, x.epoch);
   x.out[i] = s;

@@ -167,6 +167,7 @@ struct L1rArgs {
   const float* w1_rd;      // [2 nets][3: w, m, v][H1][S + 1] (column S = the bias)
   float* w1_wr;
   float *cparams, *cm, *cv, *cgrads;   // the canonical vectors (row slice 0 keeps W1 / b1 current there too)
+  unsigned* w1_flag;       // PEERS: [2 nets][feature slices] -- 2 * epoch (| 1: abandoned) once the writer slice has left the summed W1 / b1 gradients of that epoch in cgrads
   long long* tl;           // optional whole-step timeline (tc::tl_stamp), diagnostic runs only
   int tl_k;                // its kernel row: 0 = this step's launch, 3 = the launch of the step after the stamped one
 };
@@ -195,7 +196,25 @@ __device__ __forceinline__ void l1r_locate(const L1rArgs& q, int e, float*& src,
   }
 }
 
+// one finished (and, with several GPUs, exchanged) sum of the reduce: gradient vector, Adam, planes / loss log
+__device__ __forceinline__ void l1r_apply(const L1rArgs& q, const AdamCoef& cf, int p, int slot, float sv, float m, float v, float w) {
+  const NetDims& d = q.a.d;
+  q.cgrads[slot] = sv;
+  if (p < d.P) {
+    const float nw = wide_adam_math(cf, sv, m, v, w);
+    q.cm[p] = m; q.cv[p] = v; q.cparams[p] = nw;
+    wide_store_planes(d, q.r.w2p, q.r.bias2, p, nw);
+  } else {
+    wide_loss_log(q.r.u, p - d.P, sv);
+  }
+}
+
+// PEERS: several GPUs -- every finished sum is exchanged over NVLink peer memory first (engine.h PeerXchg, as k_wide_reduce
+// does): the reduce warp pushes and pulls its elements; of the W1 / b1 threads the writer slice pushes, every slice pulls
+// (all 592 CTAs are resident at once, and a thread waits only for stores that are issued before any wait)
+template <bool PEERS>
 __global__ void __launch_bounds__(L1R_THREADS, L1_CTAS) k_wide_l1r(const L1rArgs q) {
+  __shared__ int s_ok;
   __shared__ __align__(16) float xs[L1R_TILE][2 * S];     // every component twice: (x, x) pairs are the FFMA2 operands of the loop
   __shared__ __align__(16) float ws[(L1R_FS / 4) * 28];   // per feature group of 4: 12 weight PAIRS (features 0|1, then 2|3, of
                                                           // component c) + 4 biases, pre-scaled by TANH_K
@@ -206,6 +225,43 @@ __global__ void __launch_bounds__(L1R_THREADS, L1_CTAS) k_wide_l1r(const L1rArgs
   const int cta = (int)((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x);
   if (tid == 0) tc::tl_stamp(q.tl, q.tl_k, 0);
   pdl_launch_dependents();
+
+  // PEERS: the reduce is spread over EVERY thread of the grid, one element each (as k_wide_reduce's one wave of threads does):
+  // all sums are on the wire before anybody waits, one NVLink latency for the lot, and that latency runs beside the W1
+  // exchange of the layer-1 threads.  (A reduce warp with 8 elements per lane, as on one GPU, pulled them one after the other:
+  // its chain ended 17-25 us after the layer-1 loop, profiles/r2/r2l_wide_timeline_2gpu.txt.)
+  const int n_red = 2 * d.H2 * H1 + 2 * (2 * d.H2 + 1) + 3;
+  float* osrc = nullptr;
+  int op = 0, oslot = 0;
+  float om = 0.f, ov = 0.f, ow = 0.f, osv = 0.f;
+  bool olive = false, oalive = true;
+  if (PEERS && q.pending) {
+    const int e = cta * L1R_THREADS + tid;
+    olive = e < n_red;
+    if (olive) {
+      l1r_locate(q, e, osrc, op, oslot);
+      if (op < d.P) { om = q.cm[op]; ov = q.cv[op]; ow = q.cparams[op]; }   // older than the kernel in front: before the wait
+    }
+  }
+  auto own_push = [&]() {                                  // after the dependency wait
+    oalive = px_alive(q.r.u.px);
+    if (olive) { osv = *osrc; *osrc = 0.f; if (oalive) px_push(q.r.u.px, oslot, osv); }
+  };
+  auto own_finish = [&](const AdamCoef& c) {
+    if (olive && oalive) {
+      bool ok = true;
+      osv = px_pull(q.r.u.px, oslot, &ok);
+      if (ok) l1r_apply(q, c, op, oslot, osv, om, ov, ow);
+    }
+    for (int e = cta * L1R_THREADS + tid + n_cta * L1R_THREADS; e < n_red; e += n_cta * L1R_THREADS) {   // (a grid smaller than the reduce)
+      float* src; int p, slot;
+      l1r_locate(q, e, src, p, slot);
+      float sv = *src; *src = 0.f;
+      bool ok = oalive;
+      if (ok) { px_push(q.r.u.px, slot, sv); sv = px_pull(q.r.u.px, slot, &ok); }
+      if (ok) l1r_apply(q, c, p, slot, sv, p < d.P ? q.cm[p] : 0.f, p < d.P ? q.cv[p] : 0.f, p < d.P ? q.cparams[p] : 0.f);
+    }
+  };
 
   if (tid >= 256) {
     // ---- the reduce warp: the pending step's W2, b2, W3, b3 and loss sums, 256 elements per CTA and round, beside the
@@ -218,8 +274,14 @@ __global__ void __launch_bounds__(L1R_THREADS, L1_CTAS) k_wide_l1r(const L1rArgs
     }
     if (!q.pending) return;
     const int lane = tid - 256;
-    const int w2n = d.H2 * H1, n_red = 2 * w2n + 2 * (2 * d.H2 + 1) + 3;
     const AdamCoef cf = *q.r.coef;
+    if (PEERS) {                                           // this warp's threads own an element each like everybody else
+      pdl_wait();
+      own_push();
+      own_finish(cf);
+      if (tid == 256) tc::tl_stamp(q.tl, q.tl_k, 4);
+      return;
+    }
     bool waited = false;
     for (int e0 = cta * 256; e0 < n_red; e0 += n_cta * 256) {
 #pragma unroll 1
@@ -241,10 +303,12 @@ __global__ void __launch_bounds__(L1R_THREADS, L1_CTAS) k_wide_l1r(const L1rArgs
         if (!waited) { pdl_wait(); waited = true; }
 #pragma unroll
         for (int u = 0; u < L1R_RB; u++) sv[u] = live[u] ? *src[u] : 0.f;
+        const bool ok = true;
 #pragma unroll
         for (int u = 0; u < L1R_RB; u++) {
           if (!live[u]) continue;
           *src[u] = 0.f;                                  // the next step adds into zeros
+          if (!ok) continue;                              // a peer never arrived: the update is abandoned (engine.h px_alive)
           q.cgrads[slot[u]] = sv[u];
           if (p[u] < d.P) {
             const float nw = wide_adam_math(cf, sv[u], m[u], v[u], w[u]);
@@ -293,17 +357,69 @@ __global__ void __launch_bounds__(L1R_THREADS, L1_CTAS) k_wide_l1r(const L1rArgs
   if (q.pending) cf = *q.r.coef;   // of the pending step: written by the launch that ran ITS layer 1
   pdl_wait();                      // the sums come from the kernels of the pending step
   if (tid == 0) tc::tl_stamp(q.tl, q.tl_k, 1);
+  const bool writer = blockIdx.x == 0;
+  // PEERS: only the writer slice of a (net, feature slice) exchanges its 224 sums with the peers; the other 36 slices wait for
+  // ONE flag word of that slice (a thread per CTA polls it) and read the summed gradients it left in the gradient vector.
+  // (Every slice pulling for itself was measured first: 132k threads polling the same 28 KB of slots queue on a few L2
+  // slices in front of the very NVLink stores they wait for -- 32.1 instead of 27.5 ms per update on two GPUs.)
+  float gsum = 0.f;
+  bool xok = true;
+  if (PEERS && q.pending) {
+    const PeerXchg& px = q.r.u.px;
+    unsigned* flag = q.w1_flag + g * gridDim.y + blockIdx.y;
+    const unsigned want = 2u * px.epoch;                   // | 1: the exchange of this step was abandoned
+    if (tid == 0) s_ok = 1;
+    own_push();
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    // the PUSH of the W1 sums is slice 1's job, not the writer's: the writer's release below would otherwise wait for the
+    // acknowledgement of its own NVLink stores (5 us); in the scatter shape slice 1 also runs the owner's publishing pull
+    const int pusher = gridDim.x > 1 ? 1 : 0;
+    if (w1t && (int)blockIdx.x == pusher && oalive) {
+      bool ok = true;
+      px_push(px, pcan, q.dw1_sum[(g * H1 + k0 + kl) * 8 + wc]);
+      if (pusher != 0 && px.scatter) (void)px_pull(px, pcan, &ok, true);
+    }
+    if (writer) {
+      if (w1t) {
+        bool ok = oalive;
+        if (ok) gsum = px_pull(px, pcan, &ok, pusher == 0);
+        if (ok) q.cgrads[pcan] = gsum; else s_ok = 0;
+        __threadfence();
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (tid == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(flag), "r"(want | (s_ok ? 0u : 1u)) : "memory");
+    } else {
+      if (tid == 0) {
+        unsigned v;
+        long long spins = 0;
+        do {
+          asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+          if ((v & ~1u) == want) break;
+          if (++spins > (1ll << 26)) { atomicOr(px.status, 2); v = want | 1u; break; }
+        } while (true);
+        if (v & 1u) s_ok = 0;
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (w1t && s_ok) gsum = __ldcg(q.cgrads + pcan);
+    }
+    xok = s_ok != 0;
+  }
   if (w1t) {
-    const bool writer = blockIdx.x == 0;
     if (q.pending) {
       const int si = (g * H1 + k0 + kl) * 8 + wc;
-      const float gs = q.dw1_sum[si];
-      pw = wide_adam_math(cf, gs, pm, pv, pw);
-      if (writer) { q.cgrads[pcan] = gs; q.cparams[pcan] = pw; q.cm[pcan] = pm; q.cv[pcan] = pv; q.dw1_zero[si] = 0.f; }
+      const float gs = PEERS ? gsum : q.dw1_sum[si];
+      const bool ok = xok;
+      if (ok) pw = wide_adam_math(cf, gs, pm, pv, pw);
+      if (writer) {
+        q.dw1_zero[si] = 0.f;
+        if (ok) { q.cgrads[pcan] = gs; q.cparams[pcan] = pw; q.cm[pcan] = pm; q.cv[pcan] = pv; }
+      }
     }
     if (writer) { q.w1_wr[(g * 3 + 0) * wblk + wi] = pw; q.w1_wr[(g * 3 + 1) * wblk + wi] = pm; q.w1_wr[(g * 3 + 2) * wblk + wi] = pv; }
     ws[(kl >> 2) * 28 + (wc < S ? (((kl & 3) >> 1) * S + wc) * 2 + (kl & 1) : 24 + (kl & 3))] = pw * TANH_K;
   }
+  if (PEERS && q.pending) own_finish(cf);                 // this thread's element of the reduce: its peers' values have had the
+                                                          // whole W1 exchange to arrive
   if (hi <= lo) return;
   asm volatile("bar.sync 1, 256;" ::: "memory");
   if (tid == 0) tc::tl_stamp(q.tl, q.tl_k, 2);            // W1 / b1 of this step in shared memory
@@ -699,9 +815,15 @@ struct WideNet {
   int* boot_count = nullptr;
   // the merged sequence (k_wide_l1r: reduce + Adam of step s-1 inside the layer-1 kernel of step s; B2_WIDE_MERGE=0: off)
   bool merge_env = true;
+  bool merge_peers = false;        // B2_WIDE_MERGE_PEERS=1: the merged sequence on TWO GPUs too (k_wide_l1r<PEERS>).  Opt-in: measured
+                                   // 27.7 vs 28.25 ms per configs[4] update on 2 x B200 -- the exchange inside the layer-1 kernel costs
+                                   // 15 us per step against 10 in k_wide_reduce, which eats most of the launch it saves -- and at
+                                   // world = 8 (reduce-scatter shape) it FAILED bench.py's multi_gpu_check (ranks ended with different
+                                   // weights; 29.6 vs 30.6 ms) and was not debugged for lack of GPU time: never taken at world > 2
   float* dw1_sum = nullptr;        // [2 phases][2][H1 * 8]
   float* head_sum = nullptr;       // [2][head_row]
   float* w1s = nullptr;            // [2 phases][2 nets][3][H1][S + 1]
+  unsigned* w1_flag = nullptr;     // [2 nets][8]: k_wide_l1r<PEERS>'s writer-slice flags
   int phase = 0;                   // flips with every k_wide_l1r launch
   bool pending = false;            // a step's sums wait for the next k_wide_l1r launch (or wide_flush)
   bool seeded = false;             // w1s[phase ^ 1] holds the current W1 state
@@ -723,7 +845,7 @@ void wide_destroy(WideNet* w) {
   dfree(w->bias2); dfree(w->h2); dfree(w->d1); dfree(w->coef); dfree(w->vtmp); dfree(w->fh_dbg);
   dfree(w->part_head); dfree(w->part_dw1); dfree(w->part_dw2); dfree(w->bar_counter);
   dfree(w->boot_idx); dfree(w->boot_count);
-  dfree(w->dw1_sum); dfree(w->head_sum); dfree(w->w1s); dfree(w->tl);
+  dfree(w->dw1_sum); dfree(w->head_sum); dfree(w->w1s); dfree(w->tl); dfree(w->w1_flag);
   delete w;
 }
 
@@ -774,12 +896,15 @@ int wide_create(WideNet** out, int H1, int H2, int64_t max_chunk, int sm_count) 
   WCK(cudaMemset(w->bar_counter, 0, sizeof(int)));
   WCK(dmalloc(&w->boot_count, sizeof(int)));
   { const char* e = getenv("B2_WIDE_MERGE"); w->merge_env = !(e && e[0] == '0'); }
+  { const char* e = getenv("B2_WIDE_MERGE_PEERS"); w->merge_peers = e && e[0] == '1'; }
   WCK(dmalloc(&w->dw1_sum, sizeof(float) * 2 * 2 * H1 * 8));
   WCK(dmalloc(&w->head_sum, sizeof(float) * 2 * w->head_row));
   WCK(dmalloc(&w->w1s, sizeof(float) * 2 * 2 * 3 * H1 * (S + 1)));
   WCK(cudaMemset(w->dw1_sum, 0, sizeof(float) * 2 * 2 * H1 * 8));
   WCK(cudaMemset(w->head_sum, 0, sizeof(float) * 2 * w->head_row));
   WCK(cudaMemset(w->w1s, 0, sizeof(float) * 2 * 2 * 3 * H1 * (S + 1)));
+  WCK(dmalloc(&w->w1_flag, sizeof(unsigned) * 16));
+  WCK(cudaMemset(w->w1_flag, 0, sizeof(unsigned) * 16));
 #ifdef B2_TIMELINE
   if (getenv("B2_WIDE_TL")) WCK(dmalloc(&w->tl, sizeof(long long) * 4 * 8 * 2));
 #endif
@@ -839,11 +964,14 @@ static cudaError_t launch_l1r(WideNet* w, const WideArgs& wa, const UpdateArgs& 
   q.w1_rd = w->w1s + (size_t)(w->phase ^ 1) * 2 * 3 * H1 * (S + 1);
   q.w1_wr = w->w1s + (size_t)w->phase * 2 * 3 * H1 * (S + 1);
   q.cparams = u.params; q.cm = u.adam_m; q.cv = u.adam_v; q.cgrads = u.grads;
+  q.w1_flag = w->w1_flag;
   if (w->tl_state == 1) { q.tl = w->tl; q.tl_k = 0; }
   else if (w->tl_state == 2) { q.tl = w->tl; q.tl_k = 3; w->tl_state = 3; }
   const int full = std::max(1, w->sm_count * L1_CTAS / (2 * n_fs));
   const int n_rs = wa.m_pad > 0 ? std::max(1, std::min(full, wa.m_pad / 16)) : full;
-  cudaError_t ce = launch_pdl(k_wide_l1r, dim3(n_rs, n_fs, 2), dim3(L1R_THREADS), 0, st, q);
+  const bool peers = (q.pending ? q.r.u.px.world : u.px.world) > 1;
+  cudaError_t ce = peers ? launch_pdl(k_wide_l1r<true>, dim3(n_rs, n_fs, 2), dim3(L1R_THREADS), 0, st, q)
+                         : launch_pdl(k_wide_l1r<false>, dim3(n_rs, n_fs, 2), dim3(L1R_THREADS), 0, st, q);
   if (ce != cudaSuccess) return ce;
   w->pending = false;
   w->seeded = true;
@@ -882,7 +1010,7 @@ int wide_step(WideNet* w, const UpdateArgs& a, bool apply_adam, bool more_follow
   const int64_t n_chunks = (a.count + w->cap - 1) / w->cap;
   // the merged sequence: one GPU, Adam applied here, one chunk, sums in the L2 (not the fixed-order mode), the fused forward +
   // head kernel and the CTA-pair dW2 kernel (the two producers that can leave sums)
-  const bool merge = w->merge_env && apply_adam && a.px.world <= 1 && n_chunks == 1 && w->dw2_add && !w->fuse_reduce && w->fused_fh &&
+  const bool merge = w->merge_env && apply_adam && (a.px.world <= 1 || (w->merge_peers && a.px.world == 2)) && n_chunks == 1 && w->dw2_add && !w->fuse_reduce && w->fused_fh &&
                      pair_env0 && gemm_mn2_supported(H2, H1) && getenv("B2_WIDE_FUSE_M") == nullptr;
   if (a.step_slot == 0 || !merge) {
     if (w->pending && !merge) { int rc = wide_flush(w, st, launches); if (rc) return rc; }

@@ -184,10 +184,18 @@ def _wide_rank(rank, world, port, q):
         dist.destroy_process_group()
 
 
-def test_two_gpu_wide_update_matches_one_gpu():
+@pytest.mark.parametrize("env", [{}, {"B2_WIDE_MERGE_PEERS": "1"}, {"B2_WIDE_MERGE_PEERS": "1", "B2_COMM_SCATTER": "1"}],
+                         ids=["reduce_own_launch", "merged_l1r_push", "merged_l1r_scatter"])
+def test_two_gpu_wide_update_matches_one_gpu(env, monkeypatch):
+    """default: the exchange in k_wide_reduce, a launch of its own; B2_WIDE_MERGE_PEERS=1 (opt-in, world 2 only): the exchange
+    of a step's sums inside the layer-1 kernel of the next step (k_wide_l1r<PEERS>: every thread of the grid pushes and pulls
+    one element of the reduce, row slice 1 pushes W1 / b1, slice 0 pulls them and flags the other slices) -- in the all-to-all
+    shape and, forced, in the reduce-scatter + all-gather shape"""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)       # spawned ranks inherit the environment
     import torch.multiprocessing as mp
     import reinforcement_learning_cpp_parallel_b200 as pkg
     from reinforcement_learning_cpp_parallel_b200 import capi
