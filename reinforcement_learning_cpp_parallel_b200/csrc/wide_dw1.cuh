@@ -116,9 +116,10 @@ constexpr int DW1_NGR = 2;                    // groups in flight per half
 constexpr int DW1_RING_BYTES = 2 * DW1_NGR * 2 * DW1_GS * 256 * 4;   // halves x groups x nets x samples x 256 floats = 64 KB
 constexpr int DW1_SMEM_ASYNC = DW1_SMEM + DW1_RING_BYTES + 64;       // + the ring's mbarriers
 
-__device__ __forceinline__ void bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-               ::"r"(tc::smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(tc::smem_u32(bar)) : "memory");
+// (evict-first hint: Z1 is read here for the last time in the step)
+__device__ __forceinline__ void bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar, uint64_t policy) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+               ::"r"(tc::smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(tc::smem_u32(bar)), "l"(policy) : "memory");
 }
 
 __device__ __forceinline__ void dw1_worker_async(const Dw1Args& w, float* sm, int t) {
@@ -151,6 +152,7 @@ __device__ __forceinline__ void dw1_worker_async(const Dw1Args& w, float* sm, in
   }
   asm volatile("bar.sync 1, %0;" ::"n"(DW1_THREADS) : "memory");   // the ring's barriers are initialised
   const int total_groups = (n + DW1_GS - 1) / DW1_GS;
+  const uint64_t pol_last = tc::l2_policy_evict_first();
   auto issue = [&](int gidx) {                         // producer only: group gidx -> ring slot gidx % NGR
     const int gi = gidx % DW1_NGR;
     const int s0 = gidx * DW1_GS, cnt = min(DW1_GS, n - s0);
@@ -158,7 +160,7 @@ __device__ __forceinline__ void dw1_worker_async(const Dw1Args& w, float* sm, in
     tc::mbar_arrive_expect_tx(&rbar[gi], 2 * bytes);
 #pragma unroll
     for (int g = 0; g < 2; g++)
-      bulk_load_1d(ring + ((gi * 2 + g) * DW1_GS) * 256, w.z1 + ((int64_t)g * w.cap + hb + s0) * H1, bytes, &rbar[gi]);
+      bulk_load_1d(ring + ((gi * 2 + g) * DW1_GS) * 256, w.z1 + ((int64_t)g * w.cap + hb + s0) * H1, bytes, &rbar[gi], pol_last);
   };
   if (producer)
     for (int gidx = 0; gidx < DW1_NGR && gidx < total_groups; gidx++) issue(gidx);

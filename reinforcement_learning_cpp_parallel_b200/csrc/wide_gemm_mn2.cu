@@ -77,6 +77,7 @@ k_gemm_mn2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
 
   if (warp == 0) {
     int stage = 0; uint32_t phase = 0;
+    const uint64_t pol_last = tc::l2_policy_evict_first();
     for (int item = pair; item < n_items; item += n_pairs) {
       const int sp = item % a.splits, g = item / a.splits;
       const int kb0 = sp * a.kb_per_split, kb1 = min(kb0 + a.kb_per_split, kb_total);
@@ -89,7 +90,7 @@ k_gemm_mn2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
         if (lane < 2 * per) {
           const int pl = lane / per, j = lane % per;
           if (j < 2)
-            tc::tma_load_3d_2sm(s + pl * A_PLANE + j * MNB_BYTES, &tmA, &full[stage], ((int)rank * 2 + j) * 64, kb * BKS, g * 2 + pl);
+            tc::tma_load_3d_2sm_hint(s + pl * A_PLANE + j * MNB_BYTES, &tmA, &full[stage], ((int)rank * 2 + j) * 64, kb * BKS, g * 2 + pl, pol_last);   // D2: last read of the step
           else
             tc::tma_load_3d_2sm(s + 2 * A_PLANE + pl * B_PLANE + (j - 2) * MNB_BYTES, &tmB, &full[stage],
                                 ((int)rank * NHB + (j - 2)) * 64, kb * BKS, g * 2 + pl);
