@@ -420,6 +420,7 @@ int setup_peer_exchange(b2_engine* E) {
   const size_t buf_bytes = xchg_slot_bytes(E);
   CK(cudaMalloc(&E->xchg, buf_bytes + 256));   // plain: cudaIpcGetMemHandle wants the allocation base
   CK(cudaMemset(E->xchg, 0, buf_bytes + 256));
+  CK(cudaDeviceSynchronize());   // (legacy-stream memset; the peers write into this buffer from THEIR streams, see b2_create)
   struct Rec { cudaIpcMemHandle_t h; int ok; int pad[3]; };
   static_assert(sizeof(Rec) == 80, "record size");
   Rec mine{};
@@ -642,6 +643,10 @@ static int create_body(b2_engine* E, const b2_config* cfg, bool is_default_net) 
   CK(dmalloc(&E->ep_log, sizeof(float) * NE * E->max_eps));
   CK(dmalloc(&E->progress, sizeof(int) * ((NE + 31) / 32)));
   CK(cudaMemset(E->state, 0, sizeof(double) * 4 * NE));   // CartPole::reset: u = 0 (cart_pole.h:86)
+  // Every cudaMemset of this function runs on the legacy default stream, and E->stream is NON-BLOCKING: nothing orders them
+  // against the engine's kernels.  Without this wait the zero fill above could land AFTER the random initial states written
+  // below (seen once in ~10 runs of test_random_init_reset_and_sharding as shards that disagree with the full engine).
+  CK(cudaDeviceSynchronize());
   if (cfg->env_flags & B2_ENV_RANDOM_INIT) {
     cudaError_t ce = launch_env_init(E->state, NE, cfg->env_flags, cfg->seed, cfg->env_offset, 0, E->stream);
     if (ce != cudaSuccess) return set_error(B2_ERR_CUDA, "env init: %s", cudaGetErrorString(ce));
@@ -657,6 +662,7 @@ static int create_body(b2_engine* E, const b2_config* cfg, bool is_default_net) 
     rc = wide_create(&E->wide, cfg->hidden1, cfg->hidden2, (B0 + cfg->n_minibatches - 1) / cfg->n_minibatches + cfg->n_minibatches, E->sm_count);
     if (rc) return rc;
   }
+  CK(cudaDeviceSynchronize());   // the remaining legacy-stream memsets (episode counters, wide_create's buffers) before anything on E->stream
   return b2_init_params(E, cfg->seed);
 }
 
@@ -825,6 +831,7 @@ int b2_load_checkpoint(b2_handle E, const char* path) {
     if ((int64_t)ctr[3] == E->cfg.n_envs) {
       if ((rc = b2_env_set_state(E, u.data(), es.data(), E->cfg.n_envs))) return rc;
       CK(cudaMemcpy(E->ep_ret, er.data(), sizeof(float) * er.size(), cudaMemcpyHostToDevice));
+      CK(cudaDeviceSynchronize());   // (pageable H2D on the legacy stream may still be in flight; E->stream is non-blocking)
     }
   }
   return B2_OK;
