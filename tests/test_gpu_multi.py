@@ -141,11 +141,17 @@ def test_scatter_shaped_exchange_equals_nccl_allreduce(monkeypatch):
 
 
 # ---- wide nets (BASELINE configs[4]): each rank holds half of every minibatch, gradients all-reduced over NCCL ----
-WB, WK, WM = 2048, 2, 2
+WK, WM = 2, 2
+
+
+def _wb():
+    """records of the wide batch: 2048, or B2_TEST_WIDE_WB (spawned ranks inherit the environment)"""
+    return int(os.environ.get("B2_TEST_WIDE_WB", "2048"))
 
 
 def _wide_batch():
     import ctypes as C
+    WB = _wb()
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import helpers as H
     rng = np.random.default_rng(99)
@@ -168,6 +174,7 @@ def _wide_rank(rank, world, port, q):
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     try:
         dims, obs, eps, reward = _wide_batch()
+        WB = _wb()
         E = pkg.Engine(capi.default_config(n_envs=WB // world, horizon=1, hidden1=256, hidden2=256, k_epochs=WK,
                                            n_minibatches=WM, device=rank))
         E.init_params(4)
@@ -184,8 +191,14 @@ def _wide_rank(rank, world, port, q):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("env", [{}, {"B2_WIDE_MERGE_PEERS": "1"}, {"B2_WIDE_MERGE_PEERS": "1", "B2_COMM_SCATTER": "1"}],
-                         ids=["reduce_own_launch", "merged_l1r_push", "merged_l1r_scatter"])
+@pytest.mark.parametrize("env", [
+    {}, {"B2_WIDE_MERGE_PEERS": "1"}, {"B2_WIDE_MERGE_PEERS": "1", "B2_COMM_SCATTER": "1"},
+    # 512 records = 128 per rank and minibatch: k_wide_l1r's grid (128 CTAs) is smaller than the reduce, so threads own
+    # several elements (the tail loop of own_finish) -- the shape bench.py's multi_gpu_check ran when the merged exchange
+    # FAILED at world 8.  Never run on two GPUs before the round's GPU budget ended: not a gate yet.
+    pytest.param({"B2_WIDE_MERGE_PEERS": "1", "B2_COMM_SCATTER": "1", "B2_TEST_WIDE_WB": "512"},
+                 marks=pytest.mark.xfail(strict=False, reason="opt-in path, unverified shape (see DESIGN.md s5)")),
+], ids=["reduce_own_launch", "merged_l1r_push", "merged_l1r_scatter", "merged_l1r_scatter_small_grid"])
 def test_two_gpu_wide_update_matches_one_gpu(env, monkeypatch):
     """default: the exchange in k_wide_reduce, a launch of its own; B2_WIDE_MERGE_PEERS=1 (opt-in, world 2 only): the exchange
     of a step's sums inside the layer-1 kernel of the next step (k_wide_l1r<PEERS>: every thread of the grid pushes and pulls
@@ -209,6 +222,7 @@ def test_two_gpu_wide_update_matches_one_gpu(env, monkeypatch):
     for p in procs:
         p.join(60)
     dims, obs, eps, reward = _wide_batch()
+    WB = _wb()
     E = pkg.Engine(capi.default_config(n_envs=WB, horizon=1, hidden1=256, hidden2=256, k_epochs=WK, n_minibatches=WM))
     E.init_params(4)
     act, lp, _ = E.act(obs, eps)
