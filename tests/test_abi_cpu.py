@@ -104,3 +104,23 @@ def test_product_never_touches_the_oracle():
                 txt = open(os.path.join(dp, f), errors="ignore").read()
                 assert "liboracle" not in txt and "oracle.h" not in txt and "import oracle" not in txt, (dp, f)
                 assert "orc_" not in txt.replace("force", ""), (dp, f)
+
+
+def test_env_switches_in_design_exist_in_the_sources():
+    """every B2_* environment switch DESIGN.md s7b documents is read somewhere in the library (or bench / tools), and
+    every getenv("B2_...") of the library is documented there -- the A/B numbers of the document must stay re-measurable"""
+    import glob
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    design = open(os.path.join(root, "DESIGN.md")).read()
+    sec = design[design.index("## 7b."):design.index("## 7c.")]
+    documented = set(re.findall(r"`(B2_[A-Z0-9_]+)", sec))
+    src = ""
+    for pat in ("reinforcement_learning_cpp_parallel_b200/csrc/*.cu", "reinforcement_learning_cpp_parallel_b200/csrc/*.cuh",
+                "reinforcement_learning_cpp_parallel_b200/csrc/*.h", "reinforcement_learning_cpp_parallel_b200/csrc/*.cpp"):
+        for f in glob.glob(os.path.join(root, pat)):
+            src += open(f).read()
+    read = set(re.findall(r'getenv\("(B2_[A-Z0-9_]+)"\)', src))
+    assert documented <= read, sorted(documented - read)
+    diagnostics = {"B2_WIDE_SKIP", "B2_FH_DBG", "B2_GEMM_DBG"}   # profiling aids described next to their code, not switches of the product
+    assert read - diagnostics <= documented, sorted(read - diagnostics - documented)
